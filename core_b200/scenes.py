@@ -1,0 +1,272 @@
+"""Procedural scene generators for the five BASELINE.json configs.
+
+Every generator only calls ``yafrayInterface_t`` methods on ``yi`` (core_b200.interface.YafrayInterface
+over libyb200.so, or the same class bound to the reference driver in the tests), so both sides are
+fed bit-identical inputs.  All randomness is seeded numpy (PCG64) — deterministic across machines.
+"""
+import numpy as np
+
+
+# ----------------------------------------------------------------------------- helpers
+def set_render(yi, width, height, spp=1, integrator="default", camera="cam", background="bg",
+               threads=1, filter_type="box", pixelwidth=1.5, xstart=0, ystart=0, passes=1, **extra):
+    yi.paramsClearAll()
+    yi.paramsSetString("camera_name", camera)
+    yi.paramsSetString("integrator_name", integrator)
+    yi.paramsSetString("volintegrator_name", "volintegr")
+    if background:
+        yi.paramsSetString("background_name", background)
+    yi.paramsSetInt("width", width)
+    yi.paramsSetInt("height", height)
+    yi.paramsSetInt("xstart", xstart)
+    yi.paramsSetInt("ystart", ystart)
+    yi.paramsSetInt("AA_minsamples", spp)
+    yi.paramsSetInt("AA_passes", passes)
+    yi.paramsSetFloat("AA_pixelwidth", pixelwidth)
+    yi.paramsSetString("filter_type", filter_type)
+    yi.paramsSetInt("threads", threads)
+    yi.paramsSetFloat("gamma", 1.0)
+    yi.paramsSetBool("clamp_rgb", False)
+    yi.paramsSetBool("z_channel", False)
+    for k, v in extra.items():
+        _set(yi, k, v)
+
+
+def _set(yi, k, v):
+    if isinstance(v, bool):
+        yi.paramsSetBool(k, v)
+    elif isinstance(v, int):
+        yi.paramsSetInt(k, v)
+    elif isinstance(v, float):
+        yi.paramsSetFloat(k, v)
+    elif isinstance(v, str):
+        yi.paramsSetString(k, v)
+    elif isinstance(v, (tuple, list)) and len(v) == 3:
+        yi.paramsSetPoint(k, *v)
+    elif isinstance(v, (tuple, list)) and len(v) == 4:
+        yi.paramsSetColor(k, *v)
+    elif isinstance(v, dict) and "point" in v:
+        yi.paramsSetPoint(k, *v["point"])
+    else:
+        raise TypeError(f"param {k}: {v!r}")
+
+
+def create(yi, kind, name, **params):
+    """kind in light|material|camera|background|integrator; colours are 4-tuples, points 3-tuples."""
+    yi.paramsClearAll()
+    for k, v in params.items():
+        _set(yi, k, v)
+    h = getattr(yi, "create" + kind.capitalize())(name)
+    if not h:
+        raise RuntimeError(f"create{kind.capitalize()}({name!r}, {params.get('type')!r}) failed")
+    return h
+
+
+def add_mesh(yi, verts, tris, mat, normals=None, smooth_angle=None, oid=None, bulk=True):
+    verts = np.asarray(verts, dtype=np.float32)
+    tris = np.asarray(tris, dtype=np.int32)
+    oid = yi.getNextFreeID() if oid is None else oid
+    assert yi.startTriMesh(oid, len(verts), len(tris), False, False, 0)
+    if bulk and hasattr(yi, "addVertices"):
+        assert yi.addVertices(verts, normals)
+        assert yi.addTriangles(tris, mat)
+    else:
+        for i, v in enumerate(verts):
+            yi.addVertex(float(v[0]), float(v[1]), float(v[2]))
+            if normals is not None:
+                yi.addNormal(*[float(x) for x in normals[i]])
+        for t in tris:
+            assert yi.addTriangle(int(t[0]), int(t[1]), int(t[2]), mat)
+    assert yi.endTriMesh()
+    if smooth_angle is not None:
+        assert yi.smoothMesh(oid, smooth_angle)
+    return oid
+
+
+def quad(p0, p1, p2, p3):
+    return np.array([p0, p1, p2, p3], dtype=np.float32), np.array([[0, 1, 2], [0, 2, 3]], dtype=np.int32)
+
+
+def box(lo, hi, rot_z=0.0):
+    lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+    c = 0.5 * (lo + hi)
+    corners = np.array([[x, y, z] for z in (lo[2], hi[2]) for y in (lo[1], hi[1]) for x in (lo[0], hi[0])])
+    if rot_z:
+        ca, sa = np.cos(rot_z), np.sin(rot_z)
+        d = corners - c
+        corners = np.stack([c[0] + ca * d[:, 0] - sa * d[:, 1], c[1] + sa * d[:, 0] + ca * d[:, 1],
+                            corners[:, 2]], 1)
+    # outward-facing winding
+    f = [[0, 2, 3], [0, 3, 1], [4, 5, 7], [4, 7, 6], [0, 1, 5], [0, 5, 4],
+         [2, 6, 7], [2, 7, 3], [0, 4, 6], [0, 6, 2], [1, 3, 7], [1, 7, 5]]
+    return corners.astype(np.float32), np.array(f, dtype=np.int32)
+
+
+def icosphere(subdiv):
+    t = (1.0 + 5 ** 0.5) / 2
+    v = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t), (0, 1, -t),
+         (t, 0, -1), (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    f = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4), (11, 10, 2),
+         (10, 7, 6), (7, 1, 8), (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9), (4, 9, 5),
+         (2, 4, 11), (6, 2, 10), (8, 6, 7), (9, 8, 1)]
+    v = np.array(v, dtype=np.float64)
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    f = np.array(f, dtype=np.int64)
+    for _ in range(subdiv):
+        e = np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]])
+        es = np.sort(e, axis=1)
+        uniq, inv = np.unique(es, axis=0, return_inverse=True)
+        mid = v[uniq[:, 0]] + v[uniq[:, 1]]
+        mid /= np.linalg.norm(mid, axis=1, keepdims=True)
+        base = len(v)
+        v = np.concatenate([v, mid])
+        n = len(f)
+        ab, bc, ca = base + inv[:n], base + inv[n:2 * n], base + inv[2 * n:]
+        f = np.concatenate([np.stack([f[:, 0], ab, ca], 1), np.stack([f[:, 1], bc, ab], 1),
+                            np.stack([f[:, 2], ca, bc], 1), np.stack([ab, bc, ca], 1)])
+    return v, f.astype(np.int32)
+
+
+def std_volintegr(yi):
+    create(yi, "integrator", "volintegr", type="none")
+
+
+# ----------------------------------------------------------------------------- C1: Cornell box
+def cornell_box(yi, width=512, height=512, spp=16, integrator="directlighting", light_samples=8,
+                mirror_box=True, threads=1, integ_params=None, **render_extra):
+    """~36 triangles, shinydiffuse walls/boxes (one box with specular_reflect), arealight bound to a
+    light_mat quad, perspective camera (BASELINE.json configs[0])."""
+    yi.startScene(0)
+    white = create(yi, "material", "white", type="shinydiffusemat", color=(0.76, 0.75, 0.5, 1.0), diffuse_reflect=1.0)
+    red = create(yi, "material", "red", type="shinydiffusemat", color=(0.63, 0.06, 0.04, 1.0), diffuse_reflect=1.0)
+    green = create(yi, "material", "green", type="shinydiffusemat", color=(0.15, 0.48, 0.09, 1.0), diffuse_reflect=1.0)
+    shiny = create(yi, "material", "shiny", type="shinydiffusemat", color=(0.7, 0.7, 0.75, 1.0),
+                   diffuse_reflect=0.8, specular_reflect=0.35 if mirror_box else 0.0,
+                   mirror_color=(1.0, 1.0, 1.0, 1.0))
+    lmat = create(yi, "material", "lightmat", type="light_mat", color=(1.0, 0.9, 0.7, 1.0), power=12.0)
+    yi.startGeometry()
+    add_mesh(yi, *quad((-1, -1, -1), (1, -1, -1), (1, 1, -1), (-1, 1, -1)), white, bulk=False)   # floor
+    add_mesh(yi, *quad((-1, -1, 1), (-1, 1, 1), (1, 1, 1), (1, -1, 1)), white, bulk=False)       # ceiling
+    add_mesh(yi, *quad((-1, 1, -1), (1, 1, -1), (1, 1, 1), (-1, 1, 1)), white, bulk=False)       # back
+    add_mesh(yi, *quad((-1, -1, -1), (-1, 1, -1), (-1, 1, 1), (-1, -1, 1)), red, bulk=False)     # left
+    add_mesh(yi, *quad((1, -1, -1), (1, -1, 1), (1, 1, 1), (1, 1, -1)), green, bulk=False)       # right
+    add_mesh(yi, *box((-0.7, -0.1, -1.0), (-0.1, 0.5, 0.2), rot_z=0.3), white)
+    add_mesh(yi, *box((0.15, -0.55, -1.0), (0.7, 0.0, -0.4), rot_z=-0.3), shiny)
+    lid = add_mesh(yi, *quad((-0.3, -0.3, 0.995), (0.3, -0.3, 0.995), (0.3, 0.3, 0.995), (-0.3, 0.3, 0.995)),
+                   lmat, bulk=False)
+    yi.endGeometry()
+    create(yi, "light", "area", type="arealight", corner=(-0.3, -0.3, 0.995), point1=(-0.3, 0.3, 0.995),
+           point2=(0.3, -0.3, 0.995), color=(1.0, 0.9, 0.7, 1.0), power=12.0, samples=light_samples,
+           object=int(lid))
+    create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -3.9, 0.0)}, to=(0.0, 0.0, 0.0),
+           up=(0.0, -3.9, 1.0), resx=width, resy=height, focal=1.4)
+    create(yi, "background", "bg", type="constant", color=(0.02, 0.02, 0.03, 1.0))
+    ip = dict(type=integrator, raydepth=5)
+    ip.update(integ_params or {})
+    create(yi, "integrator", "default", **ip)
+    std_volintegr(yi)
+    set_render(yi, width, height, spp=spp, threads=threads, **render_extra)
+
+
+# ----------------------------------------------------------------------------- C2: icosphere field
+def icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=64, bounces=4, seed=1,
+                    subdiv=3, smooth=True, threads=1, integrator="pathtracing", integ_params=None,
+                    **render_extra):
+    """Subdivided icospheres (1280 tris each at subdiv=3) on a jittered grid over a ground quad;
+    sun + point light; pathtracing (BASELINE.json configs[1])."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    v0, f0 = icosphere(subdiv)
+    per = len(f0)
+    n_sph = max(1, n_tris // per)
+    g = int(np.ceil(np.sqrt(n_sph)))
+    yi.startScene(0)
+    mats = [create(yi, "material", f"m{i}", type="shinydiffusemat", color=(*c, 1.0), diffuse_reflect=0.9)
+            for i, c in enumerate([(0.8, 0.3, 0.25), (0.3, 0.7, 0.3), (0.3, 0.4, 0.8), (0.8, 0.8, 0.7)])]
+    ground = create(yi, "material", "ground", type="shinydiffusemat", color=(0.6, 0.6, 0.6, 1.0), diffuse_reflect=0.8)
+    yi.startGeometry()
+    ext = float(g)
+    add_mesh(yi, *quad((-ext, -ext, 0), (ext, -ext, 0), (ext, ext, 0), (-ext, ext, 0)), ground, bulk=False)
+    # one mesh per material: bake the spheres (1280 tris x n_sph) into 4 big meshes
+    idx = np.arange(n_sph)
+    cx = (idx % g - (g - 1) / 2) * 2.0 + rng.uniform(-0.25, 0.25, n_sph)
+    cy = (idx // g - (g - 1) / 2) * 2.0 + rng.uniform(-0.25, 0.25, n_sph)
+    r = rng.uniform(0.45, 0.8, n_sph)
+    cz = r + rng.uniform(0.0, 0.6, n_sph)
+    which = rng.integers(0, len(mats), n_sph)
+    for m, mat in enumerate(mats):
+        sel = np.nonzero(which == m)[0]
+        if len(sel) == 0:
+            continue
+        V = (v0[None] * r[sel, None, None] + np.stack([cx[sel], cy[sel], cz[sel]], 1)[:, None]).reshape(-1, 3)
+        N = np.broadcast_to(v0[None], (len(sel),) + v0.shape).reshape(-1, 3) if smooth else None
+        F = (f0[None] + (np.arange(len(sel)) * len(v0))[:, None, None]).reshape(-1, 3)
+        add_mesh(yi, V.astype(np.float32), F.astype(np.int32), mat,
+                 normals=None if N is None else N.astype(np.float32), smooth_angle=181.0 if smooth else None)
+    yi.endGeometry()
+    create(yi, "light", "sun", type="sunlight", direction=(0.3, -0.4, 0.85), color=(1.0, 0.95, 0.85, 1.0),
+           power=1.2, angle=1.0, samples=4)
+    create(yi, "light", "pt", type="pointlight", **{"from": (0.0, 0.0, 6.0)}, color=(0.8, 0.85, 1.0, 1.0), power=30.0)
+    d = 0.55 * ext
+    create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -d * 1.6, d * 0.9)}, to=(0.0, 0.0, 0.5),
+           up=(0.0, -d * 1.6, d * 0.9 + 1.0), resx=width, resy=height, focal=1.1)
+    create(yi, "background", "bg", type="constant", color=(0.5, 0.6, 0.8, 1.0))
+    ip = dict(type=integrator, raydepth=5)
+    if integrator == "pathtracing":
+        ip.update(bounces=bounces, path_samples=1)
+    ip.update(integ_params or {})
+    create(yi, "integrator", "default", **ip)
+    std_volintegr(yi)
+    set_render(yi, width, height, spp=spp, threads=threads, **render_extra)
+    return n_sph * per + 2
+
+
+# ----------------------------------------------------------------------------- C3: triangle soup + AO
+def triangle_soup(yi, n_tris=10_000_000, width=512, height=512, spp=1, ao_samples=32, ao_distance=0.1,
+                  seed=2, threads=1, **render_extra):
+    """Random triangles: centres uniform in [-1,1]^3, edges N(0, 0.01^2); directlighting with AO —
+    the IntersectS any-hit stress (BASELINE.json configs[2])."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    c = rng.uniform(-1, 1, (n_tris, 3)).astype(np.float32)
+    e = rng.normal(0, 0.01, (n_tris, 3, 3)).astype(np.float32)
+    V = (c[:, None, :] + e).reshape(-1, 3)
+    F = np.arange(3 * n_tris, dtype=np.int32).reshape(-1, 3)
+    yi.startScene(0)
+    mat = create(yi, "material", "soup", type="shinydiffusemat", color=(0.8, 0.8, 0.8, 1.0), diffuse_reflect=1.0)
+    yi.startGeometry()
+    add_mesh(yi, V, F, mat)
+    yi.endGeometry()
+    create(yi, "light", "pt", type="pointlight", **{"from": (0.0, -3.0, 3.0)}, color=(1.0, 1.0, 1.0, 1.0), power=20.0)
+    create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -3.2, 0.4)}, to=(0.0, 0.0, 0.0),
+           up=(0.0, -3.2, 1.4), resx=width, resy=height, focal=1.2)
+    create(yi, "background", "bg", type="constant", color=(0.1, 0.1, 0.1, 1.0))
+    create(yi, "integrator", "default", type="directlighting", raydepth=2, do_AO=True, AO_samples=ao_samples,
+           AO_distance=float(ao_distance), AO_color=(0.9, 0.9, 0.9, 1.0))
+    std_volintegr(yi)
+    set_render(yi, width, height, spp=spp, threads=threads, **render_extra)
+    return n_tris
+
+
+def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0, aspect=1.0):
+    """Host restatement of perspectiveCam_t::shootRay (perspectiveCamera.cc:57-71,127-149) at pixel
+    centres — only used to make ray batches for the traversal parity tests/bench (float64 math; the
+    rays themselves are the shared input, so exactness versus the reference camera is irrelevant)."""
+    pos = np.asarray(cam_from, np.float64)
+    camY = np.asarray(cam_up, np.float64) - pos
+    camZ = np.asarray(cam_to, np.float64) - pos
+    camX = np.cross(camZ, camY)
+    camY = np.cross(camZ, camX)
+    camX /= np.linalg.norm(camX); camY /= np.linalg.norm(camY); camZ /= np.linalg.norm(camZ)
+    asp = aspect * height / width
+    vright, vup = camX, asp * camY
+    vto = camZ * focal - 0.5 * (vup + vright)
+    vup = vup / height; vright = vright / width
+    ys, xs = np.mgrid[0:height, 0:width]
+    px = xs.reshape(-1) + 0.5; py = ys.reshape(-1) + 0.5
+    if n is not None and n < px.size:
+        sel = np.random.Generator(np.random.PCG64(seed)).choice(px.size, n, replace=False)
+        px, py = px[sel], py[sel]
+    d = vright[None] * px[:, None] + vup[None] * py[:, None] + vto[None]
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros((d.shape[0], 8), dtype=np.float32)
+    rays[:, 0:3] = pos; rays[:, 3] = 0.0; rays[:, 4:7] = d; rays[:, 7] = -1.0
+    return rays

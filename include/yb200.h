@@ -1,0 +1,131 @@
+/* yb200.h — C ABI of libyb200.so: the B200-native ray/integrator hot path behind the
+ * yafrayInterface_t / renderEnvironment_t API of inferrna/Core (TheBounty 0.1.6).
+ *
+ * Every entry point replaces one reference interface (cited as file:line relative to the
+ * reference tree).  Plain pointers and sizes only; no C++/torch types cross this boundary.
+ * All functions returning int return 1 on success and 0 on failure (the reference's `bool`);
+ * on failure yb200_last_error() holds a "Y_ERROR"-style message.  Unsupported features
+ * (materials, lights, volumes, universal scene mode, shader nodes ...) FAIL — there is no
+ * CPU fallback anywhere in this library.
+ */
+#ifndef YB200_H
+#define YB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct yb200_ctx yb200_ctx;
+/* borrowed token, like the material_t* / light_t* the reference hands back
+ * (include/interface/yafrayinterface.h:103-112); 0 == NULL == creation failed */
+typedef uintptr_t yb200_handle;
+
+/* ---- lifetime: yafrayInterface_t ctor/dtor, getYafray() (src/interface/yafrayinterface.cc:11-29,386-392) */
+yb200_ctx  *yb200_create(void);
+void        yb200_destroy(yb200_ctx *c);
+const char *yb200_last_error(yb200_ctx *c);
+const char *yb200_version(void);                               /* yafrayinterface.cc:313-320 getVersion */
+int         yb200_set_device(yb200_ctx *c, int cuda_device);   /* new: which GPU this context renders on */
+void        yb200_set_verbosity(yb200_ctx *c, int level);      /* yafrayinterface.cc:360-384 (0 mute .. 3 info) */
+void        yb200_clear_all(yb200_ctx *c);                     /* yafrayinterface.cc:47-64 */
+
+/* ---- scene state machine: scene_t (src/yafraycore/scene.cc:95-135,266-319,522-662,362-520,983-1008) */
+int      yb200_start_scene(yb200_ctx *c, int type);            /* yafrayinterface.cc:66-73; type!=0 fails (universal mode) */
+int      yb200_start_geometry(yb200_ctx *c);                   /* scene.cc:95-100 */
+int      yb200_end_geometry(yb200_ctx *c);                     /* scene.cc:102-117 */
+unsigned yb200_get_next_free_id(yb200_ctx *c);                 /* scene.cc:950-966 */
+int      yb200_start_trimesh(yb200_ctx *c, unsigned id, int vertices, int triangles,
+                             int has_orco, int has_uv, int type); /* scene.cc:266-294 */
+int      yb200_end_trimesh(yb200_ctx *c);                      /* scene.cc:296-319 */
+int      yb200_add_vertex(yb200_ctx *c, double x, double y, double z);            /* scene.cc:525-542 */
+int      yb200_add_vertex_orco(yb200_ctx *c, double x, double y, double z,
+                               double ox, double oy, double oz);                  /* scene.cc:544-566 */
+void     yb200_add_normal(yb200_ctx *c, double nx, double ny, double nz);         /* scene.cc:568-583 */
+int      yb200_add_triangle(yb200_ctx *c, int a, int b, int cc, yb200_handle mat);/* scene.cc:585-626 */
+int      yb200_add_triangle_uv(yb200_ctx *c, int a, int b, int cc, int uv_a, int uv_b, int uv_c,
+                               yb200_handle mat);                                  /* scene.cc:628-646 */
+int      yb200_add_uv(yb200_ctx *c, float u, float v);                            /* scene.cc:648-662 */
+int      yb200_smooth_mesh(yb200_ctx *c, unsigned id, double angle);              /* scene.cc:362-520 */
+int      yb200_add_instance(yb200_ctx *c, unsigned base_id, const float m[16]);   /* scene.cc:983-1008; row-major 4x4 */
+/* bulk SoA forms of the three calls above (same semantics as calling them n times) */
+int      yb200_add_vertices(yb200_ctx *c, const float *xyz, const float *normals_or_null, int n);
+int      yb200_add_triangles(yb200_ctx *c, const int *abc, int n, yb200_handle mat);
+
+/* ---- parameter maps: paraMap_t (include/core_api/params.h:40-125; yafrayinterface.cc:146-222) */
+void yb200_params_set_point (yb200_ctx *c, const char *name, double x, double y, double z);
+void yb200_params_set_string(yb200_ctx *c, const char *name, const char *s);
+void yb200_params_set_bool  (yb200_ctx *c, const char *name, int b);
+void yb200_params_set_int   (yb200_ctx *c, const char *name, int i);
+void yb200_params_set_float (yb200_ctx *c, const char *name, double f);
+void yb200_params_set_color (yb200_ctx *c, const char *name, float r, float g, float b, float a);
+void yb200_params_set_matrix(yb200_ctx *c, const char *name, const float m[16], int transpose);
+void yb200_params_clear_all (yb200_ctx *c);
+void yb200_params_start_list(yb200_ctx *c);
+void yb200_params_push_list (yb200_ctx *c);
+void yb200_params_end_list  (yb200_ctx *c);
+
+/* ---- factories: renderEnvironment_t::create* (src/yafraycore/environment.cc:189-479) keyed by "type" */
+yb200_handle yb200_create_light     (yb200_ctx *c, const char *name);  /* pointlight | sunlight | arealight */
+yb200_handle yb200_create_material  (yb200_ctx *c, const char *name);  /* shinydiffusemat | glossy | coated_glossy | glass | mirror | null | light_mat */
+yb200_handle yb200_create_camera    (yb200_ctx *c, const char *name);  /* perspective */
+yb200_handle yb200_create_background(yb200_ctx *c, const char *name);  /* constant */
+yb200_handle yb200_create_integrator(yb200_ctx *c, const char *name);  /* directlighting | pathtracing | none (volume) */
+yb200_handle yb200_create_texture   (yb200_ctx *c, const char *name);  /* always fails: shader nodes/textures unsupported */
+yb200_handle yb200_create_volume_region(yb200_ctx *c, const char *name); /* always fails */
+
+/* ---- render: yafrayInterface_t::render + scene_t::render + imageFilm_t::flush
+ *      (yafrayinterface.cc:336-342, scene.cc:931-945, imagefilm.cc:383-443).
+ * The render parameters are the current paraMap (camera_name, integrator_name, volintegrator_name,
+ * background_name, width, height, xstart, ystart, AA_*, filter_type, AA_pixelwidth, gamma, clamp_rgb,
+ * premult, tile_size ...; environment.cc:493-505,607-664).
+ * rgba: caller-owned HOST buffer, memoryIO_t layout (src/yafraycore/memoryIO.cc:27-43):
+ *       width*height*4 floats, index (x + width*y)*4.  Callbacks mirror colorOutput_t/progressBar_t. */
+typedef struct yb200_callbacks {
+    void *user;
+    int  (*should_abort)(void *user);                       /* scene_t::abort flag poll (scene.cc:71-85) */
+    void (*progress)(void *user, int done, int total);      /* progressBar_t::update (monitor.h:24-36) */
+} yb200_callbacks;
+int yb200_render(yb200_ctx *c, float *rgba, int width, int height, const yb200_callbacks *cb);
+
+/* Multi-GPU form: scene update + accumulate this rank's image tiles into a DEVICE film of
+ * width*height*5 floats (r,g,b,a,weight raw sums; pixel_t, include/utilities/image_buffers.h:28-43)
+ * laid out (x + width*y)*5.  Tiles (imageSpliter_t, imagesplitter.cc:29-52) are dealt round-robin:
+ * tile i belongs to rank i % world.  The caller sums the films of all ranks (NCCL reduce) and calls
+ * yb200_film_resolve on the sum.  dev_film must be zeroed by the caller. */
+int yb200_render_film(yb200_ctx *c, float *dev_film, int rank, int world, const yb200_callbacks *cb);
+/* normalise / clamp / gamma / premult exactly like imageFilm_t::flush; dev_film device, rgba HOST or DEVICE */
+int yb200_film_resolve(yb200_ctx *c, const float *dev_film, float *rgba, int rgba_on_device);
+void yb200_abort(yb200_ctx *c);                              /* yafrayinterface.cc:278 */
+
+/* ---- scene update only (scene_t::update, scene.cc:748-850): flatten + GPU BVH build */
+int yb200_update_scene(yb200_ctx *c);
+
+/* ---- parity / benchmark hook for triKdTree_t::Intersect / IntersectS / IntersectTS
+ *      through scene_t::intersect / isShadowed (scene.cc:852-928, kdtree.cc:675-1108).
+ * rays: n records of 8 floats {from.xyz, tmin, dir.xyz, tmax}; tmax<0 = infinite (scene.cc:856,888).
+ * mode YB200_TRACE_CLOSEST: out = n records {int32 prim, float t, float b1, float b2} (prim=-1: miss);
+ *      prim indexes the global triangle order of scene.cc:760-781.
+ * mode YB200_TRACE_SHADOW:  out = n int32 (1 shadowed / 0 not)           — isShadowed(state,ray)
+ * mode YB200_TRACE_TSHADOW: out = n records {int32 shadowed, float r,g,b} — isShadowed(state,ray,depth,filt)
+ * on_device: rays/out are device pointers (no copies, asynchronous on the context stream). */
+enum { YB200_TRACE_CLOSEST = 0, YB200_TRACE_SHADOW = 1, YB200_TRACE_TSHADOW = 2 };
+int yb200_trace_batch(yb200_ctx *c, const float *rays, size_t n, int mode, int shadow_depth,
+                      void *out, int on_device);
+
+/* ---- counters (new: the reference has none) */
+typedef struct yb200_stats {
+    uint64_t n_triangles, n_bvh_nodes;
+    uint64_t rays_closest, rays_shadow;        /* scene_t::intersect / isShadowed calls of the last render */
+    uint64_t camera_samples, kernel_launches;
+    double   build_ms, render_ms, trace_closest_ms, trace_shadow_ms, shade_ms, film_ms;
+    uint64_t bvh_bytes, tri_bytes;
+} yb200_stats;
+int yb200_get_stats(yb200_ctx *c, yb200_stats *out);
+void *yb200_cuda_stream(yb200_ctx *c);          /* cudaStream_t the context launches on */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YB200_H */
