@@ -1,0 +1,774 @@
+// yb_bsdf.cuh — device restatement of the material_t interface for the supported materials:
+//   shinyDiffuseMat_t  src/materials/shinydiffuse.cc:132-469
+//   glossyMat_t        src/materials/glossy.cc:82-351       (+ include/materials/microfacet.h)
+//   coatedGlossyMat_t  src/materials/coatedglossy.cc:104-418
+//   glassMat_t/mirrorMat_t/nullMat_t  src/materials/glass.cc:84-253,336-390
+//   lightMat_t         src/materials/simple.cc:54-75
+// Constant-parameter forms only (shader nodes are rejected at creation).  The reference's behaviours
+// that look like bugs are kept on purpose: W = |wi.N|/(0.99 pdf + 0.01), no 1/pi, ...
+#pragma once
+#include "yb_types.h"
+
+namespace yb {
+
+struct Surf {            // the fields of surfacePoint_t the supported materials read (triangle.cc:12-108)
+    v3 P, N, Ng, NU, NV;
+    const Material *mat;
+};
+struct MatDat { float c[4]; };   // SDDat_t::component[4]  |  MDat_t{mDiffuse,mGlossy,pDiffuse}
+struct BSample {                 // sample_t (material.h:49-60) minus the reverse-path fields
+    float s1, s2, pdf;
+    uint32_t flags, sampledFlags;
+    YB_HD BSample(float a, float b, uint32_t f) : s1(a), s2(b), pdf(0.f), flags(f), sampledFlags(BSDF_NONE) {}
+};
+struct RState { int raylevel; bool includeLights; };
+
+#define YB_FACE_FORWARD(Ng, N, I) ((dot((Ng), (I)) < 0) ? -(N) : (N))
+
+// ================================================================== microfacet.h
+YB_HD float pdfDivisor(float c) { return 8.f * (float)YB_M_PI * (c * 0.99f + 0.04f); }
+YB_HD float ASDivisor(float cos1, float cosI, float cosO) { return 8.f * (float)YB_M_PI * ((cos1 * fmaxf_(cosI, cosO)) * 0.99f + 0.04f); }
+YB_HD void sample_quadrant_aniso(v3 &H, float s1, float s2, float e_u, float e_v)
+{
+    float phi = atanf(fSqrt((e_u + 1.f) / (e_v + 1.f)) * tanf((float)YB_M_PI_2 * s1));
+    float cosPhi = fCos(phi), sinPhi = fSin(phi);
+    float cosPhi2 = cosPhi * cosPhi, sinPhi2 = 1.f - cosPhi2;
+    float cosTheta = fPow(1.f - s2, 1.f / (e_u * cosPhi2 + e_v * sinPhi2 + 1.f));
+    float sinTheta = fSqrt(1.f - cosTheta * cosTheta);
+    H = v3(sinTheta * cosPhi, sinTheta * sinPhi, cosTheta);
+}
+YB_HD float AS_Aniso_D(v3 h, float e_u, float e_v)
+{
+    if (h.z <= 0.f) return 0.f;
+    float exponent = (e_u * h.x * h.x + e_v * h.y * h.y) / (1.00001f - h.z * h.z);
+    return fSqrt((e_u + 1.f) * (e_v + 1.f)) * fPow(fmaxf_(0.f, h.z), exponent);
+}
+YB_HD float AS_Aniso_Pdf(v3 h, float cos_w_H, float e_u, float e_v) { return AS_Aniso_D(h, e_u, e_v) / pdfDivisor(cos_w_H); }
+YB_HD void AS_Aniso_Sample(v3 &H, float s1, float s2, float e_u, float e_v)
+{
+    if (s1 < 0.25f) sample_quadrant_aniso(H, 4.f * s1, s2, e_u, e_v);
+    else if (s1 < 0.5f) { sample_quadrant_aniso(H, 1.f - 4.f * (0.5f - s1), s2, e_u, e_v); H.x = -H.x; }
+    else if (s1 < 0.75f) { sample_quadrant_aniso(H, 4.f * (s1 - 0.5f), s2, e_u, e_v); H.x = -H.x; H.y = -H.y; }
+    else { sample_quadrant_aniso(H, 1.f - 4.f * (1.f - s1), s2, e_u, e_v); H.y = -H.y; }
+}
+YB_HD float Blinn_D(float cos_h, float e) { return (e + 1.f) * fPow(cos_h, e); }
+YB_HD float Blinn_Pdf(float costheta, float cos_w_H, float e) { return Blinn_D(costheta, e) / pdfDivisor(cos_w_H); }
+YB_HD void Blinn_Sample(v3 &H, float s1, float s2, float exponent)
+{
+    float cosTheta = fPow(1.f - s2, 1.f / (exponent + 1.f));
+    float sinTheta = fSqrt(1.f - cosTheta * cosTheta);
+    float phi = s1 * (float)YB_M_2PI;
+    H = v3(sinTheta * fCos(phi), sinTheta * fSin(phi), cosTheta);
+}
+YB_HD float SchlickFresnel(float costheta, float R)
+{
+    float c1 = (1.f - costheta);
+    float c2 = c1 * c1;
+    return R + ((1.f - R) * c1 * c2 * c2);
+}
+YB_HD col3 diffuseReflect(float wiN, float woN, float mGlossy, float mDiffuse, col3 diff_base)
+{
+    float f_wi = (1.f - (0.5f * wiN));
+    float temp = f_wi * f_wi;
+    f_wi = temp * temp * f_wi;
+    float f_wo = (1.f - (0.5f * woN));
+    temp = f_wo * f_wo;
+    f_wo = temp * temp * f_wo;
+    return (float)(0.387507688 * mDiffuse * (1.f - mGlossy) * (1.f - f_wi) * (1.f - f_wo)) * diff_base;
+}
+
+// ================================================================== shinyDiffuseMat_t
+YB_HD void sd_getFresnel(const Material &m, v3 wo, v3 n, float &Kr)      // shinydiffuse.cc:100-128
+{
+    if (m.hasFresnel) {
+        v3 N = (dot(wo, n) < 0.f) ? -n : n;
+        float c = dot(wo, N);
+        float g = m.iorSquared + c * c - 1.f;
+        if (g < 0.f) g = 0.f; else g = fSqrt(g);
+        float aux = c * (g + c);
+        Kr = ((0.5f * (g - c) * (g - c)) / ((g + c) * (g + c))) * (1.f + ((aux - 1) * (aux - 1)) / ((aux + 1) * (aux + 1)));
+    } else Kr = 1.f;
+}
+YB_HD void sd_accumulate(const float *component, float *accum, float Kr)  // :133-143
+{
+    accum[0] = component[0] * Kr;
+    float acc = 1.f - accum[0];
+    accum[1] = component[1] * acc;
+    acc *= 1.f - component[1];
+    accum[2] = component[2] * acc;
+    acc *= 1.f - component[2];
+    accum[3] = component[3] * acc;
+}
+YB_HD float sd_OrenNayar(const Material &m, v3 wi, v3 wo, v3 N)            // :185-220
+{
+    float cos_ti = fmaxf_(1e-8f, fminf_(1.f, dot(N, wi)));
+    float cos_to = fmaxf_(1e-8f, fminf_(1.f, dot(N, wo)));
+    float maxcos_f = 0.f;
+    if (cos_ti < 0.9999f && cos_to < 0.9999f) {
+        v3 v1 = normalize(wi - N * cos_ti);
+        v3 v2 = normalize(wo - N * cos_to);
+        maxcos_f = fmaxf_(0.f, dot(v1, v2));
+    }
+    float sin_alpha, tan_beta;
+    if (cos_to >= cos_ti) { sin_alpha = fSqrt(1.f - cos_ti * cos_ti); tan_beta = fSqrt(1.f - cos_to * cos_to) / cos_to; }
+    else { sin_alpha = fSqrt(1.f - cos_to * cos_to); tan_beta = fSqrt(1.f - cos_ti * cos_ti) / cos_ti; }
+    return m.orenA + m.orenB * maxcos_f * sin_alpha * tan_beta;
+}
+YB_HD void sd_initBSDF(const Material &m, MatDat &d)                       // :145-166 + getComponents :82-98
+{
+    d.c[0] = d.c[1] = d.c[2] = d.c[3] = 0.f;
+    if (m.isMirror) d.c[0] = m.mirrorStrength;
+    if (m.isTransparent) d.c[1] = m.transparencyStrength;
+    if (m.isTranslucent) d.c[2] = m.translucencyStrength;
+    if (m.isDiffuse) d.c[3] = m.diffuseStrength;
+}
+YB_HD col3 sd_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)   // :223-249
+{
+    float cos_Ng_wo = dot(sp.Ng, wo), cos_Ng_wl = dot(sp.Ng, wl);
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    if (!(bsdfs & m.bsdfFlags & BSDF_DIFFUSE)) return col3(0.f);
+    float Kr;
+    sd_getFresnel(m, wo, N, Kr);
+    float mT = (1.f - Kr * d.c[0]) * (1.f - d.c[1]);
+    bool transmit = (cos_Ng_wo * cos_Ng_wl) < 0.f;
+    if (transmit) { if (m.isTranslucent) return (d.c[2] * mT) * m.diffuseColor; }
+    if (dot(N, wl) < 0.0f) return col3(0.f);
+    float mD = mT * (1.f - d.c[2]) * d.c[3];
+    if (m.useOrenNayar) mD *= sd_OrenNayar(m, wo, wl, N);
+    return mD * m.diffuseColor;
+}
+YB_HD col3 sd_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)   // :259-336
+{
+    float accumC[4];
+    float cos_Ng_wo = dot(sp.Ng, wo), cos_Ng_wi, cos_N;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    float Kr;
+    sd_getFresnel(m, wo, N, Kr);
+    sd_accumulate(d.c, accumC, Kr);
+    float sum = 0.f, val[4], width[4];
+    uint32_t choice[4];
+    int nMatch = 0, pick = -1;
+    for (int i = 0; i < m.nBSDF; ++i) {
+        if ((s.flags & m.cFlags[i]) == m.cFlags[i]) {
+            width[nMatch] = accumC[m.cIndex[i]];
+            sum += width[nMatch];
+            choice[nMatch] = m.cFlags[i];
+            val[nMatch] = sum;
+            ++nMatch;
+        }
+    }
+    if (!nMatch || sum < 0.00001) { s.sampledFlags = BSDF_NONE; s.pdf = 0.f; return col3(1.f); }
+    float inv_sum = 1.f / sum;
+    for (int i = 0; i < nMatch; ++i) {
+        val[i] *= inv_sum;
+        width[i] *= inv_sum;
+        if ((s.s1 <= val[i]) && (pick < 0)) pick = i;
+    }
+    if (pick < 0) pick = nMatch - 1;
+    float s1;
+    if (pick > 0) s1 = (s.s1 - val[pick - 1]) / width[pick];
+    else s1 = s.s1 / width[pick];
+    col3 scolor(0.f);
+    switch (choice[pick]) {
+        case (BSDF_SPECULAR | BSDF_REFLECT):
+            wi = reflect_dir(N, wo);
+            s.pdf = width[pick];
+            scolor = m.mirrorColor * accumC[0];
+            scolor *= 1.f / fabsf(dot(sp.N, wi));
+            break;
+        case (BSDF_TRANSMIT | BSDF_FILTER):
+            wi = -wo;
+            scolor = accumC[1] * (m.transmitFilterStrength * m.diffuseColor + col3(1.f - m.transmitFilterStrength));
+            cos_N = fabsf(dot(wi, N));
+            if (cos_N < 1e-6) s.pdf = 0.f; else s.pdf = width[pick];
+            break;
+        case (BSDF_DIFFUSE | BSDF_TRANSMIT):
+            wi = SampleCosHemisphere(-N, sp.NU, sp.NV, s1, s.s2);
+            cos_Ng_wi = dot(sp.Ng, wi);
+            if (cos_Ng_wo * cos_Ng_wi < 0) scolor = accumC[2] * m.diffuseColor;
+            s.pdf = fabsf(dot(wi, N)) * width[pick];
+            break;
+        case (BSDF_DIFFUSE | BSDF_REFLECT):
+        default:
+            wi = SampleCosHemisphere(N, sp.NU, sp.NV, s1, s.s2);
+            cos_Ng_wi = dot(sp.Ng, wi);
+            if (cos_Ng_wo * cos_Ng_wi > 0) scolor = accumC[3] * m.diffuseColor;
+            if (m.useOrenNayar) scolor *= sd_OrenNayar(m, wo, wi, N);
+            s.pdf = fabsf(dot(wi, N)) * width[pick];
+            break;
+    }
+    s.sampledFlags = choice[pick];
+    W = fabsf(dot(wi, sp.N)) / (s.pdf * 0.99f + 0.01f);
+    return scolor;
+}
+YB_HD float sd_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)   // :338-377
+{
+    if (!(bsdfs & BSDF_DIFFUSE)) return 0.f;
+    float pdf = 0.f, accumC[4];
+    float cos_Ng_wo = dot(sp.Ng, wo), cos_Ng_wi;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    float Kr;
+    sd_getFresnel(m, wo, N, Kr);
+    sd_accumulate(d.c, accumC, Kr);
+    float sum = 0.f, width;
+    int nMatch = 0;
+    for (int i = 0; i < m.nBSDF; ++i) {
+        if (bsdfs & m.cFlags[i]) {
+            width = accumC[m.cIndex[i]];
+            sum += width;
+            switch (m.cFlags[i]) {
+                case (BSDF_DIFFUSE | BSDF_TRANSMIT):
+                    cos_Ng_wi = dot(sp.Ng, wi);
+                    if (cos_Ng_wo * cos_Ng_wi < 0) pdf += fabsf(dot(wi, N)) * width;
+                    break;
+                case (BSDF_DIFFUSE | BSDF_REFLECT):
+                    pdf += fabsf(dot(wi, N)) * width;
+                    break;
+            }
+            ++nMatch;
+        }
+    }
+    if (!nMatch || sum < 0.00001) return 0.f;
+    return pdf / sum;
+}
+YB_HD void sd_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, bool &doReflect, bool &doRefract, v3 *wi, col3 *col)   // :391-433
+{
+    const bool backface = dot(wo, sp.Ng) < 0.f;
+    const v3 N = backface ? -sp.N : sp.N;
+    const v3 Ng = backface ? -sp.Ng : sp.Ng;
+    float Kr;
+    sd_getFresnel(m, wo, N, Kr);
+    if (m.isTransparent) {
+        doRefract = true;
+        wi[1] = -wo;
+        col3 tcol = m.transmitFilterStrength * m.diffuseColor + col3(1.f - m.transmitFilterStrength);
+        col[1] = ((1.f - d.c[0] * Kr) * d.c[1]) * tcol;
+    } else doRefract = false;
+    if (m.isMirror) {
+        doReflect = true;
+        wi[0] = reflect_about(wo, N);
+        float cos_wi_Ng = dot(wi[0], Ng);
+        if (cos_wi_Ng < 0.01) {
+            wi[0] += (float)(0.01 - cos_wi_Ng) * Ng;
+            wi[0] = normalize(wi[0]);
+        }
+        col[0] = m.mirrorColor * (d.c[0] * Kr);
+    } else doReflect = false;
+}
+YB_HD col3 sd_getTransparency(const Material &m, const Surf &sp, v3 wo)      // :435-455
+{
+    float accum = 1.f, Kr;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    sd_getFresnel(m, wo, N, Kr);
+    if (m.isMirror) accum = 1.f - Kr * m.mirrorStrength;
+    if (m.isTransparent) accum *= m.transparencyStrength * accum;
+    col3 tcol = m.transmitFilterStrength * m.diffuseColor + col3(1.f - m.transmitFilterStrength);
+    return accum * tcol;
+}
+YB_HD float sd_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)   // :457-469
+{
+    if (m.isTransparent) {
+        v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+        float Kr;
+        sd_getFresnel(m, wo, N, Kr);
+        float refl = (1.f - d.c[0] * Kr) * d.c[1];
+        return 1.f - refl;
+    }
+    return 1.f;
+}
+
+// ================================================================== glossyMat_t / coatedGlossyMat_t shared
+YB_HD void gl_initBSDF(const Material &m, MatDat &d)                         // glossy.cc:82-95, coatedglossy.cc:104-117
+{
+    d.c[0] = m.mDiffuse;
+    d.c[1] = m.reflectivity;
+    d.c[2] = fminf_(0.6f, 1.f - (d.c[1] / (d.c[1] + (1.f - d.c[1]) * d.c[0])));
+    d.c[3] = 0.f;
+}
+YB_HD float gl_OrenNayar(const Material &m, v3 wi, v3 wo, v3 N)               // glossy.cc:105-132
+{
+    float cos_ti = fmaxf_(-1.f, fminf_(1.f, dot(N, wi)));
+    float cos_to = fmaxf_(-1.f, fminf_(1.f, dot(N, wo)));
+    float maxcos_f = 0.f;
+    if (cos_ti < 0.9999f && cos_to < 0.9999f) {
+        v3 v1 = normalize(wi - N * cos_ti);
+        v3 v2 = normalize(wo - N * cos_to);
+        maxcos_f = fmaxf_(0.f, dot(v1, v2));
+    }
+    float sin_alpha, tan_beta;
+    if (cos_to >= cos_ti) { sin_alpha = fSqrt(1.f - cos_ti * cos_ti); tan_beta = fSqrt(1.f - cos_to * cos_to) / ((cos_to == 0.f) ? 1e-8f : cos_to); }
+    else { sin_alpha = fSqrt(1.f - cos_to * cos_to); tan_beta = fSqrt(1.f - cos_ti * cos_ti) / ((cos_ti == 0.f) ? 1e-8f : cos_ti); }
+    return m.orenA + m.orenB * maxcos_f * sin_alpha * tan_beta;
+}
+
+// ================================================================== glossyMat_t
+YB_HD col3 gl_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)    // glossy.cc:134-173
+{
+    if (!(bsdfs & BSDF_DIFFUSE) || (dot(sp.Ng, wi) * dot(sp.Ng, wo)) < 0.f) return col3(0.f);
+    col3 col(0.f);
+    bool diffuse_flag = bsdfs & BSDF_DIFFUSE;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    float wiN = fabsf(dot(wi, N)), woN = fabsf(dot(wo, N));
+    if ((m.asDiffuse && diffuse_flag) || (!m.asDiffuse && (bsdfs & BSDF_GLOSSY))) {
+        v3 H = normalize(wo + wi);
+        float cos_wi_H = fmaxf_(0.f, dot(wi, H));
+        float glossy;
+        if (m.anisotropic) {
+            v3 Hs(dot(H, sp.NU), dot(H, sp.NV), dot(H, N));
+            glossy = AS_Aniso_D(Hs, m.expU, m.expV) * SchlickFresnel(cos_wi_H, d.c[1]) / ASDivisor(cos_wi_H, woN, wiN);
+        } else glossy = Blinn_D(dot(H, N), m.exponent) * SchlickFresnel(cos_wi_H, d.c[1]) / ASDivisor(cos_wi_H, woN, wiN);
+        col = glossy * m.glossColor;
+    }
+    if (m.withDiffuse && diffuse_flag)
+        col += (d.c[0] * (1.f - d.c[1])) * m.diffColor * (m.orenNayar ? gl_OrenNayar(m, wi, wo, N) : 1.f);
+    return col;
+}
+YB_HD col3 gl_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)   // glossy.cc:176-305
+{
+    float cos_Ng_wo = dot(sp.Ng, wo), cos_Ng_wi;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    v3 Hs;
+    s.pdf = 0.f;
+    float wiN = 0.f, woN = fabsf(dot(wo, N)), cos_wo_H = 0.f;
+    col3 scolor(0.f);
+    float s1 = s.s1;
+    float cur_pDiffuse = d.c[2];
+    bool use_glossy = m.asDiffuse ? (s.flags & BSDF_DIFFUSE) : (s.flags & BSDF_GLOSSY);
+    bool use_diffuse = m.withDiffuse && (s.flags & BSDF_DIFFUSE);
+    float glossy = 0.f;
+    if (use_diffuse) {
+        float s_pDiffuse = use_glossy ? cur_pDiffuse : 1.f;
+        if (s1 < s_pDiffuse) {
+            s1 /= s_pDiffuse;
+            wi = SampleCosHemisphere(N, sp.NU, sp.NV, s1, s.s2);
+            cos_Ng_wi = dot(sp.Ng, wi);
+            if (cos_Ng_wi * cos_Ng_wo < 0.f) return scolor;
+            wiN = fabsf(dot(wi, N));
+            s.pdf = wiN;
+            if (use_glossy) {
+                v3 H = normalize(wi + wo);
+                cos_wo_H = dot(wo, H);
+                float cos_wi_H = fabsf(dot(wi, H));
+                float cos_N_H = dot(N, H);
+                if (m.anisotropic) {
+                    v3 Hs2(dot(H, sp.NU), dot(H, sp.NV), cos_N_H);
+                    s.pdf = s.pdf * cur_pDiffuse + AS_Aniso_Pdf(Hs2, cos_wo_H, m.expU, m.expV) * (1.f - cur_pDiffuse);
+                    glossy = AS_Aniso_D(Hs2, m.expU, m.expV) * SchlickFresnel(cos_wi_H, d.c[1]) / ASDivisor(cos_wi_H, woN, wiN);
+                } else {
+                    s.pdf = s.pdf * cur_pDiffuse + Blinn_Pdf(cos_N_H, cos_wo_H, m.exponent) * (1.f - cur_pDiffuse);
+                    glossy = Blinn_D(cos_N_H, m.exponent) * SchlickFresnel(cos_wi_H, d.c[1]) / ASDivisor(cos_wi_H, woN, wiN);
+                }
+            }
+            s.sampledFlags = BSDF_DIFFUSE | BSDF_REFLECT;
+            if (!(s.flags & BSDF_REFLECT)) return col3(0.f);
+            scolor = glossy * m.glossColor;
+            if (use_diffuse) scolor += diffuseReflect(wiN, woN, d.c[1], d.c[0], m.diffColor) * (m.orenNayar ? gl_OrenNayar(m, wi, wo, N) : 1.f);
+            W = wiN / (s.pdf * 0.99f + 0.01f);
+            return scolor;
+        }
+        s1 -= cur_pDiffuse;
+        s1 /= (1.f - cur_pDiffuse);
+    }
+    if (use_glossy) {
+        if (m.anisotropic) AS_Aniso_Sample(Hs, s1, s.s2, m.expU, m.expV);
+        else Blinn_Sample(Hs, s1, s.s2, m.exponent);
+        v3 H = Hs.x * sp.NU + Hs.y * sp.NV + Hs.z * N;
+        cos_wo_H = dot(wo, H);
+        if (cos_wo_H < 0.f) { H = reflect_about(H, N); cos_wo_H = dot(wo, H); }
+        wi = reflect_dir(H, wo);
+        cos_Ng_wi = dot(sp.Ng, wi);
+        if (cos_Ng_wo * cos_Ng_wi < 0.f) return col3(0.f);
+        wiN = fabsf(dot(wi, N));
+        if (m.anisotropic) {
+            s.pdf = AS_Aniso_Pdf(Hs, cos_wo_H, m.expU, m.expV);
+            glossy = AS_Aniso_D(Hs, m.expU, m.expV) * SchlickFresnel(cos_wo_H, d.c[1]) / ASDivisor(cos_wo_H, woN, wiN);
+        } else {
+            float cosHN = dot(H, N);
+            s.pdf = Blinn_Pdf(cosHN, cos_wo_H, m.exponent);
+            glossy = Blinn_D(cosHN, m.exponent) * SchlickFresnel(cos_wo_H, d.c[1]) / ASDivisor(cos_wo_H, woN, wiN);
+        }
+        scolor = glossy * m.glossColor;
+        s.sampledFlags = m.asDiffuse ? (BSDF_DIFFUSE | BSDF_REFLECT) : (BSDF_GLOSSY | BSDF_REFLECT);
+    }
+    if (use_diffuse) {
+        s.pdf = wiN * cur_pDiffuse + s.pdf * (1.f - cur_pDiffuse);
+        scolor += diffuseReflect(wiN, woN, d.c[1], d.c[0], m.diffColor) * (m.orenNayar ? gl_OrenNayar(m, wi, wo, N) : 1.f);
+    }
+    W = wiN / (s.pdf * 0.99f + 0.01f);
+    return scolor;
+}
+YB_HD float gl_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t flags)    // glossy.cc:307-351
+{
+    if (dot(sp.Ng, wo) * dot(sp.Ng, wi) < 0.f) return 0.f;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    float pdf = 0.f, cos_wo_H, cos_N_H, cur_pDiffuse = d.c[2];
+    bool use_glossy = m.asDiffuse ? (flags & BSDF_DIFFUSE) : (flags & BSDF_GLOSSY);
+    bool use_diffuse = m.withDiffuse && (flags & BSDF_DIFFUSE);
+    if (use_diffuse) {
+        pdf = fabsf(dot(wi, N));
+        if (use_glossy) {
+            v3 H = normalize(wi + wo);
+            cos_wo_H = dot(wo, H);
+            cos_N_H = dot(N, H);
+            if (m.anisotropic) {
+                v3 Hs(dot(H, sp.NU), dot(H, sp.NV), cos_N_H);
+                pdf = pdf * cur_pDiffuse + AS_Aniso_Pdf(Hs, cos_wo_H, m.expU, m.expV) * (1.f - cur_pDiffuse);
+            } else pdf = pdf * cur_pDiffuse + Blinn_Pdf(cos_N_H, cos_wo_H, m.exponent) * (1.f - cur_pDiffuse);
+        }
+        return pdf;
+    }
+    if (use_glossy) {
+        v3 H = normalize(wi + wo);
+        cos_wo_H = dot(wo, H);
+        cos_N_H = dot(N, H);
+        if (m.anisotropic) {
+            v3 Hs(dot(H, sp.NU), dot(H, sp.NV), cos_N_H);
+            pdf = AS_Aniso_Pdf(Hs, cos_wo_H, m.expU, m.expV);
+        } else pdf = Blinn_Pdf(cos_N_H, cos_wo_H, m.exponent);
+    }
+    return pdf;
+}
+
+// ================================================================== coatedGlossyMat_t
+#define YB_C_SPECULAR 0
+#define YB_C_GLOSSY 1
+#define YB_C_DIFFUSE 2
+YB_HD col3 cg_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)     // coatedglossy.cc:156-193
+{
+    col3 col(0.f);
+    bool diffuse_flag = bsdfs & BSDF_DIFFUSE;
+    if (!diffuse_flag || (dot(sp.Ng, wi) * dot(sp.Ng, wo)) < 0.f) return col;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    float Kr, Kt;
+    float wiN = fabsf(dot(wi, N)), woN = fabsf(dot(wo, N));
+    fresnel(wo, N, m.ior, Kr, Kt);
+    if ((m.asDiffuse && diffuse_flag) || (!m.asDiffuse && (bsdfs & BSDF_GLOSSY))) {
+        v3 H = normalize(wo + wi);
+        float cos_wi_H = dot(wi, H);
+        float glossy;
+        if (m.anisotropic) {
+            v3 Hs(dot(H, sp.NU), dot(H, sp.NV), dot(H, N));
+            glossy = Kt * AS_Aniso_D(Hs, m.expU, m.expV) * SchlickFresnel(cos_wi_H, d.c[1]) / ASDivisor(cos_wi_H, woN, wiN);
+        } else glossy = Kt * Blinn_D(dot(H, N), m.exponent) * SchlickFresnel(cos_wi_H, d.c[1]) / ASDivisor(cos_wi_H, woN, wiN);
+        col = glossy * m.glossColor;
+    }
+    if (m.withDiffuse && diffuse_flag)
+        col += (d.c[0] * (1.f - d.c[1])) * m.diffColor * Kt * (m.orenNayar ? gl_OrenNayar(m, wi, wo, N) : 1.f);
+    return col;
+}
+YB_HD col3 cg_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)   // :195-336
+{
+    float cos_Ng_wo = dot(sp.Ng, wo), cos_Ng_wi;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    v3 Hs(0.f);
+    s.pdf = 0.f;
+    float Kr, Kt, wiN = 0.f, woN = 0.f;
+    fresnel(wo, N, m.ior, Kr, Kt);
+    bool use[3] = {false, false, false};
+    float sum = 0.f, accumC[3], val[3], width[3];
+    int cIndex[3] = {0, 0, 0}, rcIndex[3] = {0, 0, 0};
+    accumC[0] = Kr;
+    accumC[1] = Kt * (1.f - d.c[2]);
+    accumC[2] = Kt * (d.c[2]);
+    int nMatch = 0, pick = -1;
+    for (int i = 0; i < m.nBSDF; ++i) {
+        if ((s.flags & m.cFlags[i]) == m.cFlags[i]) {
+            use[i] = true;
+            width[nMatch] = accumC[i];
+            cIndex[nMatch] = i;
+            rcIndex[i] = nMatch;
+            sum += width[nMatch];
+            val[nMatch] = sum;
+            ++nMatch;
+        }
+    }
+    if (!nMatch || sum < 0.00001) return col3(0.f);
+    else if (nMatch == 1) { pick = 0; width[0] = 1.f; }
+    else {
+        float inv_sum = 1.f / sum;
+        for (int i = 0; i < nMatch; ++i) {
+            val[i] *= inv_sum;
+            width[i] *= inv_sum;
+            if ((s.s1 <= val[i]) && (pick < 0)) pick = i;
+        }
+    }
+    if (pick < 0) pick = nMatch - 1;
+    float s1;
+    if (pick > 0) s1 = (s.s1 - val[pick - 1]) / width[pick];
+    else s1 = s.s1 / width[pick];
+    col3 scolor(0.f);
+    wi = v3(0.f);   // reference reads an uninitialised wi for the glossy pick before overwriting wiN; value unused
+    switch (cIndex[pick]) {
+        case YB_C_SPECULAR:
+            wi = reflect_dir(N, wo);
+            scolor = m.mirrorColor * Kr;
+            s.pdf = width[pick];
+            break;
+        case YB_C_GLOSSY:
+            if (m.anisotropic) AS_Aniso_Sample(Hs, s1, s.s2, m.expU, m.expV);
+            else Blinn_Sample(Hs, s1, s.s2, m.exponent);
+            break;
+        case YB_C_DIFFUSE:
+        default:
+            wi = SampleCosHemisphere(N, sp.NU, sp.NV, s1, s.s2);
+            cos_Ng_wi = dot(sp.Ng, wi);
+            if (cos_Ng_wo * cos_Ng_wi < 0) return col3(0.f);
+    }
+    wiN = fabsf(dot(wi, N));
+    woN = fabsf(dot(wo, N));
+    if (cIndex[pick] != YB_C_SPECULAR) {
+        if (use[YB_C_GLOSSY]) {
+            float glossy, cos_wo_H;
+            v3 H(0.f);
+            if (cIndex[pick] != YB_C_GLOSSY) {
+                H = normalize(wi + wo);
+                Hs = v3(dot(H, sp.NU), dot(H, sp.NV), dot(H, N));
+                cos_wo_H = dot(wo, H);
+            } else {
+                H = Hs.x * sp.NU + Hs.y * sp.NV + Hs.z * N;
+                cos_wo_H = dot(wo, H);
+                if (cos_wo_H < 0.f) { H = reflect_about(H, N); cos_wo_H = dot(wo, H); }
+                wi = reflect_dir(H, wo);
+                cos_Ng_wi = dot(sp.Ng, wi);
+                if (cos_Ng_wo * cos_Ng_wi < 0) return col3(0.f);
+            }
+            wiN = fabsf(dot(wi, N));
+            if (m.anisotropic) {
+                s.pdf += AS_Aniso_Pdf(Hs, cos_wo_H, m.expU, m.expV) * width[rcIndex[YB_C_GLOSSY]];
+                glossy = AS_Aniso_D(Hs, m.expU, m.expV) * SchlickFresnel(cos_wo_H, d.c[1]) / ASDivisor(cos_wo_H, woN, wiN);
+            } else {
+                float cosHN = dot(H, N);
+                s.pdf += Blinn_Pdf(cosHN, cos_wo_H, m.exponent) * width[rcIndex[YB_C_GLOSSY]];
+                glossy = Blinn_D(cosHN, m.exponent) * SchlickFresnel(cos_wo_H, d.c[1]) / ASDivisor(cos_wo_H, woN, wiN);
+            }
+            scolor = (glossy * Kt) * m.glossColor;
+        }
+        if (use[YB_C_DIFFUSE]) {
+            scolor += Kt * diffuseReflect(wiN, woN, d.c[1], d.c[0], m.diffColor) * (m.orenNayar ? gl_OrenNayar(m, wi, wo, N) : 1.f);
+            s.pdf += wiN * width[rcIndex[YB_C_DIFFUSE]];
+        }
+        W = wiN / (s.pdf * 0.99f + 0.01f);
+    } else W = 1.f;
+    s.sampledFlags = m.cFlags[cIndex[pick]];
+    return scolor;
+}
+YB_HD float cg_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t flags)     // :338-382
+{
+    bool transmit = (dot(sp.Ng, wo) * dot(sp.Ng, wi)) < 0.f;
+    if (transmit) return 0.f;
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    float pdf = 0.f, Kr, Kt;
+    fresnel(wo, N, m.ior, Kr, Kt);
+    float accumC[3], sum = 0.f, width;
+    accumC[0] = Kr;
+    accumC[1] = Kt * (1.f - d.c[2]);
+    accumC[2] = Kt * (d.c[2]);
+    int nMatch = 0;
+    for (int i = 0; i < m.nBSDF; ++i) {
+        if ((flags & m.cFlags[i]) == m.cFlags[i]) {
+            width = accumC[i];
+            sum += width;
+            if (i == YB_C_GLOSSY) {
+                v3 H = normalize(wi + wo);
+                float cos_wo_H = dot(wo, H), cos_N_H = dot(N, H);
+                if (m.anisotropic) {
+                    v3 Hs(dot(H, sp.NU), dot(H, sp.NV), cos_N_H);
+                    pdf += AS_Aniso_Pdf(Hs, cos_wo_H, m.expU, m.expV) * width;
+                } else pdf += Blinn_Pdf(cos_N_H, cos_wo_H, m.exponent) * width;
+            } else if (i == YB_C_DIFFUSE) pdf += fabsf(dot(wi, N)) * width;
+            ++nMatch;
+        }
+    }
+    if (!nMatch || sum < 0.00001) return 0.f;
+    return pdf / sum;
+}
+// glass.cc:113-116 / coatedglossy.cc:387-398: the "bent" shading normal
+YB_HD v3 bent_normal(const Surf &sp, v3 wo, bool outside)
+{
+    float cos_wo_N = dot(sp.N, wo);
+    if (outside) return (cos_wo_N >= 0) ? sp.N : normalize(sp.N - (float)(1.00001 * cos_wo_N) * wo);
+    return (cos_wo_N <= 0) ? sp.N : normalize(sp.N - (float)(1.00001 * cos_wo_N) * wo);
+}
+YB_HD void cg_getSpecular(const Material &m, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)  // :384-418
+{
+    bool outside = dot(sp.Ng, wo) >= 0;
+    v3 N = bent_normal(sp, wo, outside);
+    v3 Ng = outside ? sp.Ng : -sp.Ng;
+    float Kr, Kt;
+    fresnel(wo, N, m.ior, Kr, Kt);
+    refr = false;
+    if (raylevel > 5) return;
+    dir[0] = reflect_about(wo, N);
+    col[0] = Kr * m.mirrorColor;
+    float cos_wi_Ng = dot(dir[0], Ng);
+    if (cos_wi_Ng < 0.01) {
+        dir[0] += (float)(0.01 - cos_wi_Ng) * Ng;
+        dir[0] = normalize(dir[0]);
+    }
+    refl = true;
+}
+
+// ================================================================== glassMat_t (no dispersion, no absorption: rejected at creation)
+#define YB_MATCHES(bits, flags) (((bits) & (flags)) == (flags))
+YB_HD col3 glass_sample(const Material &m, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)          // glass.cc:84-188 (else-branch :143-186)
+{
+    if (!(s.flags & BSDF_SPECULAR)) { s.pdf = 0.f; return col3(0.f); }
+    v3 refdir;
+    bool outside = dot(sp.Ng, wo) > 0;
+    v3 N = bent_normal(sp, wo, outside);
+    s.pdf = 1.f;
+    const uint32_t tmFlags = m.fakeShadow ? (BSDF_FILTER | BSDF_TRANSMIT) : (BSDF_SPECULAR | BSDF_TRANSMIT);
+    if (refract(N, wo, refdir, m.ior)) {
+        float Kr, Kt;
+        fresnel(wo, N, m.ior, Kr, Kt);
+        float pKr = (float)(0.01 + 0.99 * Kr), pKt = (float)(0.01 + 0.99 * Kt);
+        if (s.s1 < pKt && YB_MATCHES(s.flags, tmFlags)) {
+            wi = refdir;
+            s.pdf = pKt;
+            s.sampledFlags = tmFlags;
+            W = 1.f;
+            return m.filterCol;
+        } else if (YB_MATCHES(s.flags, BSDF_SPECULAR | BSDF_REFLECT)) {
+            wi = reflect_about(wo, N);
+            s.pdf = pKr;
+            s.sampledFlags = BSDF_SPECULAR | BSDF_REFLECT;
+            W = 1.f;
+            return m.specRefCol;
+        }
+    } else if (YB_MATCHES(s.flags, BSDF_SPECULAR | BSDF_REFLECT)) {   // total inner reflection
+        wi = reflect_about(wo, N);
+        s.sampledFlags = BSDF_SPECULAR | BSDF_REFLECT;
+        W = 1.f;
+        return col3(1.f);
+    }
+    s.pdf = 0.f;
+    return col3(0.f);
+}
+YB_HD col3 glass_getTransparency(const Material &m, const Surf &sp, v3 wo)                                // :190-196
+{
+    v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    float Kr, Kt;
+    fresnel(wo, N, m.ior, Kr, Kt);
+    return Kt * m.filterCol;
+}
+YB_HD float col_energy(col3 c) { return (c.x + c.y + c.z) * 0.333333f; }                                  // color.h energy()
+YB_HD void glass_getSpecular(const Material &m, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)  // :204-247
+{
+    bool outside = dot(sp.Ng, wo) > 0;
+    v3 N = bent_normal(sp, wo, outside);
+    v3 refdir;
+    if (refract(N, wo, refdir, m.ior)) {
+        float Kr, Kt;
+        fresnel(wo, N, m.ior, Kr, Kt);
+        col[1] = Kt * m.filterCol;
+        dir[1] = refdir;
+        refr = true;
+        if (outside || raylevel < 3) {
+            dir[0] = reflect_about(wo, N);
+            col[0] = m.specRefCol * Kr;
+            refl = true;
+        } else refl = false;
+    } else {
+        col[0] = col3(1.f);
+        dir[0] = reflect_about(wo, N);
+        refl = true;
+        refr = false;
+    }
+}
+
+// ================================================================== dispatch: material_t virtuals
+YB_HD void mat_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
+{
+    bsdfs = m.bsdfFlags;
+    switch (m.type) {
+        case MAT_SHINYDIFFUSE: sd_initBSDF(m, d); break;
+        case MAT_GLOSSY: case MAT_COATED_GLOSSY: gl_initBSDF(m, d); break;
+        case MAT_NULL: bsdfs = BSDF_NONE;   // glass.cc:374
+        default: d.c[0] = d.c[1] = d.c[2] = d.c[3] = 0.f; break;
+    }
+}
+YB_HD col3 mat_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
+{
+    switch (m.type) {
+        case MAT_SHINYDIFFUSE: return sd_eval(m, d, sp, wo, wl, bsdfs);
+        case MAT_GLOSSY: return gl_eval(m, d, sp, wo, wl, bsdfs);
+        case MAT_COATED_GLOSSY: return cg_eval(m, d, sp, wo, wl, bsdfs);
+        default: return col3(0.f);
+    }
+}
+YB_HD col3 mat_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
+{
+    switch (m.type) {
+        case MAT_SHINYDIFFUSE: return sd_sample(m, d, sp, wo, wi, s, W);
+        case MAT_GLOSSY: return gl_sample(m, d, sp, wo, wi, s, W);
+        case MAT_COATED_GLOSSY: return cg_sample(m, d, sp, wo, wi, s, W);
+        case MAT_GLASS: return glass_sample(m, sp, wo, wi, s, W);
+        case MAT_MIRROR:                                                 // glass.cc:348-354
+            wi = reflect_dir(sp.N, wo);
+            s.sampledFlags = BSDF_SPECULAR | BSDF_REFLECT;
+            W = 1.f;
+            return m.specRefCol * (1.f / fabsf(dot(sp.N, wi)));
+        default:                                                         // nullMat_t / lightMat_t
+            s.pdf = 0.f; W = 0.f; wi = v3(0.f);
+            return col3(0.f);
+    }
+}
+YB_HD float mat_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
+{
+    switch (m.type) {
+        case MAT_SHINYDIFFUSE: return sd_pdf(m, d, sp, wo, wi, bsdfs);
+        case MAT_GLOSSY: return gl_pdf(m, d, sp, wo, wi, bsdfs);
+        case MAT_COATED_GLOSSY: return cg_pdf(m, d, sp, wo, wi, bsdfs);
+        default: return 0.f;
+    }
+}
+YB_HD col3 mat_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
+{
+    if (m.type == MAT_SHINYDIFFUSE) return m.emitColor;                 // shinydiffuse.cc:251-257
+    if (m.type == MAT_LIGHT) {                                          // simple.cc:63-70
+        if (!includeLights) return col3(0.f);
+        if (m.doubleSided) return m.lightCol;
+        return (dot(wo, sp.N) > 0) ? m.lightCol : col3(0.f);
+    }
+    return col3(0.f);
+}
+YB_HD void mat_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
+{
+    switch (m.type) {
+        case MAT_SHINYDIFFUSE: sd_getSpecular(m, d, sp, wo, refl, refr, dir, col); break;
+        case MAT_COATED_GLOSSY: cg_getSpecular(m, sp, wo, raylevel, refl, refr, dir, col); break;
+        case MAT_GLASS: glass_getSpecular(m, sp, wo, raylevel, refl, refr, dir, col); break;
+        case MAT_MIRROR: {                                               // glass.cc:356-364
+            col[0] = m.specRefCol; col[1] = col3(1.f);
+            v3 N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+            dir[0] = reflect_dir(N, wo);
+            refl = true; refr = false;
+            break;
+        }
+        default: refl = false; refr = false; break;                      // material.h:141-144
+    }
+}
+YB_HD bool mat_isTransparent(const Material &m)
+{
+    if (m.type == MAT_SHINYDIFFUSE) return m.isTransparent != 0;        // shinydiff.h isTransparent(){return mIsTransparent;}
+    if (m.type == MAT_GLASS) return m.fakeShadow != 0;
+    return false;
+}
+YB_HD col3 mat_getTransparency(const Material &m, const Surf &sp, v3 wo)
+{
+    if (m.type == MAT_SHINYDIFFUSE) return sd_getTransparency(m, sp, wo);
+    if (m.type == MAT_GLASS) return glass_getTransparency(m, sp, wo);
+    return col3(0.f);
+}
+YB_HD float mat_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
+{
+    if (m.type == MAT_SHINYDIFFUSE) return sd_getAlpha(m, d, sp, wo);
+    if (m.type == MAT_GLASS) {                                          // glass.cc:198-202
+        float alpha = (float)(1.0 - col_energy(glass_getTransparency(m, sp, wo)));
+        if (alpha < 0.0f) alpha = 0.0f;
+        return alpha;
+    }
+    return 1.f;
+}
+
+}  // namespace yb

@@ -1,0 +1,357 @@
+// yb_bvh.cu — GPU build of the 8-wide quantised BVH that replaces triKdTree_t (src/yafraycore/kdtree.cc:75-666).
+//
+// Pipeline (every step a kernel; only the level loop of the collapse talks to the host):
+//   bounds -> 63-bit Morton codes of triangle centroids -> radix sort -> binary radix tree (Karras 2012)
+//   -> bottom-up AABB fit -> top-down collapse to 8-wide nodes (open the child with the largest surface area
+//   until 8 slots are used; subtrees of <= 4 triangles become leaf children) with octant-ordered slots and
+//   8-bit quantised child boxes -> triangles re-laid out leaf by leaf (48 B each).
+// The reference's SAH kd-tree is replaced, not restated; only its query semantics are kept.
+#include "yb_scene.h"
+#include "yb_trace.cuh"
+#include <vector>
+#include <algorithm>
+#ifndef YB_HOSTEMU
+#include <cub/device/device_radix_sort.cuh>
+#endif
+
+namespace yb {
+
+uint64_t g_kernel_launches = 0;
+
+// order-preserving float <-> int map for atomic min/max
+YB_HD int32_t f2ord(float f) { int32_t i = f2i(f); return i >= 0 ? i : (int32_t)(i ^ 0x7fffffff); }
+YB_HD float ord2f(int32_t i) { return i2f(i >= 0 ? i : (int32_t)(i ^ 0x7fffffff)); }
+
+struct BoundsArgs { const f4 *v; int32_t *ob; };    // ob[0..2] = min, ob[3..5] = max (ordered ints)
+YB_KERNEL(k_bounds, BoundsArgs)
+{
+    const f4 A = a.v[3 * tid], B = a.v[3 * tid + 1], C = a.v[3 * tid + 2];
+    YB_ATOMIC_MIN_I32(a.ob + 0, f2ord(fminf_(A.x, fminf_(B.x, C.x))));
+    YB_ATOMIC_MIN_I32(a.ob + 1, f2ord(fminf_(A.y, fminf_(B.y, C.y))));
+    YB_ATOMIC_MIN_I32(a.ob + 2, f2ord(fminf_(A.z, fminf_(B.z, C.z))));
+    YB_ATOMIC_MAX_I32(a.ob + 3, f2ord(fmaxf_(A.x, fmaxf_(B.x, C.x))));
+    YB_ATOMIC_MAX_I32(a.ob + 4, f2ord(fmaxf_(A.y, fmaxf_(B.y, C.y))));
+    YB_ATOMIC_MAX_I32(a.ob + 5, f2ord(fmaxf_(A.z, fmaxf_(B.z, C.z))));
+}
+
+YB_HD uint64_t spread21(uint32_t v)
+{
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+struct MortonArgs { const f4 *v; uint64_t *keys; uint32_t *idx; v3 lo, inv; };
+YB_KERNEL(k_morton, MortonArgs)
+{
+    const f4 A = a.v[3 * tid], B = a.v[3 * tid + 1], C = a.v[3 * tid + 2];
+    float cx = (fminf_(A.x, fminf_(B.x, C.x)) + fmaxf_(A.x, fmaxf_(B.x, C.x))) * 0.5f;
+    float cy = (fminf_(A.y, fminf_(B.y, C.y)) + fmaxf_(A.y, fmaxf_(B.y, C.y))) * 0.5f;
+    float cz = (fminf_(A.z, fminf_(B.z, C.z)) + fmaxf_(A.z, fmaxf_(B.z, C.z))) * 0.5f;
+    float fx = fminf_(fmaxf_((cx - a.lo.x) * a.inv.x, 0.f), 1.f) * 2097151.f;
+    float fy = fminf_(fmaxf_((cy - a.lo.y) * a.inv.y, 0.f), 1.f) * 2097151.f;
+    float fz = fminf_(fmaxf_((cz - a.lo.z) * a.inv.z, 0.f), 1.f) * 2097151.f;
+    a.keys[tid] = (spread21((uint32_t)fx) << 2) | (spread21((uint32_t)fy) << 1) | spread21((uint32_t)fz);
+    a.idx[tid] = tid;
+}
+
+// ---- binary radix tree (Karras 2012).  child refs: >= 0 internal node, < 0 leaf ~i
+YB_HD int clz64(uint64_t x)
+{
+#if defined(__CUDA_ARCH__)
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+struct KarrasArgs { const uint64_t *keys; int32_t n; int32_t *left, *right, *parent, *first, *last; };
+YB_HD int karras_delta(const KarrasArgs &a, int i, int j)
+{
+    if (j < 0 || j >= a.n) return -1;
+    uint64_t ki = a.keys[i], kj = a.keys[j];
+    if (ki == kj) return 64 + (yb_clz((uint32_t)i ^ (uint32_t)j));
+    return clz64(ki ^ kj);
+}
+YB_KERNEL(k_karras, KarrasArgs)
+{
+    const int i = (int)tid;
+    const int d = (karras_delta(a, i, i + 1) - karras_delta(a, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = karras_delta(a, i, i - d);
+    int lmax = 2;
+    while (karras_delta(a, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (karras_delta(a, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = karras_delta(a, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) / 2;
+        if (karras_delta(a, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int gamma = i + s * d + (d < 0 ? d : 0);
+    const int lo = i < j ? i : j, hi = i < j ? j : i;
+    const int L = (lo == gamma) ? ~gamma : gamma;
+    const int R = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    a.left[i] = L; a.right[i] = R;
+    a.first[i] = lo; a.last[i] = hi;
+    // parent array: internal nodes at [0, n-1), leaves at [n-1, 2n-1)
+    a.parent[L >= 0 ? L : (a.n - 1 + ~L)] = i;
+    a.parent[R >= 0 ? R : (a.n - 1 + ~R)] = i;
+}
+
+YB_HD void tri_bounds(const f4 *v, uint32_t t, v3 &lo, v3 &hi)
+{
+    const f4 A = v[3 * t], B = v[3 * t + 1], C = v[3 * t + 2];
+    lo = v3(fminf_(A.x, fminf_(B.x, C.x)), fminf_(A.y, fminf_(B.y, C.y)), fminf_(A.z, fminf_(B.z, C.z)));
+    hi = v3(fmaxf_(A.x, fmaxf_(B.x, C.x)), fmaxf_(A.y, fmaxf_(B.y, C.y)), fmaxf_(A.z, fmaxf_(B.z, C.z)));
+}
+struct FitArgs { const f4 *v; const uint32_t *idx; int32_t n; const int32_t *left, *right, *parent; uint32_t *flag; v3 *nlo, *nhi; };
+YB_HD void fit_child_bounds(const FitArgs &a, int ref, v3 &lo, v3 &hi)
+{
+    if (ref < 0) tri_bounds(a.v, a.idx[~ref], lo, hi);
+    else { lo = a.nlo[ref]; hi = a.nhi[ref]; }
+}
+YB_KERNEL(k_fit, FitArgs)
+{
+    int node = a.parent[a.n - 1 + (int)tid];
+    for (;;) {
+        YB_THREADFENCE();
+        if (YB_ATOMIC_ADD_U32(a.flag + node, 1u) == 0u) return;   // first arrival: the sibling will finish this node
+        YB_THREADFENCE();
+        v3 l0, h0, l1, h1;
+        fit_child_bounds(a, a.left[node], l0, h0);
+        fit_child_bounds(a, a.right[node], l1, h1);
+        a.nlo[node] = v3(fminf_(l0.x, l1.x), fminf_(l0.y, l1.y), fminf_(l0.z, l1.z));
+        a.nhi[node] = v3(fmaxf_(h0.x, h1.x), fmaxf_(h0.y, h1.y), fmaxf_(h0.z, h1.z));
+        if (node == 0) return;
+        node = a.parent[node];
+    }
+}
+
+// ---- collapse to 8-wide
+#define YB_MAX_LEAF 4
+struct CollapseItem { int32_t bnode; uint32_t wnode; };
+struct CollapseArgs {
+    const CollapseItem *in;
+    CollapseItem *out;
+    uint32_t *counters;               // [0] wide nodes allocated, [1] triangles allocated, [2] items written, [3] max leaf seen
+    const f4 *v; const v3 *nrm; const uint32_t *idx; int32_t n;
+    const int32_t *left, *right, *first, *last;
+    const v3 *nlo, *nhi;
+    BvhNode *nodes; f4 *out_v; v3 *out_n;
+    uint32_t nodeCap;
+};
+YB_HD int cref_count(const CollapseArgs &a, int ref) { return ref < 0 ? 1 : (a.last[ref] - a.first[ref] + 1); }
+YB_HD float box_area(v3 lo, v3 hi) { v3 e = hi - lo; return e.x * e.y + e.y * e.z + e.z * e.x; }
+YB_HD void cref_bounds(const CollapseArgs &a, int ref, v3 &lo, v3 &hi)
+{
+    if (ref < 0) tri_bounds(a.v, a.idx[~ref], lo, hi);
+    else { lo = a.nlo[ref]; hi = a.nhi[ref]; }
+}
+// smallest e (as biased exponent byte) with 2^(e-127) * 255 >= extent
+YB_HD uint32_t quant_exp(float extent)
+{
+    if (!(extent > 0.f)) return 0u;
+    float cell = extent / 255.f;
+    uint32_t bits = (uint32_t)f2i(cell);
+    uint32_t e = (bits >> 23) & 0xffu;
+    if (bits & 0x7fffffu) e += 1;       // round the cell size up to a power of two
+    if (e < 1u) e = 1u;
+    if (e > 254u) e = 254u;
+    return e;
+}
+YB_KERNEL(k_collapse, CollapseArgs)
+{
+    const CollapseItem it = a.in[tid];
+    int child[8];
+    int nc = 0;
+    if (it.bnode >= 0) { child[0] = a.left[it.bnode]; child[1] = a.right[it.bnode]; nc = 2; }
+    else { child[0] = it.bnode; nc = 1; }           // single-triangle scene
+    // open the largest expandable child until 8 slots are used
+    while (nc < 8) {
+        int best = -1; float bestA = -1.f;
+        for (int i = 0; i < nc; ++i) {
+            if (child[i] < 0 || cref_count(a, child[i]) <= YB_MAX_LEAF) continue;
+            float ar = box_area(a.nlo[child[i]], a.nhi[child[i]]);
+            if (ar > bestA) { bestA = ar; best = i; }
+        }
+        if (best < 0) break;
+        int b = child[best];
+        child[best] = a.left[b];
+        child[nc++] = a.right[b];
+    }
+    v3 plo, phi;
+    if (it.bnode >= 0) { plo = a.nlo[it.bnode]; phi = a.nhi[it.bnode]; } else cref_bounds(a, it.bnode, plo, phi);
+    const v3 pc = (plo + phi) * 0.5f;
+    v3 clo[8], chi[8];
+    for (int i = 0; i < nc; ++i) cref_bounds(a, child[i], clo[i], chi[i]);
+    // greedy octant slot assignment: child i -> slot s maximising dot(centroid_i - pc, dir_s)
+    int slotOf[8], childIn[8];
+    for (int i = 0; i < 8; ++i) { slotOf[i] = -1; childIn[i] = -1; }
+    for (int round = 0; round < nc; ++round) {
+        float bestC = -INFINITY; int bi = -1, bs = -1;
+        for (int i = 0; i < nc; ++i) {
+            if (slotOf[i] >= 0) continue;
+            v3 dc = (clo[i] + chi[i]) * 0.5f - pc;
+            for (int s = 0; s < 8; ++s) {
+                if (childIn[s] >= 0) continue;
+                float c = ((s & 1) ? dc.x : -dc.x) + ((s & 2) ? dc.y : -dc.y) + ((s & 4) ? dc.z : -dc.z);
+                if (c > bestC) { bestC = c; bi = i; bs = s; }
+            }
+        }
+        slotOf[bi] = bs; childIn[bs] = bi;
+    }
+    // count internal children / leaf triangles
+    uint32_t nInt = 0, nTri = 0;
+    for (int s = 0; s < 8; ++s) {
+        int i = childIn[s];
+        if (i < 0) continue;
+        int cnt = cref_count(a, child[i]);
+        if (child[i] >= 0 && cnt > YB_MAX_LEAF) nInt++; else nTri += (uint32_t)cnt;
+    }
+    const uint32_t childBase = nInt ? YB_ATOMIC_ADD_U32(a.counters + 0, nInt) : 0u;
+    const uint32_t triBase = nTri ? YB_ATOMIC_ADD_U32(a.counters + 1, nTri) : 0u;
+    const uint32_t itemBase = nInt ? YB_ATOMIC_ADD_U32(a.counters + 2, nInt) : 0u;
+    BvhNode nd;
+    memset(&nd, 0, sizeof(nd));
+    nd.px = plo.x; nd.py = plo.y; nd.pz = plo.z;
+    const uint32_t ex = quant_exp(phi.x - plo.x), ey = quant_exp(phi.y - plo.y), ez = quant_exp(phi.z - plo.z);
+    nd.ex = (uint8_t)ex; nd.ey = (uint8_t)ey; nd.ez = (uint8_t)ez;
+    const float cellx = i2f((int32_t)(ex << 23)), celly = i2f((int32_t)(ey << 23)), cellz = i2f((int32_t)(ez << 23));
+    nd.childBase = childBase; nd.triBase = triBase;
+    uint32_t kInt = 0, triOff = 0;
+    for (int s = 0; s < 8; ++s) {
+        int i = childIn[s];
+        if (i < 0) continue;
+        // conservative 8-bit box
+        float lo3[3] = {clo[i].x, clo[i].y, clo[i].z}, hi3[3] = {chi[i].x, chi[i].y, chi[i].z};
+        float p3[3] = {plo.x, plo.y, plo.z}, cell3[3] = {cellx, celly, cellz};
+        uint8_t ql[3], qh[3];
+        for (int ax = 0; ax < 3; ++ax) {
+            int l = 0, h = 0;
+            if (cell3[ax] > 0.f) {
+                l = (int)floorf((lo3[ax] - p3[ax]) / cell3[ax]);
+                h = (int)ceilf((hi3[ax] - p3[ax]) / cell3[ax]);
+                if (l < 0) l = 0; if (l > 255) l = 255;
+                if (h < 0) h = 0; if (h > 255) h = 255;
+                while (l > 0 && p3[ax] + (float)l * cell3[ax] > lo3[ax]) --l;
+                while (h < 255 && p3[ax] + (float)h * cell3[ax] < hi3[ax]) ++h;
+            }
+            ql[ax] = (uint8_t)l; qh[ax] = (uint8_t)h;
+        }
+        nd.qlox[s] = ql[0]; nd.qloy[s] = ql[1]; nd.qloz[s] = ql[2];
+        nd.qhix[s] = qh[0]; nd.qhiy[s] = qh[1]; nd.qhiz[s] = qh[2];
+        int ref = child[i];
+        int cnt = cref_count(a, ref);
+        if (ref >= 0 && cnt > YB_MAX_LEAF) {
+            nd.imask |= (uint8_t)(1u << s);
+            nd.meta[s] = (uint8_t)(0xE0u | kInt);
+            CollapseItem o; o.bnode = ref; o.wnode = childBase + kInt;
+            a.out[itemBase + kInt] = o;
+            ++kInt;
+        } else {
+            nd.meta[s] = (uint8_t)(((uint32_t)cnt << 5) | triOff);
+            int f = ref < 0 ? ~ref : a.first[ref];
+            for (int j = 0; j < cnt; ++j) {
+                uint32_t src = a.idx[f + j], dst = triBase + triOff + (uint32_t)j;
+                a.out_v[3 * dst] = a.v[3 * src]; a.out_v[3 * dst + 1] = a.v[3 * src + 1]; a.out_v[3 * dst + 2] = a.v[3 * src + 2];
+                if (a.nrm) { a.out_n[3 * dst] = a.nrm[3 * src]; a.out_n[3 * dst + 1] = a.nrm[3 * src + 1]; a.out_n[3 * dst + 2] = a.nrm[3 * src + 2]; }
+            }
+            triOff += (uint32_t)cnt;
+        }
+    }
+    if (it.wnode < a.nodeCap) a.nodes[it.wnode] = nd;
+}
+
+// ---------------------------------------------------------------------------------------------- host driver
+void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &nodes, DevBuf<f4> &out_v, DevBuf<v3> &out_n,
+               uint32_t &nNodes, uint32_t &maxDepth, v3 &boundLo, v3 &boundHi, rt_stream s)
+{
+    nNodes = 0; maxDepth = 0;
+    boundLo = v3(0.f); boundHi = v3(0.f);
+    if (n == 0) return;
+    DevBuf<int32_t> ob; ob.reserve(8);
+    int32_t init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int32_t)0x80000000, (int32_t)0x80000000, (int32_t)0x80000000};
+    rt_h2d(ob.p, init, sizeof(init), s);
+    BoundsArgs ba; ba.v = in_v; ba.ob = ob.p;
+    k_bounds(n, ba, s);
+    int32_t obh[6];
+    rt_d2h(obh, ob.p, sizeof(obh), s);
+    boundLo = v3(ord2f(obh[0]), ord2f(obh[1]), ord2f(obh[2]));
+    boundHi = v3(ord2f(obh[3]), ord2f(obh[4]), ord2f(obh[5]));
+    v3 ext = boundHi - boundLo;
+
+    DevBuf<uint64_t> keys; DevBuf<uint32_t> idx;
+    keys.reserve(n); idx.reserve(n);
+    MortonArgs ma; ma.v = in_v; ma.keys = keys.p; ma.idx = idx.p; ma.lo = boundLo;
+    ma.inv = v3(ext.x > 0 ? 1.f / ext.x : 0.f, ext.y > 0 ? 1.f / ext.y : 0.f, ext.z > 0 ? 1.f / ext.z : 0.f);
+    k_morton(n, ma, s);
+#ifndef YB_HOSTEMU
+    {
+        DevBuf<uint64_t> keys2; DevBuf<uint32_t> idx2; DevBuf<char> tmp;
+        keys2.reserve(n); idx2.reserve(n);
+        size_t tmpBytes = 0;
+        YB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, keys.p, keys2.p, idx.p, idx2.p, (int)n, 0, 63, s));
+        tmp.reserve(tmpBytes);
+        YB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp.p, tmpBytes, keys.p, keys2.p, idx.p, idx2.p, (int)n, 0, 63, s));
+        rt_d2d(keys.p, keys2.p, n * sizeof(uint64_t), s);
+        rt_d2d(idx.p, idx2.p, n * sizeof(uint32_t), s);
+        rt_sync(s);
+        g_kernel_launches += 4;
+    }
+#else
+    {
+        std::vector<std::pair<uint64_t, uint32_t>> kv(n);
+        for (uint32_t i = 0; i < n; ++i) kv[i] = std::make_pair(keys.p[i], idx.p[i]);
+        std::stable_sort(kv.begin(), kv.end(), [](const std::pair<uint64_t, uint32_t> &x, const std::pair<uint64_t, uint32_t> &y) { return x.first < y.first; });
+        for (uint32_t i = 0; i < n; ++i) { keys.p[i] = kv[i].first; idx.p[i] = kv[i].second; }
+    }
+#endif
+    const uint32_t nInt = n > 1 ? n - 1 : 0;
+    DevBuf<int32_t> left, right, parent, first, last; DevBuf<uint32_t> flag; DevBuf<v3> nlo, nhi;
+    left.reserve(nInt); right.reserve(nInt); first.reserve(nInt); last.reserve(nInt); parent.reserve(2 * (size_t)n);
+    flag.reserve(nInt); nlo.reserve(nInt); nhi.reserve(nInt);
+    if (nInt) {
+        KarrasArgs ka; ka.keys = keys.p; ka.n = (int32_t)n; ka.left = left.p; ka.right = right.p; ka.parent = parent.p; ka.first = first.p; ka.last = last.p;
+        k_karras(nInt, ka, s);
+        rt_memset(flag.p, 0, nInt * sizeof(uint32_t), s);
+        FitArgs fa; fa.v = in_v; fa.idx = idx.p; fa.n = (int32_t)n; fa.left = left.p; fa.right = right.p; fa.parent = parent.p; fa.flag = flag.p; fa.nlo = nlo.p; fa.nhi = nhi.p;
+        k_fit(n, fa, s);
+    }
+    // collapse, level by level
+    const uint32_t nodeCap = n / 2 + 16;       // every internal wide node has >= 2 children with > YB_MAX_LEAF/… tris; generous bound
+    nodes.reserve(nodeCap); out_v.reserve(3 * (size_t)n);
+    if (in_n) out_n.reserve(3 * (size_t)n);
+    DevBuf<CollapseItem> qa, qb; qa.reserve(nodeCap); qb.reserve(nodeCap);
+    DevBuf<uint32_t> counters; counters.reserve(4);
+    uint32_t c0[4] = {1, 0, 0, 0};
+    rt_h2d(counters.p, c0, sizeof(c0), s);
+    CollapseItem root; root.bnode = nInt ? 0 : ~0; root.wnode = 0;
+    rt_h2d(qa.p, &root, sizeof(root), s);
+    uint32_t nItems = 1;
+    CollapseArgs ca; ca.counters = counters.p; ca.v = in_v; ca.nrm = in_n; ca.idx = idx.p; ca.n = (int32_t)n;
+    ca.left = left.p; ca.right = right.p; ca.first = first.p; ca.last = last.p; ca.nlo = nlo.p; ca.nhi = nhi.p;
+    ca.nodes = nodes.p; ca.out_v = out_v.p; ca.out_n = in_n ? out_n.p : 0; ca.nodeCap = nodeCap;
+    DevBuf<CollapseItem> *qin = &qa, *qout = &qb;
+    while (nItems) {
+        ++maxDepth;
+        ca.in = qin->p; ca.out = qout->p;
+        k_collapse(nItems, ca, s);
+        uint32_t ch[4];
+        rt_d2h(ch, counters.p, sizeof(ch), s);
+        if (ch[0] > nodeCap) throw RtError("bvh_build: node capacity exceeded");
+        nItems = ch[2];
+        ch[2] = 0;
+        rt_h2d(counters.p, ch, sizeof(ch), s);
+        nNodes = ch[0];
+        std::swap(qin, qout);
+    }
+    rt_sync(s);
+    if (maxDepth > YB_STACK_SIZE - 2) throw RtError("bvh_build: tree deeper than the traversal stack");
+}
+
+}  // namespace yb

@@ -1,0 +1,773 @@
+// yb_host.cc — host side of the drop-in boundary: parameter maps, the scene_t geometry state machine
+// (src/yafraycore/scene.cc:95-135,266-319,362-662,950-1008), the factories of the supported plugin types
+// (renderEnvironment_t::create*, src/yafraycore/environment.cc:189-479, and each plugin's factory()),
+// render setup (environment.cc:481-531,596-694) and the flattener that turns meshes into device SoA buffers
+// in the global primitive order of scene_t::update (scene.cc:760-781).
+// Anything unsupported fails loudly (Y_ERROR-style message + failed call); there is no CPU render path here.
+#include "yb_scene.h"
+#include <stdio.h>
+#include <math.h>
+#include <limits.h>
+#include <algorithm>
+#include <chrono>
+
+namespace yb {
+
+// ------------------------------------------------------------------------------------------------ ParaMap
+#define YB_GET(T, field, TYPE)                                                       \
+    bool ParaMap::get(const std::string &n, T &o) const                              \
+    {                                                                                \
+        std::map<std::string, Param>::const_iterator i = dicc.find(n);               \
+        if (i == dicc.end() || i->second.type != Param::TYPE) return false;          \
+        o = (T)i->second.field;                                                      \
+        return true;                                                                 \
+    }
+YB_GET(int, ival, T_INT)
+YB_GET(bool, bval, T_BOOL)
+YB_GET(float, fval, T_FLOAT)
+YB_GET(double, fval, T_FLOAT)
+bool ParaMap::get(const std::string &n, std::string &s) const
+{
+    std::map<std::string, Param>::const_iterator i = dicc.find(n);
+    if (i == dicc.end() || i->second.type != Param::T_STRING) return false;
+    s = i->second.sval;
+    return true;
+}
+bool ParaMap::getPoint(const std::string &n, v3 &p) const
+{
+    std::map<std::string, Param>::const_iterator i = dicc.find(n);
+    if (i == dicc.end() || i->second.type != Param::T_POINT) return false;
+    p = v3(i->second.v[0], i->second.v[1], i->second.v[2]);
+    return true;
+}
+bool ParaMap::getColor(const std::string &n, col3 &c) const
+{
+    std::map<std::string, Param>::const_iterator i = dicc.find(n);
+    if (i == dicc.end() || i->second.type != Param::T_COLOR) return false;
+    c = col3(i->second.v[0], i->second.v[1], i->second.v[2]);
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------ Context
+Context::Context()
+    : verbosity(2), device(-1), stream(0), streamOwned(false), cparams(&params), sceneStarted(false), sceneMode(0),
+      curObj(0), curId(0), lastVertId(0), curOrco(false), nextFreeID(INT_MAX), geomChanged(true), abortFlag(0),
+      nTris(0), nNodes(0), bvhDepth(0), haveNormals(false), sceneReady(false), rb(0)
+{
+    memset(&sc, 0, sizeof(sc));
+    memset(&stats, 0, sizeof(stats));
+    stateStack.push_back(ST_READY);
+}
+Context::~Context()
+{
+    render_release(rb);
+#ifndef YB_HOSTEMU
+    if (streamOwned && stream) cudaStreamDestroy(stream);
+#endif
+}
+bool Context::fail(const std::string &msg)
+{
+    err = msg;
+    if (verbosity >= 1) fprintf(stderr, "ERROR: yb200: %s\n", msg.c_str());
+    return false;
+}
+void Context::warn(const std::string &msg) { if (verbosity >= 2) fprintf(stderr, "WARNING: yb200: %s\n", msg.c_str()); }
+void Context::info(const std::string &msg) { if (verbosity >= 3) fprintf(stderr, "INFO: yb200: %s\n", msg.c_str()); }
+
+void Context::clearAll()   // yafrayinterface.cc:47-64
+{
+    params.clear(); eparams.clear(); cparams = &params;
+    materials.clear(); materialNames.clear(); lights.clear(); lightNames.clear(); lightObj.clear();
+    cameras.clear(); backgrounds.clear(); integrators.clear();
+    meshes.clear(); curObj = 0; stateStack.clear(); stateStack.push_back(ST_READY);
+    nextFreeID = INT_MAX; geomChanged = true; sceneReady = false; sceneStarted = false;
+}
+
+// ------------------------------------------------------------------------------------------------ scene state machine
+bool Context::startScene(int type)   // yafrayinterface.cc:66-73
+{
+    if (type != 0) return fail("startScene: universal scene mode (type 1) is not supported (triangle mode only)");
+    meshes.clear(); curObj = 0; stateStack.clear(); stateStack.push_back(ST_READY);
+    nextFreeID = INT_MAX; geomChanged = true; sceneReady = false;
+    sceneStarted = true; sceneMode = 0;
+    return true;
+}
+bool Context::startGeometry()
+{
+    if (stateStack.back() != ST_READY) return false;
+    stateStack.push_back(ST_GEOMETRY);
+    return true;
+}
+bool Context::endGeometry()
+{
+    if (stateStack.back() != ST_GEOMETRY) return false;
+    stateStack.pop_back();
+    return true;
+}
+unsigned Context::getNextFreeID()   // scene.cc:950-966
+{
+    unsigned id = nextFreeID;
+    while (meshes.find(id) != meshes.end()) { --nextFreeID; id = nextFreeID; }
+    --nextFreeID;
+    return id;
+}
+bool Context::startTriMesh(unsigned id, int vertices, int triangles, bool hasOrco, bool hasUV, int type)   // scene.cc:266-294
+{
+    if (stateStack.back() != ST_GEOMETRY) return false;
+    int ptype = type & 0xFF;
+    if (ptype != 0) { fail("startTriMesh: only TRIM (type 0) meshes are supported (VTRIM/MTRIM need universal mode)"); return false; }
+    MeshObj &o = meshes[id];
+    o = MeshObj();
+    o.has_orco = hasOrco; o.has_uv = hasUV;
+    o.visible = !(type & 0x0100);     // INVISIBLEM (scene.h:44-46)
+    o.is_base = (type & 0x0200) != 0; // BASEMESH
+    if (vertices > 0) o.points.reserve((size_t)vertices * (hasOrco ? 2 : 1));
+    if (triangles > 0) { o.tri_idx.reserve(3 * (size_t)triangles); o.tri_nidx.reserve(3 * (size_t)triangles); o.tri_mat.reserve(triangles); }
+    stateStack.push_back(ST_OBJECT);
+    geomChanged = true;
+    curOrco = hasOrco; curObj = &o; curId = id; lastVertId = 0;
+    return true;
+}
+bool Context::endTriMesh()   // scene.cc:296-319
+{
+    if (stateStack.back() != ST_OBJECT) return false;
+    if (curObj->has_uv && (size_t)curObj->n_uv_offsets != 3 * curObj->tri_mat.size()) { fail("Scene: UV-offsets mismatch!"); return false; }
+    stateStack.pop_back();
+    return true;
+}
+int Context::addVertex(double x, double y, double z)   // scene.cc:522-542
+{
+    if (stateStack.back() != ST_OBJECT) return -1;
+    curObj->points.push_back(v3((float)x, (float)y, (float)z));
+    lastVertId = (int)curObj->points.size() - 1;
+    return lastVertId;
+}
+int Context::addVertexOrco(double x, double y, double z, double ox, double oy, double oz)   // scene.cc:544-566
+{
+    if (stateStack.back() != ST_OBJECT) return -1;
+    curObj->points.push_back(v3((float)x, (float)y, (float)z));
+    curObj->points.push_back(v3((float)ox, (float)oy, (float)oz));
+    lastVertId = ((int)curObj->points.size() - 1) / 2;
+    return lastVertId;
+}
+void Context::addNormal(double x, double y, double z)   // scene.cc:568-583
+{
+    if (!curObj) return;
+    MeshObj &o = *curObj;
+    if (o.points.size() > (size_t)lastVertId && o.points.size() > o.normals.size()) {
+        if (o.normals.size() < o.points.size()) o.normals.resize(o.points.size(), v3(0.f));
+        o.normals[lastVertId] = v3((float)x, (float)y, (float)z);
+        o.normals_exported = true;
+    }
+}
+bool Context::addTriangle(int a, int b, int c, uintptr_t mat)   // scene.cc:585-626
+{
+    if (stateStack.back() != ST_OBJECT) return false;
+    if ((mat & 0xff000000u) != HANDLE_MAT_TAG || (mat & 0xffffffu) == 0 || (mat & 0xffffffu) > materials.size()) {
+        fail("addTriangle: invalid material handle");
+        return false;
+    }
+    MeshObj &o = *curObj;
+    if (curOrco) { a *= 2; b *= 2; c *= 2; }
+    o.tri_idx.push_back(a); o.tri_idx.push_back(b); o.tri_idx.push_back(c);
+    if (o.normals_exported) {
+        if (curOrco) { o.tri_nidx.push_back(a >> 1); o.tri_nidx.push_back(b >> 1); o.tri_nidx.push_back(c >> 1); }
+        else { o.tri_nidx.push_back(a); o.tri_nidx.push_back(b); o.tri_nidx.push_back(c); }
+    } else { o.tri_nidx.push_back(-1); o.tri_nidx.push_back(-1); o.tri_nidx.push_back(-1); }
+    o.tri_mat.push_back((uint32_t)((mat & 0xffffffu) - 1));
+    return true;
+}
+bool Context::addTriangleUV(int a, int b, int c, int, int, int, uintptr_t mat)   // scene.cc:628-646
+{
+    if (!addTriangle(a, b, c, mat)) return false;
+    curObj->n_uv_offsets += 3;      // UV sets are accepted and ignored: no supported material reads sp.U/V (textures are rejected)
+    return true;
+}
+int Context::addUV(float, float)
+{
+    if (stateStack.back() != ST_OBJECT) return 0;
+    static int counter = 0;
+    return counter++;
+}
+bool Context::addInstance(unsigned baseId, const float m[16])   // scene.cc:983-1008
+{
+    std::map<unsigned, MeshObj>::iterator it = meshes.find(baseId);
+    if (it == meshes.end()) { fail("Base mesh for instance doesn't exist"); return false; }
+    unsigned id = getNextFreeID();
+    if ((int)id <= 0) return false;
+    MeshObj &o = meshes[id];
+    o = MeshObj();
+    o.base = &meshes[baseId];
+    memcpy(o.m, m, sizeof(o.m));
+    o.has_orco = o.base->has_orco; o.has_uv = o.base->has_uv; o.is_smooth = o.base->is_smooth;
+    o.normals_exported = o.base->normals_exported;
+    geomChanged = true;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------ smoothMesh
+static inline v3 tri_rec_normal(const MeshObj &o, size_t t)   // triangle_t::recNormal (triangle_inline.h:100-107)
+{
+    const v3 &a = o.points[o.tri_idx[3 * t]], &b = o.points[o.tri_idx[3 * t + 1]], &c = o.points[o.tri_idx[3 * t + 2]];
+    return normalize(cross(b - a, c - a));
+}
+static inline float sinFromVectors(v3 a, v3 b)   // vector3d.h:263-268
+{
+    float div = (length(a) * length(b)) * 0.99999f + 0.00001f;
+    float ret = (length(cross(a, b)) / div) * 0.99999f;
+    if (ret > 1.f) ret = 1.f;
+    if (ret < -1.f) ret = -1.f;
+    return asinf(ret);
+}
+bool Context::smoothMesh(unsigned id, double angle_)   // scene.cc:362-520
+{
+    if (stateStack.back() != ST_GEOMETRY) return false;
+    const float angle = (float)angle_;
+    MeshObj *o;
+    if (id) {
+        std::map<unsigned, MeshObj>::iterator it = meshes.find(id);
+        if (it == meshes.end()) return false;
+        o = &it->second;
+    } else { o = curObj; if (!o) return false; }
+    if (o->base) return false;
+    if (o->normals_exported && o->points.size() == o->normals.size()) { o->is_smooth = true; return true; }
+    const size_t points = o->points.size(), ntri = o->tri_mat.size();
+    std::vector<v3> &normals = o->normals;
+    normals.resize(points, v3(0.f));
+    const std::vector<v3> &vertices = o->points;
+    if (angle >= 180) {
+        for (size_t t = 0; t < ntri; ++t) {
+            const int pa = o->tri_idx[3 * t], pb = o->tri_idx[3 * t + 1], pc = o->tri_idx[3 * t + 2];
+            v3 n = tri_rec_normal(*o, t);
+            float alpha = sinFromVectors(vertices[pb] - vertices[pa], vertices[pc] - vertices[pa]);
+            normals[pa] += n * alpha;
+            alpha = sinFromVectors(vertices[pa] - vertices[pb], vertices[pc] - vertices[pb]);
+            normals[pb] += n * alpha;
+            alpha = sinFromVectors(vertices[pa] - vertices[pc], vertices[pb] - vertices[pc]);
+            normals[pc] += n * alpha;
+            o->tri_nidx[3 * t] = pa; o->tri_nidx[3 * t + 1] = pb; o->tri_nidx[3 * t + 2] = pc;
+        }
+        for (size_t i = 0; i < normals.size(); ++i) normals[i] = normalize(normals[i]);
+    } else if (angle > 0.1) {
+        const float thresh = fCos((float)(angle * 0.01745329251994329576922));
+        std::vector<std::vector<size_t> > vface(points);
+        std::vector<std::vector<float> > alphas(points);
+        for (size_t t = 0; t < ntri; ++t) {
+            const int pa = o->tri_idx[3 * t], pb = o->tri_idx[3 * t + 1], pc = o->tri_idx[3 * t + 2];
+            alphas[pa].push_back(sinFromVectors(vertices[pb] - vertices[pa], vertices[pc] - vertices[pa])); vface[pa].push_back(t);
+            alphas[pb].push_back(sinFromVectors(vertices[pa] - vertices[pb], vertices[pc] - vertices[pb])); vface[pb].push_back(t);
+            alphas[pc].push_back(sinFromVectors(vertices[pa] - vertices[pc], vertices[pb] - vertices[pc])); vface[pc].push_back(t);
+        }
+        std::vector<v3> fn(ntri);
+        for (size_t t = 0; t < ntri; ++t) fn[t] = tri_rec_normal(*o, t);
+        std::vector<v3> vnormals; std::vector<int> vn_index;
+        for (int i = 0; i < (int)vface.size(); ++i) {
+            std::vector<size_t> &tris = vface[i];
+            for (size_t j = 0; j < tris.size(); ++j) {
+                const size_t f = tris[j];
+                bool smooth = false;
+                v3 fnorm = fn[f];
+                v3 vnorm = fnorm * alphas[i][j];
+                for (size_t k = 0; k < tris.size(); ++k) {
+                    const size_t f2 = tris[k];
+                    if (f == f2) continue;          // triangle_t::operator== compares selfIndex (triangle.h:68-71)
+                    v3 f2norm = fn[f2];
+                    if (dot(fnorm, f2norm) > thresh) { smooth = true; vnorm += f2norm * alphas[i][k]; }
+                }
+                int n_idx = -1;
+                if (smooth) {
+                    vnorm = normalize(vnorm);
+                    for (size_t l = 0; l < vnormals.size(); ++l)
+                        if (dot(vnorm, vnormals[l]) > 0.999) { n_idx = vn_index[l]; break; }
+                    if (n_idx == -1) {
+                        n_idx = (int)normals.size();
+                        vnormals.push_back(vnorm); vn_index.push_back(n_idx); normals.push_back(vnorm);
+                    }
+                }
+                if (o->tri_idx[3 * f] == i) o->tri_nidx[3 * f] = n_idx;
+                else if (o->tri_idx[3 * f + 1] == i) o->tri_nidx[3 * f + 1] = n_idx;
+                else if (o->tri_idx[3 * f + 2] == i) o->tri_nidx[3 * f + 2] = n_idx;
+                else { fail("Scene: Mesh smoothing error!"); return false; }
+            }
+            vnormals.clear(); vn_index.clear();
+        }
+    }
+    o->is_smooth = true;
+    geomChanged = true;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------ factories
+static bool has_shader_params(const ParaMap &p, const std::list<ParaMap> &ep, std::string &which)
+{
+    static const char *keys[] = {"diffuse_shader", "mirror_color_shader", "bump_shader", "mirror_shader", "transparency_shader",
+                                 "translucency_shader", "glossy_shader", "glossy_reflect_shader", 0};
+    for (int i = 0; keys[i]; ++i) if (p.has(keys[i])) { which = keys[i]; return true; }
+    if (!ep.empty()) { which = "shader node list"; return true; }
+    return false;
+}
+
+uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 + the plugins' factory()
+{
+    std::string type;
+    if (!params.get("type", type)) { fail(std::string("Environment: Type of material not specified for ") + name); return 0; }
+    if (materialNames.count(name)) { warn(std::string("Environment: Sorry, material already in table: ") + name); return 0; }
+    std::string which;
+    if (has_shader_params(params, eparams, which)) { fail("material '" + std::string(name) + "': shader nodes / textures are not supported (" + which + ")"); return 0; }
+    Material m;
+    memset(&m, 0, sizeof(m));
+    const ParaMap &p = params;
+    if (type == "shinydiffusemat") {              // shinydiffuse.cc:470-515 + ctor :5-14 + config :32-80
+        col3 diffuseColor(1.f), mirrorColor(1.f);
+        float diffuseStrength = 1.f, transparency = 0.f, translucency = 0.f, mirrorStrength = 0.f, emit = 0.f;
+        bool fresnelEffect = false; double IOR = 1.33, filt = 1.0;
+        p.getColor("color", diffuseColor); p.getColor("mirror_color", mirrorColor);
+        p.get("transparency", transparency); p.get("translucency", translucency); p.get("diffuse_reflect", diffuseStrength);
+        p.get("specular_reflect", mirrorStrength); p.get("emit", emit); p.get("IOR", IOR); p.get("fresnel_effect", fresnelEffect);
+        p.get("transmit_filter", filt);
+        m.type = MAT_SHINYDIFFUSE;
+        m.diffuseColor = diffuseColor; m.mirrorColor = mirrorColor;
+        m.mirrorStrength = mirrorStrength; m.transparencyStrength = transparency; m.translucencyStrength = translucency;
+        m.diffuseStrength = diffuseStrength; m.transmitFilterStrength = (float)filt;
+        m.emitColor = emit * diffuseColor;
+        m.bsdfFlags = BSDF_NONE;
+        if (emit > 0.f) m.bsdfFlags |= BSDF_EMIT;
+        if (fresnelEffect) { m.iorSquared = (float)(IOR * IOR); m.hasFresnel = 1; }
+        std::string brdf;
+        if (p.get("diffuse_brdf", brdf) && brdf == "oren_nayar") {
+            double sigma = 0.1; p.get("sigma", sigma);
+            double s2 = sigma * sigma;
+            m.orenA = (float)(1.0 - 0.5 * (s2 / (s2 + 0.33)));
+            m.orenB = (float)(0.45 * s2 / (s2 + 0.09));
+            m.useOrenNayar = 1;
+        }
+        // config()
+        float acc = 1.f; int n = 0;
+        if (m.mirrorStrength > 0.00001f) {
+            m.isMirror = 1;
+            if (!m.hasFresnel) acc = 1.f - m.mirrorStrength;
+            m.bsdfFlags |= BSDF_SPECULAR | BSDF_REFLECT; m.cFlags[n] = BSDF_SPECULAR | BSDF_REFLECT; m.cIndex[n] = 0; ++n;
+        }
+        if (m.transparencyStrength * acc > 0.00001f) {
+            m.isTransparent = 1; acc *= 1.f - m.transparencyStrength;
+            m.bsdfFlags |= BSDF_TRANSMIT | BSDF_FILTER; m.cFlags[n] = BSDF_TRANSMIT | BSDF_FILTER; m.cIndex[n] = 1; ++n;
+        }
+        if (m.translucencyStrength * acc > 0.00001f) {
+            m.isTranslucent = 1; acc *= 1.f - m.transparencyStrength;   // sic (shinydiffuse.cc:57)
+            m.bsdfFlags |= BSDF_DIFFUSE | BSDF_TRANSMIT; m.cFlags[n] = BSDF_DIFFUSE | BSDF_TRANSMIT; m.cIndex[n] = 2; ++n;
+        }
+        if (m.diffuseStrength * acc > 0.00001f) {
+            m.isDiffuse = 1;
+            m.bsdfFlags |= BSDF_DIFFUSE | BSDF_REFLECT; m.cFlags[n] = BSDF_DIFFUSE | BSDF_REFLECT; m.cIndex[n] = 3; ++n;
+        }
+        m.nBSDF = n;
+    } else if (type == "glossy" || type == "coated_glossy") {   // glossy.cc:353-395, coatedglossy.cc:420-470
+        const bool coated = type == "coated_glossy";
+        col3 col(1.f), dcol(1.f), mirCol(1.f);
+        float refl = 1.f, diff = 0.f, exponent = 50.f; double ior = 1.4; bool as_diff = true, aniso = false;
+        p.getColor("color", col); p.getColor("diffuse_color", dcol); p.get("diffuse_reflect", diff); p.get("glossy_reflect", refl);
+        p.get("as_diffuse", as_diff); p.get("exponent", exponent); p.get("anisotropic", aniso);
+        if (coated) { p.get("IOR", ior); p.getColor("mirror_color", mirCol); if (ior == 1.f) ior = 1.0000001f; }
+        m.type = coated ? MAT_COATED_GLOSSY : MAT_GLOSSY;
+        m.glossColor = col; m.diffColor = dcol; m.mirrorColor = mirCol; m.reflectivity = refl; m.mDiffuse = diff;
+        m.exponent = exponent; m.asDiffuse = as_diff; m.ior = (float)ior;
+        if (aniso) {
+            if (coated) { double eu = 50.0, ev = 50.0; p.get("exp_u", eu); p.get("exp_v", ev); m.expU = (float)eu; m.expV = (float)ev; }
+            else { float eu = 50.f, ev = 50.f; p.get("exp_u", eu); p.get("exp_v", ev); m.expU = eu; m.expV = ev; }
+            m.anisotropic = 1;
+        }
+        std::string brdf;
+        if (p.get("diffuse_brdf", brdf) && brdf == "Oren-Nayar") {
+            double sigma = 0.1; p.get("sigma", sigma);
+            double s2 = sigma * sigma;
+            m.orenA = (float)(1.0 - 0.5 * (s2 / (s2 + 0.33)));
+            m.orenB = (float)(0.45 * s2 / (s2 + 0.09));
+            m.orenNayar = 1;
+        }
+        const uint32_t glossyFlags = as_diff ? (BSDF_DIFFUSE | BSDF_REFLECT) : (BSDF_GLOSSY | BSDF_REFLECT);
+        if (coated) {
+            m.cFlags[0] = BSDF_SPECULAR | BSDF_REFLECT; m.cFlags[1] = glossyFlags;
+            if (diff > 0) { m.cFlags[2] = BSDF_DIFFUSE | BSDF_REFLECT; m.withDiffuse = 1; m.nBSDF = 3; }
+            else { m.cFlags[2] = BSDF_NONE; m.nBSDF = 2; }
+            m.bsdfFlags = m.cFlags[0] | m.cFlags[1] | m.cFlags[2];
+        } else {
+            m.bsdfFlags = BSDF_NONE;
+            if (diff > 0) { m.bsdfFlags = BSDF_DIFFUSE | BSDF_REFLECT; m.withDiffuse = 1; }
+            m.bsdfFlags |= glossyFlags;
+        }
+    } else if (type == "glass") {                 // glass.cc:255-300
+        double IOR = 1.4, filt = 0.f, disp_power = 0.0; col3 filtCol(1.f), absorp(1.f), srCol(1.f); bool fake = false;
+        p.get("IOR", IOR); p.getColor("filter_color", filtCol); p.get("transmit_filter", filt); p.getColor("mirror_color", srCol);
+        p.get("dispersion_power", disp_power); p.get("fake_shadows", fake);
+        if (disp_power > 0.0) { fail("glass '" + std::string(name) + "': dispersion is not supported"); return 0; }
+        if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
+        m.type = MAT_GLASS;
+        m.ior = (float)IOR;
+        m.filterCol = (float)filt * filtCol + col3((float)(1.f - filt));
+        m.specRefCol = srCol; m.fakeShadow = fake;
+        m.bsdfFlags = BSDF_ALL_SPECULAR;
+        if (fake) m.bsdfFlags |= BSDF_FILTER;
+    } else if (type == "mirror") {                // glass.cc:336-371
+        col3 col(1.f); float refl = 1.f;
+        p.getColor("color", col); p.get("reflect", refl);
+        m.type = MAT_MIRROR; m.specRefCol = col * refl; m.mirrorRefl = refl > 1.f ? 1.f : refl;
+        m.bsdfFlags = BSDF_SPECULAR;
+    } else if (type == "null") {
+        m.type = MAT_NULL; m.bsdfFlags = BSDF_NONE;
+    } else if (type == "light_mat") {             // simple.cc:77-86
+        col3 col(1.f); double power = 1.0; bool ds = false;
+        p.getColor("color", col); p.get("power", power); p.get("double_sided", ds);
+        m.type = MAT_LIGHT; m.lightCol = col * (float)power; m.doubleSided = ds; m.bsdfFlags = BSDF_EMIT;
+    } else {
+        fail("Environment: material type '" + type + "' is not supported by the B200 path (supported: shinydiffusemat, glossy, coated_glossy, glass, mirror, null, light_mat)");
+        return 0;
+    }
+    if (materials.size() >= TRI_MAT_MASK) { fail("too many materials"); return 0; }
+    materials.push_back(m);
+    materialNames[name] = (int)materials.size() - 1;
+    return HANDLE_MAT_TAG | (uintptr_t)materials.size();
+}
+
+uintptr_t Context::createLight(const char *name)   // environment.cc:189-216 + light factories
+{
+    std::string type;
+    if (!params.get("type", type)) { fail(std::string("Environment: Type of light not specified for ") + name); return 0; }
+    if (lightNames.count(name)) { warn(std::string("Environment: Sorry, light already in table: ") + name); return 0; }
+    const ParaMap &p = params;
+    Light l;
+    memset(&l, 0, sizeof(l));
+    unsigned obj = 0;
+    if (type == "pointlight") {                    // pointlight.cc:43-52,117-129
+        v3 from(0.f); col3 color(1.f); float power = 1.0f;
+        p.getPoint("from", from); p.getColor("color", color); p.get("power", power);
+        l.type = LIGHT_POINT; l.position = from; l.color = color * power; l.samples = 1;
+    } else if (type == "sunlight") {               // sunlight.cc:52-63,121-136
+        v3 dir(0.f, 0.f, 1.f); col3 color(1.f); float power = 1.0f, angle = 0.27f; int samples = 4;
+        p.getPoint("direction", dir); p.getColor("color", color); p.get("power", power); p.get("angle", angle); p.get("samples", samples);
+        l.type = LIGHT_SUN; l.samples = samples;
+        l.color = color * power;
+        l.direction = normalize(dir);
+        createCS(dir, l.du, l.dv);                 // sic: from the un-normalised vector (sunlight.cc:57)
+        if (angle > 80.f) angle = 80.f;
+        l.cosAngle = fCos((float)(angle * 0.01745329251994329576922));
+        l.invpdf = (float)(YB_M_2PI * (1.f - l.cosAngle));
+        l.pdf = (float)(1.0 / l.invpdf);
+        l.colPdf = l.color * l.pdf;
+    } else if (type == "arealight") {              // arealight.cc:33-49,181-199
+        v3 corner(0.f), p1(0.f), p2(0.f); col3 color(1.f); float power = 1.0f; int samples = 4, object = 0;
+        p.getPoint("corner", corner); p.getPoint("point1", p1); p.getPoint("point2", p2); p.getColor("color", color);
+        p.get("power", power); p.get("samples", samples); p.get("object", object);
+        l.type = LIGHT_AREA; l.samples = samples;
+        l.corner = corner; l.toX = p1 - corner; l.toY = p2 - corner;
+        l.fnormal = cross(l.toY, l.toX);
+        l.color = (color * power) * (float)YB_M_PI;
+        l.area = normLen(l.fnormal);
+        l.invArea = (float)(1.0 / l.area);
+        l.normal = -l.fnormal;
+        l.du = normalize(l.toX); l.dv = cross(l.normal, l.du);
+        l.c2 = corner + l.toX; l.c3 = corner + (l.toX + l.toY); l.c4 = corner + l.toY;
+        obj = (unsigned)object;
+    } else {
+        fail("Environment: light type '" + type + "' is not supported by the B200 path (supported: pointlight, sunlight, arealight)");
+        return 0;
+    }
+    lights.push_back(l); lightObj.push_back(obj);
+    lightNames[name] = (int)lights.size() - 1;
+    return 0x4c000000u | (uintptr_t)lights.size();
+}
+
+uintptr_t Context::createCamera(const char *name)   // environment.cc:292-330 + perspectiveCamera.cc:28-71,181-232; camera.h:41-61
+{
+    std::string type;
+    if (!params.get("type", type)) { fail(std::string("Environment: Type of camera not specified for ") + name); return 0; }
+    if (cameras.count(name)) { warn(std::string("Environment: Sorry, camera already in table: ") + name); return 0; }
+    if (type != "perspective") { fail("Environment: camera type '" + type + "' is not supported by the B200 path (supported: perspective)"); return 0; }
+    const ParaMap &p = params;
+    v3 from(0, 1, 0), to(0, 0, 0), up(0, 1, 1);
+    int resx = 320, resy = 200;
+    float aspect = 1, dfocal = 1, apt = 0, dofd = 0, nearClip = 0.0f, farClip = -1.0f;
+    std::string bkhtype = "disk1", bkhbias = "uniform";
+    p.getPoint("from", from); p.getPoint("to", to); p.getPoint("up", up); p.get("resx", resx); p.get("resy", resy);
+    p.get("focal", dfocal); p.get("aperture", apt); p.get("dof_distance", dofd); p.get("bokeh_type", bkhtype); p.get("bokeh_bias", bkhbias);
+    p.get("aspect_ratio", aspect); p.get("nearClip", nearClip); p.get("farClip", farClip);
+    if (apt != 0 && bkhtype != "disk1") { fail("camera '" + std::string(name) + "': bokeh_type '" + bkhtype + "' is not supported (disk1 only)"); return 0; }
+    CameraDesc d;
+    memset(&d, 0, sizeof(d));
+    Camera &c = d.cam;
+    c.position = from; c.resx = resx; c.resy = resy;
+    const float aspect_ratio = aspect * (float)resy / (float)resx;
+    v3 camY = up - from, camZ = to - from;
+    v3 camX = cross(camZ, camY);
+    camY = cross(camZ, camX);
+    camX = normalize(camX); camY = normalize(camY); camZ = normalize(camZ);
+    c.camZ = camZ;
+    c.near_p = from + camZ * nearClip;
+    c.far_p = from + camZ * farClip;
+    c.aperture = apt; c.dof_distance = dofd; c.sampleLens = apt != 0;
+    c.dof_rt = apt * camX; c.dof_up = apt * camY;
+    c.vright = camX;
+    c.vup = aspect_ratio * camY;
+    c.vto = (camZ * dfocal) - 0.5f * (c.vup + c.vright);
+    c.vup = v3(c.vup.x / (float)resy, c.vup.y / (float)resy, c.vup.z / (float)resy);
+    c.vright = v3(c.vright.x / (float)resx, c.vright.y / (float)resx, c.vright.z / (float)resx);
+    cameras[name] = d;
+    return 0x43000000u | (uintptr_t)cameras.size();
+}
+
+uintptr_t Context::createBackground(const char *name)   // environment.cc:332-365 + textureback.cc:205-235
+{
+    std::string type;
+    if (!params.get("type", type)) { fail(std::string("Environment: Type of background not specified for ") + name); return 0; }
+    if (backgrounds.count(name)) { warn(std::string("Environment: Sorry, background already in table: ") + name); return 0; }
+    if (type != "constant") { fail("Environment: background type '" + type + "' is not supported by the B200 path (supported: constant)"); return 0; }
+    col3 col(0.f); float power = 1.0f; bool ibl = false;
+    params.getColor("color", col); params.get("power", power); params.get("ibl", ibl);
+    if (ibl) { fail("background '" + std::string(name) + "': ibl=true (background light) is not supported"); return 0; }
+    BackgroundDesc b; b.color = col * power;
+    backgrounds[name] = b;
+    return 0x42000000u | (uintptr_t)backgrounds.size();
+}
+
+uintptr_t Context::createIntegrator(const char *name)   // environment.cc:367-400 + directlight.cc:184-257, pathtracer.cc:335-409
+{
+    std::string type;
+    if (!params.get("type", type)) { fail(std::string("Environment: Type of integrator not specified for ") + name); return 0; }
+    if (integrators.count(name)) { warn(std::string("Environment: Sorry, integrator already in table: ") + name); return 0; }
+    const ParaMap &p = params;
+    IntegratorDesc d;
+    memset(&d, 0, sizeof(d));
+    Integrator &I = d.p;
+    if (type == "none") { d.surface = false; d.volume_none = true; }          // EmptyVolumeIntegrator.cc:21-33
+    else if (type == "directlighting" || type == "pathtracing") {
+        d.surface = true;
+        bool transpShad = false, bg_transp = true, bg_transp_refract = true, useSSS = false;
+        int shadowDepth = 5, raydepth = 5;
+        p.get("raydepth", raydepth); p.get("transpShad", transpShad); p.get("shadowDepth", shadowDepth);
+        p.get("bg_transp", bg_transp); p.get("bg_transp_refract", bg_transp_refract); p.get("useSSS", useSSS);
+        if (useSSS) { fail("integrator '" + std::string(name) + "': useSSS (subsurface photon maps) is not supported"); return 0; }
+        I.trShad = transpShad; I.sDepth = shadowDepth; I.rDepth = raydepth;
+        I.transpBackground = bg_transp; I.transpRefractedBackground = bg_transp_refract;
+        if (type == "directlighting") {
+            bool caustics = false, do_AO = false; int AO_samples = 32; double AO_dist = 1.0; col3 AO_col(1.f);
+            p.get("caustics", caustics); p.get("do_AO", do_AO); p.get("AO_samples", AO_samples); p.get("AO_distance", AO_dist); p.getColor("AO_color", AO_col);
+            if (caustics) { fail("integrator '" + std::string(name) + "': caustic photon maps are not supported"); return 0; }
+            I.type = INTEG_DIRECT; I.useAO = do_AO; I.aoSamples = AO_samples; I.aoDist = (float)AO_dist; I.aoCol = AO_col;
+        } else {
+            bool noRec = false; int path_samples = 32, bounces = 3; std::string cMethod;
+            p.get("path_samples", path_samples); p.get("bounces", bounces); p.get("no_recursive", noRec);
+            if (p.get("caustic_type", cMethod)) {
+                if (cMethod == "photon" || cMethod == "both") { fail("integrator '" + std::string(name) + "': caustic_type '" + cMethod + "' (photon maps) is not supported"); return 0; }
+                I.traceCaustics = (cMethod == "none") ? 0 : 1;     // pathtracer.cc:370-372,113 (default PATH)
+            } else I.traceCaustics = 1;
+            I.type = INTEG_PATH; I.nPaths = path_samples; I.maxBounces = bounces; I.noRecursive = noRec;
+            // opt-in extension, not in the reference (SURVEY.md discrepancy 1): unbiased Russian roulette on path throughput
+            bool rr = false; float rrMin = 0.05f;
+            p.get("russian_roulette", rr); p.get("rr_min_prob", rrMin);
+            I.russianRoulette = rr; I.rrMinProb = rrMin;
+        }
+    } else {
+        fail("Environment: integrator type '" + type + "' is not supported by the B200 path (supported: directlighting, pathtracing, none)");
+        return 0;
+    }
+    integrators[name] = d;
+    return 0x49000000u | (uintptr_t)integrators.size();
+}
+
+// ------------------------------------------------------------------------------------------------ film (imagefilm.cc:59-165)
+static float filt_box(float, float) { return 1.f; }
+static float filt_mitchell(float dx, float dy)
+{
+    float x = 2.f * fSqrt(dx * dx + dy * dy);
+    if (x >= 2.f) return 0.f;
+    if (x >= 1.f) return (float)(x * (x * (x * -0.38888889f + 2.0f) - 3.33333333f) + 1.77777778f);
+    return (float)(x * x * (1.16666666f * x - 2.0f) + 0.88888889f);
+}
+static float filt_gauss(float dx, float dy)
+{
+    float r2 = dx * dx + dy * dy;
+    return std::max(0.f, float(fExp(-6 * r2) - 0.00247875));
+}
+static float filt_lanczos(float dx, float dy)
+{
+    float x = fSqrt(dx * dx + dy * dy);
+    if (x == 0.f) return 1.f;
+    if (-2 < x && x < 2) {
+        float a = (float)YB_M_PI * x, b = (float)YB_M_PI_2 * x;
+        return ((fSin(a) * fSin(b)) / (a * b));
+    }
+    return 0.f;
+}
+
+bool Context::setupRender(int width, int height)   // environment.cc:596-694 + createImageFilm :481-531
+{
+    const ParaMap &p = params;
+    std::string name;
+    if (!p.get("camera_name", name)) return fail("Environment: Specify a Camera!!");
+    std::map<std::string, CameraDesc>::iterator ci = cameras.find(name);
+    if (ci == cameras.end()) return fail("Environment: Specify an _existing_ Camera!!");
+    if (!p.get("integrator_name", name)) return fail("Environment: Specify an Integrator!!");
+    std::map<std::string, IntegratorDesc>::iterator ii = integrators.find(name);
+    if (ii == integrators.end()) return fail("Environment: Specify an _existing_ Integrator!!");
+    if (!ii->second.surface) return fail("Environment: Integrator is no surface integrator!");
+    if (!p.get("volintegrator_name", name)) return fail("Environment: Specify a Volume Integrator!");
+    std::map<std::string, IntegratorDesc>::iterator vi = integrators.find(name);
+    if (vi == integrators.end() || !vi->second.volume_none)
+        return fail("volume integrator '" + name + "' must be of type 'none' (participating media are not supported)");
+    sc.integ = ii->second.p;
+    sc.integ.hasBackground = 0; sc.integ.bgColor = col3(0.f);
+    if (p.get("background_name", name)) {
+        std::map<std::string, BackgroundDesc>::iterator bi = backgrounds.find(name);
+        if (bi == backgrounds.end()) { if (verbosity >= 1) fprintf(stderr, "ERROR: yb200: please specify an _existing_ Background!!\n"); }
+        else { sc.integ.hasBackground = 1; sc.integ.bgColor = bi->second.color; }
+    }
+    sc.cam = ci->second.cam;
+    int AA_passes = 1, AA_samples = 1, AA_inc = 1; double AA_threshold = 0.05; bool z_chan = false;
+    p.get("AA_passes", AA_passes); p.get("AA_minsamples", AA_samples); AA_inc = AA_samples; p.get("AA_inc_samples", AA_inc);
+    p.get("AA_threshold", AA_threshold); p.get("z_channel", z_chan);
+    if (z_chan) return fail("z_channel (depth map output) is not supported yet");
+    if (AA_passes > 1) return fail("AA_passes > 1 (adaptive multi-pass anti-aliasing) is not supported yet");
+    // createImageFilm
+    int w = 320, h = 240, xstart = 0, ystart = 0, tileSize = 32; float filt_sz = 1.5f, gamma = 1.f; bool clamp = false, premult = false;
+    std::string ftype; bool haveF = p.get("filter_type", ftype);
+    p.get("gamma", gamma); p.get("clamp_rgb", clamp); p.get("AA_pixelwidth", filt_sz); p.get("width", w); p.get("height", h);
+    p.get("xstart", xstart); p.get("ystart", ystart); p.get("tile_size", tileSize); p.get("premult", premult);
+    if (width > 0 && height > 0 && (w != width || h != height)) return fail("render: output buffer size differs from the 'width'/'height' render parameters");
+    Film &f = sc.film;
+    memset(&f, 0, sizeof(f));
+    f.w = w; f.h = h; f.cx0 = xstart; f.cy0 = ystart; f.cx1 = xstart + w; f.cy1 = ystart + h;
+    f.filterw = filt_sz * 0.5f;
+    float (*ffunc)(float, float) = filt_box;
+    if (haveF) {
+        if (ftype == "mitchell") { ffunc = filt_mitchell; f.filterw *= 2.6f; }
+        else if (ftype == "lanczos") ffunc = filt_lanczos;
+        else if (ftype == "gauss") { ffunc = filt_gauss; f.filterw *= 2.f; }
+    }
+    f.filterw = std::min(std::max(0.501f, f.filterw), 0.5f * YB_MAX_FILTER_SIZE);
+    const float scale = 1.f / (float)YB_FILTER_TABLE_SIZE;
+    for (int y = 0; y < YB_FILTER_TABLE_SIZE; ++y)
+        for (int x = 0; x < YB_FILTER_TABLE_SIZE; ++x) f.filterTable[y * YB_FILTER_TABLE_SIZE + x] = ffunc((x + .5f) * scale, (y + .5f) * scale);
+    f.tableScale = (float)(0.9999 * YB_FILTER_TABLE_SIZE / f.filterw);
+    f.clamp = clamp; f.premult = premult; f.gamma = gamma > 0 ? 1.f / gamma : 1.f;   // imagefilm.cc:631-635
+    f.correctGamma = (gamma > 0 && fabsf(1.f - gamma) > 0.001f) ? 1 : 0;
+    f.tileSize = tileSize > 0 ? tileSize : 32;
+    f.AA_passes = AA_passes; f.n_samples = AA_samples > 0 ? AA_samples : 1; f.pass_offs = 0;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------ flatten + build
+bool Context::ensureDevice()
+{
+#ifndef YB_HOSTEMU
+    if (device < 0) {
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess || n == 0) return fail(std::string("no CUDA device available (") + cudaGetErrorString(e) + "): the B200 path has no CPU fallback");
+        int cur = 0; cudaGetDevice(&cur); device = cur;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) return fail("cudaSetDevice failed");
+    if (!stream) { if (cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) != cudaSuccess) return fail("cudaStreamCreate failed"); streamOwned = true; }
+#endif
+    return true;
+}
+
+// scene_t::update (scene.cc:748-850): gather the triangles of every visible, non-base TRIM mesh in ascending
+// object-id order (this defines the global primitive index used by the parity hook), bake instance transforms
+// (meshtypes.h:133-143), upload as SoA, build the BVH on the device.
+bool Context::flattenAndBuild()
+{
+    if (!ensureDevice()) return false;
+    auto t0 = std::chrono::steady_clock::now();
+    size_t ntri = 0; bool anySmooth = false;
+    for (std::map<unsigned, MeshObj>::iterator i = meshes.begin(); i != meshes.end(); ++i) {
+        MeshObj &o = i->second;
+        if (!o.visible || o.is_base) continue;
+        const MeshObj &g = o.base ? *o.base : o;
+        ntri += g.tri_mat.size();
+        if (o.is_smooth || (o.base && o.normals_exported)) anySmooth = true;
+    }
+    if (ntri >= 0x7fffffffu / 3) return fail("scene has too many triangles for 32-bit indexing");
+    std::vector<f4> hv(3 * ntri);
+    std::vector<v3> hn(anySmooth ? 3 * ntri : 0);
+    size_t k = 0;
+    for (std::map<unsigned, MeshObj>::iterator i = meshes.begin(); i != meshes.end(); ++i) {
+        MeshObj &o = i->second;
+        if (!o.visible || o.is_base) continue;
+        const MeshObj &g = o.base ? *o.base : o;
+        const bool inst = o.base != 0;
+        const float *m = o.m;
+        const bool smooth = inst ? (o.is_smooth || o.normals_exported) : o.is_smooth;   // triangle.cc:18 vs :188
+        for (size_t t = 0; t < g.tri_mat.size(); ++t, ++k) {
+            uint32_t info = g.tri_mat[t] & TRI_MAT_MASK;
+            if (smooth) info |= TRI_SMOOTH;
+            for (int c = 0; c < 3; ++c) {
+                const int pi = g.tri_idx[3 * t + c];
+                if (pi < 0 || (size_t)pi >= g.points.size()) return fail("triangle references a vertex that does not exist");
+                v3 pt = g.points[pi];
+                if (inst) pt = v3(m[0] * pt.x + m[1] * pt.y + m[2] * pt.z + m[3], m[4] * pt.x + m[5] * pt.y + m[6] * pt.z + m[7],
+                                  m[8] * pt.x + m[9] * pt.y + m[10] * pt.z + m[11]);      // matrix4.h:92-97
+                f4 &d = hv[3 * k + c];
+                d.x = pt.x; d.y = pt.y; d.z = pt.z; d.w = 0.f;
+                if (anySmooth) {
+                    const int ni = g.tri_nidx[3 * t + c];
+                    const bool has = inst ? (ni > 0) : (ni >= 0);                        // triangle.cc:20-22 vs :190-192
+                    v3 nn(0.f);
+                    if (smooth && has) {
+                        if ((size_t)ni >= g.normals.size()) return fail("triangle references a normal that does not exist");
+                        nn = g.normals[ni];
+                        if (inst) nn = v3(m[0] * nn.x + m[1] * nn.y + m[2] * nn.z, m[4] * nn.x + m[5] * nn.y + m[6] * nn.z, m[8] * nn.x + m[9] * nn.y + m[10] * nn.z);
+                        info |= (TRI_HAS_NA << c);
+                    }
+                    hn[3 * k + c] = nn;
+                }
+            }
+            hv[3 * k].w = i2f((int32_t)k);
+            hv[3 * k + 1].w = i2f((int32_t)info);
+        }
+    }
+    nTris = (uint32_t)ntri; haveNormals = anySmooth;
+    // upload + build
+    DevBuf<f4> in_v; DevBuf<v3> in_n;
+    try {
+        in_v.reserve(3 * ntri + 1);
+        rt_h2d(in_v.p, hv.data(), hv.size() * sizeof(f4), stream);
+        if (anySmooth) { in_n.reserve(3 * ntri + 1); rt_h2d(in_n.p, hn.data(), hn.size() * sizeof(v3), stream); }
+        rt_sync(stream);
+        bvh_build(in_v.p, anySmooth ? in_n.p : 0, nTris, d_nodes, d_tri_v, d_tri_n, nNodes, bvhDepth, boundLo, boundHi, stream);
+        d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
+        rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
+        rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
+        rt_sync(stream);
+    } catch (const RtError &e) { return fail(std::string("scene update failed: ") + e.what()); }
+    sc.nodes = d_nodes.p; sc.tri_v = d_tri_v.p; sc.tri_n = anySmooth ? d_tri_n.p : 0;
+    sc.materials = d_materials.p; sc.lights = d_lights.p;
+    sc.nLights = (int32_t)lights.size(); sc.nMaterials = (int32_t)materials.size();
+    sc.nTris = nTris; sc.nNodes = nNodes; sc.boundLo = boundLo; sc.boundHi = boundHi;
+    geomChanged = false;
+    stats.n_triangles = nTris; stats.n_bvh_nodes = nNodes;
+    stats.bvh_bytes = (uint64_t)nNodes * sizeof(BvhNode);
+    stats.tri_bytes = (uint64_t)nTris * (3 * sizeof(f4) + (anySmooth ? 3 * sizeof(v3) : 0));
+    stats.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (nTris == 0) warn("Scene: Scene is empty...");
+    return true;
+}
+
+bool Context::updateScene()
+{
+    if (!sceneStarted) return fail("no scene: call startScene first");
+    if (stateStack.back() != ST_READY) return fail("scene update inside startGeometry/startTriMesh");
+    if (!setupRender(0, 0)) return false;
+    if (geomChanged || !sceneReady) { if (!flattenAndBuild()) return false; }
+    else {
+        try {   // materials / lights may have changed
+            d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
+            rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
+            rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
+            sc.materials = d_materials.p; sc.lights = d_lights.p;
+            sc.nLights = (int32_t)lights.size(); sc.nMaterials = (int32_t)materials.size();
+        } catch (const RtError &e) { return fail(e.what()); }
+    }
+    sceneReady = true;
+    return true;
+}
+
+}  // namespace yb

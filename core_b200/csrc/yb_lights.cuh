@@ -1,0 +1,140 @@
+// yb_lights.cuh — device restatement of light_t for pointLight_t / sunLight_t / areaLight_t, the
+// perspective camera and the triangle surface-point computation.
+//   src/lights/pointlight.cc:54-91, src/lights/sunlight.cc:74-95, src/lights/arealight.cc:68-154
+//   src/cameras/perspectiveCamera.cc:127-149, include/utilities/geometry.h:33-36
+//   src/yafraycore/triangle.cc:12-108 (getSurface), include/yafraycore/triangle_inline.h:27-64
+#pragma once
+#include "yb_bsdf.cuh"
+
+namespace yb {
+
+struct LSample { float s1, s2; col3 col; float pdf; };   // lSample_t fields used on this path (light.h)
+
+YB_HD bool light_dirac(const Light &l) { return l.type == LIGHT_POINT; }
+YB_HD bool light_canIntersect(const Light &l) { return l.type != LIGHT_POINT; }
+
+// pointLight_t::illuminate (pointlight.cc:54-70)
+YB_HD bool light_illuminate(const Light &l, v3 P, col3 &col, Ray &wi)
+{
+    if (l.type != LIGHT_POINT) return false;
+    v3 ldir = l.position - P;
+    float dist_sqr = ldir.x * ldir.x + ldir.y * ldir.y + ldir.z * ldir.z;
+    float dist = fSqrt(dist_sqr);
+    if (dist == 0.0f) return false;
+    float idist_sqr = 1.f / dist_sqr;
+    ldir *= 1.f / dist;
+    wi.tmax = dist;
+    wi.dir = ldir;
+    col = l.color * idist_sqr;
+    return true;
+}
+// sunLight_t::illumSample (sunlight.cc:74-85), areaLight_t::illumSample (arealight.cc:68-96)
+YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s, Ray &wi)
+{
+    if (l.type == LIGHT_SUN) {
+        wi.dir = sampleCone(l.direction, l.du, l.dv, (float)l.cosAngle, s.s1, s.s2);
+        wi.tmax = -1.f;
+        s.col = l.colPdf;
+        s.pdf = l.pdf;
+        return true;
+    }
+    if (l.type == LIGHT_AREA) {
+        v3 p = l.corner + s.s1 * l.toX + s.s2 * l.toY;
+        v3 ldir = p - P;
+        float dist_sqr = dot(ldir, ldir);
+        float dist = fSqrt(dist_sqr);
+        if (dist <= 0.0f) return false;
+        ldir *= 1.f / dist;
+        float cos_angle = dot(ldir, l.fnormal);
+        if (cos_angle <= 0) return false;
+        wi.tmax = dist;
+        wi.dir = ldir;
+        s.col = l.color;
+        s.pdf = (float)(dist_sqr * YB_M_PI / (l.area * cos_angle));
+        return true;
+    }
+    return false;
+}
+// arealight.cc:117-134
+YB_HD bool light_triIntersect(v3 a, v3 b, v3 c, v3 from, v3 dir, float &t)
+{
+    v3 edge1 = b - a, edge2 = c - a;
+    v3 pvec = cross(dir, edge2);
+    float det = dot(edge1, pvec);
+    if (det == 0.0f) return false;
+    float inv_det = (float)(1.0 / det);
+    v3 tvec = from - a;
+    float u = dot(tvec, pvec) * inv_det;
+    if (u < 0.0f || u > 1.0f) return false;
+    v3 qvec = cross(tvec, edge1);
+    float v = dot(dir, qvec) * inv_det;
+    if ((v < 0.0f) || ((u + v) > 1.0f)) return false;
+    t = dot(edge2, qvec) * inv_det;
+    return true;
+}
+// sunLight_t::intersect (sunlight.cc:87-95), areaLight_t::intersect (arealight.cc:136-154)
+YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, float &t, col3 &col, float &ipdf)
+{
+    if (l.type == LIGHT_SUN) {
+        float cosine = dot(dir, l.direction);
+        if ((double)cosine < l.cosAngle) return false;
+        col = l.colPdf;
+        t = -1;
+        ipdf = l.invpdf;
+        return true;
+    }
+    if (l.type == LIGHT_AREA) {
+        float cos_angle = dot(dir, l.fnormal);
+        if (cos_angle <= 0) return false;
+        if (!light_triIntersect(l.corner, l.c2, l.c3, from, dir, t)) {
+            if (!light_triIntersect(l.corner, l.c3, l.c4, from, dir, t)) return false;
+        }
+        if (!(t > 1.0e-10f)) return false;
+        col = l.color;
+        ipdf = (float)(1.f / (t * t) * l.area * cos_angle * YB_M_1_PI);
+        return true;
+    }
+    return false;
+}
+
+// perspectiveCam_t::shootRay (perspectiveCamera.cc:127-149); bokeh disk1 only (others rejected at creation)
+YB_HD Ray cam_shootRay(const Camera &c, float px, float py, float lu, float lv, float &wt)
+{
+    Ray ray;
+    wt = 1;
+    ray.from = c.position;
+    ray.dir = normalize(c.vright * px + c.vup * py + c.vto);
+    float denom = dot(ray.dir, c.camZ);
+    ray.tmin = dot(c.camZ, c.near_p - ray.from) / denom;      // geometry.h:33-36
+    ray.tmax = dot(c.camZ, c.far_p - ray.from) / denom;
+    if (c.aperture != 0) {
+        float u, v;
+        ShirleyDisk(lu, lv, u, v);
+        v3 LI = c.dof_rt * u + c.dof_up * v;
+        ray.from = ray.from + LI;
+        ray.dir = normalize((ray.dir * c.dof_distance) - LI);
+    }
+    return ray;
+}
+
+// triangle_t::getSurface (triangle.cc:12-108) without orco/uv (rejected at flatten time):
+// sp.N from the vertex normals, createCS(N, NU, NV); Ng = normalize((b-a)^(c-a)) as recNormal (triangle_inline.h:100-107)
+YB_HD void tri_getSurface(const SceneDev &sc, int tri, v3 hitP, float b1, float b2, Surf &sp)
+{
+    const f4 A = sc.tri_v[3 * tri], B = sc.tri_v[3 * tri + 1], C = sc.tri_v[3 * tri + 2];
+    v3 a(A.x, A.y, A.z), b(B.x, B.y, B.z), c(C.x, C.y, C.z);
+    sp.Ng = normalize(cross(b - a, c - a));
+    uint32_t info = (uint32_t)f2i(B.w);
+    float u = 1 - b1 - b2, v = b1, w = b2;        // data.b0, b1, b2
+    if (info & TRI_SMOOTH) {
+        v3 va = (info & TRI_HAS_NA) ? sc.tri_n[3 * tri] : sp.Ng;
+        v3 vb = (info & TRI_HAS_NB) ? sc.tri_n[3 * tri + 1] : sp.Ng;
+        v3 vc = (info & TRI_HAS_NC) ? sc.tri_n[3 * tri + 2] : sp.Ng;
+        sp.N = normalize(u * va + v * vb + w * vc);
+    } else sp.N = sp.Ng;
+    sp.P = hitP;
+    sp.mat = &sc.materials[info & TRI_MAT_MASK];
+    createCS(sp.N, sp.NU, sp.NV);
+}
+
+}  // namespace yb

@@ -1,0 +1,683 @@
+// yb_render.cu — the wavefront form of tiledIntegrator_t::renderTile + directLighting_t / pathIntegrator_t
+// ::integrate (src/yafraycore/integrator.cc:229-339, src/integrators/directlight.cc:112-182,
+// src/integrators/pathtracer.cc:134-333, src/yafraycore/mcintegrator.cc:45-195,421-683) and of
+// imageFilm_t::addSample / flush (src/yafraycore/imagefilm.cc:453-511,383-443).
+//
+// The reference recursion integrate() -> recursiveRaytrace() -> integrate() is linear in the returned colour,
+// so it is unrolled into a pool of independent tasks: every task carries the product of the weights above it
+// (`thr`) and adds its own terms straight into the camera sample's accumulator.  One wave = closest-hit trace of
+// a chunk of tasks, shading (which appends shadow rays and child tasks), any-hit trace of the shadow rays.
+// All sample streams are replayed exactly as SURVEY.md §3.6 maps them.
+#include "yb_scene.h"
+#include "yb_trace.cuh"
+#include <chrono>
+#include <vector>
+#include <algorithm>
+
+namespace yb {
+
+#if defined(__CUDACC__) && !defined(YB_HOSTEMU)
+#define YB_TABLE __device__ __constant__
+#else
+#define YB_TABLE static
+#endif
+#include "yb_faure.inc"
+
+#define YB_MIN_RAYDIST 0.00005f      // CMakeLists.txt:44
+#define YB_SHADOW_BIAS 0.0005f       // CMakeLists.txt:48
+#define YB_LOFFS_DELTA 4567u         // mcintegrator.cc:43
+
+// scr_halton.h:47-69 (dim < 50 on this path: SURVEY.md §5)
+YB_HD double scrHalton(int dim, uint32_t n)
+{
+    double value = 0.0;
+    if (dim < 50) {
+        const unsigned char *sigma = yb_faure_flat + yb_faure_offs[dim];
+        uint32_t base = (uint32_t)yb_prims[dim];
+        double f, factor, dn = (double)n;
+        f = factor = yb_invPrims[dim];
+        while (n > 0) {
+            value += (double)sigma[n % base] * factor;
+            dn *= f;
+            n = (uint32_t)dn;
+            factor *= f;
+        }
+    }
+    return value < 1.0e-36 ? 1.0e-36 : (value > 1.0 ? 1.0 : value);
+}
+
+struct RenderArgs {
+    SceneDev sc;
+    Task *tasks;            // chunk being processed
+    Hit *hits;
+    Task *out_tasks;        // children appended here
+    ShadowTask *shadow;     // shadow rays appended here
+    uint32_t *counters;     // [0] out_tasks count, [1] shadow count
+    f4 *acc;                // per camera sample: rgb + alpha
+    const uint32_t *pix;    // owned pixels: x | y << 16
+    float *film;            // (x + w*y)*5: r,g,b,a,weight
+    uint32_t sampleBase;    // first global camera-sample index of this batch
+    uint32_t outCap, shadowCap;
+};
+
+// per-camera-sample identity (integrator.cc:251-273)
+struct SampleId { int x, y, s; uint32_t samplingOffs; int pixelSample; };
+YB_HD SampleId sample_id(const RenderArgs &a, uint32_t sid)
+{
+    SampleId r;
+    const uint32_t gid = a.sampleBase + sid;
+    const uint32_t ns = (uint32_t)a.sc.film.n_samples;
+    const uint32_t p = a.pix[gid / ns];
+    r.s = (int)(gid % ns);
+    r.x = (int)(p & 0xffffu); r.y = (int)(p >> 16);
+    r.samplingOffs = fnv_32a_buf((uint32_t)r.y * fnv_32a_buf((uint32_t)r.x));
+    r.pixelSample = a.sc.film.pass_offs + r.s;
+    return r;
+}
+// sub-pixel position of a sample (integrator.cc:238,277-286)
+YB_HD void sample_dxdy(const Film &f, const SampleId &id, float &dx, float &dy)
+{
+    dx = 0.5f; dy = 0.5f;
+    if (f.AA_passes > 1) { dx = RI_vdC((uint32_t)id.pixelSample, id.samplingOffs); dy = RI_S((uint32_t)id.pixelSample, id.samplingOffs); }
+    else if (f.n_samples > 1) {
+        const float d1 = (float)(1.0 / (float)f.n_samples);
+        dx = (float)((0.5 + (double)(float)id.s) * (double)d1);
+        dy = RI_LP((uint32_t)id.s + id.samplingOffs);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ raygen
+YB_KERNEL(k_raygen, RenderArgs)
+{
+    const SampleId id = sample_id(a, tid);
+    float dx, dy;
+    sample_dxdy(a.sc.film, id, dx, dy);
+    float lens_u = 0.5f, lens_v = 0.5f;
+    if (a.sc.cam.sampleLens) {          // integrator.cc:248-249,266-267,287-291
+        Halton halU(3), halV(5);
+        halU.setStart((uint32_t)a.sc.film.pass_offs + id.samplingOffs);
+        halV.setStart((uint32_t)a.sc.film.pass_offs + id.samplingOffs);
+        for (int k = 0; k <= id.s; ++k) { lens_u = halU.getNext(); lens_v = halV.getNext(); }
+    }
+    float wt;
+    Task t;
+    t.ray = cam_shootRay(a.sc.cam, (float)id.x + dx, (float)id.y + dy, lens_u, lens_v, wt);
+    t.thr = col3(1.f); t.aw = 1.f; t.sid = tid;
+    t.bits = task_bits(TASK_INTEGRATE, true, 0, 0);
+    t.rayDivision = 1; t.rayOffset = 0; t.dc1 = 0.f; t.dc2 = 0.f; t.pathOffs = 0; t.pad = 0;
+    a.tasks[tid] = t;
+    f4 z; z.x = z.y = z.z = z.w = 0.f;
+    a.acc[tid] = z;
+}
+
+// ------------------------------------------------------------------------------------------------ trace kernels
+YB_KERNEL(k_trace_closest, RenderArgs)
+{
+    Hit h;
+    scene_intersect(a.sc, a.tasks[tid].ray, h);
+    a.hits[tid] = h;
+}
+YB_HD void acc_add(const RenderArgs &a, uint32_t sid, col3 c)
+{
+    YB_ATOMIC_ADD_F32(&a.acc[sid].x, c.x); YB_ATOMIC_ADD_F32(&a.acc[sid].y, c.y); YB_ATOMIC_ADD_F32(&a.acc[sid].z, c.z);
+}
+YB_HD void acc_add_alpha(const RenderArgs &a, uint32_t sid, float v) { YB_ATOMIC_ADD_F32(&a.acc[sid].w, v); }
+YB_KERNEL(k_trace_shadow, RenderArgs)
+{
+    const ShadowTask st = a.shadow[tid];
+    if (a.sc.integ.trShad) {
+        col3 filt;
+        if (!scene_isShadowedT(a.sc, st.ray, a.sc.integ.sDepth, filt)) acc_add(a, st.sid, mul(st.c, filt));
+    } else if (!scene_isShadowed(a.sc, st.ray)) acc_add(a, st.sid, st.c);
+}
+
+// ------------------------------------------------------------------------------------------------ queues
+YB_HD void push_shadow(const RenderArgs &a, const Ray &r, col3 c, uint32_t sid)
+{
+    if (isBlack(c)) return;                                   // contributes nothing either way
+    const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + 1, 1u);
+    if (i >= a.shadowCap) return;                             // cannot happen: the host sizes chunks for the worst case
+    ShadowTask st; st.ray = r; st.c = c; st.sid = sid;
+    a.shadow[i] = st;
+}
+YB_HD void push_task(const RenderArgs &a, const Task &t)
+{
+    const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + 0, 1u);
+    if (i >= a.outCap) return;
+    a.out_tasks[i] = t;
+}
+
+// ------------------------------------------------------------------------------------------------ direct lighting
+// mcIntegrator_t::doLightEstimation (mcintegrator.cc:73-195).  Every term that the reference adds after an
+// isShadowed() test becomes a shadow task carrying weight*term.
+YB_HD void doLightEstimation(const RenderArgs &a, const Light &light, uint32_t loffs, const Surf &sp, const MatDat &md, v3 wo,
+                             const SampleId &id, uint32_t rayDivision, col3 weight, uint32_t sid)
+{
+    const Material &mat = *sp.mat;
+    const uint32_t l_offs = loffs * YB_LOFFS_DELTA;
+    Ray lightRay;
+    lightRay.from = sp.P; lightRay.tmin = 0.f; lightRay.tmax = -1.f; lightRay.dir = v3(0.f);
+    const uint32_t allBSDFIntersect = BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_DISPERSIVE | BSDF_REFLECT | BSDF_TRANSMIT;
+    if (light_dirac(light)) {
+        col3 lcol(0.f);
+        if (light_illuminate(light, sp.P, lcol, lightRay)) {
+            lightRay.tmin = YB_SHADOW_BIAS;
+            col3 surfCol = mat_eval(mat, md, sp, wo, lightRay.dir, BSDF_ALL);
+            col3 c = mul(surfCol, lcol) * fabsf(dot(sp.N, lightRay.dir));
+            push_shadow(a, lightRay, mul(weight, c), sid);
+        }
+        return;
+    }
+    int n = light.samples;
+    if (rayDivision > 1) n = (n / (int)rayDivision) > 1 ? (n / (int)rayDivision) : 1;
+    const float invNS = 1.f / (float)n;
+    const uint32_t offs = (uint32_t)n * (uint32_t)id.pixelSample + id.samplingOffs + l_offs;
+    const bool canIntersect = light_canIntersect(light);
+    Halton hal2(2), hal3(3);
+    hal2.setStart(offs - 1); hal3.setStart(offs - 1);
+    for (int i = 0; i < n; ++i) {
+        LSample ls;
+        ls.s1 = hal2.getNext(); ls.s2 = hal3.getNext();
+        ls.col = col3(0.f); ls.pdf = 0.f;
+        if (light_illumSample(light, sp.P, ls, lightRay)) {
+            lightRay.tmin = YB_SHADOW_BIAS;
+            if (ls.pdf > 1e-6f) {
+                col3 surfCol = mat_eval(mat, md, sp, wo, lightRay.dir, BSDF_ALL);
+                col3 c;
+                if (canIntersect) {
+                    float mPdf = mat_pdf(mat, md, sp, wo, lightRay.dir, allBSDFIntersect);
+                    if (mPdf > 1e-6f) {
+                        float l2 = ls.pdf * ls.pdf, m2 = mPdf * mPdf;
+                        float w = l2 / (l2 + m2);
+                        c = mul(surfCol, ls.col) * (fabsf(dot(sp.N, lightRay.dir)) * w / ls.pdf);
+                    } else c = mul(surfCol, ls.col) * (fabsf(dot(sp.N, lightRay.dir)) / ls.pdf);
+                } else c = mul(surfCol, ls.col) * (fabsf(dot(sp.N, lightRay.dir)) / ls.pdf);
+                push_shadow(a, lightRay, mul(weight, c) * invNS, sid);
+            }
+        }
+    }
+    if (canIntersect) {   // sample from BSDF to complete MIS
+        hal2.setStart(offs - 1); hal3.setStart(offs - 1);
+        for (int i = 0; i < n; ++i) {
+            Ray bRay;
+            bRay.tmin = YB_MIN_RAYDIST; bRay.from = sp.P; bRay.tmax = -1.f;
+            float s1 = hal2.getNext(), s2 = hal3.getNext(), W = 0.f;
+            BSample s(s1, s2, allBSDFIntersect);
+            col3 surfCol = mat_sample(mat, md, sp, wo, bRay.dir, s, W);
+            col3 lcol; float lightPdf;
+            if (s.pdf > 1e-6f && light_intersect(light, bRay.from, bRay.dir, bRay.tmax, lcol, lightPdf)) {
+                if (lightPdf > 1e-6f) {
+                    float lPdf = 1.f / lightPdf;
+                    float l2 = lPdf * lPdf, m2 = s.pdf * s.pdf;
+                    float w = m2 / (l2 + m2);
+                    col3 c = mul(surfCol, lcol) * (w * W);
+                    push_shadow(a, bRay, mul(weight, c) * invNS, sid);
+                }
+            }
+        }
+    }
+}
+// estimateAllDirectLight (mcintegrator.cc:45-56)
+YB_HD void estimateAllDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, col3 weight, uint32_t sid)
+{
+    for (int l = 0; l < a.sc.nLights; ++l) doLightEstimation(a, a.sc.lights[l], (uint32_t)l, sp, md, wo, id, rayDivision, weight, sid);
+}
+// estimateOneDirectLight (mcintegrator.cc:58-71)
+YB_HD void estimateOneDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, int n, col3 weight, uint32_t sid)
+{
+    const int lightNum = a.sc.nLights;
+    if (lightNum == 0) return;
+    Halton hal2(2);
+    hal2.setStart((uint32_t)(n - 1));
+    int lnum = (int)(hal2.getNext() * (float)lightNum);
+    if (lnum > lightNum - 1) lnum = lightNum - 1;
+    doLightEstimation(a, a.sc.lights[lnum], (uint32_t)lnum, sp, md, wo, id, rayDivision, weight * (float)lightNum, sid);
+}
+// sampleAmbientOcclusion (mcintegrator.cc:629-683)
+YB_HD void sampleAmbientOcclusion(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision,
+                                  float dc1, float dc2, bool includeLights, col3 weight, uint32_t sid)
+{
+    const Integrator &I = a.sc.integ;
+    const Material &mat = *sp.mat;
+    int n = I.aoSamples;
+    if (rayDivision > 1) n = (n / (int)rayDivision) > 1 ? (n / (int)rayDivision) : 1;
+    const uint32_t offs = (uint32_t)n * (uint32_t)id.pixelSample + id.samplingOffs;
+    Halton hal2(2), hal3(3);
+    hal2.setStart(offs - 1); hal3.setStart(offs - 1);
+    const float invN = 1.f / (float)n;
+    col3 ecol(0.f);
+    for (int i = 0; i < n; ++i) {
+        float s1 = hal2.getNext(), s2 = hal3.getNext();
+        if (rayDivision > 1) { s1 = addMod1(s1, dc1); s2 = addMod1(s2, dc2); }
+        Ray lightRay;
+        lightRay.from = sp.P; lightRay.tmin = YB_SHADOW_BIAS; lightRay.tmax = I.aoDist;
+        float W = 0.f;
+        BSample s(s1, s2, BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_REFLECT);
+        col3 surfCol = mat_sample(mat, md, sp, wo, lightRay.dir, s, W);
+        if (mat.bsdfFlags & BSDF_EMIT) ecol += mat_emit(mat, sp, wo, includeLights) * s.pdf;
+        float cosv = fabsf(dot(sp.N, lightRay.dir));
+        col3 c = mul(I.aoCol, surfCol) * cosv * W;
+        push_shadow(a, lightRay, mul(weight, c) * invN, sid);
+    }
+    if (!isBlack(ecol)) acc_add(a, sid, mul(weight, ecol) * invN);
+}
+
+// ------------------------------------------------------------------------------------------------ shading
+YB_HD Task child_task(const Task &T, v3 P, v3 dir, col3 thr, float aw, uint32_t bits)
+{
+    Task c = T;
+    c.ray.from = P; c.ray.dir = dir; c.ray.tmin = YB_MIN_RAYDIST; c.ray.tmax = -1.f;
+    c.thr = thr; c.aw = aw; c.bits = bits;
+    return c;
+}
+
+// One call of directLighting_t::integrate / pathIntegrator_t::integrate after its scene->intersect
+// (directlight.cc:112-182, pathtracer.cc:134-333), including the recursiveRaytrace fan-out (mcintegrator.cc:421-627).
+YB_HD void shade_integrate(const RenderArgs &a, const Task &T, const Hit &H)
+{
+    const Integrator &I = a.sc.integ;
+    const uint32_t sid = T.sid;
+    const float a0 = I.transpBackground ? 0.f : 1.f;
+    if (H.tri < 0) {                                            // nothing hit: background (directlight.cc:166-169)
+        if (I.hasBackground) acc_add(a, sid, mul(T.thr, I.bgColor));
+        if (T.aw != 0.f) acc_add_alpha(a, sid, T.aw * a0);
+        return;
+    }
+    const SampleId id = sample_id(a, sid);
+    Surf sp;
+    tri_getSurface(a.sc, H.tri, T.ray.from + H.t * T.ray.dir, H.b1, H.b2, sp);
+    const Material &mat = *sp.mat;
+    MatDat md; uint32_t bsdfs;
+    mat_initBSDF(mat, md, bsdfs);
+    const v3 wo = -T.ray.dir;
+    const int raylevel = (int)task_level(T.bits);
+    const bool includeLights = raylevel == 0 ? true : task_lights(T.bits);
+    if (bsdfs & BSDF_EMIT) acc_add(a, sid, mul(T.thr, mat_emit(mat, sp, wo, includeLights)));
+    if (bsdfs & BSDF_DIFFUSE) {
+        estimateAllDirectLight(a, sp, md, wo, id, T.rayDivision, T.thr, sid);
+        if (I.type == INTEG_DIRECT && I.useAO) sampleAmbientOcclusion(a, sp, md, wo, id, T.rayDivision, T.dc1, T.dc2, includeLights, T.thr, sid);
+    }
+    if (I.type == INTEG_PATH) {                                 // pathtracer.cc:184-303: first path segment
+        uint32_t path_flags = I.noRecursive ? BSDF_ALL : BSDF_DIFFUSE;
+        if (bsdfs & path_flags) {
+            path_flags |= (BSDF_DIFFUSE | BSDF_REFLECT | BSDF_TRANSMIT);
+            int nSamples = I.nPaths / (int)T.rayDivision; if (nSamples < 1) nSamples = 1;
+            const float invN = 1.f / (float)nSamples;
+            for (int i = 0; i < nSamples; ++i) {
+                const uint32_t offs = (uint32_t)I.nPaths * (uint32_t)id.pixelSample + id.samplingOffs + (uint32_t)i;
+                float s1 = RI_vdC(offs), s2 = (float)scrHalton(2, offs), W = 0.f;
+                if (T.rayDivision > 1) { s1 = addMod1(s1, T.dc1); s2 = addMod1(s2, T.dc2); }
+                BSample s(s1, s2, path_flags);
+                v3 wi(0.f);
+                col3 scol = mat_sample(mat, md, sp, wo, wi, s, W);
+                scol *= W;
+                if (isBlack(scol)) continue;                     // every later term of this path is multiplied by it
+                Task c = child_task(T, sp.P, wi, mul(T.thr, scol) * invN, 0.f, task_bits(TASK_PATH, false, (uint32_t)raylevel, 0));
+                c.pathOffs = offs;
+                push_task(a, c);
+            }
+        }
+    }
+    // ---- recursiveRaytrace (mcintegrator.cc:421-627)
+    float residualAlpha = 0.f; bool alphaTaken = false;
+    float m_alpha = 1.f;
+    if (I.transpRefractedBackground) m_alpha = mat_getAlpha(mat, md, sp, wo);
+    if (T.aw != 0.f) {
+        if (I.transpRefractedBackground) { acc_add_alpha(a, sid, T.aw * m_alpha); residualAlpha = T.aw * (1.f - m_alpha); }
+        else acc_add_alpha(a, sid, T.aw);
+    }
+    const int newlevel = raylevel + 1;
+    if (newlevel <= I.rDepth) {
+        if ((bsdfs & BSDF_GLOSSY) && newlevel < 20 && (mat.bsdfFlags & BSDF_GLOSSY)) {
+            // supported glossy materials reflect only (BSDF_REFLECT without BSDF_TRANSMIT): mcintegrator.cc:519-537
+            int gsam = 8;
+            const uint32_t oldDivision = T.rayDivision, oldOffset = T.rayOffset;
+            if (oldDivision > 1) { gsam = gsam / (int)oldDivision; if (gsam < 1) gsam = 1; }
+            const uint32_t newDivision = oldDivision * (uint32_t)gsam;
+            uint32_t branch = newDivision * oldOffset;
+            uint32_t offs = (uint32_t)gsam * (uint32_t)id.pixelSample + id.samplingOffs;
+            const float d_1 = 1.f / (float)gsam;
+            Halton hal2(2), hal3(3);
+            hal2.setStart(offs); hal3.setStart(offs);
+            for (int ns = 0; ns < gsam; ++ns) {
+                const float dc1 = (float)scrHalton(2 * newlevel + 1, branch + id.samplingOffs);
+                const float dc2 = (float)scrHalton(2 * newlevel + 2, branch + id.samplingOffs);
+                const uint32_t rayOffset = branch;
+                ++offs; ++branch;
+                const float s1 = hal2.getNext(), s2 = hal3.getNext();
+                if ((mat.bsdfFlags & BSDF_REFLECT) && !(mat.bsdfFlags & BSDF_TRANSMIT)) {
+                    float W = 0.f;
+                    BSample s(s1, s2, BSDF_GLOSSY | BSDF_REFLECT);
+                    v3 wi(0.f);
+                    col3 mcol = mat_sample(mat, md, sp, wo, wi, s, W);
+                    col3 w = mul(T.thr, mcol) * W * d_1;
+                    if (isBlack(w)) continue;
+                    Task c = child_task(T, sp.P, wi, w, 0.f, task_bits(TASK_INTEGRATE, true, (uint32_t)newlevel, 0));
+                    c.rayDivision = newDivision; c.rayOffset = rayOffset; c.dc1 = dc1; c.dc2 = dc2;
+                    push_task(a, c);
+                }
+            }
+        }
+        if ((bsdfs & (BSDF_SPECULAR | BSDF_FILTER)) && newlevel < 20) {
+            bool reflect = false, refract = false;
+            v3 dir[2]; col3 rcol[2];
+            dir[0] = dir[1] = v3(0.f); rcol[0] = rcol[1] = col3(0.f);
+            mat_getSpecular(mat, md, sp, wo, newlevel, reflect, refract, dir, rcol);
+            if (reflect) {
+                col3 w = mul(T.thr, rcol[0]);
+                if (!isBlack(w)) push_task(a, child_task(T, sp.P, dir[0], w, 0.f, task_bits(TASK_INTEGRATE, true, (uint32_t)newlevel, 0)));
+            }
+            if (refract) {
+                col3 w = mul(T.thr, rcol[1]);
+                // alpha = integ.A of the refracted call (mcintegrator.cc:622): the residual alpha weight travels with it
+                if (!isBlack(w) || residualAlpha != 0.f) {
+                    push_task(a, child_task(T, sp.P, dir[1], w, residualAlpha, task_bits(TASK_INTEGRATE, true, (uint32_t)newlevel, 0)));
+                    alphaTaken = true;
+                }
+            }
+        }
+    }
+    if (!alphaTaken && residualAlpha != 0.f) acc_add_alpha(a, sid, residualAlpha * a0);
+}
+
+// One vertex of the bounce loop of pathIntegrator_t::integrate (pathtracer.cc:232-299)
+YB_HD void shade_path(const RenderArgs &a, const Task &T, const Hit &H)
+{
+    const Integrator &I = a.sc.integ;
+    const uint32_t sid = T.sid;
+    const uint32_t depth = task_depth(T.bits);                  // number of bounces already taken
+    const bool caustic = task_lights(T.bits);                   // state.includeLights == caustic on a path (pathtracer.cc:266-267)
+    if (H.tri < 0) {
+        if (depth >= 1 && caustic && I.hasBackground) acc_add(a, sid, mul(T.thr, I.bgColor));   // pathtracer.cc:273-280
+        return;
+    }
+    const SampleId id = sample_id(a, sid);
+    Surf sp;
+    tri_getSurface(a.sc, H.tri, T.ray.from + H.t * T.ray.dir, H.b1, H.b2, sp);
+    const Material &mat = *sp.mat;
+    MatDat md; uint32_t bsdfs;
+    mat_initBSDF(mat, md, bsdfs);
+    const v3 pwo = -T.ray.dir;
+    const uint32_t offs = T.pathOffs;
+    if (depth == 0) {
+        estimateOneDirectLight(a, sp, md, pwo, id, T.rayDivision, (int)offs, T.thr, sid);
+        if (bsdfs & BSDF_EMIT) acc_add(a, sid, mul(T.thr, mat_emit(mat, sp, pwo, false)));
+    } else {
+        if (bsdfs & BSDF_DIFFUSE) estimateOneDirectLight(a, sp, md, pwo, id, T.rayDivision, (int)offs, T.thr, sid);
+        // `matBSDFs & (BSDF_EMIT && caustic)` == matBSDFs & 1 when caustic (pathtracer.cc:295)
+        if (caustic && (bsdfs & BSDF_SPECULAR)) acc_add(a, sid, mul(T.thr, mat_emit(mat, sp, pwo, caustic)));
+    }
+    const uint32_t nd = depth + 1;
+    if ((int)nd >= I.maxBounces) return;
+    const int d4 = 4 * (int)nd;
+    BSample s((float)scrHalton(d4 + 3, offs), (float)scrHalton(d4 + 4, offs), BSDF_ALL);
+    float W = 0.f; v3 wi(0.f);
+    col3 scol = mat_sample(mat, md, sp, pwo, wi, s, W);
+    scol *= W;
+    if (isBlack(scol)) return;
+    col3 thr = mul(T.thr, scol);
+    if (I.russianRoulette) {     // opt-in extension (not in the reference): survive with p = clamp(max(thr)), weight 1/p
+        float p = fmaxf_(thr.x, fmaxf_(thr.y, thr.z));
+        p = fminf_(1.f, fmaxf_(I.rrMinProb, p));
+        const float u = (float)scrHalton((d4 + 5) < 50 ? (d4 + 5) : 49, offs + 0x9e3779b9u * nd);
+        if (u >= p) return;
+        thr = thr * (1.f / p);
+    }
+    const bool ncaustic = I.traceCaustics && (s.sampledFlags & (BSDF_SPECULAR | BSDF_GLOSSY | BSDF_FILTER));
+    push_task(a, child_task(T, sp.P, wi, thr, 0.f, task_bits(TASK_PATH, ncaustic, task_level(T.bits), nd)));
+}
+
+YB_KERNEL(k_shade, RenderArgs)
+{
+    const Task T = a.tasks[tid];
+    const Hit H = a.hits[tid];
+    if (task_kind(T.bits) == TASK_INTEGRATE) shade_integrate(a, T, H);
+    else shade_path(a, T, H);
+}
+
+// ------------------------------------------------------------------------------------------------ film
+// imageFilm_t::addSample (imagefilm.cc:453-511); film layout (x + w*y)*5 = r,g,b,a,weight (pixel_t)
+YB_KERNEL(k_film, RenderArgs)
+{
+    const Film &f = a.sc.film;
+    const SampleId id = sample_id(a, tid);
+    float dx, dy;
+    sample_dxdy(f, id, dx, dy);
+    f4 c = a.acc[tid];                                           // wt == 1 for the perspective camera
+    if (f.clamp) {
+        c.x = c.x < 0.f ? 0.f : (c.x > 1.f ? 1.f : c.x); c.y = c.y < 0.f ? 0.f : (c.y > 1.f ? 1.f : c.y); c.z = c.z < 0.f ? 0.f : (c.z > 1.f ? 1.f : c.z);
+    }
+    const int x = id.x, y = id.y;
+    int dx0 = Round2Int((double)dx - f.filterw), dx1 = Round2Int((double)dx + f.filterw - 1.0);
+    int dy0 = Round2Int((double)dy - f.filterw), dy1 = Round2Int((double)dy + f.filterw - 1.0);
+    if (dx0 < f.cx0 - x) dx0 = f.cx0 - x;
+    if (dx1 > f.cx1 - x - 1) dx1 = f.cx1 - x - 1;
+    if (dy0 < f.cy0 - y) dy0 = f.cy0 - y;
+    if (dy1 > f.cy1 - y - 1) dy1 = f.cy1 - y - 1;
+    int xIndex[YB_MAX_FILTER_SIZE + 1], yIndex[YB_MAX_FILTER_SIZE + 1];
+    const double x_offs = dx - 0.5, y_offs = dy - 0.5;
+    for (int i = dx0, n = 0; i <= dx1 && n <= YB_MAX_FILTER_SIZE; ++i, ++n) xIndex[n] = Floor2Int(fabs(((double)i - x_offs) * f.tableScale));
+    for (int i = dy0, n = 0; i <= dy1 && n <= YB_MAX_FILTER_SIZE; ++i, ++n) yIndex[n] = Floor2Int(fabs(((double)i - y_offs) * f.tableScale));
+    const int x0 = x + dx0, x1 = x + dx1, y0 = y + dy0, y1 = y + dy1;
+    for (int j = y0; j <= y1; ++j)
+        for (int i = x0; i <= x1; ++i) {
+            const int offset = yIndex[j - y0] * YB_FILTER_TABLE_SIZE + xIndex[i - x0];
+            const float filterWt = f.filterTable[offset];
+            if (f.premult) { c.x *= c.w; c.y *= c.w; c.z *= c.w; }      // sic: inside the footprint loop (imagefilm.cc:502)
+            float *px = a.film + ((size_t)(i - f.cx0) + (size_t)f.w * (size_t)(j - f.cy0)) * 5;
+            YB_ATOMIC_ADD_F32(px + 0, c.x * filterWt); YB_ATOMIC_ADD_F32(px + 1, c.y * filterWt);
+            YB_ATOMIC_ADD_F32(px + 2, c.z * filterWt); YB_ATOMIC_ADD_F32(px + 3, c.w * filterWt);
+            YB_ATOMIC_ADD_F32(px + 4, filterWt);
+        }
+}
+
+// imageFilm_t::flush (imagefilm.cc:383-443) + pixel_t::normalized (image_buffers.h:32-43), memoryIO_t layout
+struct ResolveArgs { Film f; const float *film; float *rgba; };
+YB_KERNEL(k_resolve, ResolveArgs)
+{
+    const float *px = a.film + (size_t)tid * 5;
+    float r = 0.f, g = 0.f, b = 0.f, al = 0.f;
+    const float wgt = px[4];
+    if (wgt > 0.f) { const float inv = 1.f / wgt; r = px[0] * inv; g = px[1] * inv; b = px[2] * inv; al = px[3] * inv; }
+    if (r < 0.f) r = 0.f; if (g < 0.f) g = 0.f; if (b < 0.f) b = 0.f;
+    if (a.f.correctGamma) { r = fPow(r, a.f.gamma); g = fPow(g, a.f.gamma); b = fPow(b, a.f.gamma); }
+    if (a.f.premult) { r *= al; g *= al; b *= al; }
+    float *o = a.rgba + (size_t)tid * 4;
+    o[0] = r; o[1] = g; o[2] = b; o[3] = al;
+}
+
+// ------------------------------------------------------------------------------------------------ parity / bench hook kernels
+struct TraceArgs { SceneDev sc; const Ray *rays; void *out; int shadowDepth; };
+struct ClosestOut { int32_t prim; float t, b1, b2; };
+struct TShadowOut { int32_t s; float r, g, b; };
+YB_KERNEL(k_batch_closest, TraceArgs)
+{
+    Hit h;
+    ClosestOut o;
+    if (scene_intersect(a.sc, a.rays[tid], h)) { o.prim = f2i(a.sc.tri_v[3 * h.tri].w); o.t = h.t; o.b1 = h.b1; o.b2 = h.b2; }
+    else { o.prim = -1; o.t = 0.f; o.b1 = 0.f; o.b2 = 0.f; }
+    ((ClosestOut *)a.out)[tid] = o;
+}
+YB_KERNEL(k_batch_shadow, TraceArgs) { ((int32_t *)a.out)[tid] = scene_isShadowed(a.sc, a.rays[tid]) ? 1 : 0; }
+YB_KERNEL(k_batch_tshadow, TraceArgs)
+{
+    col3 filt;
+    TShadowOut o;
+    o.s = scene_isShadowedT(a.sc, a.rays[tid], a.shadowDepth, filt) ? 1 : 0;
+    o.r = filt.x; o.g = filt.y; o.b = filt.z;
+    ((TShadowOut *)a.out)[tid] = o;
+}
+
+// ================================================================================================ host driver
+struct RenderBuffers {
+    DevBuf<Task> poolA, poolB;
+    DevBuf<Hit> hits;
+    DevBuf<ShadowTask> shadow;
+    DevBuf<uint32_t> counters;
+    DevBuf<f4> acc;
+    DevBuf<uint32_t> pix;
+    DevBuf<float> film, rgba;
+    DevBuf<char> io_in, io_out;     // staging for host-pointer ray batches
+};
+void render_release(RenderBuffers *rb) { delete rb; }
+
+struct StageTimer {
+#ifndef YB_HOSTEMU
+    cudaEvent_t e0, e1; rt_stream s;
+    StageTimer(rt_stream s_) : s(s_) { cudaEventCreate(&e0); cudaEventCreate(&e1); }
+    ~StageTimer() { cudaEventDestroy(e0); cudaEventDestroy(e1); }
+    void start() { cudaEventRecord(e0, s); }
+    void stop() { cudaEventRecord(e1, s); }
+    double ms() { cudaEventSynchronize(e1); float m = 0; cudaEventElapsedTime(&m, e0, e1); return m; }
+#else
+    std::chrono::steady_clock::time_point t0, t1;
+    StageTimer(rt_stream) {}
+    void start() { t0 = std::chrono::steady_clock::now(); }
+    void stop() { t1 = std::chrono::steady_clock::now(); }
+    double ms() { return std::chrono::duration<double, std::milli>(t1 - t0).count(); }
+#endif
+};
+
+static size_t env_size(const char *name, size_t dflt)
+{
+    const char *e = getenv(name);
+    if (!e || !*e) return dflt;
+    return (size_t)strtoull(e, 0, 10);
+}
+
+bool render_film_device(Context &c, float *d_film, int rank, int world, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user)
+{
+    if (!c.sceneReady) return c.fail("render: scene not updated");
+    if (world < 1 || rank < 0 || rank >= world) return c.fail("render_film: bad rank/world");
+    try {
+        if (!c.rb) c.rb = new RenderBuffers();
+        RenderBuffers &rb = *c.rb;
+        rt_stream s = c.stream;
+        const Film &f = c.sc.film;
+        const Integrator &I = c.sc.integ;
+        auto tstart = std::chrono::steady_clock::now();
+        // ---- owned pixels: tiles of imageSpliter_t (imagesplitter.cc:29-52) dealt round-robin to ranks
+        std::vector<uint32_t> pix;
+        {
+            if (f.cx1 > 65535 || f.cy1 > 65535) return c.fail("render: image coordinates above 65535 are not supported");
+            const int bs = f.tileSize, nx = (f.w + bs - 1) / bs, ny = (f.h + bs - 1) / bs;
+            int tile = 0;
+            for (int j = 0; j < ny; ++j)
+                for (int i = 0; i < nx; ++i, ++tile) {
+                    if (tile % world != rank) continue;
+                    const int x0 = f.cx0 + i * bs, y0 = f.cy0 + j * bs;
+                    const int tw = std::min(bs, f.cx0 + f.w - x0), th = std::min(bs, f.cy0 + f.h - y0);
+                    for (int y = y0; y < y0 + th; ++y)
+                        for (int x = x0; x < x0 + tw; ++x) pix.push_back((uint32_t)x | ((uint32_t)y << 16));
+                }
+        }
+        const uint64_t totalSamples = (uint64_t)pix.size() * (uint64_t)f.n_samples;
+        if (totalSamples >= 0xffffffffull) return c.fail("render: more than 2^32 camera samples per rank are not supported");
+        rb.pix.reserve(pix.size() + 1);
+        rt_h2d(rb.pix.p, pix.data(), pix.size() * sizeof(uint32_t), s);
+        // ---- worst-case fan-out per task, from the integrator and the materials present
+        bool anyGlossy = false; int specChildren = 0;
+        for (size_t i = 0; i < c.materials.size(); ++i) {
+            const Material &m = c.materials[i];
+            if (m.bsdfFlags & BSDF_GLOSSY) anyGlossy = true;
+            int sc_ = 0;
+            if (m.type == MAT_GLASS) sc_ = 2;
+            else if (m.type == MAT_SHINYDIFFUSE) sc_ = (m.isMirror ? 1 : 0) + (m.isTransparent ? 1 : 0);
+            else if (m.type == MAT_COATED_GLOSSY || m.type == MAT_MIRROR) sc_ = 1;
+            specChildren = std::max(specChildren, sc_);
+        }
+        size_t F = (I.type == INTEG_PATH ? (size_t)std::max(1, I.nPaths) : 0) + (anyGlossy ? 8 : 0) + (size_t)specChildren;
+        if (F < 1) F = 1;
+        size_t S = 0;
+        for (size_t i = 0; i < c.lights.size(); ++i) S += c.lights[i].type == LIGHT_POINT ? 1 : 2 * (size_t)std::max(1, c.lights[i].samples);
+        if (I.type == INTEG_DIRECT && I.useAO) S += (size_t)std::max(1, I.aoSamples);
+        if (S < 1) S = 1;
+#ifdef YB_HOSTEMU
+        const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)512 << 20), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 16);
+#else
+        const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)24 << 30), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 22);
+#endif
+        const size_t perSample = (F + 1) * sizeof(Task) * 2 + S * sizeof(ShadowTask) + sizeof(Hit) + sizeof(f4);
+        size_t B = std::min<size_t>(Bmax, std::max<size_t>(1024, budget / perSample));
+        B = std::min<size_t>(B, (size_t)totalSamples);
+        if (B == 0) return true;
+        const size_t poolCap = B * (F + 1), shadowCap = B * S;
+        rb.poolA.reserve(poolCap); rb.poolB.reserve(poolCap);
+        rb.hits.reserve(B); rb.shadow.reserve(shadowCap); rb.counters.reserve(4); rb.acc.reserve(B);
+        RenderArgs a;
+        memset((void *)&a, 0, sizeof(a));
+        a.sc = c.sc; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
+        a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
+        Task *pool = rb.poolA.p, *alt = rb.poolB.p;
+        StageTimer tc(s), tsh(s), tsd(s), tf(s);
+        uint64_t raysClosest = 0, raysShadow = 0; double msClosest = 0, msShadow = 0, msShade = 0, msFilm = 0;
+        const uint64_t launches0 = g_kernel_launches;
+        const int nBatches = (int)((totalSamples + B - 1) / B);
+        for (int b = 0; b < nBatches; ++b) {
+            if (c.abortFlag || (should_abort && should_abort(user))) break;
+            const uint32_t base = (uint32_t)((uint64_t)b * B);
+            const uint32_t nb = (uint32_t)std::min<uint64_t>(B, totalSamples - base);
+            a.sampleBase = base; a.tasks = pool;
+            k_raygen(nb, a, s);
+            size_t top = nb;
+            while (top > 0) {
+                size_t M = std::min(top, B);
+                M = std::min(M, shadowCap / S);
+                if (M * F > poolCap - top) M = (poolCap - top) / F;
+                if (M == 0) throw RtError("render: task pool exhausted (raise YB200_QUEUE_BYTES)");
+                const bool whole = (M == top);
+                a.tasks = pool + (top - M);
+                a.out_tasks = whole ? alt : pool + top;
+                a.outCap = (uint32_t)std::min<size_t>(whole ? poolCap : poolCap - top, 0xffffffffu);
+                rt_memset(rb.counters.p, 0, 4 * sizeof(uint32_t), s);
+                tc.start(); k_trace_closest((uint32_t)M, a, s); tc.stop();
+                tsd.start(); k_shade((uint32_t)M, a, s); tsd.stop();
+                uint32_t cnt[4];
+                rt_d2h(cnt, rb.counters.p, sizeof(cnt), s);
+                if (cnt[0] > a.outCap || cnt[1] > a.shadowCap) throw RtError("render: internal queue overflow");
+                tsh.start(); k_trace_shadow(cnt[1], a, s); tsh.stop();
+                raysClosest += M; raysShadow += cnt[1];
+                msClosest += tc.ms(); msShade += tsd.ms(); if (cnt[1]) msShadow += tsh.ms();
+                if (whole) { std::swap(pool, alt); top = cnt[0]; }
+                else {
+                    const size_t k = std::min<size_t>(M, cnt[0]);
+                    rt_d2d(pool + (top - M), pool + (top + cnt[0] - k), k * sizeof(Task), s);
+                    top = top - M + cnt[0];
+                }
+            }
+            a.tasks = pool;
+            tf.start(); k_film(nb, a, s); tf.stop();
+            rt_sync(s);
+            msFilm += tf.ms();
+            if (progress) progress(user, b + 1, nBatches);
+        }
+        rt_sync(s);
+        Stats &st = c.stats;
+        st.rays_closest = raysClosest; st.rays_shadow = raysShadow; st.camera_samples = totalSamples;
+        st.kernel_launches = g_kernel_launches - launches0;
+        st.trace_closest_ms = msClosest; st.trace_shadow_ms = msShadow; st.shade_ms = msShade; st.film_ms = msFilm;
+        st.render_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tstart).count();
+    } catch (const RtError &e) { return c.fail(std::string("render failed: ") + e.what()); }
+    return true;
+}
+
+void film_resolve_device(Context &c, const float *d_film, float *d_rgba)
+{
+    ResolveArgs ra; ra.f = c.sc.film; ra.film = d_film; ra.rgba = d_rgba;
+    k_resolve((uint32_t)((size_t)c.sc.film.w * c.sc.film.h), ra, c.stream);
+}
+
+void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int shadow_depth, void *d_out)
+{
+    TraceArgs ta; ta.sc = c.sc; ta.rays = (const Ray *)d_rays; ta.out = d_out; ta.shadowDepth = shadow_depth;
+    const size_t step = (size_t)1 << 30;
+    for (size_t o = 0; o < n; o += step) {
+        const uint32_t m = (uint32_t)std::min(step, n - o);
+        TraceArgs t2 = ta; t2.rays = ta.rays + o;
+        if (mode == TRACE_CLOSEST) { t2.out = (ClosestOut *)d_out + o; k_batch_closest(m, t2, c.stream); }
+        else if (mode == TRACE_SHADOW) { t2.out = (int32_t *)d_out + o; k_batch_shadow(m, t2, c.stream); }
+        else { t2.out = (TShadowOut *)d_out + o; k_batch_tshadow(m, t2, c.stream); }
+    }
+}
+
+}  // namespace yb

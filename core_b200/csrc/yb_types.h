@@ -1,0 +1,166 @@
+// yb_types.h — plain-data records shared by the host flattener and the kernels.
+// Layout notes (HBM): see DESIGN.md §"Data layout".  All records are PODs that are memcpy'd to the device.
+#pragma once
+#include "yb_math.cuh"
+
+namespace yb {
+
+// BSDF_t bits — include/core_api/material.h:32-45
+enum : uint32_t {
+    BSDF_NONE = 0x0000, BSDF_SPECULAR = 0x0001, BSDF_GLOSSY = 0x0002, BSDF_DIFFUSE = 0x0004,
+    BSDF_DISPERSIVE = 0x0008, BSDF_REFLECT = 0x0010, BSDF_TRANSMIT = 0x0020, BSDF_FILTER = 0x0040,
+    BSDF_EMIT = 0x0080, BSDF_VOLUMETRIC = 0x0100, BSDF_TRANSLUCENT = 0x0200,
+    BSDF_ALL_SPECULAR = BSDF_SPECULAR | BSDF_REFLECT | BSDF_TRANSMIT,
+    BSDF_ALL_GLOSSY = BSDF_GLOSSY | BSDF_REFLECT | BSDF_TRANSMIT,
+    BSDF_ALL = BSDF_SPECULAR | BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_DISPERSIVE | BSDF_REFLECT | BSDF_TRANSMIT | BSDF_FILTER
+};
+
+enum MatType : int32_t { MAT_SHINYDIFFUSE = 0, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_MIRROR, MAT_NULL, MAT_LIGHT };
+
+// One record per material; the union of the constant parameters of the supported material_t classes
+// (shader-node inputs are rejected at creation).  ~260 B, read through the read-only cache.
+struct Material {
+    int32_t type;
+    uint32_t bsdfFlags;
+    // --- shinyDiffuseMat_t (include/materials/shinydiff.h:63-108; config() shinydiffuse.cc:32-80)
+    col3 diffuseColor, mirrorColor, emitColor;
+    float mirrorStrength, transparencyStrength, translucencyStrength, diffuseStrength, transmitFilterStrength;
+    float iorSquared, orenA, orenB;
+    int32_t hasFresnel, useOrenNayar, isMirror, isTransparent, isTranslucent, isDiffuse;
+    int32_t nBSDF;
+    uint32_t cFlags[4];
+    int32_t cIndex[4];
+    // --- glossyMat_t / coatedGlossyMat_t (glossy.cc:31-80, coatedglossy.cc:38-101)
+    col3 glossColor, diffColor;     // mirrorColor above doubles as the coat's mirror_color
+    float exponent, expU, expV, reflectivity, mDiffuse, ior;
+    int32_t asDiffuse, withDiffuse, anisotropic, orenNayar;
+    // --- glassMat_t / mirrorMat_t (glass.cc:30-82,300-340)
+    col3 filterCol, specRefCol;
+    int32_t fakeShadow;
+    float mirrorRefl;               // mirrorMat_t::ref
+    // --- lightMat_t (simple.cc:36-70)
+    col3 lightCol;
+    int32_t doubleSided;
+};
+
+enum LightType : int32_t { LIGHT_POINT = 0, LIGHT_SUN, LIGHT_AREA };
+struct Light {
+    int32_t type, samples;
+    col3 color;                      // point: col*power; area: col*power*pi; sun: col*power
+    v3 position;                     // point
+    v3 direction, du, dv;            // sun (du/dv from the UN-normalised direction, sunlight.cc:57); area du/dv unused
+    col3 colPdf;                     // sun
+    float pdf, invpdf;               // sun
+    double cosAngle;                 // sun (double member, sunlight.cc:44)
+    v3 corner, c2, c3, c4, toX, toY, normal, fnormal;   // area (arealight.cc:33-49)
+    float area, invArea;
+};
+
+struct Camera {                       // perspectiveCam_t (perspectiveCamera.cc:28-71,127-149; camera.h:41-61)
+    v3 position, vto, vup, vright, dof_rt, dof_up, camZ;
+    v3 near_p, far_p;                // plane points (plane normal = camZ)
+    float aperture, dof_distance;
+    int32_t resx, resy, sampleLens;
+};
+
+enum IntegType : int32_t { INTEG_DIRECT = 0, INTEG_PATH = 1 };
+struct Integrator {
+    int32_t type;
+    int32_t trShad, sDepth, rDepth;
+    int32_t useAO, aoSamples;
+    float aoDist;
+    col3 aoCol;
+    int32_t nPaths, maxBounces, noRecursive, traceCaustics;
+    int32_t transpBackground, transpRefractedBackground;
+    int32_t hasBackground;
+    col3 bgColor;
+    int32_t russianRoulette;          // opt-in extension (north_star); OFF by default and in every parity test
+    float rrMinProb;
+};
+
+#define YB_FILTER_TABLE_SIZE 16
+#define YB_MAX_FILTER_SIZE 8
+struct Film {                         // imageFilm_t (imagefilm.cc:119-165,453-511,383-443)
+    int32_t w, h, cx0, cy0, cx1, cy1;
+    float filterw;
+    float tableScale;                 // float member in the reference (imagefilm.h:161)
+    float filterTable[YB_FILTER_TABLE_SIZE * YB_FILTER_TABLE_SIZE];
+    int32_t clamp, premult, correctGamma;
+    float gamma;
+    int32_t tileSize;
+    // sampling plan of this render pass (integrator.cc:229-290)
+    int32_t AA_passes, n_samples, pass_offs;
+};
+
+// ---- geometry in HBM ------------------------------------------------------------------------------
+// tri_v : 3 x float4 per triangle, in BVH leaf order.  v0.w carries the global primitive index of
+//         scene.cc:760-781 (as int bits), v1.w the material/flags word, v2.w is free.
+// tri_n : 3 x v3 vertex normals per triangle (same order), only when some mesh is smooth.
+struct alignas(16) f4 { float x, y, z, w; };
+struct alignas(16) u4 { uint32_t x, y, z, w; };
+enum : uint32_t {
+    TRI_MAT_MASK = 0x000fffffu,
+    TRI_SMOOTH = 1u << 20,            // mesh->is_smooth
+    TRI_HAS_NA = 1u << 21, TRI_HAS_NB = 1u << 22, TRI_HAS_NC = 1u << 23,   // na/nb/nc >= 0 (triangle.cc:20-22)
+};
+
+// 8-wide BVH node with child boxes quantised to 8 bits on a per-node power-of-two grid (80 B = 5 x 16 B).
+struct alignas(16) BvhNode {
+    float px, py, pz;                 // grid origin (node box lower corner)
+    uint8_t ex, ey, ez;               // grid scale exponents: cell = 2^(e-127) as float bits (e<<23)
+    uint8_t imask;                    // bit s set: child slot s is an internal node
+    uint32_t childBase;               // index of the first internal child (children are stored contiguously in slot order)
+    uint32_t triBase;                 // index of the first triangle of this node's leaf children
+    uint8_t meta[8];                  // 0: empty; internal: 0xE0 | k (k-th internal child); leaf: (ntri << 5) | offset from triBase
+    uint8_t qlox[8], qloy[8], qloz[8], qhix[8], qhiy[8], qhiz[8];
+};
+static_assert(sizeof(BvhNode) == 80, "BvhNode must be 80 bytes");
+
+struct SceneDev {
+    const BvhNode *nodes;
+    const f4 *tri_v;
+    const v3 *tri_n;                  // may be null
+    const Material *materials;
+    const Light *lights;
+    int32_t nLights, nMaterials;
+    uint32_t nTris, nNodes;
+    v3 boundLo, boundHi;
+    Camera cam;
+    Integrator integ;
+    Film film;
+};
+
+// ---- trace records ----------------------------------------------------------------------------------
+struct Ray { v3 from; float tmin; v3 dir; float tmax; };   // 32 B; tmax < 0 == infinite (scene.cc:856,888)
+struct Hit { int32_t tri; float t, b1, b2; };              // tri = index into tri_v order, -1 = miss
+
+// ---- wavefront records ------------------------------------------------------------------------------
+enum : uint32_t { TASK_INTEGRATE = 0, TASK_PATH = 1 };
+// One pending scene_t::intersect + shading step: either a whole integrate(state, ray) call (camera ray or a
+// recursiveRaytrace child) or the next vertex of a path of pathIntegrator_t::integrate's bounce loop.
+struct Task {
+    Ray ray;                          // 32
+    col3 thr;                         // product of the weights above this call (linear in the result)
+    float aw;                         // weight with which this call's alpha enters the camera sample's alpha
+    uint32_t sid;                     // camera sample slot in the batch
+    uint32_t bits;                    // kind:1 | includeLights:1 | caustic:1 | raylevel:6 | depth:8 | ...
+    uint32_t rayDivision, rayOffset;  // renderState_t trajectory splitting (scene.h:86-88)
+    float dc1, dc2;
+    uint32_t pathOffs;                // `offs` of the path this vertex belongs to (pathtracer.cc:202)
+    uint32_t pad;
+};
+static_assert(sizeof(Task) == 80, "Task is 80 bytes");
+YB_HD uint32_t task_kind(uint32_t b) { return b & 1u; }
+YB_HD bool task_lights(uint32_t b) { return (b >> 1) & 1u; }
+YB_HD uint32_t task_level(uint32_t b) { return (b >> 3) & 63u; }
+YB_HD uint32_t task_depth(uint32_t b) { return (b >> 9) & 255u; }
+YB_HD uint32_t task_bits(uint32_t kind, bool lights, uint32_t level, uint32_t depth)
+{
+    return kind | (lights ? 2u : 0u) | (level << 3) | (depth << 9);
+}
+
+// One pending scene_t::isShadowed: if unoccluded, `c` (times the transparent-shadow filter) is added to the sample.
+struct ShadowTask { Ray ray; col3 c; uint32_t sid; };     // 48 B
+static_assert(sizeof(ShadowTask) == 48, "ShadowTask is 48 bytes");
+
+}  // namespace yb
