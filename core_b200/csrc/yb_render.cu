@@ -28,7 +28,7 @@ namespace yb {
 #define YB_LOFFS_DELTA 4567u         // mcintegrator.cc:43
 
 // scr_halton.h:47-69 (dim < 50 on this path: SURVEY.md §5)
-YB_HD double scrHalton(int dim, uint32_t n)
+YB_D double scrHalton(int dim, uint32_t n)
 {
     double value = 0.0;
     if (dim < 50) {
@@ -62,7 +62,7 @@ struct RenderArgs {
 
 // per-camera-sample identity (integrator.cc:251-273)
 struct SampleId { int x, y, s; uint32_t samplingOffs; int pixelSample; };
-YB_HD SampleId sample_id(const RenderArgs &a, uint32_t sid)
+YB_D SampleId sample_id(const RenderArgs &a, uint32_t sid)
 {
     SampleId r;
     const uint32_t gid = a.sampleBase + sid;
@@ -75,7 +75,7 @@ YB_HD SampleId sample_id(const RenderArgs &a, uint32_t sid)
     return r;
 }
 // sub-pixel position of a sample (integrator.cc:238,277-286)
-YB_HD void sample_dxdy(const Film &f, const SampleId &id, float &dx, float &dy)
+YB_D void sample_dxdy(const Film &f, const SampleId &id, float &dx, float &dy)
 {
     dx = 0.5f; dy = 0.5f;
     if (f.AA_passes > 1) { dx = RI_vdC((uint32_t)id.pixelSample, id.samplingOffs); dy = RI_S((uint32_t)id.pixelSample, id.samplingOffs); }
@@ -117,11 +117,11 @@ YB_KERNEL(k_trace_closest, RenderArgs)
     scene_intersect(a.sc, a.tasks[tid].ray, h);
     a.hits[tid] = h;
 }
-YB_HD void acc_add(const RenderArgs &a, uint32_t sid, col3 c)
+YB_D void acc_add(const RenderArgs &a, uint32_t sid, col3 c)
 {
     YB_ATOMIC_ADD_F32(&a.acc[sid].x, c.x); YB_ATOMIC_ADD_F32(&a.acc[sid].y, c.y); YB_ATOMIC_ADD_F32(&a.acc[sid].z, c.z);
 }
-YB_HD void acc_add_alpha(const RenderArgs &a, uint32_t sid, float v) { YB_ATOMIC_ADD_F32(&a.acc[sid].w, v); }
+YB_D void acc_add_alpha(const RenderArgs &a, uint32_t sid, float v) { YB_ATOMIC_ADD_F32(&a.acc[sid].w, v); }
 YB_KERNEL(k_trace_shadow, RenderArgs)
 {
     const ShadowTask st = a.shadow[tid];
@@ -132,7 +132,7 @@ YB_KERNEL(k_trace_shadow, RenderArgs)
 }
 
 // ------------------------------------------------------------------------------------------------ queues
-YB_HD void push_shadow(const RenderArgs &a, const Ray &r, col3 c, uint32_t sid)
+YB_D void push_shadow(const RenderArgs &a, const Ray &r, col3 c, uint32_t sid)
 {
     if (isBlack(c)) return;                                   // contributes nothing either way
     const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + 1, 1u);
@@ -140,7 +140,7 @@ YB_HD void push_shadow(const RenderArgs &a, const Ray &r, col3 c, uint32_t sid)
     ShadowTask st; st.ray = r; st.c = c; st.sid = sid;
     a.shadow[i] = st;
 }
-YB_HD void push_task(const RenderArgs &a, const Task &t)
+YB_D void push_task(const RenderArgs &a, const Task &t)
 {
     const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + 0, 1u);
     if (i >= a.outCap) return;
@@ -150,7 +150,7 @@ YB_HD void push_task(const RenderArgs &a, const Task &t)
 // ------------------------------------------------------------------------------------------------ direct lighting
 // mcIntegrator_t::doLightEstimation (mcintegrator.cc:73-195).  Every term that the reference adds after an
 // isShadowed() test becomes a shadow task carrying weight*term.
-YB_HD void doLightEstimation(const RenderArgs &a, const Light &light, uint32_t loffs, const Surf &sp, const MatDat &md, v3 wo,
+YB_D void doLightEstimation(const RenderArgs &a, const Light &light, uint32_t loffs, const Surf &sp, const MatDat &md, v3 wo,
                              const SampleId &id, uint32_t rayDivision, col3 weight, uint32_t sid)
 {
     const Material &mat = *sp.mat;
@@ -218,12 +218,12 @@ YB_HD void doLightEstimation(const RenderArgs &a, const Light &light, uint32_t l
     }
 }
 // estimateAllDirectLight (mcintegrator.cc:45-56)
-YB_HD void estimateAllDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, col3 weight, uint32_t sid)
+YB_D void estimateAllDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, col3 weight, uint32_t sid)
 {
     for (int l = 0; l < a.sc.nLights; ++l) doLightEstimation(a, a.sc.lights[l], (uint32_t)l, sp, md, wo, id, rayDivision, weight, sid);
 }
 // estimateOneDirectLight (mcintegrator.cc:58-71)
-YB_HD void estimateOneDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, int n, col3 weight, uint32_t sid)
+YB_D void estimateOneDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, int n, col3 weight, uint32_t sid)
 {
     const int lightNum = a.sc.nLights;
     if (lightNum == 0) return;
@@ -234,7 +234,7 @@ YB_HD void estimateOneDirectLight(const RenderArgs &a, const Surf &sp, const Mat
     doLightEstimation(a, a.sc.lights[lnum], (uint32_t)lnum, sp, md, wo, id, rayDivision, weight * (float)lightNum, sid);
 }
 // sampleAmbientOcclusion (mcintegrator.cc:629-683)
-YB_HD void sampleAmbientOcclusion(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision,
+YB_D void sampleAmbientOcclusion(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision,
                                   float dc1, float dc2, bool includeLights, col3 weight, uint32_t sid)
 {
     const Integrator &I = a.sc.integ;
@@ -263,7 +263,7 @@ YB_HD void sampleAmbientOcclusion(const RenderArgs &a, const Surf &sp, const Mat
 }
 
 // ------------------------------------------------------------------------------------------------ shading
-YB_HD Task child_task(const Task &T, v3 P, v3 dir, col3 thr, float aw, uint32_t bits)
+YB_D Task child_task(const Task &T, v3 P, v3 dir, col3 thr, float aw, uint32_t bits)
 {
     Task c = T;
     c.ray.from = P; c.ray.dir = dir; c.ray.tmin = YB_MIN_RAYDIST; c.ray.tmax = -1.f;
@@ -273,7 +273,7 @@ YB_HD Task child_task(const Task &T, v3 P, v3 dir, col3 thr, float aw, uint32_t 
 
 // One call of directLighting_t::integrate / pathIntegrator_t::integrate after its scene->intersect
 // (directlight.cc:112-182, pathtracer.cc:134-333), including the recursiveRaytrace fan-out (mcintegrator.cc:421-627).
-YB_HD void shade_integrate(const RenderArgs &a, const Task &T, const Hit &H)
+YB_D void shade_integrate(const RenderArgs &a, const Task &T, const Hit &H)
 {
     const Integrator &I = a.sc.integ;
     const uint32_t sid = T.sid;
@@ -381,7 +381,7 @@ YB_HD void shade_integrate(const RenderArgs &a, const Task &T, const Hit &H)
 }
 
 // One vertex of the bounce loop of pathIntegrator_t::integrate (pathtracer.cc:232-299)
-YB_HD void shade_path(const RenderArgs &a, const Task &T, const Hit &H)
+YB_D void shade_path(const RenderArgs &a, const Task &T, const Hit &H)
 {
     const Integrator &I = a.sc.integ;
     const uint32_t sid = T.sid;

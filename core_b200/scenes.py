@@ -270,3 +270,61 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
     rays = np.zeros((d.shape[0], 8), dtype=np.float32)
     rays[:, 0:3] = pos; rays[:, 3] = 0.0; rays[:, 4:7] = d; rays[:, 7] = -1.0
     return rays
+
+
+# ----------------------------------------------------------------------------- C4: glossy / coated / glass materials
+def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
+                    integ_params=None, area_samples=8, sun_samples=4, raydepth=5, **render_extra):
+    """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
+    coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
+    shinydiffuse; sun (1 degree, 4 samples) + point + area (8 samples) lights; pathtracing with 8 bounces
+    (BASELINE.json configs[3]).  The area light has no emitter mesh (includeLights ordering)."""
+    yi.startScene(0)
+    M = {}
+    M["ground"] = create(yi, "material", "ground", type="shinydiffusemat", color=(0.55, 0.55, 0.5, 1.0), diffuse_reflect=0.9)
+    M["glossy"] = create(yi, "material", "glossy", type="glossy", color=(0.9, 0.6, 0.3, 1.0), diffuse_color=(0.5, 0.2, 0.1, 1.0),
+                         diffuse_reflect=0.4, glossy_reflect=0.8, exponent=50.0, as_diffuse=False)
+    M["aniso"] = create(yi, "material", "aniso", type="glossy", color=(0.7, 0.8, 0.9, 1.0), diffuse_color=(0.2, 0.3, 0.5, 1.0),
+                        diffuse_reflect=0.3, glossy_reflect=0.9, anisotropic=True, exp_u=20.0, exp_v=200.0, as_diffuse=False)
+    M["gdiff"] = create(yi, "material", "gdiff", type="glossy", color=(0.6, 0.9, 0.6, 1.0), diffuse_color=(0.3, 0.6, 0.3, 1.0),
+                        diffuse_reflect=0.6, glossy_reflect=0.5, exponent=120.0, as_diffuse=True,
+                        diffuse_brdf="Oren-Nayar", sigma=0.3)
+    M["coated"] = create(yi, "material", "coated", type="coated_glossy", color=(0.8, 0.2, 0.2, 1.0),
+                         diffuse_color=(0.6, 0.1, 0.1, 1.0), diffuse_reflect=0.5, glossy_reflect=0.6, exponent=80.0,
+                         IOR=1.4, as_diffuse=False, mirror_color=(1.0, 1.0, 1.0, 1.0))
+    M["glass"] = create(yi, "material", "glass", type="glass", IOR=1.5, filter_color=(0.8, 1.0, 0.9, 1.0), transmit_filter=0.6,
+                        mirror_color=(1.0, 1.0, 1.0, 1.0), fake_shadows=True)
+    M["glass2"] = create(yi, "material", "glass2", type="glass", IOR=1.33, filter_color=(1.0, 0.9, 0.8, 1.0), transmit_filter=0.4,
+                         fake_shadows=False)
+    M["mirror"] = create(yi, "material", "mirror", type="mirror", color=(0.9, 0.9, 1.0, 1.0), reflect=0.85)
+    M["shiny"] = create(yi, "material", "shiny", type="shinydiffusemat", color=(0.3, 0.5, 0.9, 1.0), diffuse_reflect=0.7,
+                        specular_reflect=0.3, transparency=0.4, transmit_filter=0.8, fresnel_effect=True, IOR=1.6,
+                        mirror_color=(1.0, 0.95, 0.9, 1.0), diffuse_brdf="oren_nayar", sigma=0.25)
+    order = ["glossy", "aniso", "coated", "glass", "gdiff", "glass2", "mirror", "shiny"]
+    v0, f0 = icosphere(subdiv)
+    yi.startGeometry()
+    add_mesh(yi, *quad((-9, -6, 0), (9, -6, 0), (9, 8, 0), (-9, 8, 0)), M["ground"], bulk=False)
+    add_mesh(yi, *quad((-9, 8, 0), (9, 8, 0), (9, 8, 6), (-9, 8, 6)), M["ground"], bulk=False)
+    for i, name in enumerate(order):
+        cx = (i % 4 - 1.5) * 2.4
+        cy = 0.0 if i < 4 else 3.2
+        r = 1.0 if i < 4 else 0.9
+        V = (v0 * r + np.array([cx, cy, r + 0.02])).astype(np.float32)
+        add_mesh(yi, V, f0, M[name], normals=v0.astype(np.float32), smooth_angle=181.0)
+    yi.endGeometry()
+    create(yi, "light", "sun", type="sunlight", direction=(0.4, -0.5, 0.8), color=(1.0, 0.95, 0.9, 1.0), power=0.9,
+           angle=1.0, samples=sun_samples)
+    create(yi, "light", "pt", type="pointlight", **{"from": (-4.0, -3.0, 5.0)}, color=(0.9, 0.9, 1.0, 1.0), power=18.0)
+    create(yi, "light", "area", type="arealight", corner=(2.0, -3.0, 5.0), point1=(2.0, -1.5, 5.0), point2=(3.5, -3.0, 5.0),
+           color=(1.0, 0.85, 0.7, 1.0), power=20.0, samples=area_samples)
+    create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -9.5, 4.2)}, to=(0.0, 1.0, 0.8),
+           up=(0.0, -9.5, 5.2), resx=width, resy=height, focal=1.3)
+    create(yi, "background", "bg", type="constant", color=(0.35, 0.45, 0.7, 1.0))
+    ip = dict(type=integrator, raydepth=raydepth)
+    if integrator == "pathtracing":
+        ip.update(bounces=bounces, path_samples=1)
+    ip.update(integ_params or {})
+    create(yi, "integrator", "default", **ip)
+    std_volintegr(yi)
+    set_render(yi, width, height, spp=spp, threads=threads, **render_extra)
+    return len(order) * len(f0) + 4

@@ -144,8 +144,8 @@ int yref_render(yref_ctx *c, float *rgba, int w, int h, const yref_callbacks *)
     memset(rgba, 0, sizeof(float) * 4 * (size_t)w * h);
     gTimer.addEvent("yref_render");
     gTimer.start("yref_render");
-    silentBar_t bar;
-    c->yi->render(out, &bar);
+    // imageFilm_t takes ownership of the progress bar and deletes it (imagefilm.cc:175,637-641): heap-allocate
+    c->yi->render(out, new silentBar_t());
     gTimer.stop("yref_render");
     c->render_s = gTimer.getTime("rendert");           // integrator.cc:146-167
     if (!c->yi->film) { c->err = "reference render failed (setupScene)"; return 0; }

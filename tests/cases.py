@@ -1,0 +1,71 @@
+"""The parity cases shared by the golden generator, the CPU (emulator) tests and the GPU tests.
+Each case = (name, scene builder, kwargs); every builder only talks to a yafrayInterface_t-shaped object."""
+import numpy as np
+
+from core_b200 import scenes
+
+IMAGE_CASES = {
+    # BASELINE.json configs[0] (reduced): Cornell box, shinydiffuse + mirror component, area light, directlighting
+    "c1_cornell_direct": (scenes.cornell_box, dict(width=64, height=64, spp=4, light_samples=4, mirror_box=True)),
+    "c1_cornell_path": (scenes.cornell_box, dict(width=64, height=64, spp=4, light_samples=4, mirror_box=True,
+                                                 integrator="pathtracing", integ_params=dict(bounces=4, path_samples=1))),
+    "c1_cornell_gauss": (scenes.cornell_box, dict(width=48, height=48, spp=3, light_samples=2, mirror_box=False,
+                                                  filter_type="gauss", pixelwidth=2.0)),
+    # configs[1] (reduced): icosphere field, sun + point light, pathtracing 4 bounces
+    "c2_field_path": (scenes.icosphere_field, dict(n_tris=20000, subdiv=2, width=96, height=54, spp=2, bounces=4)),
+    "c2_field_flat_direct": (scenes.icosphere_field, dict(n_tris=6000, subdiv=1, width=64, height=36, spp=2, smooth=False,
+                                                          integrator="directlighting")),
+    # configs[2] (reduced): triangle soup, directlighting + ambient occlusion (IntersectS stress)
+    "c3_soup_ao": (scenes.triangle_soup, dict(n_tris=3000, width=64, height=64, spp=1, ao_samples=8, ao_distance=0.3)),
+    # configs[3] (reduced): glossy / coated glossy / glass, sun + point + area lights, pathtracing 8 bounces
+    "c4_materials_path": (scenes.materials_scene, dict(width=80, height=45, spp=2, bounces=8)),
+    "c4_materials_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting")),
+    "c4_materials_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
+                                                          integ_params=dict(transpShad=True, shadowDepth=4))),
+}
+
+RAY_CASES = {
+    "rays_cornell": (scenes.cornell_box, dict(width=32, height=32, spp=1)),
+    "rays_field": (scenes.icosphere_field, dict(n_tris=20000, subdiv=2, width=64, height=36, spp=1)),
+    "rays_soup": (scenes.triangle_soup, dict(n_tris=5000, width=32, height=32, spp=1)),
+}
+
+
+def ray_batch(name, n=4096, seed=7):
+    """Deterministic mixed ray set: directions from scene-dependent origins, finite and infinite tmax."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    o = rng.uniform(-1.0, 1.0, (n, 3))
+    if name == "rays_field":
+        o = o * np.array([8.0, 8.0, 1.0]) + np.array([0.0, 0.0, 2.0])
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, 0:3] = o
+    rays[:, 3] = np.where(rng.uniform(size=n) < 0.5, 0.0, 0.0005)
+    rays[:, 4:7] = d
+    rays[:, 7] = np.where(rng.uniform(size=n) < 0.5, -1.0, rng.uniform(0.2, 6.0, n))
+    return rays
+
+
+def compare_images(a, b):
+    """mean relative error over RGB, PSNR (peak = max(1, ref max)), max alpha difference"""
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    rel = np.abs(a[..., :3] - b[..., :3]).sum() / max(a[..., :3].sum(), 1e-12)
+    mse = ((a[..., :3] - b[..., :3]) ** 2).mean()
+    peak = max(1.0, a[..., :3].max())
+    psnr = 10 * np.log10(peak * peak / max(mse, 1e-30))
+    return rel, psnr, np.abs(a[..., 3] - b[..., 3]).max()
+
+
+def compare_hits(ref, got, ties=None):
+    """ref/got structured arrays (prim,t,b1,b2). Returns (id mismatch fraction excluding t-ties, max rel t err, max bary err)."""
+    n = len(ref)
+    same = ref["prim"] == got["prim"]
+    both = (ref["prim"] >= 0) & (got["prim"] >= 0)
+    tie = both & ~same & (np.abs(ref["t"] - got["t"]) <= 1e-5 * np.maximum(np.abs(ref["t"]), 1e-6))
+    bad = ~same & ~tie
+    ok = same & both
+    terr = np.max(np.abs(ref["t"][ok] - got["t"][ok]) / np.maximum(np.abs(ref["t"][ok]), 1e-6)) if ok.any() else 0.0
+    berr = max(np.max(np.abs(ref["b1"][ok] - got["b1"][ok])), np.max(np.abs(ref["b2"][ok] - got["b2"][ok]))) if ok.any() else 0.0
+    return bad.sum() / max(n, 1), float(terr), float(berr), int(tie.sum())
