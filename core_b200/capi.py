@@ -81,6 +81,7 @@ _PRODUCT_ONLY = {
     "film_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "get_stats": (C.c_int, [C.POINTER(Stats)]),
     "cuda_stream": (C.c_void_p, []),
+    "touch_geometry": (None, []),
 }
 EXPORTED_SYMBOLS = (["create", "version"] + sorted(_CTX_FUNCS) + sorted(_PRODUCT_ONLY))
 

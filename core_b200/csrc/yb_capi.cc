@@ -108,6 +108,8 @@ int yb200_update_scene(yb200_ctx *ctx)
     GUARD_END(0)
 }
 
+void yb200_touch_geometry(yb200_ctx *ctx) { CTX.geomChanged = true; }
+
 int yb200_render_film(yb200_ctx *ctx, float *dev_film, int rank, int world, const yb200_callbacks *cb)
 {
     GUARD_BEGIN

@@ -175,5 +175,8 @@ class YafrayInterface:
         self._call("get_stats", C.byref(s))
         return {k: getattr(s, k) for k, _ in capi.Stats._fields_}
 
+    def touchGeometry(self):
+        self._call("touch_geometry")
+
     def cudaStream(self):
         return self._call("cuda_stream")

@@ -101,6 +101,9 @@ void yb200_abort(yb200_ctx *c);                              /* yafrayinterface.
 
 /* ---- scene update only (scene_t::update, scene.cc:748-850): flatten + GPU BVH build */
 int yb200_update_scene(yb200_ctx *c);
+/* mark the geometry as changed (what every geometry call does through state.changes |= C_GEOM, scene.cc:288):
+ * the next render/update re-flattens, re-uploads and rebuilds the BVH.  Used to time the full host-to-host path. */
+void yb200_touch_geometry(yb200_ctx *c);
 
 /* ---- parity / benchmark hook for triKdTree_t::Intersect / IntersectS / IntersectTS
  *      through scene_t::intersect / isShadowed (scene.cc:852-928, kdtree.cc:675-1108).

@@ -1,0 +1,87 @@
+"""The drop-in boundary: libyb200.so exports exactly what include/yb200.h declares, mirrors the reference's error
+behaviour, and fails LOUDLY (no CPU fallback) for unsupported features or when no CUDA device exists."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import refapi
+from core_b200 import capi, scenes
+from core_b200.interface import YafrayInterface
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    h = open(os.path.join(ROOT, "include", "yb200.h")).read()
+    return sorted(set(re.findall(r"\b(yb200_[a-z_0-9]+)\s*\(", h)))
+
+
+@pytest.mark.skipif(not os.path.exists(capi.LIB_PATH), reason="libyb200.so not built")
+def test_product_library_exports_every_declared_symbol():
+    lib = C.CDLL(capi.LIB_PATH)
+    for s in header_symbols():
+        assert hasattr(lib, s), s
+    assert len(header_symbols()) >= 45
+
+
+@pytest.mark.skipif(not os.path.exists(capi.LIB_PATH), reason="libyb200.so not built")
+def test_product_has_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    yi = YafrayInterface()
+    assert "EMULATOR" not in yi.getVersion()
+    scenes.cornell_box(yi, 8, 8, spp=1)
+    with pytest.raises(RuntimeError, match="no CUDA device|CPU fallback"):
+        yi.render(8, 8)
+
+
+def test_missing_library_fails_loudly(tmp_path):
+    with pytest.raises(RuntimeError, match="missing"):
+        capi.CLib(str(tmp_path / "nope.so"))
+
+
+@pytest.mark.skipif(not refapi.have_emu(), reason="host emulator could not be built")
+class TestHostLogic:
+    def test_state_machine_mirrors_scene_t(self):
+        yi = refapi.EmuInterface()
+        yi.setVerbosityMute()
+        yi.startScene(0)
+        assert not yi.startTriMesh(1, 3, 1, False)          # not inside startGeometry (scene.cc:268)
+        assert yi.startGeometry() and not yi.startGeometry()
+        assert yi.addVertex(0, 0, 0) == -1                   # no object open (scene.cc:524)
+        assert yi.getNextFreeID() == 2 ** 31 - 1 and yi.getNextFreeID() == 2 ** 31 - 2
+        m = scenes.create(yi, "material", "m", type="shinydiffusemat")
+        assert yi.startTriMesh(5, 3, 1, False)
+        assert [yi.addVertex(*p) for p in ((0, 0, 0), (1, 0, 0), (0, 1, 0))] == [0, 1, 2]
+        assert yi.addTriangle(0, 1, 2, m) and not yi.addTriangle(0, 1, 2, 12345)
+        assert yi.endTriMesh() and not yi.endTriMesh() and yi.endGeometry()
+        assert not yi.startScene(1)                          # universal mode unsupported
+
+    def test_unsupported_features_fail(self):
+        yi = refapi.EmuInterface()
+        yi.setVerbosityMute()
+        yi.startScene(0)
+        for kind, ty in (("material", "blend_mat"), ("material", "rough_glass"), ("light", "spotlight"),
+                         ("camera", "orthographic"), ("background", "sunsky"), ("integrator", "photonmapping")):
+            yi.paramsClearAll(); yi.paramsSetString("type", ty)
+            assert getattr(yi, "create" + kind.capitalize())("x") == 0
+            assert "not supported" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat"); yi.paramsSetString("diffuse_shader", "tex")
+        assert yi.createMaterial("withnodes") == 0 and "shader" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "glass"); yi.paramsSetFloat("dispersion_power", 0.1)
+        assert yi.createMaterial("disp") == 0
+        assert yi.createTexture("t") == 0 and yi.createVolumeRegion("v") == 0
+        yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat")
+        assert yi.createMaterial("dup") != 0 and yi.createMaterial("dup") == 0     # name clash (environment.cc:226)
+
+    def test_render_requires_volume_integrator_none(self):
+        yi = refapi.EmuInterface()
+        yi.setVerbosityMute()
+        scenes.cornell_box(yi, 8, 8, spp=1)
+        yi.paramsSetString("volintegrator_name", "missing")
+        with pytest.raises(RuntimeError):
+            yi.render(8, 8)

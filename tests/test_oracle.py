@@ -1,0 +1,82 @@
+"""The oracle (plain-C restatement, oracle/yb_oracle.c) against the golden vectors generated from the compiled
+reference (tests/golden/make_golden.py), and against the live reference when oracle/_ref is present."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import oracle_port as op
+import refapi
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_qmc_and_hash_bit_exact():
+    k = np.load(os.path.join(G, "kat.npz"))
+    L = op.lib()
+    n, r = k["n_idx"], k["r_idx"]
+    assert np.array_equal(np.array([L.yo_fnv(int(v)) for v in n], np.uint32), k["fnv"])
+    assert np.array_equal(np.array([L.yo_ri_vdc(int(a), int(b)) for a, b in zip(n, r)], np.float32), k["vdc"])
+    assert np.array_equal(np.array([L.yo_ri_s(int(a), int(b)) for a, b in zip(n, r)], np.float32), k["ris"])
+    assert np.array_equal(np.array([L.yo_ri_lp(int(a), int(b)) for a, b in zip(n, r)], np.float32), k["rlp"])
+    scr = np.array([[L.yo_scr_halton(int(d), int(v)) for v in n] for d in range(1, 50)])
+    assert np.array_equal(scr, k["scr"])          # FP64, same operation order: bit-exact
+    for bi, base in enumerate((2, 3, 5)):
+        for si, st in enumerate(k["hal_starts"]):
+            got = np.array([L.yo_halton(base, int(st), j + 1) for j in range(16)], np.float32)
+            assert np.array_equal(got, k["hal"][bi, si])
+
+
+def test_fast_math():
+    k = np.load(os.path.join(G, "kat.npz"))
+    L = op.lib()
+    # the reference is built with -ffast-math (reassociation allowed): tolerance 4 ulp-ish relative, stated here
+    s = np.array([L.yo_fsin(float(v)) for v in k["trig_x"]], np.float32)
+    c = np.array([L.yo_fcos(float(v)) for v in k["trig_x"]], np.float32)
+    assert np.max(np.abs(s - k["fsin"])) <= 2e-6
+    assert np.max(np.abs(c - k["fcos"])) <= 2e-6
+    p = np.array([L.yo_fpow(float(a), float(b)) for a, b in zip(k["pow_a"], k["pow_b"])], np.float32)
+    ok = np.isfinite(k["fpow"]) & (np.abs(k["fpow"]) > 1e-30)
+    assert np.max(np.abs(p[ok] - k["fpow"][ok]) / np.abs(k["fpow"][ok])) <= 2e-5
+
+
+def test_faure_tables_match_generated_include():
+    import ctypes as C
+    L = op.lib()
+    inc = open(os.path.join(op.ROOT, "core_b200", "csrc", "yb_faure.inc")).read()
+    flat = inc.split("yb_faure_flat[")[1].split("{")[1].split("}")[0]
+    flat = [int(v) for v in flat.replace("\n", "").split(",") if v.strip()]
+    pos = 0
+    buf = (C.c_int * 256)()
+    for d in range(50):
+        b = L.yo_faure(d, buf)
+        assert list(buf[:b]) == flat[pos:pos + b]
+        pos += b
+
+
+@pytest.mark.parametrize("name", list(cases.RAY_CASES))
+def test_bruteforce_against_golden_kdtree_results(name):
+    fn, kw = cases.RAY_CASES[name]
+    rec = op.Recorder()
+    fn(rec, **kw)
+    tris = rec.triangles()
+    g = np.load(os.path.join(G, name + ".npz"))
+    got, ties = op.closest(tris, g["rays"])
+    bad, terr, berr, ntie = cases.compare_hits(g["closest"], got)
+    assert bad <= 1e-3, (bad, ntie)           # kd-tree vs brute force: only edge/tie cases may differ
+    assert terr <= 1e-5 and berr <= 1e-4
+    sh = op.shadow(tris, g["rays"])
+    assert np.mean(sh != g["shadow"]) <= 1e-3
+
+
+@pytest.mark.skipif(not refapi.have_ref(), reason="oracle/_ref not built")
+def test_port_against_live_reference():
+    import ctypes as C
+    R = refapi.ref_lib().lib
+    R.yref_scr_halton.restype = C.c_double; R.yref_scr_halton.argtypes = [C.c_int, C.c_uint]
+    L = op.lib()
+    rng = np.random.Generator(np.random.PCG64(5))
+    for d in range(1, 50):
+        for n in rng.integers(0, 2 ** 32, 20, dtype=np.uint64):
+            assert L.yo_scr_halton(d, int(n)) == R.yref_scr_halton(d, int(n))
