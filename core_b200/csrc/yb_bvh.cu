@@ -3,7 +3,7 @@
 // Pipeline (every step a kernel; only the level loop of the collapse talks to the host):
 //   bounds -> 63-bit Morton codes of triangle centroids -> radix sort -> binary radix tree (Karras 2012)
 //   -> bottom-up AABB fit -> top-down collapse to 8-wide nodes (open the child with the largest surface area
-//   until 8 slots are used; subtrees of <= 4 triangles become leaf children) with octant-ordered slots and
+//   until 8 slots are used; subtrees of <= 3 triangles become leaf children) with octant-ordered slots and
 //   8-bit quantised child boxes -> triangles re-laid out leaf by leaf (48 B each).
 // The reference's SAH kd-tree is replaced, not restated; only its query semantics are kept.
 #include "yb_scene.h"
@@ -133,7 +133,7 @@ YB_KERNEL(k_fit, FitArgs)
 }
 
 // ---- collapse to 8-wide
-#define YB_MAX_LEAF 4
+#define YB_MAX_LEAF 3
 struct CollapseItem { int32_t bnode; uint32_t wnode; };
 struct CollapseArgs {
     const CollapseItem *in;
@@ -249,12 +249,12 @@ YB_KERNEL(k_collapse, CollapseArgs)
         int cnt = cref_count(a, ref);
         if (ref >= 0 && cnt > YB_MAX_LEAF) {
             nd.imask |= (uint8_t)(1u << s);
-            nd.meta[s] = (uint8_t)(0xE0u | kInt);
+            nd.meta[s] = (uint8_t)(0x20u | (24u + (uint32_t)s));
             CollapseItem o; o.bnode = ref; o.wnode = childBase + kInt;
             a.out[itemBase + kInt] = o;
             ++kInt;
         } else {
-            nd.meta[s] = (uint8_t)(((uint32_t)cnt << 5) | triOff);
+            nd.meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | triOff);
             int f = ref < 0 ? ~ref : a.first[ref];
             for (int j = 0; j < cnt; ++j) {
                 uint32_t src = a.idx[f + j], dst = triBase + triOff + (uint32_t)j;

@@ -87,6 +87,7 @@ struct Context {
     volatile int abortFlag;
     // device-side scene
     DevBuf<BvhNode> d_nodes; DevBuf<f4> d_tri_v; DevBuf<v3> d_tri_n; DevBuf<Material> d_materials; DevBuf<Light> d_lights;
+    DevBuf<uint32_t> d_traceCounter;   // ray-fetch counter of the persistent traversal kernels
     uint32_t nTris, nNodes, bvhDepth; bool haveNormals;
     v3 boundLo, boundHi;
     SceneDev sc;                     // filled by updateScene / setupRender

@@ -129,7 +129,7 @@ YB_HD bool bvh_traverse(const SceneDev &sc, v3 from, v3 dir, float tlo, float th
             const float tn = fmaxf_(fmaxf_(t0x, t0y), fmaxf_(t0z, tlo));
             const float tf = fminf_(fminf_(t1x, t1y), fminf_(t1z, thi)) * 1.0000005f;
             if (tn <= tf) {
-                if ((meta & 0xe0u) == 0xe0u) childHits |= 1u << ((uint32_t)s ^ oct);
+                if ((meta & 0x1fu) >= 24u) childHits |= 1u << ((uint32_t)s ^ oct);
                 else leafHits |= 1u << s;
             }
         }
@@ -138,15 +138,15 @@ YB_HD bool bvh_traverse(const SceneDev &sc, v3 from, v3 dir, float tlo, float th
             const int s = 31 - yb_clz(leafHits);
             leafHits &= ~(1u << s);
             const uint32_t meta = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
-            const uint32_t first = n1.y + (meta & 0x1fu), cnt = meta >> 5;
+            const uint32_t first = n1.y + (meta & 0x1fu), cnt = (uint32_t)yb_popc(meta >> 5);
             for (uint32_t ti = first; ti < first + cnt; ++ti) {
                 const f4 A = ld16f(sc.tri_v + 3 * ti), B = ld16f(sc.tri_v + 3 * ti + 1), C = ld16f(sc.tri_v + 3 * ti + 2);
                 float t, u, v;
                 if (!tri_intersect(v3(A.x, A.y, A.z), v3(B.x, B.y, B.z), v3(C.x, C.y, C.z), from, dir, t, u, v)) continue;
                 if (!(t < thi && t >= tlo)) continue;
                 if (MODE == TRACE_CLOSEST) {
-                    // exact t ties: keep the lower global primitive index (deterministic; the reference keeps the
-                    // first-tested triangle of its kd-tree order, kdtree.cc:772 — documented tie rule)
+                    // strict `<`: on exact t ties the first-tested triangle stays, as in the reference (kdtree.cc:772);
+                    // test order differs between a kd-tree and a BVH, so ties are compared by t, not by id
                     thi = t; hit.tri = (int32_t)ti; hit.t = t; hit.b1 = u; hit.b2 = v; found = true;
                 } else if (MODE == TRACE_SHADOW) {
                     hit.tri = (int32_t)ti; hit.t = t; hit.b1 = u; hit.b2 = v;

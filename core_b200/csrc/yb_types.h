@@ -111,7 +111,9 @@ struct alignas(16) BvhNode {
     uint8_t imask;                    // bit s set: child slot s is an internal node
     uint32_t childBase;               // index of the first internal child (children are stored contiguously in slot order)
     uint32_t triBase;                 // index of the first triangle of this node's leaf children
-    uint8_t meta[8];                  // 0: empty; internal: 0xE0 | k (k-th internal child); leaf: (ntri << 5) | offset from triBase
+    uint8_t meta[8];                  // 0: empty; internal child in slot s: 0x20 | (24 + s); leaf: (unary tri count 1|3|7) << 5 | offset
+                                      // from triBase (0..23).  So (meta >> 5) << (meta & 31) is the child's bit field in a 32-bit hit mask:
+                                      // bits 0..23 = triangles of the node, bits 24..31 = internal children by slot (Ylitie et al. 2017)
     uint8_t qlox[8], qloy[8], qloz[8], qhix[8], qhiy[8], qhiz[8];
 };
 static_assert(sizeof(BvhNode) == 80, "BvhNode must be 80 bytes");
