@@ -611,7 +611,6 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
         const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;
-        (void)useFast;
         StageTimer tc(s), tsh(s), tsd(s), tf(s);
         uint64_t raysClosest = 0, raysShadow = 0; double msClosest = 0, msShadow = 0, msShade = 0, msFilm = 0;
         const uint64_t launches0 = g_kernel_launches;
@@ -634,13 +633,11 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                 a.outCap = (uint32_t)std::min<size_t>(whole ? poolCap : poolCap - top, 0xffffffffu);
                 rt_memset(rb.counters.p, 0, 4 * sizeof(uint32_t), s);
                 tc.start();
-#ifndef YB_HOSTEMU
                 if (useFast) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task); j.n = (uint32_t)M;
                     j.counter = rb.counters.p + 2; j.out = a.hits; j.acc = a.acc; j.nNodes = c.sc.nNodes;
                     launch_trace_fast<false, OUT_HITS>(j, s);
                 } else
-#endif
                     k_trace_closest((uint32_t)M, a, s);
                 tc.stop();
                 tsd.start(); k_shade((uint32_t)M, a, s); tsd.stop();
@@ -648,13 +645,11 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                 rt_d2h(cnt, rb.counters.p, sizeof(cnt), s);
                 if (cnt[0] > a.outCap || cnt[1] > a.shadowCap) throw RtError("render: internal queue overflow");
                 tsh.start();
-#ifndef YB_HOSTEMU
                 if (useFast && !I.trShad) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask); j.n = cnt[1];
                     j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes;
                     launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
                 } else
-#endif
                     k_trace_shadow(cnt[1], a, s);
                 tsh.stop();
                 raysClosest += M; raysShadow += cnt[1];
@@ -693,11 +688,9 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
     TraceArgs ta; ta.sc = c.sc; ta.rays = (const Ray *)d_rays; ta.out = d_out; ta.shadowDepth = shadow_depth;
     const size_t step = (size_t)1 << 30;
     const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;
-    (void)useFast;
     for (size_t o = 0; o < n; o += step) {
         const uint32_t m = (uint32_t)std::min(step, n - o);
         TraceArgs t2 = ta; t2.rays = ta.rays + o;
-#ifndef YB_HOSTEMU
         if (useFast && mode != TRACE_TSHADOW) {
             c.d_traceCounter.reserve(4);
             FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)(ta.rays + o); j.stride = sizeof(Ray); j.n = m;
@@ -706,7 +699,6 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
             else { j.out = (int32_t *)d_out + o; launch_trace_fast<true, OUT_SHADOW_FLAG>(j, c.stream); }
             continue;
         }
-#endif
         if (mode == TRACE_CLOSEST) { t2.out = (ClosestOut *)d_out + o; k_batch_closest(m, t2, c.stream); }
         else if (mode == TRACE_SHADOW) { t2.out = (int32_t *)d_out + o; k_batch_shadow(m, t2, c.stream); }
         else { t2.out = (TShadowOut *)d_out + o; k_batch_tshadow(m, t2, c.stream); }

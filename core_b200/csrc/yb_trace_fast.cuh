@@ -12,12 +12,67 @@
 //    free), the rest spill to local memory;
 //  * triangles: three 128-bit loads, the reference's Moeller-Trumbore operation order without FMA contraction.
 #pragma once
-#ifndef YB_HOSTEMU
 #include "yb_trace.cuh"
+#include <stdio.h>
+
+#ifdef YB_HOSTEMU
+// ---- emulator shims: the kernel body below runs as ONE lane that owns a whole (1-wide) warp, so that the very same
+//      traversal code can be checked against the golden kd-tree results on a machine without a GPU (tests/emu).
+#include <cmath>
+namespace yb { namespace emu {
+struct uint2_ { uint32_t x, y; };
+struct uint4_ { uint32_t x, y, z, w; };
+struct float4_ { float x, y, z, w; };
+struct int4_ { int x, y, z, w; };
+struct tidx_ { unsigned x; };
+inline uint32_t byte_perm(uint32_t x, uint32_t y, uint32_t s)
+{
+    uint64_t src = ((uint64_t)y << 32) | x;
+    uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) {
+        uint32_t sel = (s >> (4 * i)) & 0xf;
+        uint32_t b = (uint32_t)(src >> (8 * (sel & 7))) & 0xff;
+        if (sel & 8) b = (b & 0x80) ? 0xff : 0x00;
+        r |= b << (8 * i);
+    }
+    return r;
+}
+} }
+#define uint2 yb::emu::uint2_
+#define uint4 yb::emu::uint4_
+#define float4 yb::emu::float4_
+#define int4 yb::emu::int4_
+#define make_uint2(a, b) (yb::emu::uint2_{(uint32_t)(a), (uint32_t)(b)})
+#define make_float4(a, b, c, d) (yb::emu::float4_{(a), (b), (c), (d)})
+#define make_int4(a, b, c, d) (yb::emu::int4_{(a), (b), (c), (d)})
+#define __global__
+#define __shared__ static
+#define __device__
+#define __forceinline__ inline
+#define __launch_bounds__(a, b)
+#define __syncwarp()
+#define __ballot_sync(m, p) ((p) ? 1u : 0u)
+#define __shfl_sync(m, v, l) (v)
+#define __popc(x) __builtin_popcount(x)
+#define __ffs(x) __builtin_ffs((int)(x))
+#define __clz(x) ((x) ? __builtin_clz((unsigned)(x)) : 32)
+#define __ldg(p) (*(p))
+#define __byte_perm(x, y, s) yb::emu::byte_perm((x), (y), (s))
+#define __uint_as_float(u) yb::i2f((int32_t)(u))
+#define __float_as_uint(f) ((uint32_t)yb::f2i(f))
+#define __int_as_float(i) yb::i2f(i)
+#define __float_as_int(f) yb::f2i(f)
+#define atomicAdd(p, v) yb::emu_fetch_add((p), (v))
+#define YB_FULLMASK 1u
+#define YB_TB 1
+static yb::emu::tidx_ threadIdx = {0};
+#else
+#define YB_FULLMASK 0xffffffffu
+#define YB_TB 128            // threads per block
+#endif
 
 namespace yb {
 
-#define YB_TB 128            // threads per block
 #define YB_SSTACK 8          // shared-memory stack entries per lane
 #define YB_LSTACK (YB_STACK_SIZE - YB_SSTACK)
 #define YB_REFILL_IDLE 8     // refill when at least this many lanes are idle (or all are)
@@ -35,6 +90,17 @@ struct FastJob {
     uint32_t nNodes;
 };
 
+// replicate the msb of every byte over the byte (prmt sign mode; __byte_perm only honours 3 selector bits per nibble)
+__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
+{
+#ifdef YB_HOSTEMU
+    return yb::emu::byte_perm(x, 0u, 0xba98u);
+#else
+    uint32_t r;
+    asm("prmt.b32 %0, %1, 0, 0x0000ba98;" : "=r"(r) : "r"(x));
+    return r;
+#endif
+}
 __device__ __forceinline__ float plane_f(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x3F800000u, sel)); }
 
 template <bool ANYHIT, int OUT>
@@ -42,8 +108,8 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
 {
     __shared__ uint2 sstack[YB_SSTACK][YB_TB];
     uint2 lstack[YB_LSTACK];
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;   // 0 in the emulator
+    const unsigned FULL = YB_FULLMASK;
 
     bool active = false, exhausted = false;
     uint32_t rayIdx = 0;
@@ -148,7 +214,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                         for (int h = 0; h < 2; ++h) {
                             const uint32_t meta4 = h ? n1.w : n1.z;
                             const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                            const uint32_t inner_mask4 = __byte_perm(is_inner4 << 3, 0u, 0xba98u);     // 0xff where the child is internal
+                            const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);             // 0xff where the child is internal
                             const uint32_t bit_index4 = (meta4 ^ ((oct * 0x01010101u) & inner_mask4)) & 0x1f1f1f1fu;
                             const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
                             const uint32_t wnx = h ? nX1 : nX0, wfx = h ? fX1 : fX0, wny = h ? nY1 : nY0, wfy = h ? fY1 : fY0, wnz = h ? nZ1 : nZ0, wfz = h ? fZ1 : fZ0;
@@ -166,6 +232,9 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                                 }
                             }
                         }
+#ifdef YB_TRACE_DEBUG
+                        if (rayIdx == 0) printf("DBG node %u slot %u hitmask %08x imask %02x cb %u tb %u A %g %g %g B %g %g %g thi %g meta %08x %08x\n", nodeIdx, slot, hitmask, n0.w >> 24, n1.x, n1.y, Ax, Ay, Az, Bx, By, Bz, thi, n1.z, n1.w);
+#endif
                         ng = make_uint2(n1.x, (hitmask & 0xff000000u) | (n0.w >> 24));
                         tg = make_uint2(n1.y, hitmask & 0x00ffffffu);
                     }
@@ -179,6 +248,9 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                     const float4 B = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 1));
                     const float4 C = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 2));
                     float t, u, v;
+#ifdef YB_TRACE_DEBUG
+                    if (rayIdx == 0) printf("DBG tri %u\n", ti);
+#endif
                     if (tri_intersect(v3(A.x, A.y, A.z), v3(B.x, B.y, B.z), v3(C.x, C.y, C.z), v3(ox, oy, oz), v3(dx, dy, dz), t, u, v) && t < thi && t >= tlo) {
                         if (ANYHIT) { hitTri = (int)ti; done = true; }
                         else { thi = t; hitTri = (int)ti; hitT = t; hitU = u; hitV = v; }
@@ -206,6 +278,12 @@ template <bool ANYHIT, int OUT>
 static void launch_trace_fast(const FastJob &job, rt_stream s)
 {
     if (job.n == 0) return;
+#ifdef YB_HOSTEMU
+    *job.counter = 0;
+    k_trace_fast<ANYHIT, OUT>(job);
+    g_kernel_launches++;
+    return;
+#else
     YB_CUDA_CHECK(cudaMemsetAsync(job.counter, 0, sizeof(uint32_t), s));
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -216,7 +294,19 @@ static void launch_trace_fast(const FastJob &job, rt_stream s)
     k_trace_fast<ANYHIT, OUT><<<blocks, YB_TB, 0, s>>>(job);
     YB_CUDA_CHECK(cudaGetLastError());
     g_kernel_launches++;
+#endif
 }
 
 }  // namespace yb
+#ifdef YB_HOSTEMU
+#undef uint2
+#undef uint4
+#undef float4
+#undef int4
+#undef atomicAdd
+#undef __ldg
+#undef __global__
+#undef __shared__
+#undef __device__
+#undef __forceinline__
 #endif
