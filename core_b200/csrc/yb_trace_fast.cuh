@@ -77,6 +77,11 @@ namespace yb {
 #define YB_LSTACK (YB_STACK_SIZE - YB_SSTACK)
 #define YB_REFILL_IDLE 8     // refill when at least this many lanes are idle (or all are)
 
+#if defined(YB_HOSTEMU) && defined(YB_TRACE_STATS)
+static uint64_t g_stat_nodes = 0, g_stat_tris = 0, g_stat_rays = 0;
+struct StatPrinter { ~StatPrinter() { if (g_stat_rays) fprintf(stderr, "TRACE STATS: rays %llu nodes/ray %.2f tris/ray %.2f\n", (unsigned long long)g_stat_rays, (double)g_stat_nodes / g_stat_rays, (double)g_stat_tris / g_stat_rays); } };
+static StatPrinter g_stat_printer;
+#endif
 enum { OUT_HITS = 0, OUT_SHADOW_ACC = 1, OUT_SHADOW_FLAG = 2, OUT_CLOSEST_PRIM = 3 };
 
 struct FastJob {
@@ -193,6 +198,9 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                         }
                         const uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
                         const uint32_t nodeIdx = ng.x + (uint32_t)__popc(ng.y & ((1u << slot) - 1u) & 0xffu);
+#if defined(YB_HOSTEMU) && defined(YB_TRACE_STATS)
+                        g_stat_nodes++;
+#endif
                         const uint4 *np = (const uint4 *)(job.nodes + nodeIdx);
                         const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
                         // t = (1 + q 2^-15) * A + B per plane; A = cell * 2^15 / dir, B = (p - o) / dir - A; planes widened by 1/64 cell
@@ -232,9 +240,6 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                                 }
                             }
                         }
-#ifdef YB_TRACE_DEBUG
-                        if (rayIdx == 0) printf("DBG node %u slot %u hitmask %08x imask %02x cb %u tb %u A %g %g %g B %g %g %g thi %g meta %08x %08x\n", nodeIdx, slot, hitmask, n0.w >> 24, n1.x, n1.y, Ax, Ay, Az, Bx, By, Bz, thi, n1.z, n1.w);
-#endif
                         ng = make_uint2(n1.x, (hitmask & 0xff000000u) | (n0.w >> 24));
                         tg = make_uint2(n1.y, hitmask & 0x00ffffffu);
                     }
@@ -248,8 +253,8 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                     const float4 B = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 1));
                     const float4 C = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 2));
                     float t, u, v;
-#ifdef YB_TRACE_DEBUG
-                    if (rayIdx == 0) printf("DBG tri %u\n", ti);
+#if defined(YB_HOSTEMU) && defined(YB_TRACE_STATS)
+                    g_stat_tris++;
 #endif
                     if (tri_intersect(v3(A.x, A.y, A.z), v3(B.x, B.y, B.z), v3(C.x, C.y, C.z), v3(ox, oy, oz), v3(dx, dy, dz), t, u, v) && t < thi && t >= tlo) {
                         if (ANYHIT) { hitTri = (int)ti; done = true; }
@@ -279,6 +284,9 @@ static void launch_trace_fast(const FastJob &job, rt_stream s)
 {
     if (job.n == 0) return;
 #ifdef YB_HOSTEMU
+#ifdef YB_TRACE_STATS
+    g_stat_rays += job.n;
+#endif
     *job.counter = 0;
     k_trace_fast<ANYHIT, OUT>(job);
     g_kernel_launches++;
