@@ -85,3 +85,16 @@ class TestHostLogic:
         yi.paramsSetString("volintegrator_name", "missing")
         with pytest.raises(RuntimeError):
             yi.render(8, 8)
+
+
+def test_getyafray_library_exports_the_reference_entry_point():
+    """libyb200_yafray.so exports `getYafray` (yafrayinterface.cc:386-392) and the object it returns answers
+    getVersion through the C++ vtable of include/yb200_interface.hpp (no device work)."""
+    import ctypes
+    import os
+    so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "core_b200", "libyb200_yafray.so")
+    assert os.path.exists(so), "run __graft_entry__.build()"
+    lib = ctypes.CDLL(so)
+    lib.getYafray.restype = ctypes.c_void_p
+    obj = lib.getYafray()
+    assert obj

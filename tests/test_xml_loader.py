@@ -1,0 +1,93 @@
+"""yb200-xml (tools/yb200_xml.cc + include/yb200_interface.hpp): the reference's XML dialect (xmlparser.cc:222-709)
+read through the C++ yafrayInterface_t-shaped host class must give the same frame, bit for bit, as feeding the same
+scene through the API — the C++ host side adds no arithmetic of its own.  CPU: emulator build; GPU: product build."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import cases
+import refapi
+from core_b200.xmlwriter import XmlWriter
+
+ROOT = refapi.ROOT
+EMU_XML = os.path.join(ROOT, "tests", "emu", "yb200-xml-emu")
+GPU_XML = os.path.join(ROOT, "core_b200", "bin", "yb200-xml")
+NAMES = ["c1_cornell_direct", "c2_field_flat_direct", "c4_materials_path"]
+
+
+def _write_scene(name, path, digits=None):
+    fn, kw = cases.IMAGE_CASES[name]
+    w = XmlWriter(path, digits=digits)
+    fn(w, **kw)
+    w.render()
+    return kw["width"], kw["height"]
+
+
+def _run(exe, xml, out):
+    r = subprocess.run([exe, "-vl", "1", "-o", out, xml], capture_output=True, text=True, timeout=600)
+    return r
+
+
+@pytest.mark.skipif(not (refapi.have_emu() and os.path.exists(EMU_XML)), reason="emulator xml loader not built")
+@pytest.mark.parametrize("name", NAMES)
+def test_xml_equals_api_emu(name, tmp_path):
+    xml, out = str(tmp_path / "s.xml"), str(tmp_path / "o.f32")
+    W, H = _write_scene(name, xml)
+    r = _run(EMU_XML, xml, out)
+    assert r.returncode == 0, r.stderr
+    img = np.fromfile(out, dtype=np.float32).reshape(H, W, 4)
+    fn, kw = cases.IMAGE_CASES[name]
+    yi = refapi.EmuInterface()
+    fn(yi, **kw)
+    api = yi.render(W, H)
+    assert np.array_equal(img, api)
+
+
+@pytest.mark.skipif(not (refapi.have_emu() and os.path.exists(EMU_XML)), reason="emulator xml loader not built")
+def test_xml_reference_digits_close_to_golden(tmp_path):
+    # with the reference writer's 6 significant digits (xmlinterface.cc:112) geometry moves in the last bits;
+    # the frame must still agree with the reference's API-fed golden frame far inside the north_star bar
+    name = "c1_cornell_direct"
+    xml, out = str(tmp_path / "s.xml"), str(tmp_path / "o.f32")
+    W, H = _write_scene(name, xml, digits=6)
+    r = _run(EMU_XML, xml, out)
+    assert r.returncode == 0, r.stderr
+    img = np.fromfile(out, dtype=np.float32).reshape(H, W, 4)
+    ref = np.load(os.path.join(os.path.dirname(__file__), "golden", "img_" + name + ".npz"))["img"]
+    rel, psnr, da = cases.compare_images(ref, img)
+    assert rel <= 1e-2 and psnr >= 40.0, (rel, psnr)
+
+
+@pytest.mark.skipif(not (refapi.have_emu() and os.path.exists(EMU_XML)), reason="emulator xml loader not built")
+def test_xml_unsupported_fails_loudly(tmp_path):
+    xml = tmp_path / "bad.xml"
+    xml.write_text('<?xml version="1.0"?>\n<scene type="triangle">\n<material name="m">\n\t<type sval="rough_glass"/>\n'
+                   '</material>\n<render>\n\t<width ival="8"/>\n\t<height ival="8"/>\n</render>\n</scene>\n')
+    r = _run(EMU_XML, str(xml), str(tmp_path / "o.f32"))
+    assert r.returncode != 0
+    assert "rough_glass" in r.stderr
+    assert not os.path.exists(tmp_path / "o.f32")
+    # malformed document
+    xml.write_text("<scene><material name='m'></scene>")
+    assert _run(EMU_XML, str(xml), str(tmp_path / "o.f32")).returncode != 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", NAMES)
+def test_xml_equals_api_gpu(name, tmp_path):
+    from core_b200.interface import YafrayInterface
+    assert os.path.exists(GPU_XML), "core_b200/bin/yb200-xml missing: run __graft_entry__.build()"
+    xml, out = str(tmp_path / "s.xml"), str(tmp_path / "o.f32")
+    W, H = _write_scene(name, xml)
+    r = _run(GPU_XML, xml, out)
+    assert r.returncode == 0, r.stderr
+    img = np.fromfile(out, dtype=np.float32).reshape(H, W, 4)
+    fn, kw = cases.IMAGE_CASES[name]
+    yi = YafrayInterface()
+    fn(yi, **kw)
+    api = yi.render(W, H)
+    # float atomics in the film make the summation order run-dependent: equal within rounding, not bitwise
+    rel, psnr, da = cases.compare_images(api, img)
+    assert rel <= 1e-5 and psnr >= 100.0, (rel, psnr)

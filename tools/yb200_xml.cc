@@ -1,0 +1,380 @@
+// yb200-xml — command-line renderer for the reference's XML scene dialect on top of libyb200.so.
+//
+// Role of thebounty-xml (src/xml_loader/xml-loader.cc:38-300) + parse_xml_file (src/yafraycore/xmlparser.cc:113-160):
+// read a <scene> document, feed it through the yafrayInterface_t-shaped host class (include/yb200_interface.hpp),
+// render, write the frame.  The grammar accepted is the one xmlparser.cc:222-709 accepts (and xmlInterface_t writes):
+//   <scene type="triangle">  material|light|camera|background|integrator|texture|object|volumeregion[name]
+//   with one child element per parameter (ival|fval|bval|sval, x/y/z point, r/g/b/a colour) and <list_element>
+//   sub-maps; <mesh id vertices faces has_orco has_uv type> with <p>, <n>, <uv>, <f>, <set_material>;
+//   <smooth ID angle>; <instance base_object_id><transform m00..m33/></instance>; <render> parameter map.
+// SAX events come from expat (libxml2 is what the reference uses; it is not needed for this dialect).
+//
+// usage: yb200-xml [-o out.(tga|pfm|f32)] [-dev N] [-vl 0..3] [-w W -h H] scene.xml
+#include "../include/yb200_interface.hpp"
+#include <expat.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <map>
+#include <string>
+#include <vector>
+
+namespace {
+
+using yb200::yafrayInterface_t;
+
+struct Value {                      // parameter_t (include/core_api/params.h:40-94)
+    enum Kind { NONE, INT, FLOAT, BOOL, STRING, POINT, COLOR } kind = NONE;
+    int i = 0; double f = 0; bool b = false; std::string s; double p[3] = {0, 0, 0}; float c[4] = {0, 0, 0, 0};
+};
+typedef std::vector<std::pair<std::string, Value> > ValueMap;
+
+// xmlparser.cc:222-256: one attribute named ival/fval/bval/sval is a scalar; otherwise single-letter attributes
+// x,y,z make a point and r,g,b,a a colour (whichever letter comes last decides, as in the reference loop)
+Value parseValue(const char **a)
+{
+    Value v;
+    if (!a || !a[0]) return v;
+    if (!a[2]) {
+        std::string n(a[0]);
+        if (n == "ival") { v.kind = Value::INT; v.i = atoi(a[1]); return v; }
+        if (n == "fval") { v.kind = Value::FLOAT; v.f = atof(a[1]); return v; }
+        if (n == "bval") { v.kind = Value::BOOL; v.b = !strcmp(a[1], "true"); return v; }
+        if (n == "sval") { v.kind = Value::STRING; v.s = a[1]; return v; }
+    }
+    for (int n = 0; a[n]; n += 2) {
+        if (a[n][0] == 0 || a[n][1] != 0) continue;
+        switch (a[n][0]) {
+            case 'x': v.p[0] = atof(a[n + 1]); v.kind = Value::POINT; break;
+            case 'y': v.p[1] = atof(a[n + 1]); v.kind = Value::POINT; break;
+            case 'z': v.p[2] = atof(a[n + 1]); v.kind = Value::POINT; break;
+            case 'r': v.c[0] = (float)atof(a[n + 1]); v.kind = Value::COLOR; break;
+            case 'g': v.c[1] = (float)atof(a[n + 1]); v.kind = Value::COLOR; break;
+            case 'b': v.c[2] = (float)atof(a[n + 1]); v.kind = Value::COLOR; break;
+            case 'a': v.c[3] = (float)atof(a[n + 1]); v.kind = Value::COLOR; break;
+        }
+    }
+    return v;
+}
+
+void applyValue(yafrayInterface_t &yi, const std::string &key, const Value &v)
+{
+    switch (v.kind) {
+        case Value::INT: yi.paramsSetInt(key.c_str(), v.i); break;
+        case Value::FLOAT: yi.paramsSetFloat(key.c_str(), v.f); break;
+        case Value::BOOL: yi.paramsSetBool(key.c_str(), v.b); break;
+        case Value::STRING: yi.paramsSetString(key.c_str(), v.s.c_str()); break;
+        case Value::POINT: yi.paramsSetPoint(key.c_str(), v.p[0], v.p[1], v.p[2]); break;
+        case Value::COLOR: yi.paramsSetColor(key.c_str(), v.c[0], v.c[1], v.c[2], v.c[3]); break;
+        default: break;
+    }
+}
+
+struct Loader {
+    enum State { DOCUMENT, SCENE, PARAMMAP, PARAMLIST, RENDER, MESH, INSTANCE, SKIP };
+    struct Frame { State st; int level; };
+    yafrayInterface_t &yi;
+    std::vector<Frame> stack;
+    int level = 0;
+    int errors = 0;
+    // current scene element
+    std::string elemKind, elemName;
+    ValueMap render;
+    // mesh state (mesh_dat_t, xmlparser.cc:296-304)
+    bool meshOrco = false, meshUV = false;
+    const yb200::material_t *meshMat = nullptr;
+    std::map<std::string, const yb200::material_t *> materials;   // renderEnvironment_t::getMaterial (environment.cc:162-167)
+    unsigned instanceBase = 0;
+
+    explicit Loader(yafrayInterface_t &i) : yi(i) { stack.push_back({DOCUMENT, 0}); }
+    void push(State s) { stack.push_back({s, level}); }
+    void pop() { stack.pop_back(); }
+    void error(const std::string &m) { std::fprintf(stderr, "ERROR: XMLParser: %s\n", m.c_str()); ++errors; }
+    void warn(const std::string &m) { std::fprintf(stderr, "WARNING: XMLParser: %s\n", m.c_str()); }
+
+    void start(const char *el, const char **at)
+    {
+        ++level;
+        std::string e(el);
+        switch (stack.back().st) {
+        case DOCUMENT:
+            if (e != "scene") { warn("skipping <" + e + ">"); push(SKIP); break; }
+            {
+                int type = 0;
+                for (int n = 0; at[n]; n += 2) if (!strcmp(at[n], "type") && !strcmp(at[n + 1], "universal")) type = 1;
+                if (!yi.startScene(type)) error(std::string("startScene failed: ") + yi.lastError());
+            }
+            push(SCENE);
+            break;
+        case SCENE: startScene(e, at); break;
+        case PARAMMAP:
+            if (e == "list_element") { yi.paramsPushList(); push(PARAMLIST); }
+            else { applyValue(yi, e, parseValue(at)); push(SKIP); }
+            break;
+        case PARAMLIST: applyValue(yi, e, parseValue(at)); push(SKIP); break;
+        case RENDER: render.push_back(std::make_pair(e, parseValue(at))); push(SKIP); break;
+        case MESH: startMesh(e, at); push(SKIP); break;
+        case INSTANCE:
+            if (e == "transform") {
+                yb200::matrix4x4_t m;
+                for (int n = 0; at[n]; n += 2)
+                    if (at[n][0] == 'm' && at[n][1] >= '0' && at[n][1] <= '3' && at[n][2] >= '0' && at[n][2] <= '3' && !at[n][3])
+                        m[at[n][1] - '0'][at[n][2] - '0'] = (float)atof(at[n + 1]);
+                if (!yi.addInstance(instanceBase, m)) error(std::string("addInstance failed: ") + yi.lastError());
+            }
+            push(SKIP);
+            break;
+        case SKIP: push(SKIP); break;
+        }
+    }
+
+    void end(const char *el)
+    {
+        std::string e(el);
+        Frame f = stack.back();
+        switch (f.st) {
+        case PARAMMAP: finishElement(); break;
+        case PARAMLIST: yi.paramsEndList(); break;
+        case MESH:
+            if (!yi.endTriMesh()) error("invalid scene state on endTriMesh()");
+            if (!yi.endGeometry()) error("invalid scene state on endGeometry()");
+            break;
+        default: break;
+        }
+        pop();
+        --level;
+    }
+
+    void startScene(const std::string &e, const char **at)
+    {
+        if (e == "material" || e == "integrator" || e == "light" || e == "texture" || e == "camera" || e == "background" ||
+            e == "object" || e == "volumeregion") {
+            if (!at[0] || strcmp(at[0], "name")) { error("scene element <" + e + "> needs a 'name' attribute first"); push(SKIP); return; }
+            elemKind = e; elemName = at[1];
+            yi.paramsClearAll();
+            push(PARAMMAP);
+        } else if (e == "mesh") {
+            int vertices = 0, faces = 0, type = 0, id = -1;
+            meshOrco = meshUV = false; meshMat = nullptr;
+            for (int n = 0; at[n]; n += 2) {
+                std::string k(at[n]);
+                if (k == "has_orco") meshOrco = !strcmp(at[n + 1], "true");
+                else if (k == "has_uv") meshUV = !strcmp(at[n + 1], "true");
+                else if (k == "vertices") vertices = atoi(at[n + 1]);
+                else if (k == "faces") faces = atoi(at[n + 1]);
+                else if (k == "type") type = atoi(at[n + 1]);
+                else if (k == "id") id = atoi(at[n + 1]);
+            }
+            if (!yi.startGeometry()) error("invalid scene state on startGeometry()");
+            unsigned uid = id == -1 ? yi.getNextFreeID() : (unsigned)id;
+            if (!yi.startTriMesh(uid, vertices, faces, meshOrco, meshUV, type)) error(std::string("startTriMesh failed: ") + yi.lastError());
+            push(MESH);
+        } else if (e == "smooth") {
+            unsigned id = 0; double angle = 181;
+            for (int n = 0; at[n]; n += 2) {
+                if (!strcmp(at[n], "ID")) id = (unsigned)atoi(at[n + 1]);
+                else if (!strcmp(at[n], "angle")) angle = atof(at[n + 1]);
+            }
+            yi.startGeometry();
+            if (!yi.smoothMesh(id, angle)) error("couldn't smooth mesh ID = " + std::to_string(id));
+            yi.endGeometry();
+            push(SKIP);
+        } else if (e == "render") {
+            push(RENDER);
+        } else if (e == "instance") {
+            instanceBase = (unsigned)-1;
+            for (int n = 0; at[n]; n += 2) if (!strcmp(at[n], "base_object_id")) instanceBase = (unsigned)atoi(at[n + 1]);
+            push(INSTANCE);
+        } else if (e == "curve") {
+            error("<curve> meshes are not supported by the B200 path");
+            push(SKIP);
+        } else {
+            warn("skipping unrecognized scene element <" + e + ">");
+            push(SKIP);
+        }
+    }
+
+    void startMesh(const std::string &e, const char **at)
+    {
+        if (e == "p") {
+            double p[3] = {0, 0, 0}, o[3] = {0, 0, 0};
+            for (int n = 0; at[n]; n += 2) {
+                const char *k = at[n];
+                if (k[0] == 'o' && k[1] >= 'x' && k[1] <= 'z' && !k[2]) o[k[1] - 'x'] = atof(at[n + 1]);
+                else if (k[0] >= 'x' && k[0] <= 'z' && !k[1]) p[k[0] - 'x'] = atof(at[n + 1]);
+            }
+            // the reference stores float point3d_t before addVertex (xmlparser.cc:497-500)
+            if (meshOrco) yi.addVertex((float)p[0], (float)p[1], (float)p[2], (float)o[0], (float)o[1], (float)o[2]);
+            else yi.addVertex((float)p[0], (float)p[1], (float)p[2]);
+        } else if (e == "n") {
+            double nrm[3] = {0, 0, 0}; int got = 0;
+            for (int n = 0; at[n]; n += 2)
+                if (at[n][0] >= 'x' && at[n][0] <= 'z' && !at[n][1]) { nrm[at[n][0] - 'x'] = atof(at[n + 1]); ++got; }
+            if (got == 3) yi.addNormal((float)nrm[0], (float)nrm[1], (float)nrm[2]);
+        } else if (e == "f") {
+            int a = 0, b = 0, c = 0, ua = 0, ub = 0, uc = 0;
+            for (int n = 0; at[n]; n += 2) {
+                const char *k = at[n];
+                if (!k[1]) { if (k[0] == 'a') a = atoi(at[n + 1]); else if (k[0] == 'b') b = atoi(at[n + 1]); else if (k[0] == 'c') c = atoi(at[n + 1]); }
+                else if (!strcmp(k, "uv_a")) ua = atoi(at[n + 1]);
+                else if (!strcmp(k, "uv_b")) ub = atoi(at[n + 1]);
+                else if (!strcmp(k, "uv_c")) uc = atoi(at[n + 1]);
+            }
+            bool ok = meshUV ? yi.addTriangle(a, b, c, ua, ub, uc, meshMat) : yi.addTriangle(a, b, c, meshMat);
+            if (!ok) error(std::string("addTriangle failed: ") + yi.lastError());
+        } else if (e == "uv") {
+            float u = 0, v = 0;
+            for (int n = 0; at[n]; n += 2) { if (at[n][0] == 'u') u = (float)atof(at[n + 1]); else if (at[n][0] == 'v') v = (float)atof(at[n + 1]); }
+            yi.addUV(u, v);
+        } else if (e == "set_material") {
+            std::map<std::string, const yb200::material_t *>::iterator it = at[0] ? materials.find(at[1]) : materials.end();
+            meshMat = it == materials.end() ? nullptr : it->second;
+            if (!meshMat) warn("unknown material!");
+        }
+    }
+
+    void finishElement()          // endEl_parammap (xmlparser.cc:626-684)
+    {
+        const char *n = elemName.c_str();
+        bool ok = true;
+        if (elemKind == "material") {
+            const yb200::material_t *m = yi.createMaterial(n);
+            if (m) materials[elemName] = m; else ok = false;
+        } else if (elemKind == "integrator") ok = yi.createIntegrator(n) != 0;
+        else if (elemKind == "light") ok = yi.createLight(n) != 0;
+        else if (elemKind == "texture") ok = yi.createTexture(n) != 0;
+        else if (elemKind == "camera") ok = yi.createCamera(n) != 0;
+        else if (elemKind == "background") ok = yi.createBackground(n) != 0;
+        else if (elemKind == "object") ok = yi.createObject(n) != 0;
+        else if (elemKind == "volumeregion") ok = yi.createVolumeRegion(n) != 0;
+        if (!ok) error("creating " + elemKind + " '" + elemName + "' failed: " + yi.lastError());
+        yi.paramsClearAll();
+    }
+};
+
+void XMLCALL onStart(void *u, const XML_Char *el, const XML_Char **at) { ((Loader *)u)->start(el, at); }
+void XMLCALL onEnd(void *u, const XML_Char *el) { ((Loader *)u)->end(el); }
+
+bool writePFM(const char *path, const float *rgba, int w, int h)
+{
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return false;
+    std::fprintf(f, "PF\n%d %d\n-1.0\n", w, h);
+    std::vector<float> row((size_t)w * 3);
+    for (int y = h - 1; y >= 0; --y) {          // PFM rows go bottom-up
+        for (int x = 0; x < w; ++x) for (int k = 0; k < 3; ++k) row[3 * x + k] = rgba[(size_t)(x + w * y) * 4 + k];
+        std::fwrite(row.data(), sizeof(float), row.size(), f);
+    }
+    std::fclose(f);
+    return true;
+}
+
+bool writeTGA(const char *path, const float *rgba, int w, int h)
+{
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return false;
+    unsigned char hd[18] = {0};
+    hd[2] = 2; hd[12] = w & 255; hd[13] = (w >> 8) & 255; hd[14] = h & 255; hd[15] = (h >> 8) & 255; hd[16] = 32; hd[17] = 0x28;  // top-left origin, 8 alpha bits
+    std::fwrite(hd, 1, 18, f);
+    std::vector<unsigned char> row((size_t)w * 4);
+    for (int y = 0; y < h; ++y) {
+        for (int x = 0; x < w; ++x) {
+            const float *p = rgba + (size_t)(x + w * y) * 4;
+            const int order[4] = {2, 1, 0, 3};
+            for (int k = 0; k < 4; ++k) {
+                float v = p[order[k]]; v = v < 0.f ? 0.f : (v > 1.f ? 1.f : v);
+                row[4 * x + k] = (unsigned char)std::lround(v * 255.f);
+            }
+        }
+        std::fwrite(row.data(), 1, row.size(), f);
+    }
+    std::fclose(f);
+    return true;
+}
+
+struct ConsoleBar : yb200::progressBar_t {
+    int total = 1, done_ = 0, lastPct = -1;
+    void init(int t) override { total = t > 0 ? t : 1; }
+    void update(int s = 1) override {
+        done_ += s; int pct = 100 * done_ / total;
+        if (pct != lastPct) { std::fprintf(stderr, "\rrendering: %3d%%", pct); lastPct = pct; }
+    }
+    void done() override { std::fprintf(stderr, "\rrendering: 100%%\n"); }
+    void setTag(const char *) override {}
+};
+
+}  // namespace
+
+int main(int argc, char **argv)
+{
+    std::string out = "yb200.tga", scenePath;
+    int dev = 0, vl = 2, ow = 0, oh = 0;
+    for (int i = 1; i < argc; ++i) {
+        std::string a(argv[i]);
+        if (a == "-o" && i + 1 < argc) out = argv[++i];
+        else if (a == "-dev" && i + 1 < argc) dev = atoi(argv[++i]);
+        else if (a == "-vl" && i + 1 < argc) vl = atoi(argv[++i]);
+        else if (a == "-w" && i + 1 < argc) ow = atoi(argv[++i]);
+        else if (a == "-h" && i + 1 < argc) oh = atoi(argv[++i]);
+        else if (a[0] != '-') scenePath = a;
+        else { std::fprintf(stderr, "usage: yb200-xml [-o out.(tga|pfm|f32)] [-dev N] [-vl 0..3] [-w W -h H] scene.xml\n"); return 2; }
+    }
+    if (scenePath.empty()) { std::fprintf(stderr, "yb200-xml: no scene file\n"); return 2; }
+    FILE *f = std::fopen(scenePath.c_str(), "rb");
+    if (!f) { std::fprintf(stderr, "yb200-xml: cannot open %s\n", scenePath.c_str()); return 1; }
+
+    yafrayInterface_t yi;
+    yi.setVerbosityLevel(vl);
+    if (!yi.setDevice(dev)) { std::fprintf(stderr, "yb200-xml: %s\n", yi.lastError()); return 1; }
+    Loader ld(yi);
+    XML_Parser xp = XML_ParserCreate(NULL);
+    XML_SetUserData(xp, &ld);
+    XML_SetElementHandler(xp, onStart, onEnd);
+    std::vector<char> buf(1 << 20);
+    for (;;) {
+        size_t n = std::fread(buf.data(), 1, buf.size(), f);
+        if (XML_Parse(xp, buf.data(), (int)n, n == 0) == XML_STATUS_ERROR) {
+            std::fprintf(stderr, "yb200-xml: %s at line %lu\n", XML_ErrorString(XML_GetErrorCode(xp)), (unsigned long)XML_GetCurrentLineNumber(xp));
+            return 1;
+        }
+        if (n == 0) break;
+    }
+    XML_ParserFree(xp);
+    std::fclose(f);
+    if (ld.errors) { std::fprintf(stderr, "yb200-xml: %d error(s) while loading; not rendering\n", ld.errors); return 1; }
+
+    // render parameters: the <render> map becomes the current paraMap (xml-loader.cc:226-262)
+    yi.paramsClearAll();
+    int w = 320, h = 240;      // defaults of renderEnvironment_t::setupScene (environment.cc:607-608)
+    for (size_t i = 0; i < ld.render.size(); ++i) {
+        if (ld.render[i].first == "width" && ld.render[i].second.kind == Value::INT) w = ld.render[i].second.i;
+        if (ld.render[i].first == "height" && ld.render[i].second.kind == Value::INT) h = ld.render[i].second.i;
+        applyValue(yi, ld.render[i].first, ld.render[i].second);
+    }
+    if (ow > 0) w = ow;
+    if (oh > 0) h = oh;
+    yi.paramsSetInt("width", w);
+    yi.paramsSetInt("height", h);
+
+    std::vector<float> img((size_t)w * h * 4, 0.f);
+    yb200::memoryIO_t mem(w, h, img.data());
+    yi.render(mem, vl >= 3 ? new ConsoleBar() : 0);
+    if (!yi.renderSucceeded()) { std::fprintf(stderr, "yb200-xml: render failed: %s\n", yi.lastError()); return 1; }
+    yb200_stats st;
+    if (yi.getStats(st))
+        std::fprintf(stderr, "yb200-xml: %llu tris, %llu rays, build %.1f ms, render %.1f ms\n", (unsigned long long)st.n_triangles,
+                     (unsigned long long)(st.rays_closest + st.rays_shadow), st.build_ms, st.render_ms);
+    const std::string ext = out.size() > 4 ? out.substr(out.size() - 4) : "";
+    bool ok;
+    if (ext == ".pfm") ok = writePFM(out.c_str(), img.data(), w, h);
+    else if (ext == ".f32") {           // raw memoryIO_t buffer: w*h*4 float32, (x + w*y)*4
+        FILE *o = std::fopen(out.c_str(), "wb");
+        ok = o && std::fwrite(img.data(), sizeof(float), img.size(), o) == img.size();
+        if (o) std::fclose(o);
+    } else ok = writeTGA(out.c_str(), img.data(), w, h);
+    if (!ok) {
+        std::fprintf(stderr, "yb200-xml: cannot write %s\n", out.c_str());
+        return 1;
+    }
+    return 0;
+}
