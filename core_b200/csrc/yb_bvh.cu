@@ -288,7 +288,10 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     DevBuf<uint64_t> keys; DevBuf<uint32_t> idx;
     keys.reserve(n); idx.reserve(n);
     MortonArgs ma; ma.v = in_v; ma.keys = keys.p; ma.idx = idx.p; ma.lo = boundLo;
-    ma.inv = v3(ext.x > 0 ? 1.f / ext.x : 0.f, ext.y > 0 ? 1.f / ext.y : 0.f, ext.z > 0 ? 1.f / ext.z : 0.f);
+    // one scale for all three axes (cubic Morton cells): per-axis normalisation would cut a flat scene into thin
+    // full-width slabs along its short axis at the top of the tree
+    const float extMax = fmaxf_(ext.x, fmaxf_(ext.y, ext.z));
+    ma.inv = v3(extMax > 0 ? 1.f / extMax : 0.f);
     k_morton(n, ma, s);
 #ifndef YB_HOSTEMU
     {
@@ -322,6 +325,63 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
         FitArgs fa; fa.v = in_v; fa.idx = idx.p; fa.n = (int32_t)n; fa.left = left.p; fa.right = right.p; fa.parent = parent.p; fa.flag = flag.p; fa.nlo = nlo.p; fa.nhi = nhi.p;
         k_fit(n, fa, s);
     }
+#if defined(YB_HOSTEMU) && defined(YB_EXPERIMENT_SAH)
+    if (getenv("YB_SAH") && nInt) {   // experiment: binned-SAH binary tree instead of the radix tree (host only)
+        std::vector<v3> tlo(n), thi(n), cen(n);
+        for (uint32_t i = 0; i < n; ++i) { tri_bounds(in_v, i, tlo[i], thi[i]); cen[i] = (tlo[i] + thi[i]) * 0.5f; }
+        uint32_t *ix = idx.p;
+        for (uint32_t i = 0; i < n; ++i) ix[i] = i;
+        int32_t nextNode = 0;
+        struct Rec {
+            static int32_t build(uint32_t lo, uint32_t hi, uint32_t *ix, const std::vector<v3> &tlo, const std::vector<v3> &thi, const std::vector<v3> &cen,
+                                 int32_t *left, int32_t *right, int32_t *first, int32_t *last, v3 *nlo, v3 *nhi, int32_t &nextNode) {
+                if (lo == hi) return ~(int32_t)lo;
+                const int32_t me = nextNode++;
+                v3 blo(1e30f), bhi(-1e30f), clo(1e30f), chi(-1e30f);
+                for (uint32_t i = lo; i <= hi; ++i) { uint32_t t = ix[i];
+                    blo = v3(fminf_(blo.x, tlo[t].x), fminf_(blo.y, tlo[t].y), fminf_(blo.z, tlo[t].z));
+                    bhi = v3(fmaxf_(bhi.x, thi[t].x), fmaxf_(bhi.y, thi[t].y), fmaxf_(bhi.z, thi[t].z));
+                    clo = v3(fminf_(clo.x, cen[t].x), fminf_(clo.y, cen[t].y), fminf_(clo.z, cen[t].z));
+                    chi = v3(fmaxf_(chi.x, cen[t].x), fmaxf_(chi.y, cen[t].y), fmaxf_(chi.z, cen[t].z)); }
+                nlo[me] = blo; nhi[me] = bhi; first[me] = (int32_t)lo; last[me] = (int32_t)hi;
+                const int NB = 32; float bestCost = 1e30f; int bestAx = -1, bestB = -1;
+                for (int ax = 0; ax < 3; ++ax) {
+                    const float c0 = ax == 0 ? clo.x : ax == 1 ? clo.y : clo.z, c1 = ax == 0 ? chi.x : ax == 1 ? chi.y : chi.z;
+                    if (!(c1 > c0)) continue;
+                    v3 bl[NB], bh[NB]; int cnt[NB];
+                    for (int b = 0; b < NB; ++b) { bl[b] = v3(1e30f); bh[b] = v3(-1e30f); cnt[b] = 0; }
+                    const float sc = NB / (c1 - c0);
+                    for (uint32_t i = lo; i <= hi; ++i) { uint32_t t = ix[i]; float c = ax == 0 ? cen[t].x : ax == 1 ? cen[t].y : cen[t].z;
+                        int b = (int)((c - c0) * sc); if (b >= NB) b = NB - 1; if (b < 0) b = 0; cnt[b]++;
+                        bl[b] = v3(fminf_(bl[b].x, tlo[t].x), fminf_(bl[b].y, tlo[t].y), fminf_(bl[b].z, tlo[t].z));
+                        bh[b] = v3(fmaxf_(bh[b].x, thi[t].x), fmaxf_(bh[b].y, thi[t].y), fmaxf_(bh[b].z, thi[t].z)); }
+                    float ra[NB]; int rc[NB]; v3 al(1e30f), ah(-1e30f); int c = 0;
+                    for (int b = NB - 1; b > 0; --b) { if (cnt[b]) { al = v3(fminf_(al.x, bl[b].x), fminf_(al.y, bl[b].y), fminf_(al.z, bl[b].z)); ah = v3(fmaxf_(ah.x, bh[b].x), fmaxf_(ah.y, bh[b].y), fmaxf_(ah.z, bh[b].z)); } c += cnt[b]; ra[b] = c ? box_area(al, ah) : 0.f; rc[b] = c; }
+                    al = v3(1e30f); ah = v3(-1e30f); c = 0;
+                    for (int b = 0; b < NB - 1; ++b) { if (cnt[b]) { al = v3(fminf_(al.x, bl[b].x), fminf_(al.y, bl[b].y), fminf_(al.z, bl[b].z)); ah = v3(fmaxf_(ah.x, bh[b].x), fmaxf_(ah.y, bh[b].y), fmaxf_(ah.z, bh[b].z)); } c += cnt[b];
+                        if (c == 0 || rc[b + 1] == 0) continue;
+                        float cost = box_area(al, ah) * c + ra[b + 1] * rc[b + 1];
+                        if (cost < bestCost) { bestCost = cost; bestAx = ax; bestB = b; } }
+                }
+                uint32_t mid;
+                if (bestAx < 0) mid = (lo + hi) / 2;
+                else {
+                    const float c0 = bestAx == 0 ? clo.x : bestAx == 1 ? clo.y : clo.z, c1 = bestAx == 0 ? chi.x : bestAx == 1 ? chi.y : chi.z;
+                    const float sc = NB / (c1 - c0);
+                    uint32_t *m = std::partition(ix + lo, ix + hi + 1, [&](uint32_t t) { float c = bestAx == 0 ? cen[t].x : bestAx == 1 ? cen[t].y : cen[t].z; int b = (int)((c - c0) * sc); if (b >= NB) b = NB - 1; if (b < 0) b = 0; return b <= bestB; });
+                    mid = (uint32_t)(m - ix) - 1;
+                    if (mid < lo || mid >= hi) mid = (lo + hi) / 2;
+                }
+                int32_t L = build(lo, mid, ix, tlo, thi, cen, left, right, first, last, nlo, nhi, nextNode);
+                int32_t R = build(mid + 1, hi, ix, tlo, thi, cen, left, right, first, last, nlo, nhi, nextNode);
+                left[me] = L; right[me] = R;
+                return me;
+            }
+        };
+        Rec::build(0, n - 1, ix, tlo, thi, cen, left.p, right.p, first.p, last.p, nlo.p, nhi.p, nextNode);
+        fprintf(stderr, "YB_SAH: built %d internal nodes\n", nextNode);
+    }
+#endif
     // collapse, level by level
     const uint32_t nodeCap = n / 2 + 16;       // every internal wide node has >= 2 children with > YB_MAX_LEAF/… tris; generous bound
     nodes.reserve(nodeCap); out_v.reserve(3 * (size_t)n);

@@ -546,6 +546,13 @@ static size_t env_size(const char *name, size_t dflt)
     return (size_t)strtoull(e, 0, 10);
 }
 
+// tuning knob of the traversal kernels' postponed triangle phase (yb_trace_fast.cuh); 1 = never postpone
+static uint32_t tri_threshold()
+{
+    static const uint32_t v = (uint32_t)env_size("YB200_TRI_THRESHOLD", 8);
+    return v < 1u ? 1u : (v > 32u ? 32u : v);
+}
+
 bool render_film_device(Context &c, float *d_film, int rank, int world, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user)
 {
     if (!c.sceneReady) return c.fail("render: scene not updated");
@@ -635,7 +642,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                 tc.start();
                 if (useFast) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task); j.n = (uint32_t)M;
-                    j.counter = rb.counters.p + 2; j.out = a.hits; j.acc = a.acc; j.nNodes = c.sc.nNodes;
+                    j.counter = rb.counters.p + 2; j.out = a.hits; j.acc = a.acc; j.nNodes = c.sc.nNodes; j.triThreshold = tri_threshold();
                     launch_trace_fast<false, OUT_HITS>(j, s);
                 } else
                     k_trace_closest((uint32_t)M, a, s);
@@ -647,7 +654,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                 tsh.start();
                 if (useFast && !I.trShad) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask); j.n = cnt[1];
-                    j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes;
+                    j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; j.triThreshold = tri_threshold();
                     launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
                 } else
                     k_trace_shadow(cnt[1], a, s);
@@ -694,7 +701,7 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
         if (useFast && mode != TRACE_TSHADOW) {
             c.d_traceCounter.reserve(4);
             FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)(ta.rays + o); j.stride = sizeof(Ray); j.n = m;
-            j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes;
+            j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; j.triThreshold = tri_threshold();
             if (mode == TRACE_CLOSEST) { j.out = (ClosestOut *)d_out + o; launch_trace_fast<false, OUT_CLOSEST_PRIM>(j, c.stream); }
             else { j.out = (int32_t *)d_out + o; launch_trace_fast<true, OUT_SHADOW_FLAG>(j, c.stream); }
             continue;

@@ -93,6 +93,7 @@ struct FastJob {
     void *out;               // OUT_HITS: Hit[n]; OUT_SHADOW_FLAG: int32[n]; OUT_CLOSEST_PRIM: {prim,t,b1,b2}[n]
     f4 *acc;                 // OUT_SHADOW_ACC: ShadowTask{ray, c, sid}: acc[sid].rgb += c when unoccluded
     uint32_t nNodes;
+    uint32_t triThreshold;   // triangle phase runs when this many lanes (or as many as still have node work) hold a triangle group
 };
 
 // replicate the msb of every byte over the byte (prmt sign mode; __byte_perm only honours 3 selector bits per nibble)
@@ -177,102 +178,110 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
         // ------------------------------------------------------------ a burst of traversal steps
 #pragma unroll 1
         for (int burst = 0; burst < 6; ++burst) {
-            if (active) {
-                bool done = false;
-                // ---- node step
-                if (tg.y == 0u) {
-                    if (ng.y <= 0x00ffffffu) {                  // current node group exhausted: pop
-                        if (sp == 0) done = true;
-                        else {
-                            --sp;
-                            const uint2 e = (sp < YB_SSTACK) ? sstack[sp][threadIdx.x] : lstack[sp - YB_SSTACK];
-                            if (e.y > 0x00ffffffu) ng = e; else { tg = e; ng.y = 0u; }
-                        }
+            bool done = false;
+            // ---- node phase: lanes without pending triangles pop / descend one node
+            if (active && tg.y == 0u) {
+                if (ng.y <= 0x00ffffffu) {                  // current node group exhausted: pop
+                    if (sp == 0) done = true;
+                    else {
+                        --sp;
+                        const uint2 e = (sp < YB_SSTACK) ? sstack[sp][threadIdx.x] : lstack[sp - YB_SSTACK];
+                        if (e.y > 0x00ffffffu) ng = e; else { tg = e; ng.y = 0u; }
                     }
-                    if (!done && tg.y == 0u) {
-                        const int bit = 31 - __clz((int)ng.y);
-                        ng.y &= ~(1u << bit);
-                        if (ng.y > 0x00ffffffu) {               // siblings still pending: push the rest of the group
-                            if (sp < YB_SSTACK) sstack[sp][threadIdx.x] = ng; else lstack[sp - YB_SSTACK] = ng;
-                            ++sp;
-                        }
-                        const uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
-                        const uint32_t nodeIdx = ng.x + (uint32_t)__popc(ng.y & ((1u << slot) - 1u) & 0xffu);
+                }
+                if (!done && tg.y == 0u) {
+                    const int bit = 31 - __clz((int)ng.y);
+                    ng.y &= ~(1u << bit);
+                    if (ng.y > 0x00ffffffu) {               // siblings still pending: push the rest of the group
+                        if (sp < YB_SSTACK) sstack[sp][threadIdx.x] = ng; else lstack[sp - YB_SSTACK] = ng;
+                        ++sp;
+                    }
+                    const uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
+                    const uint32_t nodeIdx = ng.x + (uint32_t)__popc(ng.y & ((1u << slot) - 1u) & 0xffu);
 #if defined(YB_HOSTEMU) && defined(YB_TRACE_STATS)
-                        g_stat_nodes++;
+                    g_stat_nodes++;
 #endif
-                        const uint4 *np = (const uint4 *)(job.nodes + nodeIdx);
-                        const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-                        // t = (1 + q 2^-15) * A + B per plane; A = cell * 2^15 / dir, B = (p - o) / dir - A; planes widened by 1/64 cell
-                        const float Ax = __uint_as_float(((n0.w & 0xffu) + 15u) << 23) * idx_;
-                        const float Ay = __uint_as_float((((n0.w >> 8) & 0xffu) + 15u) << 23) * idy;
-                        const float Az = __uint_as_float((((n0.w >> 16) & 0xffu) + 15u) << 23) * idz;
-                        const float Bx = (__uint_as_float(n0.x) - ox) * idx_ - Ax;
-                        const float By = (__uint_as_float(n0.y) - oy) * idy - Ay;
-                        const float Bz = (__uint_as_float(n0.z) - oz) * idz - Az;
-                        const float wx = fabsf(Ax) * 4.76837158e-7f, wy = fabsf(Ay) * 4.76837158e-7f, wz = fabsf(Az) * 4.76837158e-7f;   // 2^-21 |A| = cell/64
-                        const float Bnx = Bx - wx, Bfx = Bx + wx, Bny = By - wy, Bfy = By + wy, Bnz = Bz - wz, Bfz = Bz + wz;
-                        const bool nx = dx < 0, ny = dy < 0, nz = dz < 0;
-                        // words: n2 = {lox[0..3], lox[4..7], loy[0..3], loy[4..7]}, n3 = {loz, loz, hix, hix}, n4 = {hiy, hiy, hiz, hiz}
-                        const uint32_t nX0 = nx ? n3.z : n2.x, nX1 = nx ? n3.w : n2.y, fX0 = nx ? n2.x : n3.z, fX1 = nx ? n2.y : n3.w;
-                        const uint32_t nY0 = ny ? n4.x : n2.z, nY1 = ny ? n4.y : n2.w, fY0 = ny ? n2.z : n4.x, fY1 = ny ? n2.w : n4.y;
-                        const uint32_t nZ0 = nz ? n4.z : n3.x, nZ1 = nz ? n4.w : n3.y, fZ0 = nz ? n3.x : n4.z, fZ1 = nz ? n3.y : n4.w;
-                        uint32_t hitmask = 0u;
+                    const uint4 *np = (const uint4 *)(job.nodes + nodeIdx);
+                    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+                    // t = (1 + q 2^-15) * A + B per plane; A = cell * 2^15 / dir, B = (p - o) / dir - A; planes widened by 1/64 cell
+                    const float Ax = __uint_as_float(((n0.w & 0xffu) + 15u) << 23) * idx_;
+                    const float Ay = __uint_as_float((((n0.w >> 8) & 0xffu) + 15u) << 23) * idy;
+                    const float Az = __uint_as_float((((n0.w >> 16) & 0xffu) + 15u) << 23) * idz;
+                    const float Bx = (__uint_as_float(n0.x) - ox) * idx_ - Ax;
+                    const float By = (__uint_as_float(n0.y) - oy) * idy - Ay;
+                    const float Bz = (__uint_as_float(n0.z) - oz) * idz - Az;
+                    const float wx = fabsf(Ax) * 4.76837158e-7f, wy = fabsf(Ay) * 4.76837158e-7f, wz = fabsf(Az) * 4.76837158e-7f;   // 2^-21 |A| = cell/64
+                    const float Bnx = Bx - wx, Bfx = Bx + wx, Bny = By - wy, Bfy = By + wy, Bnz = Bz - wz, Bfz = Bz + wz;
+                    const bool nx = dx < 0, ny = dy < 0, nz = dz < 0;
+                    // words: n2 = {lox[0..3], lox[4..7], loy[0..3], loy[4..7]}, n3 = {loz, loz, hix, hix}, n4 = {hiy, hiy, hiz, hiz}
+                    const uint32_t nX0 = nx ? n3.z : n2.x, nX1 = nx ? n3.w : n2.y, fX0 = nx ? n2.x : n3.z, fX1 = nx ? n2.y : n3.w;
+                    const uint32_t nY0 = ny ? n4.x : n2.z, nY1 = ny ? n4.y : n2.w, fY0 = ny ? n2.z : n4.x, fY1 = ny ? n2.w : n4.y;
+                    const uint32_t nZ0 = nz ? n4.z : n3.x, nZ1 = nz ? n4.w : n3.y, fZ0 = nz ? n3.x : n4.z, fZ1 = nz ? n3.y : n4.w;
+                    uint32_t hitmask = 0u;
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            const uint32_t meta4 = h ? n1.w : n1.z;
-                            const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                            const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);             // 0xff where the child is internal
-                            const uint32_t bit_index4 = (meta4 ^ ((oct * 0x01010101u) & inner_mask4)) & 0x1f1f1f1fu;
-                            const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                            const uint32_t wnx = h ? nX1 : nX0, wfx = h ? fX1 : fX0, wny = h ? nY1 : nY0, wfy = h ? fY1 : fY0, wnz = h ? nZ1 : nZ0, wfz = h ? fZ1 : fZ0;
+                    for (int h = 0; h < 2; ++h) {
+                        const uint32_t meta4 = h ? n1.w : n1.z;
+                        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                        const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);             // 0xff where the child is internal
+                        const uint32_t bit_index4 = (meta4 ^ ((oct * 0x01010101u) & inner_mask4)) & 0x1f1f1f1fu;
+                        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                        const uint32_t wnx = h ? nX1 : nX0, wfx = h ? fX1 : fX0, wny = h ? nY1 : nY0, wfy = h ? fY1 : fY0, wnz = h ? nZ1 : nZ0, wfz = h ? fZ1 : fZ0;
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const uint32_t sel = 0x7604u | ((uint32_t)j << 4);
-                                const float t0x = fmaf(plane_f(wnx, sel), Ax, Bnx), t1x = fmaf(plane_f(wfx, sel), Ax, Bfx);
-                                const float t0y = fmaf(plane_f(wny, sel), Ay, Bny), t1y = fmaf(plane_f(wfy, sel), Ay, Bfy);
-                                const float t0z = fmaf(plane_f(wnz, sel), Az, Bnz), t1z = fmaf(plane_f(wfz, sel), Az, Bfz);
-                                const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tlo));
-                                const float tf = fminf(fminf(t1x, t1y), fminf(t1z, thi));
-                                if (tn <= tf) {
-                                    const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu, bi = (bit_index4 >> (8 * j)) & 0xffu;
-                                    hitmask |= cb << bi;
-                                }
+                        for (int j = 0; j < 4; ++j) {
+                            const uint32_t sel = 0x7604u | ((uint32_t)j << 4);
+                            const float t0x = fmaf(plane_f(wnx, sel), Ax, Bnx), t1x = fmaf(plane_f(wfx, sel), Ax, Bfx);
+                            const float t0y = fmaf(plane_f(wny, sel), Ay, Bny), t1y = fmaf(plane_f(wfy, sel), Ay, Bfy);
+                            const float t0z = fmaf(plane_f(wnz, sel), Az, Bnz), t1z = fmaf(plane_f(wfz, sel), Az, Bfz);
+                            const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tlo));
+                            const float tf = fminf(fminf(t1x, t1y), fminf(t1z, thi));
+                            if (tn <= tf) {
+                                const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu, bi = (bit_index4 >> (8 * j)) & 0xffu;
+                                hitmask |= cb << bi;
                             }
                         }
-                        ng = make_uint2(n1.x, (hitmask & 0xff000000u) | (n0.w >> 24));
-                        tg = make_uint2(n1.y, hitmask & 0x00ffffffu);
                     }
+                    ng = make_uint2(n1.x, (hitmask & 0xff000000u) | (n0.w >> 24));
+                    tg = make_uint2(n1.y, hitmask & 0x00ffffffu);
                 }
-                // ---- triangle step(s): drain this lane's triangle group
-                while (!done && tg.y != 0u) {
-                    const int tb = 31 - __clz((int)tg.y);
-                    tg.y &= ~(1u << tb);
-                    const uint32_t ti = tg.x + (uint32_t)tb;
-                    const float4 A = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti));
-                    const float4 B = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 1));
-                    const float4 C = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 2));
-                    float t, u, v;
+            }
+            // ---- triangle phase (postponed, warp-synchronous): lanes holding a triangle group wait until enough of
+            //      the warp holds one, then every such lane tests ONE triangle.  Keeps the per-ray order (a lane
+            //      never descends past untested triangles) and turns a 2-3 lane loop into one wide pass.
+            const bool hasTri = active && !done && tg.y != 0u;
+            const unsigned triMask = __ballot_sync(FULL, hasTri);
+            if (triMask != 0u) {
+                const unsigned nodeMask = __ballot_sync(FULL, active && !done && tg.y == 0u);
+                const int nT = __popc(triMask), nN = __popc(nodeMask);
+                if (nT >= (nN < (int)job.triThreshold ? nN : (int)job.triThreshold)) {
+                    if (hasTri) {
+                        const int tb = 31 - __clz((int)tg.y);
+                        tg.y &= ~(1u << tb);
+                        const uint32_t ti = tg.x + (uint32_t)tb;
+                        const float4 A = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti));
+                        const float4 B = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 1));
+                        const float4 C = __ldg((const float4 *)(job.tri_v + 3 * (size_t)ti + 2));
+                        float t, u, v;
 #if defined(YB_HOSTEMU) && defined(YB_TRACE_STATS)
-                    g_stat_tris++;
+                        g_stat_tris++;
 #endif
-                    if (tri_intersect(v3(A.x, A.y, A.z), v3(B.x, B.y, B.z), v3(C.x, C.y, C.z), v3(ox, oy, oz), v3(dx, dy, dz), t, u, v) && t < thi && t >= tlo) {
-                        if (ANYHIT) { hitTri = (int)ti; done = true; }
-                        else { thi = t; hitTri = (int)ti; hitT = t; hitU = u; hitV = v; }
+                        if (tri_intersect(v3(A.x, A.y, A.z), v3(B.x, B.y, B.z), v3(C.x, C.y, C.z), v3(ox, oy, oz), v3(dx, dy, dz), t, u, v) && t < thi && t >= tlo) {
+                            if (ANYHIT) { hitTri = (int)ti; done = true; }
+                            else { thi = t; hitTri = (int)ti; hitT = t; hitU = u; hitV = v; }
+                        }
                     }
                 }
-                if (done) {
-                    active = false;
-                    if (OUT == OUT_HITS) ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(hitTri), hitT, hitU, hitV);
-                    else if (OUT == OUT_CLOSEST_PRIM) {
-                        const int prim = hitTri >= 0 ? __float_as_int(__ldg(&job.tri_v[3 * (size_t)hitTri].w)) : -1;
-                        ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(prim), hitT, hitU, hitV);
-                    } else if (OUT == OUT_SHADOW_FLAG) ((int32_t *)job.out)[rayIdx] = hitTri >= 0 ? 1 : 0;
-                    else if (hitTri < 0) {
-                        const float4 c = __ldg((const float4 *)(job.rays + (size_t)rayIdx * job.stride + 32));
-                        const uint32_t sid = __float_as_uint(c.w);
-                        atomicAdd(&job.acc[sid].x, c.x); atomicAdd(&job.acc[sid].y, c.y); atomicAdd(&job.acc[sid].z, c.z);
-                    }
+            }
+            if (done) {
+                active = false;
+                if (OUT == OUT_HITS) ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(hitTri), hitT, hitU, hitV);
+                else if (OUT == OUT_CLOSEST_PRIM) {
+                    const int prim = hitTri >= 0 ? __float_as_int(__ldg(&job.tri_v[3 * (size_t)hitTri].w)) : -1;
+                    ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(prim), hitT, hitU, hitV);
+                } else if (OUT == OUT_SHADOW_FLAG) ((int32_t *)job.out)[rayIdx] = hitTri >= 0 ? 1 : 0;
+                else if (hitTri < 0) {
+                    const float4 c = __ldg((const float4 *)(job.rays + (size_t)rayIdx * job.stride + 32));
+                    const uint32_t sid = __float_as_uint(c.w);
+                    atomicAdd(&job.acc[sid].x, c.x); atomicAdd(&job.acc[sid].y, c.y); atomicAdd(&job.acc[sid].z, c.z);
                 }
             }
         }
