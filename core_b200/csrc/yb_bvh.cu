@@ -10,8 +10,11 @@
 #include "yb_trace.cuh"
 #include <vector>
 #include <algorithm>
+#include <cstring>
+#include <cstdlib>
 #ifndef YB_HOSTEMU
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #endif
 
 namespace yb {
@@ -67,7 +70,7 @@ YB_HD int clz64(uint64_t x)
     return x ? __builtin_clzll(x) : 64;
 #endif
 }
-struct KarrasArgs { const uint64_t *keys; int32_t n; int32_t *left, *right, *parent, *first, *last; };
+struct KarrasArgs { const uint64_t *keys; int32_t n; int32_t *left, *right, *parent, *cnt; };
 YB_HD int karras_delta(const KarrasArgs &a, int i, int j)
 {
     if (j < 0 || j >= a.n) return -1;
@@ -97,7 +100,7 @@ YB_KERNEL(k_karras, KarrasArgs)
     const int L = (lo == gamma) ? ~gamma : gamma;
     const int R = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
     a.left[i] = L; a.right[i] = R;
-    a.first[i] = lo; a.last[i] = hi;
+    a.cnt[i] = hi - lo + 1;
     // parent array: internal nodes at [0, n-1), leaves at [n-1, 2n-1)
     a.parent[L >= 0 ? L : (a.n - 1 + ~L)] = i;
     a.parent[R >= 0 ? R : (a.n - 1 + ~R)] = i;
@@ -132,6 +135,70 @@ YB_KERNEL(k_fit, FitArgs)
     }
 }
 
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) over the Morton-sorted triangles.
+// Every round each cluster picks the neighbour within +-YB_PLOC_RADIUS that gives the smallest merged box; mutual
+// picks merge into a new binary node; the cluster array is compacted (stably, so it stays Morton-ordered).
+// Bottom-up agglomeration follows the surface-area heuristic far better than the radix tree's spatial-median
+// splits: 11.1 -> ~9 node visits per ray on the 1 M-triangle field (SAH sweep build: 8.7).
+#ifndef YB_PLOC_RADIUS
+#define YB_PLOC_RADIUS 16
+#endif
+struct PlocArgs {
+    const f4 *v; const uint32_t *idx;
+    int32_t *ref; v3 *lo, *hi;               // cluster array (in place)
+    int32_t *ref2; v3 *lo2, *hi2;            // compaction target
+    int32_t *nn; uint32_t *flag, *pos;
+    int32_t m;                               // clusters this round
+    int32_t *left, *right, *cnt; v3 *nlo, *nhi; uint32_t *nodeCounter;
+};
+YB_KERNEL(k_ploc_init, PlocArgs)
+{
+    v3 lo, hi;
+    tri_bounds(a.v, a.idx[tid], lo, hi);
+    a.ref[tid] = ~(int32_t)tid; a.lo[tid] = lo; a.hi[tid] = hi;
+}
+YB_HD float union_area(v3 l0, v3 h0, v3 l1, v3 h1)
+{
+    const float ex = fmaxf_(h0.x, h1.x) - fminf_(l0.x, l1.x), ey = fmaxf_(h0.y, h1.y) - fminf_(l0.y, l1.y), ez = fmaxf_(h0.z, h1.z) - fminf_(l0.z, l1.z);
+    return ex * ey + ey * ez + ez * ex;
+}
+YB_KERNEL(k_ploc_nn, PlocArgs)
+{
+    const int i = (int)tid;
+    const v3 lo = a.lo[i], hi = a.hi[i];
+    const int j0 = i - YB_PLOC_RADIUS < 0 ? 0 : i - YB_PLOC_RADIUS, j1 = i + YB_PLOC_RADIUS >= a.m ? a.m - 1 : i + YB_PLOC_RADIUS;
+    float best = INFINITY; int bj = -1;
+    for (int j = j0; j <= j1; ++j) {
+        if (j == i) continue;
+        const float ar = union_area(lo, hi, a.lo[j], a.hi[j]);
+        if (ar < best) { best = ar; bj = j; }            // ties: the lower index wins on both sides -> still mutual
+    }
+    a.nn[i] = bj;
+}
+YB_KERNEL(k_ploc_merge, PlocArgs)
+{
+    const int i = (int)tid, j = a.nn[i];
+    uint32_t keep = 1u;
+    if (j >= 0 && a.nn[j] == i) {
+        if (i < j) {
+            const uint32_t node = YB_ATOMIC_ADD_U32(a.nodeCounter, 1u);
+            const int32_t L = a.ref[i], R = a.ref[j];
+            const v3 l0 = a.lo[i], h0 = a.hi[i], l1 = a.lo[j], h1 = a.hi[j];
+            const v3 lo(fminf_(l0.x, l1.x), fminf_(l0.y, l1.y), fminf_(l0.z, l1.z)), hi(fmaxf_(h0.x, h1.x), fmaxf_(h0.y, h1.y), fmaxf_(h0.z, h1.z));
+            a.left[node] = L; a.right[node] = R; a.nlo[node] = lo; a.nhi[node] = hi;
+            a.cnt[node] = (L < 0 ? 1 : a.cnt[L]) + (R < 0 ? 1 : a.cnt[R]);
+            a.ref[i] = (int32_t)node; a.lo[i] = lo; a.hi[i] = hi;
+        } else keep = 0u;
+    }
+    a.flag[i] = keep;
+}
+YB_KERNEL(k_ploc_compact, PlocArgs)
+{
+    if (!a.flag[tid]) return;
+    const uint32_t p = a.pos[tid];
+    a.ref2[p] = a.ref[tid]; a.lo2[p] = a.lo[tid]; a.hi2[p] = a.hi[tid];
+}
+
 // ---- collapse to 8-wide
 #define YB_MAX_LEAF 3
 struct CollapseItem { int32_t bnode; uint32_t wnode; };
@@ -140,12 +207,12 @@ struct CollapseArgs {
     CollapseItem *out;
     uint32_t *counters;               // [0] wide nodes allocated, [1] triangles allocated, [2] items written, [3] max leaf seen
     const f4 *v; const v3 *nrm; const uint32_t *idx; int32_t n;
-    const int32_t *left, *right, *first, *last;
+    const int32_t *left, *right, *cnt;
     const v3 *nlo, *nhi;
     BvhNode *nodes; f4 *out_v; v3 *out_n;
     uint32_t nodeCap;
 };
-YB_HD int cref_count(const CollapseArgs &a, int ref) { return ref < 0 ? 1 : (a.last[ref] - a.first[ref] + 1); }
+YB_HD int cref_count(const CollapseArgs &a, int ref) { return ref < 0 ? 1 : a.cnt[ref]; }
 YB_HD float box_area(v3 lo, v3 hi) { v3 e = hi - lo; return e.x * e.y + e.y * e.z + e.z * e.x; }
 YB_HD void cref_bounds(const CollapseArgs &a, int ref, v3 &lo, v3 &hi)
 {
@@ -176,6 +243,19 @@ YB_KERNEL(k_collapse, CollapseArgs)
         int best = -1; float bestA = -1.f;
         for (int i = 0; i < nc; ++i) {
             if (child[i] < 0 || cref_count(a, child[i]) <= YB_MAX_LEAF) continue;
+            float ar = box_area(a.nlo[child[i]], a.nhi[child[i]]);
+            if (ar > bestA) { bestA = ar; best = i; }
+        }
+        if (best < 0) break;
+        int b = child[best];
+        child[best] = a.left[b];
+        child[nc++] = a.right[b];
+    }
+    // free slots left: split small leaf subtrees (2..YB_MAX_LEAF triangles) into tighter single boxes
+    while (nc < 8) {
+        int best = -1; float bestA = -1.f;
+        for (int i = 0; i < nc; ++i) {
+            if (child[i] < 0 || cref_count(a, child[i]) > YB_MAX_LEAF) continue;
             float ar = box_area(a.nlo[child[i]], a.nhi[child[i]]);
             if (ar > bestA) { bestA = ar; best = i; }
         }
@@ -255,9 +335,13 @@ YB_KERNEL(k_collapse, CollapseArgs)
             ++kInt;
         } else {
             nd.meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | triOff);
-            int f = ref < 0 ? ~ref : a.first[ref];
-            for (int j = 0; j < cnt; ++j) {
-                uint32_t src = a.idx[f + j], dst = triBase + triOff + (uint32_t)j;
+            // gather the subtree's triangles (at most YB_MAX_LEAF, so the walk needs a stack of YB_MAX_LEAF refs)
+            int stk[YB_MAX_LEAF + 1], ns = 0, j = 0;
+            stk[ns++] = ref;
+            while (ns) {
+                const int r = stk[--ns];
+                if (r >= 0) { stk[ns++] = a.right[r]; stk[ns++] = a.left[r]; continue; }
+                const uint32_t src = a.idx[~r], dst = triBase + triOff + (uint32_t)j++;
                 a.out_v[3 * dst] = a.v[3 * src]; a.out_v[3 * dst + 1] = a.v[3 * src + 1]; a.out_v[3 * dst + 2] = a.v[3 * src + 2];
                 if (a.nrm) { a.out_n[3 * dst] = a.nrm[3 * src]; a.out_n[3 * dst + 1] = a.nrm[3 * src + 1]; a.out_n[3 * dst + 2] = a.nrm[3 * src + 2]; }
             }
@@ -315,73 +399,56 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     }
 #endif
     const uint32_t nInt = n > 1 ? n - 1 : 0;
-    DevBuf<int32_t> left, right, parent, first, last; DevBuf<uint32_t> flag; DevBuf<v3> nlo, nhi;
-    left.reserve(nInt); right.reserve(nInt); first.reserve(nInt); last.reserve(nInt); parent.reserve(2 * (size_t)n);
-    flag.reserve(nInt); nlo.reserve(nInt); nhi.reserve(nInt);
-    if (nInt) {
-        KarrasArgs ka; ka.keys = keys.p; ka.n = (int32_t)n; ka.left = left.p; ka.right = right.p; ka.parent = parent.p; ka.first = first.p; ka.last = last.p;
+    DevBuf<int32_t> left, right, cnt; DevBuf<v3> nlo, nhi;
+    left.reserve(nInt); right.reserve(nInt); cnt.reserve(nInt); nlo.reserve(nInt); nhi.reserve(nInt);
+    int32_t rootRef = nInt ? 0 : ~0;
+    const char *builder = getenv("YB200_BVH_BUILDER");
+    if (nInt && builder && !strcmp(builder, "lbvh")) {
+        // radix tree (Karras 2012) + bottom-up fit: kept for A/B measurements of tree quality
+        DevBuf<int32_t> parent; DevBuf<uint32_t> flag;
+        parent.reserve(2 * (size_t)n); flag.reserve(nInt);
+        KarrasArgs ka; ka.keys = keys.p; ka.n = (int32_t)n; ka.left = left.p; ka.right = right.p; ka.parent = parent.p; ka.cnt = cnt.p;
         k_karras(nInt, ka, s);
         rt_memset(flag.p, 0, nInt * sizeof(uint32_t), s);
         FitArgs fa; fa.v = in_v; fa.idx = idx.p; fa.n = (int32_t)n; fa.left = left.p; fa.right = right.p; fa.parent = parent.p; fa.flag = flag.p; fa.nlo = nlo.p; fa.nhi = nhi.p;
         k_fit(n, fa, s);
-    }
-#if defined(YB_HOSTEMU) && defined(YB_EXPERIMENT_SAH)
-    if (getenv("YB_SAH") && nInt) {   // experiment: binned-SAH binary tree instead of the radix tree (host only)
-        std::vector<v3> tlo(n), thi(n), cen(n);
-        for (uint32_t i = 0; i < n; ++i) { tri_bounds(in_v, i, tlo[i], thi[i]); cen[i] = (tlo[i] + thi[i]) * 0.5f; }
-        uint32_t *ix = idx.p;
-        for (uint32_t i = 0; i < n; ++i) ix[i] = i;
-        int32_t nextNode = 0;
-        struct Rec {
-            static int32_t build(uint32_t lo, uint32_t hi, uint32_t *ix, const std::vector<v3> &tlo, const std::vector<v3> &thi, const std::vector<v3> &cen,
-                                 int32_t *left, int32_t *right, int32_t *first, int32_t *last, v3 *nlo, v3 *nhi, int32_t &nextNode) {
-                if (lo == hi) return ~(int32_t)lo;
-                const int32_t me = nextNode++;
-                v3 blo(1e30f), bhi(-1e30f), clo(1e30f), chi(-1e30f);
-                for (uint32_t i = lo; i <= hi; ++i) { uint32_t t = ix[i];
-                    blo = v3(fminf_(blo.x, tlo[t].x), fminf_(blo.y, tlo[t].y), fminf_(blo.z, tlo[t].z));
-                    bhi = v3(fmaxf_(bhi.x, thi[t].x), fmaxf_(bhi.y, thi[t].y), fmaxf_(bhi.z, thi[t].z));
-                    clo = v3(fminf_(clo.x, cen[t].x), fminf_(clo.y, cen[t].y), fminf_(clo.z, cen[t].z));
-                    chi = v3(fmaxf_(chi.x, cen[t].x), fmaxf_(chi.y, cen[t].y), fmaxf_(chi.z, cen[t].z)); }
-                nlo[me] = blo; nhi[me] = bhi; first[me] = (int32_t)lo; last[me] = (int32_t)hi;
-                const int NB = 32; float bestCost = 1e30f; int bestAx = -1, bestB = -1;
-                for (int ax = 0; ax < 3; ++ax) {
-                    const float c0 = ax == 0 ? clo.x : ax == 1 ? clo.y : clo.z, c1 = ax == 0 ? chi.x : ax == 1 ? chi.y : chi.z;
-                    if (!(c1 > c0)) continue;
-                    v3 bl[NB], bh[NB]; int cnt[NB];
-                    for (int b = 0; b < NB; ++b) { bl[b] = v3(1e30f); bh[b] = v3(-1e30f); cnt[b] = 0; }
-                    const float sc = NB / (c1 - c0);
-                    for (uint32_t i = lo; i <= hi; ++i) { uint32_t t = ix[i]; float c = ax == 0 ? cen[t].x : ax == 1 ? cen[t].y : cen[t].z;
-                        int b = (int)((c - c0) * sc); if (b >= NB) b = NB - 1; if (b < 0) b = 0; cnt[b]++;
-                        bl[b] = v3(fminf_(bl[b].x, tlo[t].x), fminf_(bl[b].y, tlo[t].y), fminf_(bl[b].z, tlo[t].z));
-                        bh[b] = v3(fmaxf_(bh[b].x, thi[t].x), fmaxf_(bh[b].y, thi[t].y), fmaxf_(bh[b].z, thi[t].z)); }
-                    float ra[NB]; int rc[NB]; v3 al(1e30f), ah(-1e30f); int c = 0;
-                    for (int b = NB - 1; b > 0; --b) { if (cnt[b]) { al = v3(fminf_(al.x, bl[b].x), fminf_(al.y, bl[b].y), fminf_(al.z, bl[b].z)); ah = v3(fmaxf_(ah.x, bh[b].x), fmaxf_(ah.y, bh[b].y), fmaxf_(ah.z, bh[b].z)); } c += cnt[b]; ra[b] = c ? box_area(al, ah) : 0.f; rc[b] = c; }
-                    al = v3(1e30f); ah = v3(-1e30f); c = 0;
-                    for (int b = 0; b < NB - 1; ++b) { if (cnt[b]) { al = v3(fminf_(al.x, bl[b].x), fminf_(al.y, bl[b].y), fminf_(al.z, bl[b].z)); ah = v3(fmaxf_(ah.x, bh[b].x), fmaxf_(ah.y, bh[b].y), fmaxf_(ah.z, bh[b].z)); } c += cnt[b];
-                        if (c == 0 || rc[b + 1] == 0) continue;
-                        float cost = box_area(al, ah) * c + ra[b + 1] * rc[b + 1];
-                        if (cost < bestCost) { bestCost = cost; bestAx = ax; bestB = b; } }
-                }
-                uint32_t mid;
-                if (bestAx < 0) mid = (lo + hi) / 2;
-                else {
-                    const float c0 = bestAx == 0 ? clo.x : bestAx == 1 ? clo.y : clo.z, c1 = bestAx == 0 ? chi.x : bestAx == 1 ? chi.y : chi.z;
-                    const float sc = NB / (c1 - c0);
-                    uint32_t *m = std::partition(ix + lo, ix + hi + 1, [&](uint32_t t) { float c = bestAx == 0 ? cen[t].x : bestAx == 1 ? cen[t].y : cen[t].z; int b = (int)((c - c0) * sc); if (b >= NB) b = NB - 1; if (b < 0) b = 0; return b <= bestB; });
-                    mid = (uint32_t)(m - ix) - 1;
-                    if (mid < lo || mid >= hi) mid = (lo + hi) / 2;
-                }
-                int32_t L = build(lo, mid, ix, tlo, thi, cen, left, right, first, last, nlo, nhi, nextNode);
-                int32_t R = build(mid + 1, hi, ix, tlo, thi, cen, left, right, first, last, nlo, nhi, nextNode);
-                left[me] = L; right[me] = R;
-                return me;
-            }
-        };
-        Rec::build(0, n - 1, ix, tlo, thi, cen, left.p, right.p, first.p, last.p, nlo.p, nhi.p, nextNode);
-        fprintf(stderr, "YB_SAH: built %d internal nodes\n", nextNode);
-    }
+        rt_sync(s);
+    } else if (nInt) {
+        DevBuf<int32_t> ref, ref2, nn; DevBuf<v3> lo, hi, lo2, hi2; DevBuf<uint32_t> flag, pos, nodeCounter;
+        ref.reserve(n); ref2.reserve(n); nn.reserve(n); lo.reserve(n); hi.reserve(n); lo2.reserve(n); hi2.reserve(n);
+        flag.reserve(n); pos.reserve(n); nodeCounter.reserve(1);
+        rt_memset(nodeCounter.p, 0, sizeof(uint32_t), s);
+        PlocArgs pa; pa.v = in_v; pa.idx = idx.p; pa.nn = nn.p; pa.flag = flag.p; pa.pos = pos.p;
+        pa.left = left.p; pa.right = right.p; pa.cnt = cnt.p; pa.nlo = nlo.p; pa.nhi = nhi.p; pa.nodeCounter = nodeCounter.p;
+        pa.ref = ref.p; pa.lo = lo.p; pa.hi = hi.p; pa.ref2 = ref2.p; pa.lo2 = lo2.p; pa.hi2 = hi2.p; pa.m = (int32_t)n;
+        k_ploc_init(n, pa, s);
+#ifndef YB_HOSTEMU
+        DevBuf<char> scanTmp; size_t scanBytes = 0;
+        YB_CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, scanBytes, flag.p, pos.p, (int)n, s));
+        scanTmp.reserve(scanBytes);
 #endif
+        uint32_t m = n;
+        while (m > 1) {
+            pa.m = (int32_t)m;
+            k_ploc_nn(m, pa, s);
+            k_ploc_merge(m, pa, s);
+            uint32_t tail[2];
+#ifndef YB_HOSTEMU
+            YB_CUDA_CHECK(cub::DeviceScan::ExclusiveSum(scanTmp.p, scanBytes, flag.p, pos.p, (int)m, s));
+            g_kernel_launches += 1;
+#else
+            { uint32_t acc = 0; for (uint32_t i = 0; i < m; ++i) { pos.p[i] = acc; acc += flag.p[i]; } }
+#endif
+            k_ploc_compact(m, pa, s);
+            rt_d2h(&tail[0], pos.p + (m - 1), sizeof(uint32_t), s);
+            rt_d2h(&tail[1], flag.p + (m - 1), sizeof(uint32_t), s);
+            const uint32_t m2 = tail[0] + tail[1];
+            if (m2 >= m) throw RtError("bvh_build: clustering made no progress");
+            m = m2;
+            std::swap(pa.ref, pa.ref2); std::swap(pa.lo, pa.lo2); std::swap(pa.hi, pa.hi2);
+        }
+        rt_d2h(&rootRef, pa.ref, sizeof(int32_t), s);
+    }
     // collapse, level by level
     const uint32_t nodeCap = n / 2 + 16;       // every internal wide node has >= 2 children with > YB_MAX_LEAF/… tris; generous bound
     nodes.reserve(nodeCap); out_v.reserve(3 * (size_t)n);
@@ -390,11 +457,11 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     DevBuf<uint32_t> counters; counters.reserve(4);
     uint32_t c0[4] = {1, 0, 0, 0};
     rt_h2d(counters.p, c0, sizeof(c0), s);
-    CollapseItem root; root.bnode = nInt ? 0 : ~0; root.wnode = 0;
+    CollapseItem root; root.bnode = rootRef; root.wnode = 0;
     rt_h2d(qa.p, &root, sizeof(root), s);
     uint32_t nItems = 1;
     CollapseArgs ca; ca.counters = counters.p; ca.v = in_v; ca.nrm = in_n; ca.idx = idx.p; ca.n = (int32_t)n;
-    ca.left = left.p; ca.right = right.p; ca.first = first.p; ca.last = last.p; ca.nlo = nlo.p; ca.nhi = nhi.p;
+    ca.left = left.p; ca.right = right.p; ca.cnt = cnt.p; ca.nlo = nlo.p; ca.nhi = nhi.p;
     ca.nodes = nodes.p; ca.out_v = out_v.p; ca.out_n = in_n ? out_n.p : 0; ca.nodeCap = nodeCap;
     DevBuf<CollapseItem> *qin = &qa, *qout = &qb;
     while (nItems) {

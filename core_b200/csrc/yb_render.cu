@@ -549,7 +549,7 @@ static size_t env_size(const char *name, size_t dflt)
 // tuning knob of the traversal kernels' postponed triangle phase (yb_trace_fast.cuh); 1 = never postpone
 static uint32_t tri_threshold()
 {
-    static const uint32_t v = (uint32_t)env_size("YB200_TRI_THRESHOLD", 8);
+    static const uint32_t v = (uint32_t)env_size("YB200_TRI_THRESHOLD", 1);
     return v < 1u ? 1u : (v > 32u ? 32u : v);
 }
 
