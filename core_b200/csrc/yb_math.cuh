@@ -254,20 +254,34 @@ YB_HD uint32_t fnv_32a_buf(uint32_t value)                                     /
     for (int i = 0; i < 4; i++) { hash ^= (value >> (8 * i)) & 0xffu; hash *= 0x01000193u; }
     return hash;
 }
-// mcqmc.h:29-94 — incremental Halton; FP64 state, getNext() advances THEN returns
-struct Halton {
-    uint32_t mBase;
-    double mInvBase, mValue;
-    YB_HD Halton() {}
-    YB_HD explicit Halton(int base) { mBase = base; mInvBase = 1.0 / (double)base; mValue = 0; }
+// mcqmc.h:29-94 — incremental Halton; FP64 state, getNext() advances THEN returns.
+// The base is a template parameter so the digit loop divides by a constant (mul-hi instead of a 30-instruction
+// runtime division); the FP64 operation sequence — and so every bit of the stream — is the reference's.
+template <uint32_t BASE> struct HaltonT {
+    double mValue;
+    YB_HD HaltonT() : mValue(0) {}
+    YB_HD static double invBase() { return 1.0 / (double)BASE; }
     YB_HD void setStart(uint32_t i)
     {
+        if (BASE == 2u) {
+            // all partial sums are exact in binary: the loop result is the bit-reversed index scaled by 2^-32
+            uint32_t r = i;
+            r = ((r >> 1) & 0x55555555u) | ((r & 0x55555555u) << 1);
+            r = ((r >> 2) & 0x33333333u) | ((r & 0x33333333u) << 2);
+            r = ((r >> 4) & 0x0f0f0f0fu) | ((r & 0x0f0f0f0fu) << 4);
+            r = ((r >> 8) & 0x00ff00ffu) | ((r & 0x00ff00ffu) << 8);
+            r = (r >> 16) | (r << 16);
+            mValue = (double)r * 2.3283064365386963e-10;   // 2^-32
+            return;
+        }
+        const double mInvBase = invBase();
         double factor = mInvBase;
         mValue = 0.0;
-        while (i > 0) { mValue += (double)(i % mBase) * factor; i /= mBase; factor *= mInvBase; }
+        while (i > 0) { mValue += (double)(i % BASE) * factor; i /= BASE; factor *= mInvBase; }
     }
     YB_HD float getNext()
     {
+        const double mInvBase = invBase();
         double r = 0.9999999999 - mValue;
         if (mInvBase < r) mValue += mInvBase;
         else {
@@ -278,5 +292,8 @@ struct Halton {
         return fmaxf_(0.f, fminf_(1.f, (float)mValue));
     }
 };
+typedef HaltonT<2> Halton2;
+typedef HaltonT<3> Halton3;
+typedef HaltonT<5> Halton5;
 
 }  // namespace yb

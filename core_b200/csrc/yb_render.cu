@@ -29,16 +29,28 @@ namespace yb {
 #define YB_LOFFS_DELTA 4567u         // mcintegrator.cc:43
 
 // scr_halton.h:47-69 (dim < 50 on this path: SURVEY.md §5)
+YB_D uint32_t yb_umulhi(uint32_t a, uint32_t b)
+{
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return (uint32_t)(((uint64_t)a * (uint64_t)b) >> 32);
+#endif
+}
 YB_D double scrHalton(int dim, uint32_t n)
 {
     double value = 0.0;
-    if (dim < 50) {
+    if (dim > 0 && dim < 50) {
         const unsigned char *sigma = yb_faure_flat + yb_faure_offs[dim];
         uint32_t base = (uint32_t)yb_prims[dim];
         double f, factor, dn = (double)n;
         f = factor = yb_invPrims[dim];
+        const uint32_t magic = yb_primMagic[dim];
         while (n > 0) {
-            value += (double)sigma[n % base] * factor;
+            // n % base without a runtime division: the mul-hi quotient is exact or one too large
+            uint32_t r = n - yb_umulhi(n, magic) * base;
+            if ((int32_t)r < 0) r += base;
+            value += (double)sigma[r] * factor;
             dn *= f;
             n = (uint32_t)dn;
             factor *= f;
@@ -95,7 +107,7 @@ YB_KERNEL(k_raygen, RenderArgs)
     sample_dxdy(a.sc.film, id, dx, dy);
     float lens_u = 0.5f, lens_v = 0.5f;
     if (a.sc.cam.sampleLens) {          // integrator.cc:248-249,266-267,287-291
-        Halton halU(3), halV(5);
+        Halton3 halU; Halton5 halV;
         halU.setStart((uint32_t)a.sc.film.pass_offs + id.samplingOffs);
         halV.setStart((uint32_t)a.sc.film.pass_offs + id.samplingOffs);
         for (int k = 0; k <= id.s; ++k) { lens_u = halU.getNext(); lens_v = halV.getNext(); }
@@ -174,7 +186,7 @@ YB_D void doLightEstimation(const RenderArgs &a, const Light &light, uint32_t lo
     const float invNS = 1.f / (float)n;
     const uint32_t offs = (uint32_t)n * (uint32_t)id.pixelSample + id.samplingOffs + l_offs;
     const bool canIntersect = light_canIntersect(light);
-    Halton hal2(2), hal3(3);
+    Halton2 hal2; Halton3 hal3;
     hal2.setStart(offs - 1); hal3.setStart(offs - 1);
     for (int i = 0; i < n; ++i) {
         LSample ls;
@@ -228,7 +240,7 @@ YB_D void estimateOneDirectLight(const RenderArgs &a, const Surf &sp, const MatD
 {
     const int lightNum = a.sc.nLights;
     if (lightNum == 0) return;
-    Halton hal2(2);
+    Halton2 hal2;
     hal2.setStart((uint32_t)(n - 1));
     int lnum = (int)(hal2.getNext() * (float)lightNum);
     if (lnum > lightNum - 1) lnum = lightNum - 1;
@@ -243,7 +255,7 @@ YB_D void sampleAmbientOcclusion(const RenderArgs &a, const Surf &sp, const MatD
     int n = I.aoSamples;
     if (rayDivision > 1) n = (n / (int)rayDivision) > 1 ? (n / (int)rayDivision) : 1;
     const uint32_t offs = (uint32_t)n * (uint32_t)id.pixelSample + id.samplingOffs;
-    Halton hal2(2), hal3(3);
+    Halton2 hal2; Halton3 hal3;
     hal2.setStart(offs - 1); hal3.setStart(offs - 1);
     const float invN = 1.f / (float)n;
     col3 ecol(0.f);
@@ -338,7 +350,7 @@ YB_D void shade_integrate(const RenderArgs &a, const Task &T, const Hit &H)
             uint32_t branch = newDivision * oldOffset;
             uint32_t offs = (uint32_t)gsam * (uint32_t)id.pixelSample + id.samplingOffs;
             const float d_1 = 1.f / (float)gsam;
-            Halton hal2(2), hal3(3);
+            Halton2 hal2; Halton3 hal3;
             hal2.setStart(offs); hal3.setStart(offs);
             for (int ns = 0; ns < gsam; ++ns) {
                 const float dc1 = (float)scrHalton(2 * newlevel + 1, branch + id.samplingOffs);
@@ -428,7 +440,7 @@ YB_D void shade_path(const RenderArgs &a, const Task &T, const Hit &H)
     push_task(a, child_task(T, sp.P, wi, thr, 0.f, task_bits(TASK_PATH, ncaustic, task_level(T.bits), nd)));
 }
 
-YB_KERNEL(k_shade, RenderArgs)
+YB_KERNEL_OCC(k_shade, RenderArgs, 2)
 {
     const Task T = a.tasks[tid];
     const Hit H = a.hits[tid];

@@ -64,9 +64,9 @@ struct DevBuf {
 // YB_KERNEL(name, ArgsType) { body using `tid` and `a` }  defines an element-wise kernel over [0, n).
 // Device: __global__ grid-stride wrapper + launcher; emulator: a serial loop.
 #ifndef YB_HOSTEMU
-#define YB_KERNEL(name, ArgsType)                                                                      \
+#define YB_KERNEL_OCC(name, ArgsType, minBlocks)                                                                      \
     __device__ __forceinline__ void name##_body(uint32_t tid, const ArgsType &a);                      \
-    __global__ void __launch_bounds__(256) name##_kernel(uint32_t n, const ArgsType a)                 \
+    __global__ void __launch_bounds__(256, minBlocks) name##_kernel(uint32_t n, const ArgsType a)                 \
     {                                                                                                  \
         for (uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x; tid < n; tid += gridDim.x * blockDim.x) \
             name##_body(tid, a);                                                                       \
@@ -81,6 +81,7 @@ struct DevBuf {
         yb::g_kernel_launches++;                                                                       \
     }                                                                                                  \
     __device__ __forceinline__ void name##_body(uint32_t tid, const ArgsType &a)
+#define YB_KERNEL(name, ArgsType) YB_KERNEL_OCC(name, ArgsType, 1)
 #define YB_ATOMIC_ADD_U32(p, v) atomicAdd((unsigned int *)(p), (unsigned int)(v))
 #define YB_ATOMIC_ADD_F32(p, v) atomicAdd((float *)(p), (float)(v))
 #define YB_ATOMIC_MIN_I32(p, v) atomicMin((int *)(p), (int)(v))
@@ -88,6 +89,7 @@ struct DevBuf {
 #define YB_ATOMIC_EXCH_U32(p, v) atomicExch((unsigned int *)(p), (unsigned int)(v))
 #define YB_THREADFENCE() __threadfence()
 #else
+#define YB_KERNEL_OCC(name, ArgsType, minBlocks) YB_KERNEL(name, ArgsType)
 #define YB_KERNEL(name, ArgsType)                                                                      \
     inline void name##_body(uint32_t tid, const ArgsType &a);                                          \
     static void name(uint32_t n, const ArgsType &a, yb::rt_stream)                                     \
