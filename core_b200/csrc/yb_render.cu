@@ -66,6 +66,8 @@ struct RenderArgs {
     Task *out_tasks;        // children appended here
     ShadowTask *shadow;     // shadow rays appended here
     uint32_t *counters;     // [0] out_tasks count, [1] shadow count
+    const uint32_t *order;  // shading order of this wave (0 = identity): tasks binned by shade_key
+    uint32_t *orderOut; unsigned char *keys; uint32_t *bins;   // binning scratch: bins[0..7] counts, bins[8..15] cursors
     f4 *acc;                // per camera sample: rgb + alpha
     const uint32_t *pix;    // owned pixels: x | y << 16
     float *film;            // (x + w*y)*5: r,g,b,a,weight
@@ -235,15 +237,21 @@ YB_D void estimateAllDirectLight(const RenderArgs &a, const Surf &sp, const MatD
 {
     for (int l = 0; l < a.sc.nLights; ++l) doLightEstimation(a, a.sc.lights[l], (uint32_t)l, sp, md, wo, id, rayDivision, weight, sid);
 }
+// the light estimateOneDirectLight picks for path sample n (mcintegrator.cc:62-66)
+YB_D int pick_one_light(int n, int lightNum)
+{
+    Halton2 hal2;
+    hal2.setStart((uint32_t)(n - 1));
+    int lnum = (int)(hal2.getNext() * (float)lightNum);
+    if (lnum > lightNum - 1) lnum = lightNum - 1;
+    return lnum;
+}
 // estimateOneDirectLight (mcintegrator.cc:58-71)
 YB_D void estimateOneDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, int n, col3 weight, uint32_t sid)
 {
     const int lightNum = a.sc.nLights;
     if (lightNum == 0) return;
-    Halton2 hal2;
-    hal2.setStart((uint32_t)(n - 1));
-    int lnum = (int)(hal2.getNext() * (float)lightNum);
-    if (lnum > lightNum - 1) lnum = lightNum - 1;
+    const int lnum = pick_one_light(n, lightNum);
     doLightEstimation(a, a.sc.lights[lnum], (uint32_t)lnum, sp, md, wo, id, rayDivision, weight * (float)lightNum, sid);
 }
 // sampleAmbientOcclusion (mcintegrator.cc:629-683)
@@ -440,8 +448,70 @@ YB_D void shade_path(const RenderArgs &a, const Task &T, const Hit &H)
     push_task(a, child_task(T, sp.P, wi, thr, 0.f, task_bits(TASK_PATH, ncaustic, task_level(T.bits), nd)));
 }
 
-YB_KERNEL_OCC(k_shade, RenderArgs, 2)
+// ---- shading order.  After the first wave the tasks of one warp take very different code paths (hit / miss, the
+// light estimateOneDirectLight picks): measured 8 of 32 lanes active.  Tasks are binned by a small key so that warps
+// of the shade kernel are homogeneous; the kernel then gathers its task through `order`.
+#define YB_SHADE_BINS 8
+YB_D uint32_t shade_key(const RenderArgs &a, uint32_t t)
 {
+    if (a.hits[t].tri < 0) return 0u;
+    const uint32_t bits = a.tasks[t].bits;
+    if (task_kind(bits) == TASK_INTEGRATE) return 1u;
+    const int l = pick_one_light((int)a.tasks[t].pathOffs, a.sc.nLights);
+    return 2u + (uint32_t)(l < YB_SHADE_BINS - 3 ? l : YB_SHADE_BINS - 3);
+}
+#ifndef YB_HOSTEMU
+__global__ void __launch_bounds__(256) k_bin_count_kernel(uint32_t n, const RenderArgs a)
+{
+    __shared__ uint32_t h[YB_SHADE_BINS];
+    if (threadIdx.x < YB_SHADE_BINS) h[threadIdx.x] = 0u;
+    __syncthreads();
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const uint32_t k = shade_key(a, t);
+        a.keys[t] = (unsigned char)k;
+        atomicAdd(&h[k], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < YB_SHADE_BINS && h[threadIdx.x]) atomicAdd(&a.bins[threadIdx.x], h[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256) k_bin_scatter_kernel(uint32_t n, const RenderArgs a)
+{
+    __shared__ uint32_t h[YB_SHADE_BINS], base[YB_SHADE_BINS];
+    if (threadIdx.x < YB_SHADE_BINS) h[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t k = 0u, rank = 0u;
+    if (t < n) { k = a.keys[t]; rank = atomicAdd(&h[k], 1u); }
+    __syncthreads();
+    if (threadIdx.x < YB_SHADE_BINS) {
+        uint32_t before = 0u;
+        for (uint32_t b = 0; b < threadIdx.x; ++b) before += a.bins[b];
+        base[threadIdx.x] = before + (h[threadIdx.x] ? atomicAdd(&a.bins[YB_SHADE_BINS + threadIdx.x], h[threadIdx.x]) : 0u);
+    }
+    __syncthreads();
+    if (t < n) a.orderOut[base[k] + rank] = t;
+}
+#endif
+static void bin_tasks(uint32_t n, const RenderArgs &a, rt_stream s)
+{
+    rt_memset(a.bins, 0, 2 * YB_SHADE_BINS * sizeof(uint32_t), s);
+#ifndef YB_HOSTEMU
+    uint32_t blocks = (n + 255u) / 256u;
+    k_bin_count_kernel<<<blocks > 148u * 8u ? 148u * 8u : blocks, 256, 0, s>>>(n, a);
+    k_bin_scatter_kernel<<<blocks, 256, 0, s>>>(n, a);
+    YB_CUDA_CHECK(cudaGetLastError());
+#else
+    for (uint32_t t = 0; t < n; ++t) { a.keys[t] = (unsigned char)shade_key(a, t); a.bins[a.keys[t]]++; }
+    uint32_t base[YB_SHADE_BINS], acc = 0;
+    for (int b = 0; b < YB_SHADE_BINS; ++b) { base[b] = acc; acc += a.bins[b]; }
+    for (uint32_t t = 0; t < n; ++t) a.orderOut[base[a.keys[t]]++] = t;
+#endif
+    g_kernel_launches += 2;
+}
+
+YB_KERNEL_OCC(k_shade, RenderArgs, 3)
+{
+    if (a.order) tid = a.order[tid];
     const Task T = a.tasks[tid];
     const Hit H = a.hits[tid];
     if (task_kind(T.bits) == TASK_INTEGRATE) shade_integrate(a, T, H);
@@ -526,7 +596,8 @@ struct RenderBuffers {
     DevBuf<Task> poolA, poolB;
     DevBuf<Hit> hits;
     DevBuf<ShadowTask> shadow;
-    DevBuf<uint32_t> counters;
+    DevBuf<uint32_t> counters, order, bins;
+    DevBuf<unsigned char> keys;
     DevBuf<f4> acc;
     DevBuf<uint32_t> pix;
     DevBuf<float> film, rgba;
@@ -624,9 +695,12 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
         const size_t poolCap = B * (F + 1), shadowCap = B * S;
         rb.poolA.reserve(poolCap); rb.poolB.reserve(poolCap);
         rb.hits.reserve(B); rb.shadow.reserve(shadowCap); rb.counters.reserve(4); rb.acc.reserve(B);
+        rb.order.reserve(B); rb.keys.reserve(B); rb.bins.reserve(2 * YB_SHADE_BINS);
         RenderArgs a;
         memset((void *)&a, 0, sizeof(a));
         a.sc = c.sc; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
+        a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
+        const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
         const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;
@@ -641,6 +715,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
             a.sampleBase = base; a.tasks = pool;
             k_raygen(nb, a, s);
             size_t top = nb;
+            bool firstWave = true;      // camera rays come in pixel order: already coherent
             while (top > 0) {
                 size_t M = std::min(top, B);
                 M = std::min(M, shadowCap / S);
@@ -659,7 +734,12 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                 } else
                     k_trace_closest((uint32_t)M, a, s);
                 tc.stop();
-                tsd.start(); k_shade((uint32_t)M, a, s); tsd.stop();
+                tsd.start();
+                a.order = 0;
+                if (binShade && !firstWave) { bin_tasks((uint32_t)M, a, s); a.order = rb.order.p; }
+                k_shade((uint32_t)M, a, s);
+                tsd.stop();
+                firstWave = false;
                 uint32_t cnt[4];
                 rt_d2h(cnt, rb.counters.p, sizeof(cnt), s);
                 if (cnt[0] > a.outCap || cnt[1] > a.shadowCap) throw RtError("render: internal queue overflow");
