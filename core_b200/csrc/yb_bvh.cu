@@ -353,12 +353,12 @@ YB_KERNEL(k_collapse, CollapseArgs)
 
 // ---------------------------------------------------------------------------------------------- host driver
 void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &nodes, DevBuf<f4> &out_v, DevBuf<v3> &out_n,
-               uint32_t &nNodes, uint32_t &maxDepth, v3 &boundLo, v3 &boundHi, rt_stream s)
+               uint32_t &nNodes, uint32_t &maxDepth, v3 &boundLo, v3 &boundHi, BvhScratch &w, rt_stream s)
 {
     nNodes = 0; maxDepth = 0;
     boundLo = v3(0.f); boundHi = v3(0.f);
     if (n == 0) return;
-    DevBuf<int32_t> ob; ob.reserve(8);
+    DevBuf<int32_t> &ob = w.ob; ob.reserve(8);
     int32_t init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int32_t)0x80000000, (int32_t)0x80000000, (int32_t)0x80000000};
     rt_h2d(ob.p, init, sizeof(init), s);
     BoundsArgs ba; ba.v = in_v; ba.ob = ob.p;
@@ -369,7 +369,7 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     boundHi = v3(ord2f(obh[3]), ord2f(obh[4]), ord2f(obh[5]));
     v3 ext = boundHi - boundLo;
 
-    DevBuf<uint64_t> keys; DevBuf<uint32_t> idx;
+    DevBuf<uint64_t> &keys = w.keys; DevBuf<uint32_t> &idx = w.idx;
     keys.reserve(n); idx.reserve(n);
     MortonArgs ma; ma.v = in_v; ma.keys = keys.p; ma.idx = idx.p; ma.lo = boundLo;
     // one scale for all three axes (cubic Morton cells): per-axis normalisation would cut a flat scene into thin
@@ -379,7 +379,7 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     k_morton(n, ma, s);
 #ifndef YB_HOSTEMU
     {
-        DevBuf<uint64_t> keys2; DevBuf<uint32_t> idx2; DevBuf<char> tmp;
+        DevBuf<uint64_t> &keys2 = w.keys2; DevBuf<uint32_t> &idx2 = w.idx2; DevBuf<char> &tmp = w.sortTmp;
         keys2.reserve(n); idx2.reserve(n);
         size_t tmpBytes = 0;
         YB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, keys.p, keys2.p, idx.p, idx2.p, (int)n, 0, 63, s));
@@ -399,13 +399,13 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     }
 #endif
     const uint32_t nInt = n > 1 ? n - 1 : 0;
-    DevBuf<int32_t> left, right, cnt; DevBuf<v3> nlo, nhi;
+    DevBuf<int32_t> &left = w.left, &right = w.right, &cnt = w.cnt; DevBuf<v3> &nlo = w.nlo, &nhi = w.nhi;
     left.reserve(nInt); right.reserve(nInt); cnt.reserve(nInt); nlo.reserve(nInt); nhi.reserve(nInt);
     int32_t rootRef = nInt ? 0 : ~0;
     const char *builder = getenv("YB200_BVH_BUILDER");
     if (nInt && builder && !strcmp(builder, "lbvh")) {
         // radix tree (Karras 2012) + bottom-up fit: kept for A/B measurements of tree quality
-        DevBuf<int32_t> parent; DevBuf<uint32_t> flag;
+        DevBuf<int32_t> &parent = w.parent; DevBuf<uint32_t> &flag = w.flag;
         parent.reserve(2 * (size_t)n); flag.reserve(nInt);
         KarrasArgs ka; ka.keys = keys.p; ka.n = (int32_t)n; ka.left = left.p; ka.right = right.p; ka.parent = parent.p; ka.cnt = cnt.p;
         k_karras(nInt, ka, s);
@@ -414,7 +414,8 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
         k_fit(n, fa, s);
         rt_sync(s);
     } else if (nInt) {
-        DevBuf<int32_t> ref, ref2, nn; DevBuf<v3> lo, hi, lo2, hi2; DevBuf<uint32_t> flag, pos, nodeCounter;
+        DevBuf<int32_t> &ref = w.ref, &ref2 = w.ref2, &nn = w.nn; DevBuf<v3> &lo = w.lo, &hi = w.hi, &lo2 = w.lo2, &hi2 = w.hi2;
+        DevBuf<uint32_t> &flag = w.flag, &pos = w.pos, &nodeCounter = w.nodeCounter;
         ref.reserve(n); ref2.reserve(n); nn.reserve(n); lo.reserve(n); hi.reserve(n); lo2.reserve(n); hi2.reserve(n);
         flag.reserve(n); pos.reserve(n); nodeCounter.reserve(1);
         rt_memset(nodeCounter.p, 0, sizeof(uint32_t), s);
@@ -423,7 +424,7 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
         pa.ref = ref.p; pa.lo = lo.p; pa.hi = hi.p; pa.ref2 = ref2.p; pa.lo2 = lo2.p; pa.hi2 = hi2.p; pa.m = (int32_t)n;
         k_ploc_init(n, pa, s);
 #ifndef YB_HOSTEMU
-        DevBuf<char> scanTmp; size_t scanBytes = 0;
+        DevBuf<char> &scanTmp = w.scanTmp; size_t scanBytes = 0;
         YB_CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, scanBytes, flag.p, pos.p, (int)n, s));
         scanTmp.reserve(scanBytes);
 #endif
@@ -453,20 +454,21 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     const uint32_t nodeCap = n / 2 + 16;       // every internal wide node has >= 2 children with > YB_MAX_LEAF/… tris; generous bound
     nodes.reserve(nodeCap); out_v.reserve(3 * (size_t)n);
     if (in_n) out_n.reserve(3 * (size_t)n);
-    DevBuf<CollapseItem> qa, qb; qa.reserve(nodeCap); qb.reserve(nodeCap);
-    DevBuf<uint32_t> counters; counters.reserve(4);
+    static_assert(sizeof(CollapseItem) == sizeof(uint64_t), "CollapseItem packs into 8 bytes");
+    w.qa.reserve(nodeCap); w.qb.reserve(nodeCap);
+    DevBuf<uint32_t> &counters = w.counters; counters.reserve(4);
     uint32_t c0[4] = {1, 0, 0, 0};
     rt_h2d(counters.p, c0, sizeof(c0), s);
     CollapseItem root; root.bnode = rootRef; root.wnode = 0;
-    rt_h2d(qa.p, &root, sizeof(root), s);
+    rt_h2d(w.qa.p, &root, sizeof(root), s);
     uint32_t nItems = 1;
     CollapseArgs ca; ca.counters = counters.p; ca.v = in_v; ca.nrm = in_n; ca.idx = idx.p; ca.n = (int32_t)n;
     ca.left = left.p; ca.right = right.p; ca.cnt = cnt.p; ca.nlo = nlo.p; ca.nhi = nhi.p;
     ca.nodes = nodes.p; ca.out_v = out_v.p; ca.out_n = in_n ? out_n.p : 0; ca.nodeCap = nodeCap;
-    DevBuf<CollapseItem> *qin = &qa, *qout = &qb;
+    CollapseItem *qin = (CollapseItem *)w.qa.p, *qout = (CollapseItem *)w.qb.p;
     while (nItems) {
         ++maxDepth;
-        ca.in = qin->p; ca.out = qout->p;
+        ca.in = qin; ca.out = qout;
         k_collapse(nItems, ca, s);
         uint32_t ch[4];
         rt_d2h(ch, counters.p, sizeof(ch), s);

@@ -10,6 +10,8 @@
 #include <limits.h>
 #include <algorithm>
 #include <chrono>
+#include <thread>
+#include <atomic>
 
 namespace yb {
 
@@ -686,57 +688,93 @@ bool Context::flattenAndBuild()
         if (o.is_smooth || (o.base && o.normals_exported)) anySmooth = true;
     }
     if (ntri >= 0x7fffffffu / 3) return fail("scene has too many triangles for 32-bit indexing");
-    std::vector<f4> hv(3 * ntri);
-    std::vector<v3> hn(anySmooth ? 3 * ntri : 0);
-    size_t k = 0;
-    for (std::map<unsigned, MeshObj>::iterator i = meshes.begin(); i != meshes.end(); ++i) {
-        MeshObj &o = i->second;
-        if (!o.visible || o.is_base) continue;
-        const MeshObj &g = o.base ? *o.base : o;
-        const bool inst = o.base != 0;
-        const float *m = o.m;
-        const bool smooth = inst ? (o.is_smooth || o.normals_exported) : o.is_smooth;   // triangle.cc:18 vs :188
-        for (size_t t = 0; t < g.tri_mat.size(); ++t, ++k) {
-            uint32_t info = g.tri_mat[t] & TRI_MAT_MASK;
-            if (smooth) info |= TRI_SMOOTH;
-            for (int c = 0; c < 3; ++c) {
-                const int pi = g.tri_idx[3 * t + c];
-                if (pi < 0 || (size_t)pi >= g.points.size()) return fail("triangle references a vertex that does not exist");
-                v3 pt = g.points[pi];
-                if (inst) pt = v3(m[0] * pt.x + m[1] * pt.y + m[2] * pt.z + m[3], m[4] * pt.x + m[5] * pt.y + m[6] * pt.z + m[7],
-                                  m[8] * pt.x + m[9] * pt.y + m[10] * pt.z + m[11]);      // matrix4.h:92-97
-                f4 &d = hv[3 * k + c];
-                d.x = pt.x; d.y = pt.y; d.z = pt.z; d.w = 0.f;
-                if (anySmooth) {
-                    const int ni = g.tri_nidx[3 * t + c];
-                    const bool has = inst ? (ni > 0) : (ni >= 0);                        // triangle.cc:20-22 vs :190-192
-                    v3 nn(0.f);
-                    if (smooth && has) {
-                        if ((size_t)ni >= g.normals.size()) return fail("triangle references a normal that does not exist");
-                        nn = g.normals[ni];
-                        if (inst) nn = v3(m[0] * nn.x + m[1] * nn.y + m[2] * nn.z, m[4] * nn.x + m[5] * nn.y + m[6] * nn.z, m[8] * nn.x + m[9] * nn.y + m[10] * nn.z);
-                        info |= (TRI_HAS_NA << c);
-                    }
-                    hn[3 * k + c] = nn;
-                }
-            }
-            hv[3 * k].w = i2f((int32_t)k);
-            hv[3 * k + 1].w = i2f((int32_t)info);
+    h_in_v.reserve(3 * ntri + 1); if (anySmooth) h_in_n.reserve(3 * ntri + 1);
+    f4 *hv = h_in_v.p; v3 *hn = h_in_n.p;
+    // work list: (object, first global triangle) in scene order, cut into chunks that host threads fill in parallel
+    struct Chunk { const MeshObj *o; size_t t0, t1, k0; };
+    std::vector<Chunk> chunks;
+    {
+        size_t k = 0;
+        for (std::map<unsigned, MeshObj>::iterator i = meshes.begin(); i != meshes.end(); ++i) {
+            MeshObj &o = i->second;
+            if (!o.visible || o.is_base) continue;
+            const size_t nt = (o.base ? *o.base : o).tri_mat.size();
+            for (size_t t0 = 0; t0 < nt; t0 += 32768) { Chunk c = {&o, t0, std::min(nt, t0 + 32768), k + t0}; chunks.push_back(c); }
+            k += nt;
         }
     }
+    std::atomic<size_t> nextChunk(0);
+    std::atomic<int> bad(0);           // 1: vertex index out of range, 2: normal index out of range
+    auto fill = [&]() {
+        for (;;) {
+            const size_t ci = nextChunk.fetch_add(1);
+            if (ci >= chunks.size()) return;
+            const Chunk &ch = chunks[ci];
+            const MeshObj &o = *ch.o;
+            const MeshObj &g = o.base ? *o.base : o;
+            const bool inst = o.base != 0;
+            const float *m = o.m;
+            const bool smooth = inst ? (o.is_smooth || o.normals_exported) : o.is_smooth;   // triangle.cc:18 vs :188
+            size_t k = ch.k0;
+            for (size_t t = ch.t0; t < ch.t1; ++t, ++k) {
+                uint32_t info = g.tri_mat[t] & TRI_MAT_MASK;
+                if (smooth) info |= TRI_SMOOTH;
+                for (int c = 0; c < 3; ++c) {
+                    const int pi = g.tri_idx[3 * t + c];
+                    if (pi < 0 || (size_t)pi >= g.points.size()) { bad = 1; return; }
+                    v3 pt = g.points[pi];
+                    if (inst) pt = v3(m[0] * pt.x + m[1] * pt.y + m[2] * pt.z + m[3], m[4] * pt.x + m[5] * pt.y + m[6] * pt.z + m[7],
+                                      m[8] * pt.x + m[9] * pt.y + m[10] * pt.z + m[11]);      // matrix4.h:92-97
+                    f4 &d = hv[3 * k + c];
+                    d.x = pt.x; d.y = pt.y; d.z = pt.z; d.w = 0.f;
+                    if (anySmooth) {
+                        const int ni = g.tri_nidx[3 * t + c];
+                        const bool has = inst ? (ni > 0) : (ni >= 0);                        // triangle.cc:20-22 vs :190-192
+                        v3 nn(0.f);
+                        if (smooth && has) {
+                            if ((size_t)ni >= g.normals.size()) { bad = 2; return; }
+                            nn = g.normals[ni];
+                            if (inst) nn = v3(m[0] * nn.x + m[1] * nn.y + m[2] * nn.z, m[4] * nn.x + m[5] * nn.y + m[6] * nn.z, m[8] * nn.x + m[9] * nn.y + m[10] * nn.z);
+                            info |= (TRI_HAS_NA << c);
+                        }
+                        hn[3 * k + c] = nn;
+                    }
+                }
+                hv[3 * k].w = i2f((int32_t)k);
+                hv[3 * k + 1].w = i2f((int32_t)info);
+            }
+        }
+    };
+    {
+        unsigned nth = std::thread::hardware_concurrency();
+        nth = std::max(1u, std::min(std::min(nth, 16u), (unsigned)chunks.size()));
+        std::vector<std::thread> pool;
+        for (unsigned i = 1; i < nth; ++i) pool.emplace_back(fill);
+        fill();
+        for (size_t i = 0; i < pool.size(); ++i) pool[i].join();
+    }
+    if (bad == 1) return fail("triangle references a vertex that does not exist");
+    if (bad == 2) return fail("triangle references a normal that does not exist");
     nTris = (uint32_t)ntri; haveNormals = anySmooth;
+    const auto t1 = std::chrono::steady_clock::now();
     // upload + build
-    DevBuf<f4> in_v; DevBuf<v3> in_n;
+    DevBuf<f4> &in_v = d_in_v; DevBuf<v3> &in_n = d_in_n;
     try {
         in_v.reserve(3 * ntri + 1);
-        rt_h2d(in_v.p, hv.data(), hv.size() * sizeof(f4), stream);
-        if (anySmooth) { in_n.reserve(3 * ntri + 1); rt_h2d(in_n.p, hn.data(), hn.size() * sizeof(v3), stream); }
+        rt_h2d(in_v.p, hv, 3 * ntri * sizeof(f4), stream);
+        if (anySmooth) { in_n.reserve(3 * ntri + 1); rt_h2d(in_n.p, hn, 3 * ntri * sizeof(v3), stream); }
         rt_sync(stream);
-        bvh_build(in_v.p, anySmooth ? in_n.p : 0, nTris, d_nodes, d_tri_v, d_tri_n, nNodes, bvhDepth, boundLo, boundHi, stream);
+        const auto t2 = std::chrono::steady_clock::now();
+        bvh_build(in_v.p, anySmooth ? in_n.p : 0, nTris, d_nodes, d_tri_v, d_tri_n, nNodes, bvhDepth, boundLo, boundHi, bvhScratch, stream);
         d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
         rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
         rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
         rt_sync(stream);
+        if (getenv("YB200_PROFILE_BUILD")) {
+            const auto t3 = std::chrono::steady_clock::now();
+            auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+            fprintf(stderr, "yb200 build: flatten %.1f ms, upload %.1f ms, bvh %.1f ms (%u tris)\n", ms(t0, t1), ms(t1, t2), ms(t2, t3), nTris);
+        }
     } catch (const RtError &e) { return fail(std::string("scene update failed: ") + e.what()); }
     sc.nodes = d_nodes.p; sc.tri_v = d_tri_v.p; sc.tri_n = anySmooth ? d_tri_n.p : 0;
     sc.materials = d_materials.p; sc.lights = d_lights.p;

@@ -30,6 +30,8 @@ struct RtError : public std::runtime_error {
 typedef cudaStream_t rt_stream;
 inline void *rt_malloc(size_t n) { void *p = 0; if (n == 0) n = 16; YB_CUDA_CHECK(cudaMalloc(&p, n)); return p; }
 inline void rt_free(void *p) { if (p) cudaFree(p); }
+inline void *rt_malloc_host(size_t n) { void *p = 0; if (n == 0) n = 16; YB_CUDA_CHECK(cudaHostAlloc(&p, n, cudaHostAllocDefault)); return p; }
+inline void rt_free_host(void *p) { if (p) cudaFreeHost(p); }
 inline void rt_h2d(void *d, const void *h, size_t n, rt_stream s) { if (n) YB_CUDA_CHECK(cudaMemcpyAsync(d, h, n, cudaMemcpyHostToDevice, s)); }
 inline void rt_d2h(void *h, const void *d, size_t n, rt_stream s) { if (n) { YB_CUDA_CHECK(cudaMemcpyAsync(h, d, n, cudaMemcpyDeviceToHost, s)); YB_CUDA_CHECK(cudaStreamSynchronize(s)); } }
 inline void rt_d2d(void *d, const void *s_, size_t n, rt_stream s) { if (n) YB_CUDA_CHECK(cudaMemcpyAsync(d, s_, n, cudaMemcpyDeviceToDevice, s)); }
@@ -39,6 +41,8 @@ inline void rt_sync(rt_stream s) { YB_CUDA_CHECK(cudaStreamSynchronize(s)); }
 typedef void *rt_stream;
 inline void *rt_malloc(size_t n) { void *p = malloc(n ? n : 16); if (!p) throw RtError("malloc failed"); return p; }
 inline void rt_free(void *p) { free(p); }
+inline void *rt_malloc_host(size_t n) { return rt_malloc(n); }
+inline void rt_free_host(void *p) { free(p); }
 inline void rt_h2d(void *d, const void *h, size_t n, rt_stream) { memcpy(d, h, n); }
 inline void rt_d2h(void *h, const void *d, size_t n, rt_stream) { memcpy(h, d, n); }
 inline void rt_d2d(void *d, const void *s_, size_t n, rt_stream) { memmove(d, s_, n); }
@@ -58,6 +62,18 @@ struct DevBuf {
     void reserve(size_t n) { if (n > cap) { rt_free(p); p = 0; p = (T *)rt_malloc(n * sizeof(T)); cap = n; } }
     void release() { rt_free(p); p = 0; cap = 0; }
     size_t bytes() const { return cap * sizeof(T); }
+};
+
+// Pinned host staging that only grows (uploads from it run at full PCIe rate and never touch the allocator twice).
+template <class T>
+struct HostBuf {
+    T *p;
+    size_t cap;
+    HostBuf() : p(0), cap(0) {}
+    ~HostBuf() { rt_free_host(p); }
+    HostBuf(const HostBuf &) = delete;
+    HostBuf &operator=(const HostBuf &) = delete;
+    void reserve(size_t n) { if (n > cap) { rt_free_host(p); p = 0; p = (T *)rt_malloc_host(n * sizeof(T)); cap = n; } }
 };
 
 // ---- kernel definition ------------------------------------------------------------------------------

@@ -62,6 +62,17 @@ struct Stats {
 
 struct RenderBuffers;   // wavefront queues (yb_render.cu)
 
+// Scratch of the BVH build, kept across builds so that a rebuild (animation, the bench's host-to-host step) never
+// goes through cudaMalloc / cudaFree, which serialise with the whole device.
+struct BvhScratch {
+    DevBuf<int32_t> ob, left, right, cnt, parent, ref, ref2, nn;
+    DevBuf<uint64_t> keys, keys2;
+    DevBuf<uint32_t> idx, idx2, flag, pos, nodeCounter, counters;
+    DevBuf<v3> nlo, nhi, lo, hi, lo2, hi2;
+    DevBuf<char> sortTmp, scanTmp;
+    DevBuf<uint64_t> qa, qb;          // collapse work items (2 x int32 each)
+};
+
 struct Context {
     std::string err;
     int verbosity;
@@ -88,6 +99,9 @@ struct Context {
     // device-side scene
     DevBuf<BvhNode> d_nodes; DevBuf<f4> d_tri_v; DevBuf<v3> d_tri_n; DevBuf<Material> d_materials; DevBuf<Light> d_lights;
     DevBuf<uint32_t> d_traceCounter;   // ray-fetch counter of the persistent traversal kernels
+    DevBuf<f4> d_in_v; DevBuf<v3> d_in_n;             // flattened geometry in scene order (input of the build)
+    HostBuf<f4> h_in_v; HostBuf<v3> h_in_n;           // its pinned host staging
+    BvhScratch bvhScratch;
     uint32_t nTris, nNodes, bvhDepth; bool haveNormals;
     v3 boundLo, boundHi;
     SceneDev sc;                     // filled by updateScene / setupRender
@@ -133,7 +147,7 @@ static const uintptr_t HANDLE_MAT_TAG = 0x4d000000u;
 
 // ---- GPU stages
 void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &nodes, DevBuf<f4> &out_v, DevBuf<v3> &out_n,
-               uint32_t &nNodes, uint32_t &maxDepth, v3 &boundLo, v3 &boundHi, rt_stream s);
+               uint32_t &nNodes, uint32_t &maxDepth, v3 &boundLo, v3 &boundHi, BvhScratch &w, rt_stream s);
 // rays/out are DEVICE pointers; mode = TRACE_*; out layout as documented in include/yb200.h
 void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int shadow_depth, void *d_out);
 // accumulate the tiles of (rank, world) of one frame into d_film (w*h*5 floats, raw sums)
