@@ -480,7 +480,8 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
         std::swap(qin, qout);
     }
     rt_sync(s);
-    if (maxDepth > YB_STACK_SIZE - 2) throw RtError("bvh_build: tree deeper than the traversal stack");
+    // a level can leave two stack entries behind (the rest of its node group + a postponed triangle group)
+    if (2 * maxDepth > YB_STACK_SIZE - 2) throw RtError("bvh_build: tree deeper than the traversal stack");
 }
 
 }  // namespace yb

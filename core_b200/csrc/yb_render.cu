@@ -636,6 +636,13 @@ static uint32_t tri_threshold()
     return v < 1u ? 1u : (v > 32u ? 32u : v);
 }
 
+static void trace_tuning(FastJob &j)
+{
+    static const uint32_t burst = (uint32_t)env_size("YB200_BURST", 6), idle = (uint32_t)env_size("YB200_REFILL_IDLE", 8);
+    j.triThreshold = tri_threshold(); j.oneBits = 0x3F800000u;
+    j.burst = burst < 1u ? 1u : burst; j.refillIdle = idle < 1u ? 1u : (idle > 32u ? 32u : idle);
+}
+
 bool render_film_device(Context &c, float *d_film, int rank, int world, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user)
 {
     if (!c.sceneReady) return c.fail("render: scene not updated");
@@ -729,7 +736,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                 tc.start();
                 if (useFast) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task); j.n = (uint32_t)M;
-                    j.counter = rb.counters.p + 2; j.out = a.hits; j.acc = a.acc; j.nNodes = c.sc.nNodes; j.triThreshold = tri_threshold();
+                    j.counter = rb.counters.p + 2; j.out = a.hits; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j);
                     launch_trace_fast<false, OUT_HITS>(j, s);
                 } else
                     k_trace_closest((uint32_t)M, a, s);
@@ -746,7 +753,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                 tsh.start();
                 if (useFast && !I.trShad) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask); j.n = cnt[1];
-                    j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; j.triThreshold = tri_threshold();
+                    j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j);
                     launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
                 } else
                     k_trace_shadow(cnt[1], a, s);
@@ -793,7 +800,7 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
         if (useFast && mode != TRACE_TSHADOW) {
             c.d_traceCounter.reserve(4);
             FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)(ta.rays + o); j.stride = sizeof(Ray); j.n = m;
-            j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; j.triThreshold = tri_threshold();
+            j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; trace_tuning(j);
             if (mode == TRACE_CLOSEST) { j.out = (ClosestOut *)d_out + o; launch_trace_fast<false, OUT_CLOSEST_PRIM>(j, c.stream); }
             else { j.out = (int32_t *)d_out + o; launch_trace_fast<true, OUT_SHADOW_FLAG>(j, c.stream); }
             continue;

@@ -93,6 +93,8 @@ struct FastJob {
     void *out;               // OUT_HITS: Hit[n]; OUT_SHADOW_FLAG: int32[n]; OUT_CLOSEST_PRIM: {prim,t,b1,b2}[n]
     f4 *acc;                 // OUT_SHADOW_ACC: ShadowTask{ray, c, sid}: acc[sid].rgb += c when unoccluded
     uint32_t nNodes;
+    uint32_t oneBits;        // 0x3F800000 (see plane_f)
+    uint32_t burst, refillIdle;   // traversal steps between refill checks; idle lanes that trigger a refill
     uint32_t triThreshold;   // triangle phase runs when this many lanes (or as many as still have node work) hold a triangle group
 };
 
@@ -107,7 +109,10 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
     return r;
 #endif
 }
-__device__ __forceinline__ float plane_f(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x3F800000u, sel)); }
+// byte j of w into the top mantissa byte of 1.0f.  `one` (= 0x3F800000) arrives as a kernel parameter rather than a
+// literal so that it lives in ONE register and the selector becomes the PRMT immediate; with the literal, ptxas
+// encodes 0x3F800000 as the immediate and re-materialises the selector in a register before each of the 48 PRMTs.
+__device__ __forceinline__ float plane_f(uint32_t w, uint32_t one, uint32_t sel) { return __uint_as_float(__byte_perm(w, one, sel)); }
 
 template <bool ANYHIT, int OUT>
 __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
@@ -116,6 +121,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
     uint2 lstack[YB_LSTACK];
     const unsigned lane = threadIdx.x & 31u;   // 0 in the emulator
     const unsigned FULL = YB_FULLMASK;
+    const uint32_t one = job.oneBits;
 
     bool active = false, exhausted = false;
     uint32_t rayIdx = 0;
@@ -125,12 +131,13 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
     uint2 ng = make_uint2(0, 0);      // node group: x = child base, y = ordered hit bits << 24 | imask
     uint2 tg = make_uint2(0, 0);      // triangle group: x = triangle base, y = hit bits (0..23)
     int hitTri = -1; float hitT = 0, hitU = 0, hitV = 0;
+    bool tgFresh = false;
 
     for (;;) {
         // ------------------------------------------------------------ refill idle lanes (warp-converged here)
         __syncwarp();
         const unsigned idle = __ballot_sync(FULL, !active);
-        if (idle == FULL || (!exhausted && __popc(idle) >= YB_REFILL_IDLE)) {
+        if (idle == FULL || (!exhausted && __popc(idle) >= (int)job.refillIdle)) {
             if (!exhausted) {
                 const int nIdle = __popc(idle);
                 const int leader = __ffs(idle) - 1;
@@ -177,7 +184,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
 
         // ------------------------------------------------------------ a burst of traversal steps
 #pragma unroll 1
-        for (int burst = 0; burst < 6; ++burst) {
+        for (int burst = 0; burst < (int)job.burst; ++burst) {
             bool done = false;
             // ---- node phase: lanes without pending triangles pop / descend one node
             if (active && tg.y == 0u) {
@@ -229,9 +236,9 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             const uint32_t sel = 0x7604u | ((uint32_t)j << 4);
-                            const float t0x = fmaf(plane_f(wnx, sel), Ax, Bnx), t1x = fmaf(plane_f(wfx, sel), Ax, Bfx);
-                            const float t0y = fmaf(plane_f(wny, sel), Ay, Bny), t1y = fmaf(plane_f(wfy, sel), Ay, Bfy);
-                            const float t0z = fmaf(plane_f(wnz, sel), Az, Bnz), t1z = fmaf(plane_f(wfz, sel), Az, Bfz);
+                            const float t0x = fmaf(plane_f(wnx, one, sel), Ax, Bnx), t1x = fmaf(plane_f(wfx, one, sel), Ax, Bfx);
+                            const float t0y = fmaf(plane_f(wny, one, sel), Ay, Bny), t1y = fmaf(plane_f(wfy, one, sel), Ay, Bfy);
+                            const float t0z = fmaf(plane_f(wnz, one, sel), Az, Bnz), t1z = fmaf(plane_f(wfz, one, sel), Az, Bfz);
                             const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tlo));
                             const float tf = fminf(fminf(t1x, t1y), fminf(t1z, thi));
                             if (tn <= tf) {
@@ -242,11 +249,13 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                     }
                     ng = make_uint2(n1.x, (hitmask & 0xff000000u) | (n0.w >> 24));
                     tg = make_uint2(n1.y, hitmask & 0x00ffffffu);
+                    tgFresh = true;
                 }
             }
-            // ---- triangle phase (postponed, warp-synchronous): lanes holding a triangle group wait until enough of
-            //      the warp holds one, then every such lane tests ONE triangle.  Keeps the per-ray order (a lane
-            //      never descends past untested triangles) and turns a 2-3 lane loop into one wide pass.
+            // ---- triangle phase (warp-synchronous, postponed): every lane holding a triangle group tests ONE triangle,
+            //      but only when enough of the warp holds one (or nobody has node work left).  Otherwise a lane whose
+            //      group is fresh from the node step parks it on its stack and keeps descending (Ylitie et al. 2017,
+            //      "triangle postponing"); a group that came back from the stack just waits for the next pass.
             const bool hasTri = active && !done && tg.y != 0u;
             const unsigned triMask = __ballot_sync(FULL, hasTri);
             if (triMask != 0u) {
@@ -269,8 +278,13 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                             else { thi = t; hitTri = (int)ti; hitT = t; hitU = u; hitV = v; }
                         }
                     }
+                } else if (hasTri && tgFresh) {
+                    if (sp < YB_SSTACK) sstack[sp][threadIdx.x] = tg; else lstack[sp - YB_SSTACK] = tg;
+                    ++sp;
+                    tg.y = 0u;
                 }
             }
+            tgFresh = false;
             if (done) {
                 active = false;
                 if (OUT == OUT_HITS) ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(hitTri), hitT, hitU, hitV);
