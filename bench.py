@@ -21,9 +21,9 @@ import time
 
 import numpy as np
 
-# stdout carries exactly one JSON line: keep NCCL's version banner (printed at NCCL_DEBUG=VERSION/INFO) off it
-if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO"):
-    os.environ["NCCL_DEBUG_FILE"] = os.environ.get("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly one JSON line: NCCL prints its version banner there whenever NCCL_DEBUG is set
+if os.environ.get("NCCL_DEBUG"):
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
