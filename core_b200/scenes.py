@@ -221,15 +221,21 @@ def icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=64, bounc
 
 
 # ----------------------------------------------------------------------------- C3: triangle soup + AO
-def triangle_soup(yi, n_tris=10_000_000, width=512, height=512, spp=1, ao_samples=32, ao_distance=0.1,
-                  seed=2, threads=1, **render_extra):
-    """Random triangles: centres uniform in [-1,1]^3, edges N(0, 0.01^2); directlighting with AO —
-    the IntersectS any-hit stress (BASELINE.json configs[2])."""
+def soup_mesh(n_tris, seed=2):
+    """(verts, tris) of the random soup: centres uniform in [-1,1]^3, edge vectors N(0, 0.01^2)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     c = rng.uniform(-1, 1, (n_tris, 3)).astype(np.float32)
     e = rng.normal(0, 0.01, (n_tris, 3, 3)).astype(np.float32)
     V = (c[:, None, :] + e).reshape(-1, 3)
     F = np.arange(3 * n_tris, dtype=np.int32).reshape(-1, 3)
+    return V, F
+
+
+def triangle_soup(yi, n_tris=10_000_000, width=512, height=512, spp=1, ao_samples=32, ao_distance=0.1,
+                  seed=2, threads=1, **render_extra):
+    """Random triangles: centres uniform in [-1,1]^3, edges N(0, 0.01^2); directlighting with AO —
+    the IntersectS any-hit stress (BASELINE.json configs[2])."""
+    V, F = soup_mesh(n_tris, seed)
     yi.startScene(0)
     mat = create(yi, "material", "soup", type="shinydiffusemat", color=(0.8, 0.8, 0.8, 1.0), diffuse_reflect=1.0)
     yi.startGeometry()
@@ -328,3 +334,74 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     std_volintegr(yi)
     set_render(yi, width, height, spp=spp, threads=threads, **render_extra)
     return len(order) * len(f0) + 4
+
+
+# ----------------------------------------------------------------------------- C5: tessellated terrain
+def _hash2(ix, iy, seed):
+    """Integer lattice hash -> [0, 1) (uint32 arithmetic, identical on every machine)."""
+    h = (ix.astype(np.uint32) * np.uint32(0x8da6b343)) ^ (iy.astype(np.uint32) * np.uint32(0xd8163841)) ^ np.uint32(seed * 0x9e3779b1 & 0xffffffff)
+    h ^= h >> np.uint32(15); h *= np.uint32(0x2c1b3c6d)
+    h ^= h >> np.uint32(12); h *= np.uint32(0x297a2d39)
+    h ^= h >> np.uint32(15)
+    return (h >> np.uint32(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)
+
+
+def value_noise(x, y, seed):
+    x0 = np.floor(x); y0 = np.floor(y)
+    fx = (x - x0).astype(np.float32); fy = (y - y0).astype(np.float32)
+    ix = x0.astype(np.int64); iy = y0.astype(np.int64)
+    sx = fx * fx * (3 - 2 * fx); sy = fy * fy * (3 - 2 * fy)
+    a = _hash2(ix, iy, seed); b = _hash2(ix + 1, iy, seed); c = _hash2(ix, iy + 1, seed); d = _hash2(ix + 1, iy + 1, seed)
+    return (a + (b - a) * sx) + ((c + (d - c) * sx) - (a + (b - a) * sx)) * sy
+
+
+def terrain_heights(grid, extent=100.0, octaves=5, seed=3, amplitude=8.0):
+    """Heights of a (grid+1)^2 vertex lattice over [-extent/2, extent/2]^2: fBm of value noise."""
+    n = grid + 1
+    u = np.linspace(0.0, 8.0, n, dtype=np.float32)
+    z = np.zeros((n, n), np.float32)
+    amp, freq = 0.5, 1.0
+    for o in range(octaves):
+        X, Y = np.meshgrid(u * np.float32(freq), u * np.float32(freq), indexing="xy")
+        z += np.float32(amp) * value_noise(X, Y, seed + o)
+        amp *= 0.5; freq *= 2.0
+    return z * np.float32(amplitude)
+
+
+def terrain_mesh(grid, extent=100.0, **kw):
+    """(verts, tris, heights): 2*grid^2 triangles, cell (i,j) -> triangles 2*(j*grid+i) + {0,1}."""
+    n = grid + 1
+    z = terrain_heights(grid, extent, **kw)
+    xs = np.linspace(-extent / 2, extent / 2, n, dtype=np.float32)
+    V = np.empty((n, n, 3), np.float32)
+    V[..., 0] = xs[None, :]; V[..., 1] = xs[:, None]; V[..., 2] = z
+    i = np.arange(grid, dtype=np.int32)
+    a = (i[None, :] + i[:, None] * n).reshape(-1)
+    F = np.empty((grid * grid, 2, 3), np.int32)
+    F[:, 0, 0] = a; F[:, 0, 1] = a + 1; F[:, 0, 2] = a + n + 1
+    F[:, 1, 0] = a; F[:, 1, 1] = a + n + 1; F[:, 1, 2] = a + n
+    return V.reshape(-1, 3), F.reshape(-1, 3), z
+
+
+def terrain(yi, grid=5000, width=3840, height=2160, spp=1024, bounces=4, extent=100.0, seed=3, threads=1,
+            integrator="pathtracing", **render_extra):
+    """Tessellated fBm terrain, 2*grid^2 triangles (grid=5000 -> 50 M), sun + constant background,
+    pathtracing (BASELINE.json configs[4])."""
+    V, F, _ = terrain_mesh(grid, extent, seed=seed)
+    yi.startScene(0)
+    mat = create(yi, "material", "soil", type="shinydiffusemat", color=(0.55, 0.5, 0.4, 1.0), diffuse_reflect=0.9)
+    yi.startGeometry()
+    add_mesh(yi, V, F, mat)
+    yi.endGeometry()
+    create(yi, "light", "sun", type="sunlight", direction=(0.4, -0.3, 0.6), color=(1.0, 0.96, 0.9, 1.0), power=1.5, angle=0.6, samples=2)
+    e = extent
+    create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -0.62 * e, 0.35 * e)}, to=(0.0, 0.0, 0.02 * e),
+           up=(0.0, -0.62 * e, 0.35 * e + 1.0), resx=width, resy=height, focal=1.0)
+    create(yi, "background", "bg", type="constant", color=(0.55, 0.65, 0.85, 1.0))
+    ip = dict(type=integrator, raydepth=3)
+    if integrator == "pathtracing":
+        ip.update(bounces=bounces, path_samples=1)
+    create(yi, "integrator", "default", **ip)
+    std_volintegr(yi)
+    set_render(yi, width, height, spp=spp, threads=threads, **render_extra)
+    return 2 * grid * grid

@@ -22,12 +22,15 @@ IMAGE_CASES = {
     "c4_materials_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting")),
     "c4_materials_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
                                                           integ_params=dict(transpShad=True, shadowDepth=4))),
+    # configs[4] (reduced): tessellated fBm terrain, sun + sky, pathtracing 4 bounces
+    "c5_terrain_path": (scenes.terrain, dict(grid=60, width=64, height=36, spp=2, bounces=4)),
 }
 
 RAY_CASES = {
     "rays_cornell": (scenes.cornell_box, dict(width=32, height=32, spp=1)),
     "rays_field": (scenes.icosphere_field, dict(n_tris=20000, subdiv=2, width=64, height=36, spp=1)),
     "rays_soup": (scenes.triangle_soup, dict(n_tris=5000, width=32, height=32, spp=1)),
+    "rays_terrain": (scenes.terrain, dict(grid=48, width=32, height=18, spp=1)),
 }
 
 
@@ -37,6 +40,8 @@ def ray_batch(name, n=4096, seed=7):
     o = rng.uniform(-1.0, 1.0, (n, 3))
     if name == "rays_field":
         o = o * np.array([8.0, 8.0, 1.0]) + np.array([0.0, 0.0, 2.0])
+    if name == "rays_terrain":
+        o = o * np.array([45.0, 45.0, 6.0]) + np.array([0.0, 0.0, 6.0])
     d = rng.normal(size=(n, 3))
     d /= np.linalg.norm(d, axis=1, keepdims=True)
     rays = np.zeros((n, 8), np.float32)

@@ -54,8 +54,10 @@ def kat(lib):
                         hal_starts=starts, hal=hal, trig_x=x, fsin=fsin, fcos=fcos, pow_a=pa, pow_b=pb, fpow=fpow)
 
 
-def rays():
+def rays(only=None):
     for name, (fn, kw) in cases.RAY_CASES.items():
+        if only and name not in only:
+            continue
         yi = refapi.RefInterface(); yi.setVerbosityMute()
         fn(yi, **kw)
         yi.updateScene()
@@ -66,8 +68,10 @@ def rays():
         print(name, "hits", int((closest["prim"] >= 0).sum()), "shadowed", int(shadow.sum()))
 
 
-def images():
+def images(only=None):
     for name, (fn, kw) in cases.IMAGE_CASES.items():
+        if only and name not in only:
+            continue
         yi = refapi.RefInterface(); yi.setVerbosityMute()
         fn(yi, threads=1, **kw)
         img = yi.render(kw["width"], kw["height"])
@@ -77,6 +81,8 @@ def images():
 
 if __name__ == "__main__":
     assert refapi.have_ref(), "build oracle/_ref first (make -C oracle ref)"
-    kat(refapi.ref_lib())
-    rays()
-    images()
+    only = set(sys.argv[1:])      # optional: regenerate just the named cases (fixtures are deterministic)
+    if not only:
+        kat(refapi.ref_lib())
+    rays(only)
+    images(only)

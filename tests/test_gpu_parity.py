@@ -123,3 +123,68 @@ def test_tile_partition_equals_single_frame():
     torch.cuda.synchronize()
     four = yi.filmResolve(total, 96, 64)
     assert np.allclose(one, four, rtol=2e-5, atol=1e-6)
+
+
+def test_full_size_soup_10m_triangles():
+    """BASELINE.json configs[2] geometry (10 M random triangles, any-hit stress): brute-force oracle on a few rays,
+    closest/any-hit consistency on many, and the AO frame renders."""
+    n = 10_000_000
+    yi = YafrayInterface()
+    assert scenes.triangle_soup(yi, n_tris=n, width=128, height=128, spp=1, ao_samples=8, ao_distance=0.1) == n
+    yi.updateScene()
+    st = yi.getStats()
+    assert st["n_triangles"] == n and 0 < st["n_bvh_nodes"] < n
+    rays = cases.ray_batch("rays_soup", n=100000, seed=5)
+    hit = yi.traceBatch(rays, 0)
+    h = hit["prim"] >= 0
+    assert 0.2 < h.mean() <= 1.0
+    # any-hit uses origin + tmin*dir and tmax - 2*tmin (scene.cc:884-889): identical to closest-hit for tmin = 0
+    r0 = rays.copy(); r0[:, 3] = 0.0
+    assert np.array_equal(yi.traceBatch(r0, 1).astype(bool), yi.traceBatch(r0, 0)["prim"] >= 0)
+    # 48 rays against all 10 M triangles with the plain-C oracle (same Moller-Trumbore arithmetic, no accelerator)
+    V, F = scenes.soup_mesh(n)
+    tris = V.reshape(n, 3, 3)
+    sub = rays[:48]
+    want, ties = op.closest(tris, sub)
+    bad, terr, berr, ntie = cases.compare_hits(want, hit[:48], ties)
+    assert bad == 0 and terr <= 1e-6 and berr <= 1e-6, (bad, terr, berr, ntie)
+    img = yi.render(128, 128)
+    assert np.isfinite(img).all() and img[..., :3].mean() > 0.01
+
+
+def test_full_size_terrain_50m_triangles():
+    """BASELINE.json configs[4] geometry (50 M-triangle terrain): a heightfield has a closed-form answer for vertical
+    rays — the triangle is known from the cell and the diagonal side, t from the plane through its vertices."""
+    grid = 5000
+    yi = YafrayInterface()
+    n = scenes.terrain(yi, grid=grid, width=160, height=90, spp=1, bounces=2)
+    assert n == 2 * grid * grid
+    yi.updateScene()
+    st = yi.getStats()
+    assert st["n_triangles"] == n
+    V, F, z = scenes.terrain_mesh(grid)
+    xs = V[: grid + 1, 0].astype(np.float64)
+    rng = np.random.Generator(np.random.PCG64(9))
+    m = 200000
+    i = rng.integers(0, grid, m); j = rng.integers(0, grid, m)
+    fx = rng.uniform(0.05, 0.95, m); fy = rng.uniform(0.05, 0.95, m)
+    keep = np.abs(fx - fy) > 0.05
+    i, j, fx, fy = i[keep], j[keep], fx[keep], fy[keep]
+    x = xs[i] * (1 - fx) + xs[i + 1] * fx
+    y = xs[j] * (1 - fy) + xs[j + 1] * fy
+    rays = np.zeros((len(i), 8), np.float32)
+    rays[:, 0] = x; rays[:, 1] = y; rays[:, 2] = 100.0; rays[:, 6] = -1.0; rays[:, 7] = -1.0
+    # recompute the cell-local coordinates from the float32 ray origin, as the kernel sees it
+    fx = (rays[:, 0].astype(np.float64) - xs[i]) / (xs[i + 1] - xs[i]); fy = (rays[:, 1].astype(np.float64) - xs[j]) / (xs[j + 1] - xs[j])
+    z00 = z[j, i].astype(np.float64); z10 = z[j, i + 1]; z11 = z[j + 1, i + 1]; z01 = z[j + 1, i]
+    lower = fy < fx                     # triangle 0 of the cell: (i,j) (i+1,j) (i+1,j+1)
+    zt = np.where(lower, z00 + fx * (z10 - z00) + fy * (z11 - z10), z00 + fx * (z11 - z01) + fy * (z01 - z00))
+    want_prim = 2 * (j * grid + i) + np.where(lower, 0, 1)
+    hit = yi.traceBatch(rays, 0)
+    assert np.array_equal(hit["prim"], want_prim.astype(np.int32))
+    assert np.allclose(hit["t"], 100.0 - zt, rtol=1e-5, atol=1e-4)
+    assert np.all(yi.traceBatch(rays, 1) == 1)
+    up = rays.copy(); up[:, 6] = 1.0
+    assert np.all(yi.traceBatch(up, 0)["prim"] < 0)
+    img = yi.render(160, 90)
+    assert np.isfinite(img).all() and img[..., :3].mean() > 0.05
