@@ -29,8 +29,10 @@ def test_image_parity_golden(name):
     img = yi.render(kw["width"], kw["height"])
     ref = np.load(os.path.join(G, "img_" + name + ".npz"))["img"]
     rel, psnr, da = cases.compare_images(ref, img)
-    # north_star: <= 1 % mean relative error, PSNR >= 40 dB.  Held far tighter: float noise of atomics/FMA only.
-    assert rel <= 1e-3 and psnr >= 60.0 and da <= 1e-3, (rel, psnr, da)
+    # north_star: <= 1 % mean relative error, PSNR >= 40 dB.  The library is built with -fmad=false so device
+    # arithmetic rounds like the reference's SSE code; what is left is the summation order of the film atomics.
+    # Measured on B200: rel <= 2.2e-7, PSNR 128-164 dB on all ten cases.
+    assert rel <= 1e-5 and psnr >= 100.0 and da <= 1e-5, (rel, psnr, da)
     st = yi.getStats()
     assert st["kernel_launches"] > 0 and st["rays_closest"] > 0
 
