@@ -272,8 +272,18 @@ def main():
     peak, peak_src = measured_peak_hbm()
     rays_rank = rays_total / world                       # max-over-ranks kernel time vs this rank's share (balanced tiles)
     achieved = rays_rank * A / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else None
+    traffic, traffic_note = None, None
+    tfiles = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if "traffic" in f and f.endswith(".json"))
+    if tfiles and args.workload == "c2_field_1M_1080p_64spp":
+        tj = json.load(open(os.path.join(ROOT, "profiles", tfiles[-1])))
+        nl = len(tj["launches"])
+        traffic = tj["dram_bytes"] / nl
+        traffic_note = ("ncu dram__bytes_read+write per traversal launch, mean of the %d launches of one frame of this scene at the same "
+                        "batch size (profiles/%s); algorithmic bytes of those launches: %.3g per launch - the 59 MB of nodes+triangles "
+                        "stay in L2 (%.0f B/ray reach DRAM, %.0f B/ray reach L2)" %
+                        (nl, tfiles[-1], tj["rays"] * tj["algorithmic_bytes_per_ray"] / nl, tj["dram_bytes_per_ray"], tj["l2_bytes_per_ray"]))
     roofline = {"bound": "hbm", "kernel": "k_trace_closest + k_trace_shadow (BVH8 traversal)", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
+                "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_note": traffic_note, "peak_source": peak_src,
                 "algorithmic_bytes_per_ray": A, "trace_ms_per_step": trace_ms / args.steps,
                 "grays_per_s_in_trace_kernels": rays_rank / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else None,
                 "kernel_ms_per_step": {"trace_closest": float(ktime[0]) / args.steps, "trace_shadow": float(ktime[1]) / args.steps,

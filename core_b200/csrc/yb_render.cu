@@ -708,6 +708,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
         a.sc = c.sc; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
         a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
         const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
+        const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
         const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;
@@ -759,6 +760,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                     k_trace_shadow(cnt[1], a, s);
                 tsh.stop();
                 raysClosest += M; raysShadow += cnt[1];
+                if (logWaves) fprintf(stderr, "yb200 wave: batch %d closest %zu shadow %u children %u\n", b, M, cnt[1], cnt[0]);
                 msClosest += tc.ms(); msShade += tsd.ms(); if (cnt[1]) msShadow += tsh.ms();
                 if (whole) { std::swap(pool, alt); top = cnt[0]; }
                 else {
