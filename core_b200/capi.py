@@ -78,6 +78,7 @@ _CTX_FUNCS = {
 # only libyb200.so has these (the multi-GPU film path, counters, stream)
 _PRODUCT_ONLY = {
     "render_film": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "render_film_pass": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "film_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "get_stats": (C.c_int, [C.POINTER(Stats)]),
     "cuda_stream": (C.c_void_p, []),

@@ -115,7 +115,15 @@ int yb200_render_film(yb200_ctx *ctx, float *dev_film, int rank, int world, cons
     GUARD_BEGIN
     CTX.abortFlag = 0;
     if (!CTX.updateScene()) return 0;
-    return render_film_device(CTX, dev_film, rank, world, cb ? cb->should_abort : 0, cb ? cb->progress : 0, cb ? cb->user : 0) ? 1 : 0;
+    return render_film_device(CTX, dev_film, 0, rank, world, -1, cb ? cb->should_abort : 0, cb ? cb->progress : 0, cb ? cb->user : 0) ? 1 : 0;
+    GUARD_END(0)
+}
+int yb200_render_film_pass(yb200_ctx *ctx, float *dev_film, const float *dev_film_all, int rank, int world, int pass, const yb200_callbacks *cb)
+{
+    GUARD_BEGIN
+    if (pass == 0) CTX.abortFlag = 0;
+    if (!CTX.updateScene()) return 0;
+    return render_film_device(CTX, dev_film, dev_film_all, rank, world, pass, cb ? cb->should_abort : 0, cb ? cb->progress : 0, cb ? cb->user : 0) ? 1 : 0;
     GUARD_END(0)
 }
 int yb200_film_resolve(yb200_ctx *ctx, const float *dev_film, float *rgba, int on_device)
@@ -140,7 +148,7 @@ int yb200_render(yb200_ctx *ctx, float *rgba, int width, int height, const yb200
     const size_t npx = (size_t)CTX.sc.film.w * CTX.sc.film.h;
     ctx->io.film.reserve(npx * 5);
     rt_memset(ctx->io.film.p, 0, npx * 5 * sizeof(float), CTX.stream);
-    if (!render_film_device(CTX, ctx->io.film.p, 0, 1, cb ? cb->should_abort : 0, cb ? cb->progress : 0, cb ? cb->user : 0)) return 0;
+    if (!render_film_device(CTX, ctx->io.film.p, 0, 0, 1, -1, cb ? cb->should_abort : 0, cb ? cb->progress : 0, cb ? cb->user : 0)) return 0;
     return yb200_film_resolve(ctx, ctx->io.film.p, rgba, 0);
     GUARD_END(0)
 }

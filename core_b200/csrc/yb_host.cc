@@ -627,7 +627,6 @@ bool Context::setupRender(int width, int height)   // environment.cc:596-694 + c
     p.get("AA_passes", AA_passes); p.get("AA_minsamples", AA_samples); AA_inc = AA_samples; p.get("AA_inc_samples", AA_inc);
     p.get("AA_threshold", AA_threshold); p.get("z_channel", z_chan);
     if (z_chan) return fail("z_channel (depth map output) is not supported yet");
-    if (AA_passes > 1) return fail("AA_passes > 1 (adaptive multi-pass anti-aliasing) is not supported yet");
     // createImageFilm
     int w = 320, h = 240, xstart = 0, ystart = 0, tileSize = 32; float filt_sz = 1.5f, gamma = 1.f; bool clamp = false, premult = false;
     std::string ftype; bool haveF = p.get("filter_type", ftype);
@@ -653,6 +652,7 @@ bool Context::setupRender(int width, int height)   // environment.cc:596-694 + c
     f.correctGamma = (gamma > 0 && fabsf(1.f - gamma) > 0.001f) ? 1 : 0;
     f.tileSize = tileSize > 0 ? tileSize : 32;
     f.AA_passes = AA_passes; f.n_samples = AA_samples > 0 ? AA_samples : 1; f.pass_offs = 0;
+    f.AA_inc_samples = AA_inc; f.AA_threshold = (float)AA_threshold;
     return true;
 }
 

@@ -591,13 +591,37 @@ YB_KERNEL(k_batch_tshadow, TraceArgs)
     ((TShadowOut *)a.out)[tid] = o;
 }
 
+// imageFilm_t::nextPass (imagefilm.cc:213-263): flag the pixels whose normalised brightness differs from a neighbour's
+// by AA_threshold or more; both pixels of such a pair are resampled in the next pass.  film = raw sums of ALL ranks.
+struct FlagArgs { const float *film; unsigned char *flags; int32_t w, h; float thresh; };
+YB_D float film_bri(const FlagArgs &a, int x, int y, bool absv)
+{
+    const float *p = a.film + ((size_t)x + (size_t)a.w * (size_t)y) * 5;
+    const float wgt = p[4];
+    float r = 0.f, g = 0.f, b = 0.f;
+    if (wgt > 0.f) { const float f = (float)(1.0 / (double)wgt); r = p[0] * f; g = p[1] * f; b = p[2] * f; }   // pixel_t::normalized, color.h:329-333
+    if (absv) { r = fabsf(r); g = fabsf(g); b = fabsf(b); }
+    return 0.2126f * r + 0.7152f * g + 0.0722f * b;                                                         // color.h:79-80
+}
+YB_KERNEL(k_aa_flags, FlagArgs)
+{
+    const int x = (int)(tid % (uint32_t)(a.w - 1)), y = (int)(tid / (uint32_t)(a.w - 1));
+    const float c = film_bri(a, x, y, true);
+    bool need = false;
+    if (fabsf(c - film_bri(a, x + 1, y, false)) >= a.thresh) { need = true; a.flags[(size_t)(x + 1) + (size_t)a.w * y] = 1; }
+    if (fabsf(c - film_bri(a, x, y + 1, false)) >= a.thresh) { need = true; a.flags[(size_t)x + (size_t)a.w * (y + 1)] = 1; }
+    if (fabsf(c - film_bri(a, x + 1, y + 1, false)) >= a.thresh) { need = true; a.flags[(size_t)(x + 1) + (size_t)a.w * (y + 1)] = 1; }
+    if (x > 0 && fabsf(c - film_bri(a, x - 1, y + 1, false)) >= a.thresh) { need = true; a.flags[(size_t)(x - 1) + (size_t)a.w * (y + 1)] = 1; }
+    if (need) a.flags[(size_t)x + (size_t)a.w * y] = 1;
+}
+
 // ================================================================================================ host driver
 struct RenderBuffers {
     DevBuf<Task> poolA, poolB;
     DevBuf<Hit> hits;
     DevBuf<ShadowTask> shadow;
     DevBuf<uint32_t> counters, order, bins;
-    DevBuf<unsigned char> keys;
+    DevBuf<unsigned char> keys, aaFlags;
     DevBuf<f4> acc;
     DevBuf<uint32_t> pix;
     DevBuf<float> film, rgba;
@@ -643,7 +667,8 @@ static void trace_tuning(FastJob &j)
     j.burst = burst < 1u ? 1u : burst; j.refillIdle = idle < 1u ? 1u : (idle > 32u ? 32u : idle);
 }
 
-bool render_film_device(Context &c, float *d_film, int rank, int world, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user)
+bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int rank, int world, int onlyPass,
+                        int (*should_abort)(void *), void (*progress)(void *, int, int), void *user)
 {
     if (!c.sceneReady) return c.fail("render: scene not updated");
     if (world < 1 || rank < 0 || rank >= world) return c.fail("render_film: bad rank/world");
@@ -655,7 +680,7 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
         const Integrator &I = c.sc.integ;
         auto tstart = std::chrono::steady_clock::now();
         // ---- owned pixels: tiles of imageSpliter_t (imagesplitter.cc:29-52) dealt round-robin to ranks
-        std::vector<uint32_t> pix;
+        std::vector<uint32_t> owned;
         {
             if (f.cx1 > 65535 || f.cy1 > 65535) return c.fail("render: image coordinates above 65535 are not supported");
             const int bs = f.tileSize, nx = (f.w + bs - 1) / bs, ny = (f.h + bs - 1) / bs;
@@ -666,13 +691,9 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
                     const int x0 = f.cx0 + i * bs, y0 = f.cy0 + j * bs;
                     const int tw = std::min(bs, f.cx0 + f.w - x0), th = std::min(bs, f.cy0 + f.h - y0);
                     for (int y = y0; y < y0 + th; ++y)
-                        for (int x = x0; x < x0 + tw; ++x) pix.push_back((uint32_t)x | ((uint32_t)y << 16));
+                        for (int x = x0; x < x0 + tw; ++x) owned.push_back((uint32_t)x | ((uint32_t)y << 16));
                 }
         }
-        const uint64_t totalSamples = (uint64_t)pix.size() * (uint64_t)f.n_samples;
-        if (totalSamples >= 0xffffffffull) return c.fail("render: more than 2^32 camera samples per rank are not supported");
-        rb.pix.reserve(pix.size() + 1);
-        rt_h2d(rb.pix.p, pix.data(), pix.size() * sizeof(uint32_t), s);
         // ---- worst-case fan-out per task, from the integrator and the materials present
         bool anyGlossy = false; int specChildren = 0;
         for (size_t i = 0; i < c.materials.size(); ++i) {
@@ -690,6 +711,44 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
         for (size_t i = 0; i < c.lights.size(); ++i) S += c.lights[i].type == LIGHT_POINT ? 1 : 2 * (size_t)std::max(1, c.lights[i].samples);
         if (I.type == INTEG_DIRECT && I.useAO) S += (size_t)std::max(1, I.aoSamples);
         if (S < 1) S = 1;
+        StageTimer tc(s), tsh(s), tsd(s), tf(s);
+        uint64_t raysClosest = 0, raysShadow = 0, samplesDone = 0; double msClosest = 0, msShadow = 0, msShade = 0, msFilm = 0;
+        const uint64_t launches0 = g_kernel_launches;
+        // ---- passes (tiledIntegrator_t::render, integrator.cc:153-164): pass 0 = AA_minsamples on every owned pixel; pass i
+        //      = AA_inc_samples on the owned pixels flagged by nextPass from the film of ALL ranks after pass i-1
+        const int nPasses = std::max(1, f.AA_passes);
+        if (onlyPass >= nPasses) return c.fail("render: pass index beyond AA_passes");
+        if (onlyPass < 0 && world > 1 && nPasses > 1)
+            return c.fail("render: adaptive passes on several ranks need the film of all ranks between passes - use yb200_render_film_pass");
+        for (int pass = (onlyPass < 0 ? 0 : onlyPass); pass < (onlyPass < 0 ? nPasses : onlyPass + 1); ++pass) {
+        if (c.abortFlag || (should_abort && should_abort(user))) break;
+        std::vector<uint32_t> flagged;
+        const std::vector<uint32_t> *pixv = &owned;
+        const int passSamples = pass == 0 ? f.n_samples : std::max(1, f.AA_inc_samples);
+        const int passOffs = pass == 0 ? 0 : f.n_samples + (pass - 1) * std::max(1, f.AA_inc_samples);
+        if (pass > 0 && f.AA_threshold > 0.f) {
+            const size_t npx = (size_t)f.w * f.h;
+            rb.aaFlags.reserve(npx + 1);
+            rt_memset(rb.aaFlags.p, 0, npx, s);
+            if (f.w > 1 && f.h > 1) {
+                FlagArgs fa; fa.film = d_filmAll ? d_filmAll : d_film; fa.flags = rb.aaFlags.p; fa.w = f.w; fa.h = f.h; fa.thresh = f.AA_threshold;
+                k_aa_flags((uint32_t)((size_t)(f.w - 1) * (f.h - 1)), fa, s);
+            }
+            std::vector<unsigned char> hf(npx);
+            rt_d2h(hf.data(), rb.aaFlags.p, npx, s);
+            for (size_t i = 0; i < owned.size(); ++i) {
+                const int x = (int)(owned[i] & 0xffffu) - f.cx0, y = (int)(owned[i] >> 16) - f.cy0;   // doMoreSamples (imagefilm.cc:445-448)
+                if (hf[(size_t)x + (size_t)f.w * y]) flagged.push_back(owned[i]);
+            }
+            pixv = &flagged;
+        }
+        const std::vector<uint32_t> &pix = *pixv;
+        const uint64_t totalSamples = (uint64_t)pix.size() * (uint64_t)passSamples;
+        if (totalSamples >= 0xffffffffull) return c.fail("render: more than 2^32 camera samples per rank are not supported");
+        if (totalSamples == 0) continue;
+        rb.pix.reserve(pix.size() + 1);
+        rt_h2d(rb.pix.p, pix.data(), pix.size() * sizeof(uint32_t), s);
+        rt_sync(s);
 #ifdef YB_HOSTEMU
         const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)512 << 20), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 16);
 #else
@@ -698,23 +757,19 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
         const size_t perSample = (F + 1) * sizeof(Task) * 2 + S * sizeof(ShadowTask) + sizeof(Hit) + sizeof(f4);
         size_t B = std::min<size_t>(Bmax, std::max<size_t>(1024, budget / perSample));
         B = std::min<size_t>(B, (size_t)totalSamples);
-        if (B == 0) return true;
         const size_t poolCap = B * (F + 1), shadowCap = B * S;
         rb.poolA.reserve(poolCap); rb.poolB.reserve(poolCap);
         rb.hits.reserve(B); rb.shadow.reserve(shadowCap); rb.counters.reserve(4); rb.acc.reserve(B);
         rb.order.reserve(B); rb.keys.reserve(B); rb.bins.reserve(2 * YB_SHADE_BINS);
         RenderArgs a;
         memset((void *)&a, 0, sizeof(a));
-        a.sc = c.sc; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
+        a.sc = c.sc; a.sc.film.n_samples = passSamples; a.sc.film.pass_offs = passOffs; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
         a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
         const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
         const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;
-        StageTimer tc(s), tsh(s), tsd(s), tf(s);
-        uint64_t raysClosest = 0, raysShadow = 0; double msClosest = 0, msShadow = 0, msShade = 0, msFilm = 0;
-        const uint64_t launches0 = g_kernel_launches;
         const int nBatches = (int)((totalSamples + B - 1) / B);
         for (int b = 0; b < nBatches; ++b) {
             if (c.abortFlag || (should_abort && should_abort(user))) break;
@@ -773,11 +828,13 @@ bool render_film_device(Context &c, float *d_film, int rank, int world, int (*sh
             tf.start(); k_film(nb, a, s); tf.stop();
             rt_sync(s);
             msFilm += tf.ms();
-            if (progress) progress(user, b + 1, nBatches);
+            if (progress) progress(user, pass * nBatches + b + 1, nPasses * nBatches);
         }
+        samplesDone += totalSamples;
+        }   // passes
         rt_sync(s);
         Stats &st = c.stats;
-        st.rays_closest = raysClosest; st.rays_shadow = raysShadow; st.camera_samples = totalSamples;
+        st.rays_closest = raysClosest; st.rays_shadow = raysShadow; st.camera_samples = samplesDone;
         st.kernel_launches = g_kernel_launches - launches0;
         st.trace_closest_ms = msClosest; st.trace_shadow_ms = msShadow; st.shade_ms = msShade; st.film_ms = msFilm;
         st.render_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tstart).count();

@@ -151,7 +151,10 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
 // rays/out are DEVICE pointers; mode = TRACE_*; out layout as documented in include/yb200.h
 void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int shadow_depth, void *d_out);
 // accumulate the tiles of (rank, world) of one frame into d_film (w*h*5 floats, raw sums)
-bool render_film_device(Context &c, float *d_film, int rank, int world, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user);
+// accumulate the tiles of (rank, world) into d_film.  onlyPass < 0: all AA passes (single rank only when AA_passes > 1);
+// onlyPass >= 0: just that pass, with d_filmAll = raw film sums of ALL ranks after the previous pass (0: use d_film)
+bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int rank, int world, int onlyPass,
+                        int (*should_abort)(void *), void (*progress)(void *, int, int), void *user);
 void film_resolve_device(Context &c, const float *d_film, float *d_rgba);
 void render_release(RenderBuffers *rb);
 

@@ -90,6 +90,7 @@ struct Film {                         // imageFilm_t (imagefilm.cc:119-165,453-5
     int32_t tileSize;
     // sampling plan of this render pass (integrator.cc:229-290)
     int32_t AA_passes, n_samples, pass_offs;
+    int32_t AA_inc_samples; float AA_threshold;      // adaptive passes (integrator.cc:158-163, imagefilm.cc:226-262)
 };
 
 // ---- geometry in HBM ------------------------------------------------------------------------------

@@ -145,6 +145,13 @@ class YafrayInterface:
         if not self._call("render_film", film.data_ptr(), rank, world, None):
             raise RuntimeError("render_film failed: " + self.lastError())
 
+    def renderFilmPass(self, film, film_all, rank, world, aa_pass):
+        """One AA pass (adaptive sampling on several ranks): film_all = sum of the films of all ranks after the
+        previous pass (None for pass 0 / a single rank)."""
+        if not self._call("render_film_pass", film.data_ptr(), film_all.data_ptr() if film_all is not None else None,
+                          rank, world, int(aa_pass), None):
+            raise RuntimeError("render_film_pass failed: " + self.lastError())
+
     def filmResolve(self, film, width, height):
         out = np.zeros((height, width, 4), dtype=np.float32)
         if not self._call("film_resolve", film.data_ptr(), out.ctypes.data, 0):

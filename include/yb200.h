@@ -95,6 +95,13 @@ int yb200_render(yb200_ctx *c, float *rgba, int width, int height, const yb200_c
  * tile i belongs to rank i % world.  The caller sums the films of all ranks (NCCL reduce) and calls
  * yb200_film_resolve on the sum.  dev_film must be zeroed by the caller. */
 int yb200_render_film(yb200_ctx *c, float *dev_film, int rank, int world, const yb200_callbacks *cb);
+/* One anti-aliasing pass of the above (tiledIntegrator_t::render's pass loop, integrator.cc:153-164), for adaptive
+ * sampling (AA_passes > 1) on several ranks: pass 0 renders AA_minsamples on every owned pixel; pass i >= 1 renders
+ * AA_inc_samples on the owned pixels that imageFilm_t::nextPass (imagefilm.cc:213-263) flags from dev_film_all = the raw
+ * film sums of ALL ranks after pass i-1 (NULL: use dev_film, i.e. world == 1).  yb200_render_film runs all passes itself
+ * when world == 1 and fails for world > 1 with AA_passes > 1. */
+int yb200_render_film_pass(yb200_ctx *c, float *dev_film, const float *dev_film_all, int rank, int world, int pass,
+                           const yb200_callbacks *cb);
 /* normalise / clamp / gamma / premult exactly like imageFilm_t::flush; dev_film device, rgba HOST or DEVICE */
 int yb200_film_resolve(yb200_ctx *c, const float *dev_film, float *rgba, int rgba_on_device);
 void yb200_abort(yb200_ctx *c);                              /* yafrayinterface.cc:278 */

@@ -22,6 +22,11 @@ IMAGE_CASES = {
     "c4_materials_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting")),
     "c4_materials_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
                                                           integ_params=dict(transpShad=True, shadowDepth=4))),
+    # adaptive anti-aliasing (AA_passes > 1: tiledIntegrator_t::render pass loop + imageFilm_t::nextPass)
+    "c2_field_adaptive": (scenes.icosphere_field, dict(n_tris=6000, subdiv=1, width=64, height=36, spp=1, bounces=3, passes=3,
+                                                       AA_inc_samples=3, AA_threshold=0.02)),
+    "c4_materials_adaptive": (scenes.materials_scene, dict(width=80, height=45, spp=1, integrator="directlighting", passes=2,
+                                                           AA_inc_samples=2, AA_threshold=0.1)),
     # configs[4] (reduced): tessellated fBm terrain, sun + sky, pathtracing 4 bounces
     "c5_terrain_path": (scenes.terrain, dict(grid=60, width=64, height=36, spp=2, bounces=4)),
 }
