@@ -487,12 +487,11 @@ uintptr_t Context::createCamera(const char *name)   // environment.cc:292-330 + 
     const ParaMap &p = params;
     v3 from(0, 1, 0), to(0, 0, 0), up(0, 1, 1);
     int resx = 320, resy = 200;
-    float aspect = 1, dfocal = 1, apt = 0, dofd = 0, nearClip = 0.0f, farClip = -1.0f;
+    float aspect = 1, dfocal = 1, apt = 0, dofd = 0, bkhrot = 0, nearClip = 0.0f, farClip = -1.0f;
     std::string bkhtype = "disk1", bkhbias = "uniform";
     p.getPoint("from", from); p.getPoint("to", to); p.getPoint("up", up); p.get("resx", resx); p.get("resy", resy);
-    p.get("focal", dfocal); p.get("aperture", apt); p.get("dof_distance", dofd); p.get("bokeh_type", bkhtype); p.get("bokeh_bias", bkhbias);
+    p.get("focal", dfocal); p.get("aperture", apt); p.get("dof_distance", dofd); p.get("bokeh_type", bkhtype); p.get("bokeh_bias", bkhbias); p.get("bokeh_rotation", bkhrot);
     p.get("aspect_ratio", aspect); p.get("nearClip", nearClip); p.get("farClip", farClip);
-    if (apt != 0 && bkhtype != "disk1") { fail("camera '" + std::string(name) + "': bokeh_type '" + bkhtype + "' is not supported (disk1 only)"); return 0; }
     CameraDesc d;
     memset(&d, 0, sizeof(d));
     Camera &c = d.cam;
@@ -506,6 +505,15 @@ uintptr_t Context::createCamera(const char *name)   // environment.cc:292-330 + 
     c.near_p = from + camZ * nearClip;
     c.far_p = from + camZ * farClip;
     c.aperture = apt; c.dof_distance = dofd; c.sampleLens = apt != 0;
+    // bokeh shape / bias (perspectiveCamera.cc:215-225): unknown strings fall back to disk1 / uniform like the reference
+    c.bkhtype = bkhtype == "disk2" ? 1 : bkhtype == "triangle" ? 3 : bkhtype == "square" ? 4 : bkhtype == "pentagon" ? 5 : bkhtype == "hexagon" ? 6 : bkhtype == "ring" ? 7 : 0;
+    c.bkhbias = bkhbias == "center" ? 1 : bkhbias == "edge" ? 2 : 0;
+    if (c.bkhtype >= 3 && c.bkhtype <= 6) {                 // lens polygon corners (perspectiveCamera.cc:40-50)
+        int ns = c.bkhtype;
+        float w = (float)((double)bkhrot * 0.01745329251994329576922), wi = (float)(6.28318530717958647692 / (double)(float)ns);
+        ns = (ns + 2) * 2;
+        for (int i = 0; i < ns; i += 2) { c.LS[i] = fCos(w); c.LS[i + 1] = fSin(w); w += wi; }
+    }
     c.dof_rt = apt * camX; c.dof_up = apt * camY;
     c.vright = camX;
     c.vup = aspect_ratio * camY;

@@ -97,7 +97,32 @@ YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, float &t, col3 &col,
     return false;
 }
 
-// perspectiveCam_t::shootRay (perspectiveCamera.cc:127-149); bokeh disk1 only (others rejected at creation)
+// perspectiveCam_t::biasDist / sampleTSD / getLensUV (perspectiveCamera.cc:73-122)
+YB_HD void cam_biasDist(const Camera &c, float &r)
+{
+    if (c.bkhbias == 1) r = fSqrt(fSqrt(r) * r);            // BB_CENTER
+    else if (c.bkhbias == 2) r = fSqrt(1.0f - r * r);       // BB_EDGE
+    else r = fSqrt(r);
+}
+YB_HD void cam_getLensUV(const Camera &c, float r1, float r2, float &u, float &v)
+{
+    if (c.bkhtype >= 3 && c.bkhtype <= 6) {                 // BK_TRI .. BK_HEXA: sampleTSD
+        const float fn = (float)c.bkhtype;
+        int idx = (int)(r1 * fn);
+        r1 = (r1 - ((float)idx) / fn) * fn;
+        cam_biasDist(c, r1);
+        const float b1 = r1 * r2, b0 = r1 - b1;
+        idx <<= 1;
+        u = c.LS[idx] * b0 + c.LS[idx + 2] * b1;
+        v = c.LS[idx + 1] * b0 + c.LS[idx + 3] * b1;
+    } else if (c.bkhtype == 1 || c.bkhtype == 7) {          // BK_DISK2, BK_RING
+        const float w = (float)YB_M_2PI * r2;
+        if (c.bkhtype == 7) r1 = fSqrt(0.707106781f + 0.292893218f);
+        else cam_biasDist(c, r1);
+        u = r1 * fCos(w); v = r1 * fSin(w);
+    } else ShirleyDisk(r1, r2, u, v);                       // BK_DISK1
+}
+// perspectiveCam_t::shootRay (perspectiveCamera.cc:127-149)
 YB_HD Ray cam_shootRay(const Camera &c, float px, float py, float lu, float lv, float &wt)
 {
     Ray ray;
@@ -109,7 +134,7 @@ YB_HD Ray cam_shootRay(const Camera &c, float px, float py, float lu, float lv, 
     ray.tmax = dot(c.camZ, c.far_p - ray.from) / denom;
     if (c.aperture != 0) {
         float u, v;
-        ShirleyDisk(lu, lv, u, v);
+        cam_getLensUV(c, lu, lv, u, v);
         v3 LI = c.dof_rt * u + c.dof_up * v;
         ray.from = ray.from + LI;
         ray.dir = normalize((ray.dir * c.dof_distance) - LI);

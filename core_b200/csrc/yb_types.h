@@ -61,6 +61,8 @@ struct Camera {                       // perspectiveCam_t (perspectiveCamera.cc:
     v3 near_p, far_p;                // plane points (plane normal = camZ)
     float aperture, dof_distance;
     int32_t resx, resy, sampleLens;
+    int32_t bkhtype, bkhbias;        // bokehType / bkhBiasType values of perspectiveCamera.h:33-34
+    float LS[16];                    // polygon lens corners (perspectiveCamera.cc:40-50)
 };
 
 enum IntegType : int32_t { INTEG_DIRECT = 0, INTEG_PATH = 1 };

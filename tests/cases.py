@@ -22,6 +22,10 @@ IMAGE_CASES = {
     "c4_materials_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting")),
     "c4_materials_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
                                                           integ_params=dict(transpShad=True, shadowDepth=4))),
+    # depth of field with a polygonal lens (perspectiveCam_t::sampleTSD / biasDist)
+    "c4_materials_dof_hexagon": (scenes.materials_scene, dict(width=64, height=36, spp=3, integrator="directlighting",
+                                                              cam_params=dict(aperture=0.15, dof_distance=10.0, bokeh_type="hexagon",
+                                                                              bokeh_rotation=15.0, bokeh_bias="center"))),
     # adaptive anti-aliasing (AA_passes > 1: tiledIntegrator_t::render pass loop + imageFilm_t::nextPass)
     "c2_field_adaptive": (scenes.icosphere_field, dict(n_tris=6000, subdiv=1, width=64, height=36, spp=1, bounces=3, passes=3,
                                                        AA_inc_samples=3, AA_threshold=0.02)),
