@@ -292,7 +292,36 @@ template <uint32_t BASE> struct HaltonT {
         return fmaxf_(0.f, fminf_(1.f, (float)mValue));
     }
 };
-typedef HaltonT<2> Halton2;
+// Base 2: every quantity of the incremental scheme is a dyadic rational with <= 33 bits, so the FP64 arithmetic of
+// setStart / getNext is exact and the stream is simply the bit-reversed counter; 0.9999999999 only decides comparisons
+// that are >= 1e-10 away from a tie.  The counter wrap at 2^32 (where the reference's value is NOT Phi2(0)) falls back
+// to the generic incremental code.
+struct Halton2 {
+    uint32_t idx; bool slow; HaltonT<2> gen;
+    YB_HD Halton2() : idx(0), slow(false) {}
+    YB_HD static uint32_t brev(uint32_t r)
+    {
+#if defined(__CUDA_ARCH__)
+        return __brev(r);
+#else
+        r = ((r >> 1) & 0x55555555u) | ((r & 0x55555555u) << 1);
+        r = ((r >> 2) & 0x33333333u) | ((r & 0x33333333u) << 2);
+        r = ((r >> 4) & 0x0f0f0f0fu) | ((r & 0x0f0f0f0fu) << 4);
+        r = ((r >> 8) & 0x00ff00ffu) | ((r & 0x00ff00ffu) << 8);
+        return (r >> 16) | (r << 16);
+#endif
+    }
+    YB_HD void setStart(uint32_t i) { idx = i; slow = false; }
+    YB_HD float getNext()
+    {
+        if (!slow && idx != 0xffffffffu) {
+            ++idx;
+            return fmaxf_(0.f, fminf_(1.f, (float)((double)brev(idx) * 2.3283064365386963e-10)));
+        }
+        if (!slow) { gen.setStart(idx); slow = true; }
+        return gen.getNext();
+    }
+};
 typedef HaltonT<3> Halton3;
 typedef HaltonT<5> Halton5;
 
