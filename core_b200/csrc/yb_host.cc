@@ -469,8 +469,44 @@ uintptr_t Context::createLight(const char *name)   // environment.cc:189-216 + l
         l.du = normalize(l.toX); l.dv = cross(l.normal, l.du);
         l.c2 = corner + l.toX; l.c3 = corner + (l.toX + l.toY); l.c4 = corner + l.toY;
         obj = (unsigned)object;
+    } else if (type == "directional") {            // directional.cc:52-61,142-160
+        v3 from(0.f), dir(0.f, 0.f, 1.f); col3 color(1.f); float power = 1.0f, rad = 1.f; bool inf = true;
+        p.getPoint("direction", dir); p.getColor("color", color); p.get("power", power); p.get("infinite", inf);
+        if (!inf) {
+            if (!p.getPoint("from", from)) { if (p.getPoint("position", from)) info("DirectionalLight: Deprecated parameter 'position', use 'from' instead"); }
+            p.get("radius", rad);
+        }
+        l.type = LIGHT_DIRECTIONAL; l.samples = 1;
+        l.color = color * power; l.position = from; l.radius = rad; l.infinite = inf ? 1 : 0;
+        l.direction = normalize(dir);
+        createCS(l.direction, l.du, l.dv);
+    } else if (type == "spotlight") {              // spotlight.cc:64-76,282-306
+        v3 from(0.f), to(0.f, 0.f, -1.f); col3 color(1.f); float power = 1.0f, angle = 45.f, falloff = 0.15f, ssfuzzy = 1.f;
+        bool pOnly = false, soft = false; int smpl = 8;
+        p.getPoint("from", from); p.getPoint("to", to); p.getColor("color", color); p.get("power", power); p.get("cone_angle", angle);
+        p.get("blend", falloff); p.get("photon_only", pOnly); p.get("soft_shadows", soft); p.get("shadowFuzzyness", ssfuzzy); p.get("samples", smpl);
+        l.type = LIGHT_SPOT; l.samples = smpl; l.position = from;
+        l.ndir = normalize(from - to); l.direction = -l.ndir;
+        l.color = color * power;
+        createCS(l.direction, l.du, l.dv);
+        const double rad_angle = (double)angle * 0.01745329251994329576922;
+        const double rad_inner_angle = rad_angle * (double)(1.f - falloff);
+        l.cosStart = fCos((float)rad_inner_angle);
+        l.cosEnd = fCos((float)rad_angle);
+        l.icosDiff = (float)(1.0 / (double)(l.cosStart - l.cosEnd));
+        l.softShadows = soft ? 1 : 0; l.photonOnly = pOnly ? 1 : 0; l.shadowFuzzy = ssfuzzy;
+    } else if (type == "spherelight") {            // spherelight.cc:62-70,194-213
+        v3 from(0.f); col3 color(1.f); float power = 1.0f, radius = 1.f; int samples = 4, object = 0;
+        p.getPoint("from", from); p.getColor("color", color); p.get("power", power); p.get("radius", radius); p.get("samples", samples); p.get("object", object);
+        l.type = LIGHT_SPHERE; l.samples = samples; l.position = from; l.radius = radius;
+        l.color = color * power;
+        l.squareRadius = radius * radius;
+        l.squareRadiusEps = (float)((double)l.squareRadius * 1.000003815);
+        l.area = (float)((double)l.squareRadius * 4.0 * YB_M_PI);
+        l.invArea = 1.f / l.area;
+        if (object != 0) { fail("spherelight '" + std::string(name) + "': binding to a sphere primitive ('object') is not supported (triangle meshes only)"); return 0; }
     } else {
-        fail("Environment: light type '" + type + "' is not supported by the B200 path (supported: pointlight, sunlight, arealight)");
+        fail("Environment: light type '" + type + "' is not supported by the B200 path (supported: pointlight, sunlight, arealight, directional, spotlight, spherelight)");
         return 0;
     }
     lights.push_back(l); lightObj.push_back(obj);

@@ -10,12 +10,53 @@ namespace yb {
 
 struct LSample { float s1, s2; col3 col; float pdf; };   // lSample_t fields used on this path (light.h)
 
-YB_HD bool light_dirac(const Light &l) { return l.type == LIGHT_POINT; }
-YB_HD bool light_canIntersect(const Light &l) { return l.type != LIGHT_POINT; }
+// light_t::diracLight / canIntersect of the six light types
+YB_HD bool light_dirac(const Light &l) { return l.type == LIGHT_POINT || l.type == LIGHT_DIRECTIONAL || (l.type == LIGHT_SPOT && !l.softShadows); }
+YB_HD bool light_canIntersect(const Light &l) { return l.type == LIGHT_SUN || l.type == LIGHT_AREA || (l.type == LIGHT_SPOT && l.softShadows); }
 
-// pointLight_t::illuminate (pointlight.cc:54-70)
+// spot cone falloff (spotlight.cc:117-126,163-172,263-272): smoothstep between cosEnd and cosStart
+YB_HD float spot_falloff(const Light &l, float cosa)
+{
+    if (cosa >= l.cosStart) return 1.f;
+    float v = (cosa - l.cosEnd) * l.icosDiff;
+    return v * v * (3.f - 2.f * v);
+}
+// pointLight_t::illuminate (pointlight.cc:54-70), directionalLight_t::illuminate (directional.cc:77-97),
+// spotLight_t::illuminate (spotlight.cc:103-132)
 YB_HD bool light_illuminate(const Light &l, v3 P, col3 &col, Ray &wi)
 {
+    if (l.type == LIGHT_DIRECTIONAL) {
+        if (!l.infinite) {               // outside of the illuminated cylinder?
+            v3 vec = l.position - P;
+            float dist = length(cross(l.direction, vec));
+            if (dist > l.radius) return false;
+            wi.tmax = dot(vec, l.direction);
+            if (wi.tmax <= 0.0f) return false;
+        } else wi.tmax = -1.0f;
+        wi.dir = l.direction;
+        col = l.color;
+        return true;
+    }
+    if (l.type == LIGHT_SPOT) {
+        if (l.photonOnly) return false;
+        v3 ldir = l.position - P;
+        float dist_sqr = dot(ldir, ldir);
+        float dist = fSqrt(dist_sqr);
+        if (dist == 0.0f) return false;
+        float idist_sqr = 1.f / dist_sqr;
+        ldir *= 1.f / dist;
+        float cosa = dot(l.ndir, ldir);
+        if (cosa < l.cosEnd) return false;
+        if (cosa >= l.cosStart) col = l.color * idist_sqr;
+        else {
+            float v = (cosa - l.cosEnd) * l.icosDiff;
+            v = v * v * (3.f - 2.f * v);
+            col = l.color * (v * idist_sqr);
+        }
+        wi.tmax = dist;
+        wi.dir = ldir;
+        return true;
+    }
     if (l.type != LIGHT_POINT) return false;
     v3 ldir = l.position - P;
     float dist_sqr = ldir.x * ldir.x + ldir.y * ldir.y + ldir.z * ldir.z;
@@ -28,6 +69,20 @@ YB_HD bool light_illuminate(const Light &l, v3 P, col3 &col, Ray &wi)
     col = l.color * idist_sqr;
     return true;
 }
+// spherelight.cc:86-98 (the 2.0 / 4.0 literals make eb, osc and the roots double expressions rounded to float)
+YB_HD bool sphereIntersect(v3 from, v3 dir, v3 c, float R2, float &d1, float &d2)
+{
+    v3 vf = from - c;
+    float ea = dot(dir, dir);
+    float eb = (float)(2.0 * (double)dot(vf, dir));
+    float ec = dot(vf, vf) - R2;
+    float osc = (float)((double)(eb * eb) - 4.0 * (double)ea * (double)ec);
+    if (osc < 0) { d1 = fSqrt(ec / ea); return false; }
+    osc = fSqrt(osc);
+    d1 = (float)((double)(-eb - osc) / (2.0 * (double)ea));
+    d2 = (float)((double)(-eb + osc) / (2.0 * (double)ea));
+    return true;
+}
 // sunLight_t::illumSample (sunlight.cc:74-85), areaLight_t::illumSample (arealight.cc:68-96)
 YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s, Ray &wi)
 {
@@ -36,6 +91,39 @@ YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s, Ray &wi)
         wi.tmax = -1.f;
         s.col = l.colPdf;
         s.pdf = l.pdf;
+        return true;
+    }
+    if (l.type == LIGHT_SPOT) {                  // spotLight_t::illumSample (spotlight.cc:134-177)
+        if (l.photonOnly) return false;
+        v3 ldir = l.position - P;
+        float dist_sqr = dot(ldir, ldir);
+        if (dist_sqr == 0.0f) return false;
+        float dist = fSqrt(dist_sqr);
+        ldir *= 1.f / dist;
+        float cosa = dot(l.ndir, ldir);
+        if (cosa < l.cosEnd) return false;
+        wi.tmax = dist;
+        wi.dir = sampleCone(ldir, l.du, l.dv, l.cosEnd, s.s1 * l.shadowFuzzy, s.s2 * l.shadowFuzzy);
+        s.col = l.color * spot_falloff(l, cosa);
+        s.pdf = dist_sqr;
+        return true;
+    }
+    if (l.type == LIGHT_SPHERE) {                // sphereLight_t::illumSample (spherelight.cc:100-132)
+        v3 cdir = l.position - P;
+        float dist_sqr = dot(cdir, cdir);
+        if (dist_sqr <= l.squareRadius) return false;     // only emits on the outside
+        float dist = fSqrt(dist_sqr);
+        float idist_sqr = 1.f / dist_sqr;
+        float cosAlpha = fSqrt(1.f - l.squareRadius * idist_sqr);
+        cdir *= 1.f / dist;
+        v3 du, dv;
+        createCS(cdir, du, dv);
+        wi.dir = sampleCone(cdir, du, dv, cosAlpha, s.s1, s.s2);
+        float d1, d2;
+        if (!sphereIntersect(wi.from, wi.dir, l.position, l.squareRadiusEps, d1, d2)) return false;
+        wi.tmax = d1;
+        s.pdf = 1.f / (2.f * (1.f - cosAlpha));
+        s.col = l.color;
         return true;
     }
     if (l.type == LIGHT_AREA) {
@@ -82,6 +170,23 @@ YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, float &t, col3 &col,
         t = -1;
         ipdf = l.invpdf;
         return true;
+    }
+    if (l.type == LIGHT_SPOT) {                  // spotLight_t::intersect (spotlight.cc:243-280), quirks included
+        float cosA = dot(l.direction, dir);
+        if (cosA == 0.f) return false;
+        t = dot(l.direction, l.position - from) / cosA;
+        if (t < 0.f) return false;
+        v3 P = from + t * dir;
+        if (dot(l.direction, P - l.position) == 0) {
+            if (dot(P, P) <= 1e-2f) {
+                float cosa = dot(l.direction, dir);
+                if (cosa < l.cosEnd) return false;
+                col = l.color * spot_falloff(l, cosa);
+                ipdf = 1.f / (t * t);
+                return true;
+            }
+        }
+        return false;
     }
     if (l.type == LIGHT_AREA) {
         float cos_angle = dot(dir, l.fnormal);

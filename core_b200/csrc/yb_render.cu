@@ -708,7 +708,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         size_t F = (I.type == INTEG_PATH ? (size_t)std::max(1, I.nPaths) : 0) + (anyGlossy ? 8 : 0) + (size_t)specChildren;
         if (F < 1) F = 1;
         size_t S = 0;
-        for (size_t i = 0; i < c.lights.size(); ++i) S += c.lights[i].type == LIGHT_POINT ? 1 : 2 * (size_t)std::max(1, c.lights[i].samples);
+        for (size_t i = 0; i < c.lights.size(); ++i) S += light_dirac(c.lights[i]) ? 1 : 2 * (size_t)std::max(1, c.lights[i].samples);
         if (I.type == INTEG_DIRECT && I.useAO) S += (size_t)std::max(1, I.aoSamples);
         if (S < 1) S = 1;
         StageTimer tc(s), tsh(s), tsd(s), tf(s);

@@ -43,7 +43,7 @@ struct Material {
     int32_t doubleSided;
 };
 
-enum LightType : int32_t { LIGHT_POINT = 0, LIGHT_SUN, LIGHT_AREA };
+enum LightType : int32_t { LIGHT_POINT = 0, LIGHT_SUN, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE };
 struct Light {
     int32_t type, samples;
     col3 color;                      // point: col*power; area: col*power*pi; sun: col*power
@@ -54,6 +54,11 @@ struct Light {
     double cosAngle;                 // sun (double member, sunlight.cc:44)
     v3 corner, c2, c3, c4, toX, toY, normal, fnormal;   // area (arealight.cc:33-49)
     float area, invArea;
+    // directional (directional.cc:52-61): direction, position, radius, infinite.  spot (spotlight.cc:64-76): position,
+    // direction = cone axis, ndir, du/dv, cosStart/cosEnd/icosDiff, softShadows, shadowFuzzy.  sphere (spherelight.cc:62-70)
+    v3 ndir;
+    float radius, cosStart, cosEnd, icosDiff, shadowFuzzy, squareRadius, squareRadiusEps;
+    int32_t infinite, softShadows, photonOnly;
 };
 
 struct Camera {                       // perspectiveCam_t (perspectiveCamera.cc:28-71,127-149; camera.h:41-61)

@@ -280,7 +280,7 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
 
 # ----------------------------------------------------------------------------- C4: glossy / coated / glass materials
 def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
-                    integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, **render_extra):
+                    integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None, **render_extra):
     """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
     coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
     shinydiffuse; sun (1 degree, 4 samples) + point + area (8 samples) lights; pathtracing with 8 bounces
@@ -318,11 +318,15 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
         V = (v0 * r + np.array([cx, cy, r + 0.02])).astype(np.float32)
         add_mesh(yi, V, f0, M[name], normals=v0.astype(np.float32), smooth_angle=181.0)
     yi.endGeometry()
-    create(yi, "light", "sun", type="sunlight", direction=(0.4, -0.5, 0.8), color=(1.0, 0.95, 0.9, 1.0), power=0.9,
-           angle=1.0, samples=sun_samples)
-    create(yi, "light", "pt", type="pointlight", **{"from": (-4.0, -3.0, 5.0)}, color=(0.9, 0.9, 1.0, 1.0), power=18.0)
-    create(yi, "light", "area", type="arealight", corner=(2.0, -3.0, 5.0), point1=(2.0, -1.5, 5.0), point2=(3.5, -3.0, 5.0),
-           color=(1.0, 0.85, 0.7, 1.0), power=20.0, samples=area_samples)
+    if lights is None:
+        create(yi, "light", "sun", type="sunlight", direction=(0.4, -0.5, 0.8), color=(1.0, 0.95, 0.9, 1.0), power=0.9,
+               angle=1.0, samples=sun_samples)
+        create(yi, "light", "pt", type="pointlight", **{"from": (-4.0, -3.0, 5.0)}, color=(0.9, 0.9, 1.0, 1.0), power=18.0)
+        create(yi, "light", "area", type="arealight", corner=(2.0, -3.0, 5.0), point1=(2.0, -1.5, 5.0), point2=(3.5, -3.0, 5.0),
+               color=(1.0, 0.85, 0.7, 1.0), power=20.0, samples=area_samples)
+    else:                                   # explicit light set: list of (name, params)
+        for lname, lp in lights:
+            create(yi, "light", lname, **lp)
     create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -9.5, 4.2)}, to=(0.0, 1.0, 0.8),
            up=(0.0, -9.5, 5.2), resx=width, resy=height, focal=1.3, **(cam_params or {}))
     create(yi, "background", "bg", type="constant", color=(0.35, 0.45, 0.7, 1.0))

@@ -22,6 +22,17 @@ IMAGE_CASES = {
     "c4_materials_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting")),
     "c4_materials_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
                                                           integ_params=dict(transpShad=True, shadowDepth=4))),
+    # the other cheap lights: directional (infinite and cylinder), spot (soft shadows: illumSample + MIS intersect), sphere
+    "c4_lights_all_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, integrator="pathtracing", bounces=4, lights=[
+        ("d", dict(type="directional", direction=(0.3, -0.5, 0.8), color=(1.0, 0.95, 0.9, 1.0), power=0.5)),
+        ("s", dict(type="spotlight", to=(0.5, 0.5, 0.5), color=(1.0, 0.9, 0.8, 1.0), power=40.0, cone_angle=35.0, blend=0.2,
+                   soft_shadows=True, samples=2, **{"from": (-3.0, -4.0, 6.0)})),
+        ("sp", dict(type="spherelight", color=(0.8, 0.9, 1.0, 1.0), power=15.0, radius=0.6, samples=3, **{"from": (1.0, -3.0, 4.5)}))])),
+    "c4_lights_dirac_direct": (scenes.materials_scene, dict(width=64, height=36, spp=2, integrator="directlighting", lights=[
+        ("d", dict(type="directional", direction=(0.1, -0.2, 0.9), color=(1.0, 1.0, 1.0, 1.0), power=1.5, infinite=False, radius=3.0,
+                   **{"from": (0.5, -0.5, 6.0)})),
+        ("s", dict(type="spotlight", to=(0.5, 0.5, 0.5), color=(1.0, 0.9, 0.8, 1.0), power=60.0, cone_angle=30.0, blend=0.3,
+                   **{"from": (-3.0, -4.0, 6.0)}))])),
     # depth of field with a polygonal lens (perspectiveCam_t::sampleTSD / biasDist)
     "c4_materials_dof_hexagon": (scenes.materials_scene, dict(width=64, height=36, spp=3, integrator="directlighting",
                                                               cam_params=dict(aperture=0.15, dof_distance=10.0, bokeh_type="hexagon",
