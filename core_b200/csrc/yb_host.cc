@@ -519,15 +519,24 @@ uintptr_t Context::createCamera(const char *name)   // environment.cc:292-330 + 
     std::string type;
     if (!params.get("type", type)) { fail(std::string("Environment: Type of camera not specified for ") + name); return 0; }
     if (cameras.count(name)) { warn(std::string("Environment: Sorry, camera already in table: ") + name); return 0; }
-    if (type != "perspective") { fail("Environment: camera type '" + type + "' is not supported by the B200 path (supported: perspective)"); return 0; }
+    const bool persp = type == "perspective", archi = type == "architect", ortho = type == "orthographic", angular = type == "angular";
+    if (!persp && !archi && !ortho && !angular) { fail("Environment: camera type '" + type + "' is not supported by the B200 path (supported: perspective, architect, orthographic, angular)"); return 0; }
     const ParaMap &p = params;
     v3 from(0, 1, 0), to(0, 0, 0), up(0, 1, 1);
     int resx = 320, resy = 200;
     float aspect = 1, dfocal = 1, apt = 0, dofd = 0, bkhrot = 0, nearClip = 0.0f, farClip = -1.0f;
+    double aspect_d = 1.0, scale_d = 1.0, angle_d = 90, max_angle_d = 90; bool circular = true, mirrored = false;
     std::string bkhtype = "disk1", bkhbias = "uniform";
     p.getPoint("from", from); p.getPoint("to", to); p.getPoint("up", up); p.get("resx", resx); p.get("resy", resy);
-    p.get("focal", dfocal); p.get("aperture", apt); p.get("dof_distance", dofd); p.get("bokeh_type", bkhtype); p.get("bokeh_bias", bkhbias); p.get("bokeh_rotation", bkhrot);
-    p.get("aspect_ratio", aspect); p.get("nearClip", nearClip); p.get("farClip", farClip);
+    p.get("nearClip", nearClip); p.get("farClip", farClip);
+    if (persp || archi) {
+        p.get("focal", dfocal); p.get("aperture", apt); p.get("dof_distance", dofd); p.get("bokeh_type", bkhtype); p.get("bokeh_bias", bkhbias); p.get("bokeh_rotation", bkhrot);
+        p.get("aspect_ratio", aspect);
+    } else {      // orthographicCamera.cc:83-101, angularCamera.cc:73-99: double-typed aspect / scale / angle parameters
+        p.get("aspect_ratio", aspect_d); aspect = (float)aspect_d;
+        p.get("scale", scale_d);
+        p.get("angle", angle_d); max_angle_d = angle_d; p.get("max_angle", max_angle_d); p.get("circular", circular); p.get("mirrored", mirrored);
+    }
     CameraDesc d;
     memset(&d, 0, sizeof(d));
     Camera &c = d.cam;
@@ -540,6 +549,27 @@ uintptr_t Context::createCamera(const char *name)   // environment.cc:292-330 + 
     c.camZ = camZ;
     c.near_p = from + camZ * nearClip;
     c.far_p = from + camZ * farClip;
+    c.aspectRatio = aspect_ratio;
+    if (ortho) {                                            // orthoCam_t::setAxis (orthographicCamera.cc:36-49)
+        const float scale = (float)scale_d;
+        c.camType = CAM_ORTHO;
+        c.vright = camX; c.vup = aspect_ratio * camY; c.vto = camZ;
+        c.opos = from - (float)(0.5 * scale) * (c.vup + c.vright);
+        c.vup *= scale / (float)resy; c.vright *= scale / (float)resx;
+        cameras[name] = d;
+        return 0x43000000u | (uintptr_t)cameras.size();
+    }
+    if (angular) {                                          // angularCam_t ctor / setAxis / factory (angularCamera.cc:27-48,97-99)
+        c.camType = CAM_ANGULAR;
+        c.horPhi = (float)((float)angle_d * YB_M_PI / 180.f);
+        c.circular = circular ? 1 : 0;
+        c.vright = camX; c.vup = camY; c.vto = camZ;
+        if (mirrored) c.vright *= -1.0f;
+        c.maxR = (float)(max_angle_d / angle_d);
+        cameras[name] = d;
+        return 0x43000000u | (uintptr_t)cameras.size();
+    }
+    c.camType = CAM_PERSPECTIVE;
     c.aperture = apt; c.dof_distance = dofd; c.sampleLens = apt != 0;
     // bokeh shape / bias (perspectiveCamera.cc:215-225): unknown strings fall back to disk1 / uniform like the reference
     c.bkhtype = bkhtype == "disk2" ? 1 : bkhtype == "triangle" ? 3 : bkhtype == "square" ? 4 : bkhtype == "pentagon" ? 5 : bkhtype == "hexagon" ? 6 : bkhtype == "ring" ? 7 : 0;
@@ -552,7 +582,7 @@ uintptr_t Context::createCamera(const char *name)   // environment.cc:292-330 + 
     }
     c.dof_rt = apt * camX; c.dof_up = apt * camY;
     c.vright = camX;
-    c.vup = aspect_ratio * camY;
+    c.vup = archi ? aspect_ratio * v3(0.f, 0.f, -1.f) : aspect_ratio * camY;     // architectCam_t::setAxis (architectCamera.cc:53-67)
     c.vto = (camZ * dfocal) - 0.5f * (c.vup + c.vright);
     c.vup = v3(c.vup.x / (float)resy, c.vup.y / (float)resy, c.vup.z / (float)resy);
     c.vright = v3(c.vright.x / (float)resx, c.vright.y / (float)resx, c.vright.z / (float)resx);

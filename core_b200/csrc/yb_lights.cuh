@@ -232,6 +232,31 @@ YB_HD Ray cam_shootRay(const Camera &c, float px, float py, float lu, float lv, 
 {
     Ray ray;
     wt = 1;
+    if (c.camType == CAM_ORTHO) {                               // orthoCam_t::shootRay (orthographicCamera.cc:52-64)
+        ray.from = c.opos + c.vright * px + c.vup * py;
+        ray.dir = c.vto;
+        float den = dot(ray.dir, c.camZ);
+        ray.tmin = dot(c.camZ, c.near_p - ray.from) / den;
+        ray.tmax = dot(c.camZ, c.far_p - ray.from) / den;
+        return ray;
+    }
+    if (c.camType == CAM_ANGULAR) {                             // angularCam_t::shootRay (angularCamera.cc:50-71)
+        ray.from = c.position;
+        ray.dir = v3(0.f, 0.f, 1.f); ray.tmin = 0.f; ray.tmax = 0.f;
+        float u = 1.f - 2.f * (px / (float)c.resx);
+        float v = 2.f * (py / (float)c.resy) - 1.f;
+        v *= c.aspectRatio;
+        float radius = fSqrt(u * u + v * v);
+        if (c.circular && radius > c.maxR) { wt = 0; return ray; }
+        float theta = 0;
+        if (!((u == 0) && (v == 0))) theta = atan2f(v, u);
+        float phi = radius * c.horPhi;
+        ray.dir = fSin(phi) * (fCos(theta) * c.vright + fSin(theta) * c.vup) + fCos(phi) * c.vto;
+        float den = dot(ray.dir, c.camZ);
+        ray.tmin = dot(c.camZ, c.near_p - ray.from) / den;
+        ray.tmax = dot(c.camZ, c.far_p - ray.from) / den;
+        return ray;
+    }
     ray.from = c.position;
     ray.dir = normalize(c.vright * px + c.vup * py + c.vto);
     float denom = dot(ray.dir, c.camZ);

@@ -118,6 +118,9 @@ YB_KERNEL(k_raygen, RenderArgs)
     Task t;
     t.ray = cam_shootRay(a.sc.cam, (float)id.x + dx, (float)id.y + dy, lens_u, lens_v, wt);
     t.thr = col3(1.f); t.aw = 1.f; t.sid = tid;
+    // wt == 0 (angular camera outside its circle): the reference adds a black, alpha-0 sample without tracing
+    // (integrator.cc:293-297); here the slot keeps a ray that cannot hit (tmin = tmax = 0) and carries zero weights
+    if (wt == 0.f) { t.thr = col3(0.f); t.aw = 0.f; }
     t.bits = task_bits(TASK_INTEGRATE, true, 0, 0);
     t.rayDivision = 1; t.rayOffset = 0; t.dc1 = 0.f; t.dc2 = 0.f; t.pathOffs = 0; t.pad = 0;
     a.tasks[tid] = t;

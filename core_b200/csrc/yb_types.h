@@ -68,7 +68,14 @@ struct Camera {                       // perspectiveCam_t (perspectiveCamera.cc:
     int32_t resx, resy, sampleLens;
     int32_t bkhtype, bkhbias;        // bokehType / bkhBiasType values of perspectiveCamera.h:33-34
     float LS[16];                    // polygon lens corners (perspectiveCamera.cc:40-50)
+    // camType: CAM_PERSPECTIVE also covers architectCam_t (same shootRay, vup = aspect * (0,0,-1), architectCamera.cc:53-67);
+    // CAM_ORTHO (orthographicCamera.cc:36-64): opos = position - 0.5 scale (vup + vright), direction vto = camZ;
+    // CAM_ANGULAR (angularCamera.cc:38-71): fisheye, wt = 0 outside max_r when circular
+    int32_t camType, circular;
+    v3 opos;
+    float horPhi, maxR, aspectRatio;
 };
+enum CamType : int32_t { CAM_PERSPECTIVE = 0, CAM_ORTHO = 1, CAM_ANGULAR = 2 };
 
 enum IntegType : int32_t { INTEG_DIRECT = 0, INTEG_PATH = 1 };
 struct Integrator {

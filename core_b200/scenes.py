@@ -327,8 +327,10 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     else:                                   # explicit light set: list of (name, params)
         for lname, lp in lights:
             create(yi, "light", lname, **lp)
-    create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -9.5, 4.2)}, to=(0.0, 1.0, 0.8),
-           up=(0.0, -9.5, 5.2), resx=width, resy=height, focal=1.3, **(cam_params or {}))
+    cp = dict(type="perspective", focal=1.3)
+    cp.update(cam_params or {})
+    create(yi, "camera", "cam", **{"from": (0.0, -9.5, 4.2)}, to=(0.0, 1.0, 0.8),
+           up=(0.0, -9.5, 5.2), resx=width, resy=height, **cp)
     create(yi, "background", "bg", type="constant", color=(0.35, 0.45, 0.7, 1.0))
     ip = dict(type=integrator, raydepth=raydepth)
     if integrator == "pathtracing":

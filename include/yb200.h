@@ -69,7 +69,7 @@ void yb200_params_end_list  (yb200_ctx *c);
 /* ---- factories: renderEnvironment_t::create* (src/yafraycore/environment.cc:189-479) keyed by "type" */
 yb200_handle yb200_create_light     (yb200_ctx *c, const char *name);  /* pointlight | sunlight | arealight | directional | spotlight | spherelight */
 yb200_handle yb200_create_material  (yb200_ctx *c, const char *name);  /* shinydiffusemat | glossy | coated_glossy | glass | mirror | null | light_mat */
-yb200_handle yb200_create_camera    (yb200_ctx *c, const char *name);  /* perspective */
+yb200_handle yb200_create_camera    (yb200_ctx *c, const char *name);  /* perspective | architect | orthographic | angular */
 yb200_handle yb200_create_background(yb200_ctx *c, const char *name);  /* constant */
 yb200_handle yb200_create_integrator(yb200_ctx *c, const char *name);  /* directlighting | pathtracing | none (volume) */
 yb200_handle yb200_create_texture   (yb200_ctx *c, const char *name);  /* always fails: shader nodes/textures unsupported */

@@ -37,6 +37,15 @@ IMAGE_CASES = {
     "c4_materials_dof_hexagon": (scenes.materials_scene, dict(width=64, height=36, spp=3, integrator="directlighting",
                                                               cam_params=dict(aperture=0.15, dof_distance=10.0, bokeh_type="hexagon",
                                                                               bokeh_rotation=15.0, bokeh_bias="center"))),
+    # the other cameras: architect (perspective with a vertical image plane), orthographic, angular (fisheye; samples
+    # outside the circle get camera weight 0)
+    "c4_cam_architect": (scenes.materials_scene, dict(width=64, height=36, spp=2, integrator="directlighting",
+                                                      cam_params=dict(type="architect", focal=1.1))),
+    "c4_cam_ortho": (scenes.materials_scene, dict(width=64, height=36, spp=2, integrator="directlighting",
+                                                  cam_params=dict(type="orthographic", scale=11.0))),
+    "c4_cam_angular": (scenes.materials_scene, dict(width=64, height=36, spp=2, integrator="pathtracing", bounces=3,
+                                                    cam_params=dict(type="angular", angle=70.0, max_angle=60.0, circular=True,
+                                                                    mirrored=True))),
     # adaptive anti-aliasing (AA_passes > 1: tiledIntegrator_t::render pass loop + imageFilm_t::nextPass)
     "c2_field_adaptive": (scenes.icosphere_field, dict(n_tris=6000, subdiv=1, width=64, height=36, spp=1, bounces=3, passes=3,
                                                        AA_inc_samples=3, AA_threshold=0.02)),
