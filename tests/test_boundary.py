@@ -66,7 +66,7 @@ class TestHostLogic:
         yi.setVerbosityMute()
         yi.startScene(0)
         for kind, ty in (("material", "blend_mat"), ("material", "rough_glass"), ("light", "ieslight"),
-                         ("camera", "orthographic"), ("background", "sunsky"), ("integrator", "photonmapping")):
+                         ("camera", "equirectangular"), ("background", "sunsky"), ("integrator", "photonmapping")):
             yi.paramsClearAll(); yi.paramsSetString("type", ty)
             assert getattr(yi, "create" + kind.capitalize())("x") == 0
             assert "not supported" in yi.lastError()
