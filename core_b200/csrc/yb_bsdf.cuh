@@ -676,8 +676,163 @@ YB_HD void glass_getSpecular(const Material &m, const Surf &sp, v3 wo, int rayle
     }
 }
 
-// ================================================================== dispatch: material_t virtuals
-YB_HD void mat_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
+// ================================================================== roughGlassMat_t (no dispersion, no absorption: rejected at creation)
+// microfacet.h:118-193
+YB_HD void GGX_Sample(v3 &H, float alpha2, float s1, float s2)
+{
+    float tanTheta2 = alpha2 * (s1 / (1.00001f - s1));
+    float cosTheta = 1.f / fSqrt(1.f + tanTheta2);
+    float sinTheta = fSqrt(1.00001f - (cosTheta * cosTheta));
+    float phi = (float)(YB_M_2PI * (double)s2);
+    H = v3(sinTheta * fCos(phi), sinTheta * fSin(phi), cosTheta);
+}
+YB_HD float GGX_D(float alpha2, float cosTheta2, float tanTheta2)
+{
+    float cosTheta4 = cosTheta2 * cosTheta2;
+    float aTan = alpha2 + tanTheta2;
+    float div = (float)(YB_M_PI * (double)cosTheta4 * (double)aTan * (double)aTan);
+    return alpha2 / div;
+}
+YB_HD float GGX_G(float alpha2, float woN, float wiN)
+{
+    float woN2 = woN * woN, wiN2 = wiN * wiN;
+    float sqrTerm1 = fSqrt(1.f + alpha2 * ((1.f - woN2) / woN2));
+    float sqrTerm2 = fSqrt(1.f + alpha2 * ((1.f - wiN2) / wiN2));
+    float G1wo = 2.f / (1.f + sqrTerm1), G1wi = 2.f / (1.f + sqrTerm2);
+    return G1wo * G1wi;
+}
+YB_HD float GGX_Pdf(float D, float cosTheta, float Jacobian) { return D * cosTheta * Jacobian; }
+YB_HD float microfacetFresnel(float woH, float ior)
+{
+    float c = fabsf(woH);
+    float g = ior * ior - 1 + c * c;
+    if (g > 0) {
+        g = fSqrt(g);
+        float A = (g - c) / (g + c);
+        float B = (c * (g + c) - 1) / (c * (g - c) + 1);
+        return 0.5f * A * A * (1 + B * B);
+    }
+    return 1.0f;
+}
+YB_HD bool refractMicrofacet(float eta, v3 wo, v3 &wi, v3 H, float woH, float woN, float &Kr, float &Kt)
+{
+    wi = v3(0.f);
+    float c = -dot(wo, H);
+    float sign = (c > 0.f) ? 1.f : -1.f;
+    float t1 = 1 - (eta * eta * (1 - c * c));
+    if (t1 < 0.f) return false;
+    wi = eta * wo + (eta * c - sign * fSqrt(t1)) * H;
+    wi = -wi;
+    Kr = 0.f; Kt = 0.f;
+    Kr = microfacetFresnel(woH, 1.f / eta);
+    if (Kr == 1.f) return false;
+    Kt = 1 - Kr;
+    return true;
+}
+YB_HD void reflectMicrofacet(v3 wo, v3 &wi, v3 H, float woH)
+{
+    wi = wo + (2.f * dot(H, -wo) * H);
+    wi = -wi;
+}
+// The two sample() overloads of roughGlassMat_t share everything up to the Fresnel split (roughglass.cc:56-90,146-181)
+struct RGState { v3 N, H, wiT; bool outside, refr; float D, cosTheta, woH, woN, Kr, Kt; };
+YB_HD void rg_setup(const Material &m, const Surf &sp, v3 wo, float s1, float s2, RGState &r)
+{
+    r.N = YB_FACE_FORWARD(sp.Ng, sp.N, wo);
+    r.outside = dot(sp.Ng, wo) > 0.f;
+    v3 H(0.f);
+    GGX_Sample(H, m.rgAlpha2, s1, s2);
+    H = H.x * sp.NU + H.y * sp.NV + H.z * r.N;
+    r.H = normalize(H);
+    r.D = 0.f;
+    r.cosTheta = dot(r.H, r.N);
+    float cosTheta2 = r.cosTheta * r.cosTheta;
+    float tanTheta2 = (1.f - cosTheta2) / (cosTheta2 * 0.99f + 0.01f);
+    if (r.cosTheta > 0.f) r.D = GGX_D(m.rgAlpha2, cosTheta2, tanTheta2);
+    r.woH = dot(wo, r.H);
+    r.woN = dot(wo, r.N);
+    r.Kr = r.Kt = 0.f;
+    r.refr = refractMicrofacet(r.outside ? 1.f / m.ior : m.ior, wo, r.wiT, r.H, r.woH, r.woN, r.Kr, r.Kt);
+}
+YB_HD col3 rg_transmit(const Material &m, const RGState &r, v3 wi, float &pdf, float &W)    // roughglass.cc:94-116
+{
+    float wiN = dot(wi, r.N), wiH = dot(wi, r.H), G = 0.f;
+    if ((wiH * wiN) > 0.f && (r.woH * r.woN) > 0.f) G = GGX_G(m.rgAlpha2, wiN, r.woN);
+    float IORwi = 1.f, IORwo = 1.f;
+    if (r.outside) IORwi = m.ior; else IORwo = m.ior;
+    float ht = IORwo * r.woH + IORwi * wiH;
+    float Jacobian = (IORwi * IORwi) / fmaxf_(1.0e-8f, ht * ht);
+    float glossy = fabsf((r.woH * wiH) / (wiN * r.woN)) * r.Kt * G * r.D * Jacobian;
+    pdf = GGX_Pdf(r.D, r.cosTheta, Jacobian * fabsf(wiH));
+    W = fabsf(wiN) / (pdf * 0.99f + 0.01f);
+    return glossy * m.filterCol;
+}
+YB_HD col3 rg_reflect(const Material &m, const RGState &r, v3 wo, v3 &wi, float &pdf, float &W)   // roughglass.cc:118-136
+{
+    reflectMicrofacet(wo, wi, r.H, r.woH);
+    float wiN = dot(wi, r.N), wiH = dot(wi, r.H);
+    float G = GGX_G(m.rgAlpha2, wiN, r.woN);
+    float Jacobian = 1.f / ((4.f * fabsf(wiH)) * 0.99f + 0.01f);
+    float glossy = (r.Kr * G * r.D) / ((4.f * fabsf(r.woN * wiN)) * 0.99f + 0.01f);
+    pdf = GGX_Pdf(r.D, r.cosTheta, Jacobian);
+    W = fabsf(wiN) / (pdf * 0.99f + 0.01f);
+    return glossy * m.specRefCol;
+}
+YB_HD col3 rg_sample(const Material &m, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)      // roughglass.cc:56-139
+{
+    RGState r;
+    s.pdf = 1.f;
+    rg_setup(m, sp, wo, s.s1, s.s2, r);
+    wi = r.wiT;
+    col3 ret(0.f);
+    if (r.refr) {
+        if (s.s1 < r.Kt && (s.flags & BSDF_TRANSMIT)) {
+            ret = rg_transmit(m, r, wi, s.pdf, W);
+            s.sampledFlags = BSDF_GLOSSY | BSDF_TRANSMIT;
+        } else if (s.flags & BSDF_REFLECT) {
+            ret = rg_reflect(m, r, wo, wi, s.pdf, W);
+            s.sampledFlags = BSDF_GLOSSY | BSDF_REFLECT;
+        }
+    } else {                                                            // total inner reflection
+        wi = reflect_about(wo, r.H);
+        s.sampledFlags = BSDF_GLOSSY | BSDF_REFLECT;
+        ret = col3(1.f);
+        W = 1.f;
+    }
+    return ret;
+}
+// the two-direction overload used by recursiveRaytrace (roughglass.cc:141-236): slot 0 = refraction (or the TIR mirror
+// direction), slot 1 = reflection; the integrator reads slot 0 under BSDF_REFLECT and slot 1 under BSDF_TRANSMIT
+// (mcintegrator.cc:551-575), so both slots are traced whenever refraction exists
+YB_HD void rg_sample2(const Material &m, const Surf &sp, v3 wo, v3 *dir, col3 *col, float *W, BSample &s)
+{
+    RGState r;
+    s.pdf = 1.f;
+    rg_setup(m, sp, wo, s.s1, s.s2, r);
+    s.sampledFlags = 0;
+    col[0] = col[1] = col3(0.f); W[0] = W[1] = 0.f; dir[0] = dir[1] = v3(0.f);
+    if (r.refr) {
+        if (s.flags & BSDF_TRANSMIT) {
+            col[0] = rg_transmit(m, r, r.wiT, s.pdf, W[0]);
+            s.sampledFlags = BSDF_GLOSSY | BSDF_TRANSMIT;
+            dir[0] = r.wiT;
+        }
+        if (s.flags & BSDF_REFLECT) {
+            v3 wi;
+            col[1] = rg_reflect(m, r, wo, wi, s.pdf, W[1]);
+            s.sampledFlags |= BSDF_GLOSSY | BSDF_REFLECT;
+            dir[1] = wi;
+        }
+    } else {
+        dir[0] = reflect_about(wo, r.H);
+        s.sampledFlags |= BSDF_GLOSSY | BSDF_REFLECT;
+        col[0] = col3(1.f);
+        W[0] = 1.f;
+    }
+}
+
+// ================================================================== dispatch over the leaf materials: material_t virtuals
+YB_HD void leaf_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
 {
     bsdfs = m.bsdfFlags;
     switch (m.type) {
@@ -687,7 +842,7 @@ YB_HD void mat_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
         default: d.c[0] = d.c[1] = d.c[2] = d.c[3] = 0.f; break;
     }
 }
-YB_HD col3 mat_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
+YB_HD col3 leaf_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
 {
     switch (m.type) {
         case MAT_SHINYDIFFUSE: return sd_eval(m, d, sp, wo, wl, bsdfs);
@@ -696,13 +851,14 @@ YB_HD col3 mat_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v
         default: return col3(0.f);
     }
 }
-YB_HD col3 mat_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
+template <int EXT> YB_HD col3 leaf_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
 {
     switch (m.type) {
         case MAT_SHINYDIFFUSE: return sd_sample(m, d, sp, wo, wi, s, W);
         case MAT_GLOSSY: return gl_sample(m, d, sp, wo, wi, s, W);
         case MAT_COATED_GLOSSY: return cg_sample(m, d, sp, wo, wi, s, W);
         case MAT_GLASS: return glass_sample(m, sp, wo, wi, s, W);
+        case MAT_ROUGH_GLASS: if (EXT) return rg_sample(m, sp, wo, wi, s, W);   // falls through to the empty default in builds without it
         case MAT_MIRROR:                                                 // glass.cc:348-354
             wi = reflect_dir(sp.N, wo);
             s.sampledFlags = BSDF_SPECULAR | BSDF_REFLECT;
@@ -713,7 +869,7 @@ YB_HD col3 mat_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo,
             return col3(0.f);
     }
 }
-YB_HD float mat_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
+YB_HD float leaf_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
 {
     switch (m.type) {
         case MAT_SHINYDIFFUSE: return sd_pdf(m, d, sp, wo, wi, bsdfs);
@@ -722,7 +878,7 @@ YB_HD float mat_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v
         default: return 0.f;
     }
 }
-YB_HD col3 mat_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
+YB_HD col3 leaf_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
 {
     if (m.type == MAT_SHINYDIFFUSE) return m.emitColor;                 // shinydiffuse.cc:251-257
     if (m.type == MAT_LIGHT) {                                          // simple.cc:63-70
@@ -732,7 +888,7 @@ YB_HD col3 mat_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights
     }
     return col3(0.f);
 }
-YB_HD void mat_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
+YB_HD void leaf_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
 {
     switch (m.type) {
         case MAT_SHINYDIFFUSE: sd_getSpecular(m, d, sp, wo, refl, refr, dir, col); break;
@@ -748,19 +904,19 @@ YB_HD void mat_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v
         default: refl = false; refr = false; break;                      // material.h:141-144
     }
 }
-YB_HD bool mat_isTransparent(const Material &m)
+YB_HD bool leaf_isTransparent(const Material &m)
 {
     if (m.type == MAT_SHINYDIFFUSE) return m.isTransparent != 0;        // shinydiff.h isTransparent(){return mIsTransparent;}
-    if (m.type == MAT_GLASS) return m.fakeShadow != 0;
+    if (m.type == MAT_GLASS || m.type == MAT_ROUGH_GLASS) return m.fakeShadow != 0;
     return false;
 }
-YB_HD col3 mat_getTransparency(const Material &m, const Surf &sp, v3 wo)
+YB_HD col3 leaf_getTransparency(const Material &m, const Surf &sp, v3 wo)
 {
     if (m.type == MAT_SHINYDIFFUSE) return sd_getTransparency(m, sp, wo);
-    if (m.type == MAT_GLASS) return glass_getTransparency(m, sp, wo);
+    if (m.type == MAT_GLASS || m.type == MAT_ROUGH_GLASS) return glass_getTransparency(m, sp, wo);   // roughglass.cc:238-244 is the same formula
     return col3(0.f);
 }
-YB_HD float mat_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
+YB_HD float leaf_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
 {
     if (m.type == MAT_SHINYDIFFUSE) return sd_getAlpha(m, d, sp, wo);
     if (m.type == MAT_GLASS) {                                          // glass.cc:198-202
@@ -768,7 +924,133 @@ YB_HD float mat_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 
         if (alpha < 0.0f) alpha = 0.0f;
         return alpha;
     }
+    if (m.type == MAT_ROUGH_GLASS)                                      // roughglass.cc:246-250
+        return fmaxf_(0.f, fminf_(1.f, 1.f - col_energy(glass_getTransparency(m, sp, wo))));
     return 1.f;
+}
+
+// ================================================================== blendMat_t (blend.cc:49-393) over two leaf materials, constant blend_value
+// EXT: the shade kernel is compiled twice (yb_render.cu); scenes without rough_glass / blend_mat / mesh lights run the EXT = 0
+// build, which carries none of this code (register pressure of the common path)
+// userdata of the sub-materials (SDDat_t / MDat_t) depends only on the material constants here, so it is recomputed
+// where the reference reads it back from state.userdata
+YB_HD const Material &blend_m1(const Material &m) { return (&m)[m.blendOff1]; }
+YB_HD const Material &blend_m2(const Material &m) { return (&m)[m.blendOff2]; }
+YB_HD float blend_ival(float val) { return fminf_(1.f, fmaxf_(0.f, 1.f - val)); }                       // :60
+YB_HD uint32_t blend_flags(const Material &sub) { return sub.type == MAT_NULL ? (uint32_t)BSDF_NONE : sub.bsdfFlags; }   // mat1Flags / mat2Flags
+
+template <int EXT> YB_HD void mat_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
+{
+    if (!EXT || m.type != MAT_BLEND) { leaf_initBSDF(m, d, bsdfs); return; }
+    d.c[0] = d.c[1] = d.c[2] = d.c[3] = 0.f;
+    bsdfs = blend_flags(blend_m1(m)) | blend_flags(blend_m2(m));
+}
+// blendMat_t::initBSDF replaces the surface point by blend_surface_points(sp, sp, ival) (blend.cc:72-82, surface.cc:82-96,
+// interpolation.h:29-35): without bump mapping both inputs are equal, and v*a + v*(1-a) is kept as the reference computes it
+template <int EXT> YB_HD void mat_blendSurface(const Material &m, Surf &sp)
+{
+    if (!EXT || m.type != MAT_BLEND) return;
+    const double alpha = (double)blend_ival(m.blendVal);
+    const float a = (float)alpha, b = (float)(1.0 - alpha);
+    sp.N = sp.N * a + sp.N * b;
+    sp.NU = sp.NU * a + sp.NU * b;
+    sp.NV = sp.NV * a + sp.NV * b;
+}
+template <int EXT> YB_HD col3 mat_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
+{
+    if (!EXT || m.type != MAT_BLEND) return leaf_eval(m, d, sp, wo, wl, bsdfs);
+    const float val = m.blendVal, ival = blend_ival(val);
+    MatDat d1, d2; uint32_t f;
+    leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);
+    col3 col1 = leaf_eval(blend_m1(m), d1, sp, wo, wl, bsdfs);
+    col3 col2 = leaf_eval(blend_m2(m), d2, sp, wo, wl, bsdfs);
+    return col1 * ival + col2 * val;
+}
+template <int EXT> YB_HD col3 mat_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
+{
+    if (!EXT || m.type != MAT_BLEND) return leaf_sample<EXT>(m, d, sp, wo, wi, s, W);
+    const float val = m.blendVal, ival = blend_ival(val);
+    const Material &m1 = blend_m1(m), &m2 = blend_m2(m);
+    bool mat1Sampled = false, mat2Sampled = false;
+    col3 col1(0.f), col2(0.f);
+    BSample s1 = s, s2 = s;
+    v3 wi1(0.f), wi2(0.f);
+    float W1 = 0.f, W2 = 0.f;
+    s2.pdf = s1.pdf = s.pdf = 0.f;
+    MatDat dd; uint32_t f;
+    if (s.flags & blend_flags(m1)) { leaf_initBSDF(m1, dd, f); col1 = leaf_sample<EXT>(m1, dd, sp, wo, wi1, s1, W1); mat1Sampled = true; }
+    if (s.flags & blend_flags(m2)) { leaf_initBSDF(m2, dd, f); col2 = leaf_sample<EXT>(m2, dd, sp, wo, wi2, s2, W2); mat2Sampled = true; }
+    if (mat1Sampled && mat2Sampled) {
+        wi = normalize(wi2 + wi1);
+        s.pdf = s1.pdf * ival + s2.pdf * val;
+        s.sampledFlags = s1.sampledFlags | s2.sampledFlags;
+        col1 = (col1 * W1) * ival + (col2 * W2) * val;
+        W = 1.f;
+    } else if (mat1Sampled) {
+        wi = wi1; s.pdf = s1.pdf; s.sampledFlags = s1.sampledFlags; W = W1;
+    } else if (mat2Sampled) {
+        wi = wi2; s.pdf = s2.pdf; s.sampledFlags = s2.sampledFlags; col1 = col2; W = W2;
+    }
+    return col1;
+}
+template <int EXT> YB_HD float mat_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
+{
+    if (!EXT || m.type != MAT_BLEND) return leaf_pdf(m, d, sp, wo, wi, bsdfs);
+    const float val = m.blendVal, ival = blend_ival(val);
+    MatDat d1, d2; uint32_t f;
+    leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);
+    float pdf1 = leaf_pdf(blend_m1(m), d1, sp, wo, wi, bsdfs), pdf2 = leaf_pdf(blend_m2(m), d2, sp, wo, wi, bsdfs);
+    return pdf1 * ival + pdf2 * val;
+}
+template <int EXT> YB_HD col3 mat_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
+{
+    if (!EXT || m.type != MAT_BLEND) return leaf_emit(m, sp, wo, includeLights);
+    const float val = m.blendVal, ival = blend_ival(val);
+    col3 col1 = leaf_emit(blend_m1(m), sp, wo, includeLights), col2 = leaf_emit(blend_m2(m), sp, wo, includeLights);
+    return col1 * ival + col2 * val;
+}
+template <int EXT> YB_HD void mat_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
+{
+    if (!EXT || m.type != MAT_BLEND) { leaf_getSpecular(m, d, sp, wo, raylevel, refl, refr, dir, col); return; }
+    const float val = m.blendVal, ival = blend_ival(val);
+    refl = false; refr = false;
+    bool m1_refl = false, m1_refr = false;
+    v3 m1_dir[2]; col3 m1_col[2];
+    m1_col[0] = m1_col[1] = col3(0.f); m1_dir[0] = m1_dir[1] = v3(0.f);
+    MatDat dd; uint32_t f;
+    leaf_initBSDF(blend_m1(m), dd, f);
+    leaf_getSpecular(blend_m1(m), dd, sp, wo, raylevel, m1_refl, m1_refr, m1_dir, m1_col);
+    leaf_initBSDF(blend_m2(m), dd, f);
+    leaf_getSpecular(blend_m2(m), dd, sp, wo, raylevel, refl, refr, dir, col);
+    if (refl && m1_refl) { col[0] = m1_col[0] * ival + col[0] * val; dir[0] = normalize(dir[0] + m1_dir[0]); }
+    else if (m1_refl) { col[0] = m1_col[0] * ival; dir[0] = m1_dir[0]; }
+    else col[0] = col[0] * val;
+    if (refr && m1_refr) { col[1] = m1_col[1] * ival + col[1] * val; dir[1] = normalize(dir[1] + m1_dir[1]); }
+    else if (m1_refr) { col[1] = m1_col[1] * ival; dir[1] = m1_dir[1]; }
+    else col[1] = col[1] * val;
+    refr = refr || m1_refr;
+    refl = refl || m1_refl;
+}
+template <int EXT> YB_HD bool mat_isTransparent(const Material &m)
+{
+    if (!EXT || m.type != MAT_BLEND) return leaf_isTransparent(m);
+    return leaf_isTransparent(blend_m1(m)) || leaf_isTransparent(blend_m2(m));
+}
+template <int EXT> YB_HD col3 mat_getTransparency(const Material &m, const Surf &sp, v3 wo)
+{
+    if (!EXT || m.type != MAT_BLEND) return leaf_getTransparency(m, sp, wo);
+    const float val = m.blendVal, ival = blend_ival(val);
+    col3 col1 = leaf_getTransparency(blend_m1(m), sp, wo), col2 = leaf_getTransparency(blend_m2(m), sp, wo);
+    return col1 * ival + col2 * val;
+}
+template <int EXT> YB_HD float mat_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
+{
+    if (!EXT || m.type != MAT_BLEND) return leaf_getAlpha(m, d, sp, wo);
+    if (!mat_isTransparent<EXT>(m)) return 1.f;
+    MatDat d1, d2; uint32_t f;
+    leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);
+    float al1 = leaf_getAlpha(blend_m1(m), d1, sp, wo), al2 = leaf_getAlpha(blend_m2(m), d2, sp, wo);
+    return fminf_(al1, al2);
 }
 
 }  // namespace yb

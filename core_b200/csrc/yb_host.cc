@@ -409,6 +409,30 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         m.specRefCol = srCol; m.fakeShadow = fake;
         m.bsdfFlags = BSDF_ALL_SPECULAR;
         if (fake) m.bsdfFlags |= BSDF_FILTER;
+    } else if (type == "rough_glass") {           // roughglass.cc:257-285
+        float IOR = 1.4f, filt = 0.f, alpha = 0.5f, disp_power = 0.f; col3 filtCol(1.f), absorp(1.f), srCol(1.f); bool fake = false;
+        p.get("IOR", IOR); p.getColor("filter_color", filtCol); p.get("transmit_filter", filt); p.getColor("mirror_color", srCol);
+        p.get("alpha", alpha); p.get("dispersion_power", disp_power); p.get("fake_shadows", fake);
+        if (disp_power > 0.0) { fail("rough_glass '" + std::string(name) + "': dispersion is not supported"); return 0; }
+        if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("rough_glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
+        alpha = std::max(1e-4f, std::min(alpha * 0.5f, 1.f));
+        m.type = MAT_ROUGH_GLASS;
+        m.ior = IOR; m.rgAlpha2 = alpha * alpha;
+        m.filterCol = filt * filtCol + col3(1.f - filt);
+        m.specRefCol = srCol; m.fakeShadow = fake;
+        m.bsdfFlags = BSDF_ALL_GLOSSY;
+        if (fake) m.bsdfFlags |= BSDF_FILTER;
+    } else if (type == "blend_mat") {             // blend.cc:395-431 + ctor :32-41
+        std::string n1, n2; double blend_val = 0.5;
+        if (!p.get("material1", n1) || !p.get("material2", n2)) { fail("blend_mat '" + std::string(name) + "': material1 / material2 missing"); return 0; }
+        std::map<std::string, int>::const_iterator i1 = materialNames.find(n1), i2 = materialNames.find(n2);
+        if (i1 == materialNames.end() || i2 == materialNames.end()) { fail("blend_mat '" + std::string(name) + "': material '" + (i1 == materialNames.end() ? n1 : n2) + "' does not exist"); return 0; }
+        if (p.has("mask")) { fail("blend_mat '" + std::string(name) + "': a blend mask shader node is not supported (constant blend_value only)"); return 0; }
+        if (materials[i1->second].type == MAT_BLEND || materials[i2->second].type == MAT_BLEND) { fail("blend_mat '" + std::string(name) + "': blending a blend_mat is not supported (one level only)"); return 0; }
+        p.get("blend_value", blend_val);
+        const int self = (int)materials.size();
+        m.type = MAT_BLEND; m.blendOff1 = i1->second - self; m.blendOff2 = i2->second - self; m.blendVal = (float)blend_val;
+        m.bsdfFlags = materials[i1->second].bsdfFlags | materials[i2->second].bsdfFlags;
     } else if (type == "mirror") {                // glass.cc:336-371
         col3 col(1.f); float refl = 1.f;
         p.getColor("color", col); p.get("reflect", refl);
@@ -421,7 +445,7 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         p.getColor("color", col); p.get("power", power); p.get("double_sided", ds);
         m.type = MAT_LIGHT; m.lightCol = col * (float)power; m.doubleSided = ds; m.bsdfFlags = BSDF_EMIT;
     } else {
-        fail("Environment: material type '" + type + "' is not supported by the B200 path (supported: shinydiffusemat, glossy, coated_glossy, glass, mirror, null, light_mat)");
+        fail("Environment: material type '" + type + "' is not supported by the B200 path (supported: shinydiffusemat, glossy, coated_glossy, glass, rough_glass, blend_mat, mirror, null, light_mat)");
         return 0;
     }
     if (materials.size() >= TRI_MAT_MASK) { fail("too many materials"); return 0; }

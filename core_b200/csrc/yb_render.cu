@@ -165,81 +165,6 @@ YB_D void push_task(const RenderArgs &a, const Task &t)
     a.out_tasks[i] = t;
 }
 
-// ------------------------------------------------------------------------------------------------ direct lighting
-// mcIntegrator_t::doLightEstimation (mcintegrator.cc:73-195).  Every term that the reference adds after an
-// isShadowed() test becomes a shadow task carrying weight*term.
-YB_D void doLightEstimation(const RenderArgs &a, const Light &light, uint32_t loffs, const Surf &sp, const MatDat &md, v3 wo,
-                             const SampleId &id, uint32_t rayDivision, col3 weight, uint32_t sid)
-{
-    const Material &mat = *sp.mat;
-    const uint32_t l_offs = loffs * YB_LOFFS_DELTA;
-    Ray lightRay;
-    lightRay.from = sp.P; lightRay.tmin = 0.f; lightRay.tmax = -1.f; lightRay.dir = v3(0.f);
-    const uint32_t allBSDFIntersect = BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_DISPERSIVE | BSDF_REFLECT | BSDF_TRANSMIT;
-    if (light_dirac(light)) {
-        col3 lcol(0.f);
-        if (light_illuminate(light, sp.P, lcol, lightRay)) {
-            lightRay.tmin = YB_SHADOW_BIAS;
-            col3 surfCol = mat_eval(mat, md, sp, wo, lightRay.dir, BSDF_ALL);
-            col3 c = mul(surfCol, lcol) * fabsf(dot(sp.N, lightRay.dir));
-            push_shadow(a, lightRay, mul(weight, c), sid);
-        }
-        return;
-    }
-    int n = light.samples;
-    if (rayDivision > 1) n = (n / (int)rayDivision) > 1 ? (n / (int)rayDivision) : 1;
-    const float invNS = 1.f / (float)n;
-    const uint32_t offs = (uint32_t)n * (uint32_t)id.pixelSample + id.samplingOffs + l_offs;
-    const bool canIntersect = light_canIntersect(light);
-    Halton2 hal2; Halton3 hal3;
-    hal2.setStart(offs - 1); hal3.setStart(offs - 1);
-    for (int i = 0; i < n; ++i) {
-        LSample ls;
-        ls.s1 = hal2.getNext(); ls.s2 = hal3.getNext();
-        ls.col = col3(0.f); ls.pdf = 0.f;
-        if (light_illumSample(light, sp.P, ls, lightRay)) {
-            lightRay.tmin = YB_SHADOW_BIAS;
-            if (ls.pdf > 1e-6f) {
-                col3 surfCol = mat_eval(mat, md, sp, wo, lightRay.dir, BSDF_ALL);
-                col3 c;
-                if (canIntersect) {
-                    float mPdf = mat_pdf(mat, md, sp, wo, lightRay.dir, allBSDFIntersect);
-                    if (mPdf > 1e-6f) {
-                        float l2 = ls.pdf * ls.pdf, m2 = mPdf * mPdf;
-                        float w = l2 / (l2 + m2);
-                        c = mul(surfCol, ls.col) * (fabsf(dot(sp.N, lightRay.dir)) * w / ls.pdf);
-                    } else c = mul(surfCol, ls.col) * (fabsf(dot(sp.N, lightRay.dir)) / ls.pdf);
-                } else c = mul(surfCol, ls.col) * (fabsf(dot(sp.N, lightRay.dir)) / ls.pdf);
-                push_shadow(a, lightRay, mul(weight, c) * invNS, sid);
-            }
-        }
-    }
-    if (canIntersect) {   // sample from BSDF to complete MIS
-        hal2.setStart(offs - 1); hal3.setStart(offs - 1);
-        for (int i = 0; i < n; ++i) {
-            Ray bRay;
-            bRay.tmin = YB_MIN_RAYDIST; bRay.from = sp.P; bRay.tmax = -1.f;
-            float s1 = hal2.getNext(), s2 = hal3.getNext(), W = 0.f;
-            BSample s(s1, s2, allBSDFIntersect);
-            col3 surfCol = mat_sample(mat, md, sp, wo, bRay.dir, s, W);
-            col3 lcol; float lightPdf;
-            if (s.pdf > 1e-6f && light_intersect(light, bRay.from, bRay.dir, bRay.tmax, lcol, lightPdf)) {
-                if (lightPdf > 1e-6f) {
-                    float lPdf = 1.f / lightPdf;
-                    float l2 = lPdf * lPdf, m2 = s.pdf * s.pdf;
-                    float w = m2 / (l2 + m2);
-                    col3 c = mul(surfCol, lcol) * (w * W);
-                    push_shadow(a, bRay, mul(weight, c) * invNS, sid);
-                }
-            }
-        }
-    }
-}
-// estimateAllDirectLight (mcintegrator.cc:45-56)
-YB_D void estimateAllDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, col3 weight, uint32_t sid)
-{
-    for (int l = 0; l < a.sc.nLights; ++l) doLightEstimation(a, a.sc.lights[l], (uint32_t)l, sp, md, wo, id, rayDivision, weight, sid);
-}
 // the light estimateOneDirectLight picks for path sample n (mcintegrator.cc:62-66)
 YB_D int pick_one_light(int n, int lightNum)
 {
@@ -249,207 +174,18 @@ YB_D int pick_one_light(int n, int lightNum)
     if (lnum > lightNum - 1) lnum = lightNum - 1;
     return lnum;
 }
-// estimateOneDirectLight (mcintegrator.cc:58-71)
-YB_D void estimateOneDirectLight(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision, int n, col3 weight, uint32_t sid)
-{
-    const int lightNum = a.sc.nLights;
-    if (lightNum == 0) return;
-    const int lnum = pick_one_light(n, lightNum);
-    doLightEstimation(a, a.sc.lights[lnum], (uint32_t)lnum, sp, md, wo, id, rayDivision, weight * (float)lightNum, sid);
-}
-// sampleAmbientOcclusion (mcintegrator.cc:629-683)
-YB_D void sampleAmbientOcclusion(const RenderArgs &a, const Surf &sp, const MatDat &md, v3 wo, const SampleId &id, uint32_t rayDivision,
-                                  float dc1, float dc2, bool includeLights, col3 weight, uint32_t sid)
-{
-    const Integrator &I = a.sc.integ;
-    const Material &mat = *sp.mat;
-    int n = I.aoSamples;
-    if (rayDivision > 1) n = (n / (int)rayDivision) > 1 ? (n / (int)rayDivision) : 1;
-    const uint32_t offs = (uint32_t)n * (uint32_t)id.pixelSample + id.samplingOffs;
-    Halton2 hal2; Halton3 hal3;
-    hal2.setStart(offs - 1); hal3.setStart(offs - 1);
-    const float invN = 1.f / (float)n;
-    col3 ecol(0.f);
-    for (int i = 0; i < n; ++i) {
-        float s1 = hal2.getNext(), s2 = hal3.getNext();
-        if (rayDivision > 1) { s1 = addMod1(s1, dc1); s2 = addMod1(s2, dc2); }
-        Ray lightRay;
-        lightRay.from = sp.P; lightRay.tmin = YB_SHADOW_BIAS; lightRay.tmax = I.aoDist;
-        float W = 0.f;
-        BSample s(s1, s2, BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_REFLECT);
-        col3 surfCol = mat_sample(mat, md, sp, wo, lightRay.dir, s, W);
-        if (mat.bsdfFlags & BSDF_EMIT) ecol += mat_emit(mat, sp, wo, includeLights) * s.pdf;
-        float cosv = fabsf(dot(sp.N, lightRay.dir));
-        col3 c = mul(I.aoCol, surfCol) * cosv * W;
-        push_shadow(a, lightRay, mul(weight, c) * invN, sid);
-    }
-    if (!isBlack(ecol)) acc_add(a, sid, mul(weight, ecol) * invN);
-}
 
-// ------------------------------------------------------------------------------------------------ shading
-YB_D Task child_task(const Task &T, v3 P, v3 dir, col3 thr, float aw, uint32_t bits)
-{
-    Task c = T;
-    c.ray.from = P; c.ray.dir = dir; c.ray.tmin = YB_MIN_RAYDIST; c.ray.tmax = -1.f;
-    c.thr = thr; c.aw = aw; c.bits = bits;
-    return c;
-}
-
-// One call of directLighting_t::integrate / pathIntegrator_t::integrate after its scene->intersect
-// (directlight.cc:112-182, pathtracer.cc:134-333), including the recursiveRaytrace fan-out (mcintegrator.cc:421-627).
-YB_D void shade_integrate(const RenderArgs &a, const Task &T, const Hit &H)
-{
-    const Integrator &I = a.sc.integ;
-    const uint32_t sid = T.sid;
-    const float a0 = I.transpBackground ? 0.f : 1.f;
-    if (H.tri < 0) {                                            // nothing hit: background (directlight.cc:166-169)
-        if (I.hasBackground) acc_add(a, sid, mul(T.thr, I.bgColor));
-        if (T.aw != 0.f) acc_add_alpha(a, sid, T.aw * a0);
-        return;
-    }
-    const SampleId id = sample_id(a, sid);
-    Surf sp;
-    tri_getSurface(a.sc, H.tri, T.ray.from + H.t * T.ray.dir, H.b1, H.b2, sp);
-    const Material &mat = *sp.mat;
-    MatDat md; uint32_t bsdfs;
-    mat_initBSDF(mat, md, bsdfs);
-    const v3 wo = -T.ray.dir;
-    const int raylevel = (int)task_level(T.bits);
-    const bool includeLights = raylevel == 0 ? true : task_lights(T.bits);
-    if (bsdfs & BSDF_EMIT) acc_add(a, sid, mul(T.thr, mat_emit(mat, sp, wo, includeLights)));
-    if (bsdfs & BSDF_DIFFUSE) {
-        estimateAllDirectLight(a, sp, md, wo, id, T.rayDivision, T.thr, sid);
-        if (I.type == INTEG_DIRECT && I.useAO) sampleAmbientOcclusion(a, sp, md, wo, id, T.rayDivision, T.dc1, T.dc2, includeLights, T.thr, sid);
-    }
-    if (I.type == INTEG_PATH) {                                 // pathtracer.cc:184-303: first path segment
-        uint32_t path_flags = I.noRecursive ? BSDF_ALL : BSDF_DIFFUSE;
-        if (bsdfs & path_flags) {
-            path_flags |= (BSDF_DIFFUSE | BSDF_REFLECT | BSDF_TRANSMIT);
-            int nSamples = I.nPaths / (int)T.rayDivision; if (nSamples < 1) nSamples = 1;
-            const float invN = 1.f / (float)nSamples;
-            for (int i = 0; i < nSamples; ++i) {
-                const uint32_t offs = (uint32_t)I.nPaths * (uint32_t)id.pixelSample + id.samplingOffs + (uint32_t)i;
-                float s1 = RI_vdC(offs), s2 = (float)scrHalton(2, offs), W = 0.f;
-                if (T.rayDivision > 1) { s1 = addMod1(s1, T.dc1); s2 = addMod1(s2, T.dc2); }
-                BSample s(s1, s2, path_flags);
-                v3 wi(0.f);
-                col3 scol = mat_sample(mat, md, sp, wo, wi, s, W);
-                scol *= W;
-                if (isBlack(scol)) continue;                     // every later term of this path is multiplied by it
-                Task c = child_task(T, sp.P, wi, mul(T.thr, scol) * invN, 0.f, task_bits(TASK_PATH, false, (uint32_t)raylevel, 0));
-                c.pathOffs = offs;
-                push_task(a, c);
-            }
-        }
-    }
-    // ---- recursiveRaytrace (mcintegrator.cc:421-627)
-    float residualAlpha = 0.f; bool alphaTaken = false;
-    float m_alpha = 1.f;
-    if (I.transpRefractedBackground) m_alpha = mat_getAlpha(mat, md, sp, wo);
-    if (T.aw != 0.f) {
-        if (I.transpRefractedBackground) { acc_add_alpha(a, sid, T.aw * m_alpha); residualAlpha = T.aw * (1.f - m_alpha); }
-        else acc_add_alpha(a, sid, T.aw);
-    }
-    const int newlevel = raylevel + 1;
-    if (newlevel <= I.rDepth) {
-        if ((bsdfs & BSDF_GLOSSY) && newlevel < 20 && (mat.bsdfFlags & BSDF_GLOSSY)) {
-            // supported glossy materials reflect only (BSDF_REFLECT without BSDF_TRANSMIT): mcintegrator.cc:519-537
-            int gsam = 8;
-            const uint32_t oldDivision = T.rayDivision, oldOffset = T.rayOffset;
-            if (oldDivision > 1) { gsam = gsam / (int)oldDivision; if (gsam < 1) gsam = 1; }
-            const uint32_t newDivision = oldDivision * (uint32_t)gsam;
-            uint32_t branch = newDivision * oldOffset;
-            uint32_t offs = (uint32_t)gsam * (uint32_t)id.pixelSample + id.samplingOffs;
-            const float d_1 = 1.f / (float)gsam;
-            Halton2 hal2; Halton3 hal3;
-            hal2.setStart(offs); hal3.setStart(offs);
-            for (int ns = 0; ns < gsam; ++ns) {
-                const float dc1 = (float)scrHalton(2 * newlevel + 1, branch + id.samplingOffs);
-                const float dc2 = (float)scrHalton(2 * newlevel + 2, branch + id.samplingOffs);
-                const uint32_t rayOffset = branch;
-                ++offs; ++branch;
-                const float s1 = hal2.getNext(), s2 = hal3.getNext();
-                if ((mat.bsdfFlags & BSDF_REFLECT) && !(mat.bsdfFlags & BSDF_TRANSMIT)) {
-                    float W = 0.f;
-                    BSample s(s1, s2, BSDF_GLOSSY | BSDF_REFLECT);
-                    v3 wi(0.f);
-                    col3 mcol = mat_sample(mat, md, sp, wo, wi, s, W);
-                    col3 w = mul(T.thr, mcol) * W * d_1;
-                    if (isBlack(w)) continue;
-                    Task c = child_task(T, sp.P, wi, w, 0.f, task_bits(TASK_INTEGRATE, true, (uint32_t)newlevel, 0));
-                    c.rayDivision = newDivision; c.rayOffset = rayOffset; c.dc1 = dc1; c.dc2 = dc2;
-                    push_task(a, c);
-                }
-            }
-        }
-        if ((bsdfs & (BSDF_SPECULAR | BSDF_FILTER)) && newlevel < 20) {
-            bool reflect = false, refract = false;
-            v3 dir[2]; col3 rcol[2];
-            dir[0] = dir[1] = v3(0.f); rcol[0] = rcol[1] = col3(0.f);
-            mat_getSpecular(mat, md, sp, wo, newlevel, reflect, refract, dir, rcol);
-            if (reflect) {
-                col3 w = mul(T.thr, rcol[0]);
-                if (!isBlack(w)) push_task(a, child_task(T, sp.P, dir[0], w, 0.f, task_bits(TASK_INTEGRATE, true, (uint32_t)newlevel, 0)));
-            }
-            if (refract) {
-                col3 w = mul(T.thr, rcol[1]);
-                // alpha = integ.A of the refracted call (mcintegrator.cc:622): the residual alpha weight travels with it
-                if (!isBlack(w) || residualAlpha != 0.f) {
-                    push_task(a, child_task(T, sp.P, dir[1], w, residualAlpha, task_bits(TASK_INTEGRATE, true, (uint32_t)newlevel, 0)));
-                    alphaTaken = true;
-                }
-            }
-        }
-    }
-    if (!alphaTaken && residualAlpha != 0.f) acc_add_alpha(a, sid, residualAlpha * a0);
-}
-
-// One vertex of the bounce loop of pathIntegrator_t::integrate (pathtracer.cc:232-299)
-YB_D void shade_path(const RenderArgs &a, const Task &T, const Hit &H)
-{
-    const Integrator &I = a.sc.integ;
-    const uint32_t sid = T.sid;
-    const uint32_t depth = task_depth(T.bits);                  // number of bounces already taken
-    const bool caustic = task_lights(T.bits);                   // state.includeLights == caustic on a path (pathtracer.cc:266-267)
-    if (H.tri < 0) {
-        if (depth >= 1 && caustic && I.hasBackground) acc_add(a, sid, mul(T.thr, I.bgColor));   // pathtracer.cc:273-280
-        return;
-    }
-    const SampleId id = sample_id(a, sid);
-    Surf sp;
-    tri_getSurface(a.sc, H.tri, T.ray.from + H.t * T.ray.dir, H.b1, H.b2, sp);
-    const Material &mat = *sp.mat;
-    MatDat md; uint32_t bsdfs;
-    mat_initBSDF(mat, md, bsdfs);
-    const v3 pwo = -T.ray.dir;
-    const uint32_t offs = T.pathOffs;
-    if (depth == 0) {
-        estimateOneDirectLight(a, sp, md, pwo, id, T.rayDivision, (int)offs, T.thr, sid);
-        if (bsdfs & BSDF_EMIT) acc_add(a, sid, mul(T.thr, mat_emit(mat, sp, pwo, false)));
-    } else {
-        if (bsdfs & BSDF_DIFFUSE) estimateOneDirectLight(a, sp, md, pwo, id, T.rayDivision, (int)offs, T.thr, sid);
-        // `matBSDFs & (BSDF_EMIT && caustic)` == matBSDFs & 1 when caustic (pathtracer.cc:295)
-        if (caustic && (bsdfs & BSDF_SPECULAR)) acc_add(a, sid, mul(T.thr, mat_emit(mat, sp, pwo, caustic)));
-    }
-    const uint32_t nd = depth + 1;
-    if ((int)nd >= I.maxBounces) return;
-    const int d4 = 4 * (int)nd;
-    BSample s((float)scrHalton(d4 + 3, offs), (float)scrHalton(d4 + 4, offs), BSDF_ALL);
-    float W = 0.f; v3 wi(0.f);
-    col3 scol = mat_sample(mat, md, sp, pwo, wi, s, W);
-    scol *= W;
-    if (isBlack(scol)) return;
-    col3 thr = mul(T.thr, scol);
-    if (I.russianRoulette) {     // opt-in extension (not in the reference): survive with p = clamp(max(thr)), weight 1/p
-        float p = fmaxf_(thr.x, fmaxf_(thr.y, thr.z));
-        p = fminf_(1.f, fmaxf_(I.rrMinProb, p));
-        const float u = (float)scrHalton((d4 + 5) < 50 ? (d4 + 5) : 49, offs + 0x9e3779b9u * nd);
-        if (u >= p) return;
-        thr = thr * (1.f / p);
-    }
-    const bool ncaustic = I.traceCaustics && (s.sampledFlags & (BSDF_SPECULAR | BSDF_GLOSSY | BSDF_FILTER));
-    push_task(a, child_task(T, sp.P, wi, thr, 0.f, task_bits(TASK_PATH, ncaustic, task_level(T.bits), nd)));
-}
+// the shading code proper, compiled with and without the extended material set (see yb_shade.inc)
+#define YB_SHADE_NS shade_base
+#define YB_EXT 0
+#include "yb_shade.inc"
+#undef YB_SHADE_NS
+#undef YB_EXT
+#define YB_SHADE_NS shade_ext
+#define YB_EXT 1
+#include "yb_shade.inc"
+#undef YB_SHADE_NS
+#undef YB_EXT
 
 // ---- shading order.  After the first wave the tasks of one warp take very different code paths (hit / miss, the
 // light estimateOneDirectLight picks): measured 8 of 32 lanes active.  Tasks are binned by a small key so that warps
@@ -510,15 +246,6 @@ static void bin_tasks(uint32_t n, const RenderArgs &a, rt_stream s)
     for (uint32_t t = 0; t < n; ++t) a.orderOut[base[a.keys[t]]++] = t;
 #endif
     g_kernel_launches += 2;
-}
-
-YB_KERNEL_OCC(k_shade, RenderArgs, 3)
-{
-    if (a.order) tid = a.order[tid];
-    const Task T = a.tasks[tid];
-    const Hit H = a.hits[tid];
-    if (task_kind(T.bits) == TASK_INTEGRATE) shade_integrate(a, T, H);
-    else shade_path(a, T, H);
 }
 
 // ------------------------------------------------------------------------------------------------ film
@@ -698,17 +425,19 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 }
         }
         // ---- worst-case fan-out per task, from the integrator and the materials present
-        bool anyGlossy = false; int specChildren = 0;
+        bool anyGlossy = false, anyRoughGlass = false, extShade = false; int specChildren = 0;
         for (size_t i = 0; i < c.materials.size(); ++i) {
             const Material &m = c.materials[i];
             if (m.bsdfFlags & BSDF_GLOSSY) anyGlossy = true;
+            if (m.type == MAT_ROUGH_GLASS) anyRoughGlass = true;     // two children per glossy sample
+            if (m.type == MAT_ROUGH_GLASS || m.type == MAT_BLEND) extShade = true;
             int sc_ = 0;
-            if (m.type == MAT_GLASS) sc_ = 2;
+            if (m.type == MAT_GLASS || m.type == MAT_BLEND) sc_ = 2;
             else if (m.type == MAT_SHINYDIFFUSE) sc_ = (m.isMirror ? 1 : 0) + (m.isTransparent ? 1 : 0);
             else if (m.type == MAT_COATED_GLOSSY || m.type == MAT_MIRROR) sc_ = 1;
             specChildren = std::max(specChildren, sc_);
         }
-        size_t F = (I.type == INTEG_PATH ? (size_t)std::max(1, I.nPaths) : 0) + (anyGlossy ? 8 : 0) + (size_t)specChildren;
+        size_t F = (I.type == INTEG_PATH ? (size_t)std::max(1, I.nPaths) : 0) + (anyGlossy ? (anyRoughGlass ? 16 : 8) : 0) + (size_t)specChildren;
         if (F < 1) F = 1;
         size_t S = 0;
         for (size_t i = 0; i < c.lights.size(); ++i) S += light_dirac(c.lights[i]) ? 1 : 2 * (size_t)std::max(1, c.lights[i].samples);
@@ -803,7 +532,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 tsd.start();
                 a.order = 0;
                 if (binShade && !firstWave) { bin_tasks((uint32_t)M, a, s); a.order = rb.order.p; }
-                k_shade((uint32_t)M, a, s);
+                if (extShade) shade_ext::k_shade((uint32_t)M, a, s); else shade_base::k_shade((uint32_t)M, a, s);
                 tsd.stop();
                 firstWave = false;
                 uint32_t cnt[4];

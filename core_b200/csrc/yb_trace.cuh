@@ -153,11 +153,11 @@ YB_HD bool bvh_traverse(const SceneDev &sc, v3 from, v3 dir, float tlo, float th
                     return true;
                 } else {
                     const Material &m = sc.materials[(uint32_t)f2i(B.w) & TRI_MAT_MASK];
-                    if (!mat_isTransparent(m)) return true;
+                    if (!mat_isTransparent<1>(m)) return true;
                     if (depth >= maxDepth) return true;
                     Surf sps;
                     tri_getSurface(sc, (int)ti, from + t * dir, u, v, sps);
-                    filt *= mat_getTransparency(m, sps, dir);
+                    filt *= mat_getTransparency<1>(m, sps, dir);
                     ++depth;
                 }
             }

@@ -15,7 +15,7 @@ enum : uint32_t {
     BSDF_ALL = BSDF_SPECULAR | BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_DISPERSIVE | BSDF_REFLECT | BSDF_TRANSMIT | BSDF_FILTER
 };
 
-enum MatType : int32_t { MAT_SHINYDIFFUSE = 0, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_MIRROR, MAT_NULL, MAT_LIGHT };
+enum MatType : int32_t { MAT_SHINYDIFFUSE = 0, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_MIRROR, MAT_NULL, MAT_LIGHT, MAT_ROUGH_GLASS, MAT_BLEND };
 
 // One record per material; the union of the constant parameters of the supported material_t classes
 // (shader-node inputs are rejected at creation).  ~260 B, read through the read-only cache.
@@ -41,6 +41,12 @@ struct Material {
     // --- lightMat_t (simple.cc:36-70)
     col3 lightCol;
     int32_t doubleSided;
+    // --- roughGlassMat_t (roughglass.cc:30-43,268-285): ior, filterCol, specRefCol, fakeShadow above + GGX alpha^2
+    float rgAlpha2;
+    // --- blendMat_t (blend.cc:32-41,395-431): the two blended materials as offsets RELATIVE to this record in the
+    //     material table (sub-materials are leaf materials: a blend of blends is rejected at creation)
+    int32_t blendOff1, blendOff2;
+    float blendVal;
 };
 
 enum LightType : int32_t { LIGHT_POINT = 0, LIGHT_SUN, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE };

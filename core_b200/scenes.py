@@ -280,7 +280,8 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
 
 # ----------------------------------------------------------------------------- C4: glossy / coated / glass materials
 def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
-                    integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None, **render_extra):
+                    integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None,
+                    extra_materials=None, order=None, **render_extra):
     """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
     coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
     shinydiffuse; sun (1 degree, 4 samples) + point + area (8 samples) lights; pathtracing with 8 bounces
@@ -306,7 +307,9 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     M["shiny"] = create(yi, "material", "shiny", type="shinydiffusemat", color=(0.3, 0.5, 0.9, 1.0), diffuse_reflect=0.7,
                         specular_reflect=0.3, transparency=0.4, transmit_filter=0.8, fresnel_effect=True, IOR=1.6,
                         mirror_color=(1.0, 0.95, 0.9, 1.0), diffuse_brdf="oren_nayar", sigma=0.25)
-    order = ["glossy", "aniso", "coated", "glass", "gdiff", "glass2", "mirror", "shiny"]
+    for mname, mp in (extra_materials or []):   # e.g. rough_glass, blend_mat of two of the above
+        M[mname] = create(yi, "material", mname, **mp)
+    order = order or ["glossy", "aniso", "coated", "glass", "gdiff", "glass2", "mirror", "shiny"]
     v0, f0 = icosphere(subdiv)
     yi.startGeometry()
     add_mesh(yi, *quad((-9, -6, 0), (9, -6, 0), (9, 8, 0), (-9, 8, 0)), M["ground"], bulk=False)

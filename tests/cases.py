@@ -4,6 +4,15 @@ import numpy as np
 
 from core_b200 import scenes
 
+_RG_BLEND = dict(
+    extra_materials=[
+        ("rg", dict(type="rough_glass", IOR=1.5, alpha=0.3, filter_color=(0.8, 1.0, 0.9, 1.0), transmit_filter=0.7, fake_shadows=True)),
+        ("rg2", dict(type="rough_glass", IOR=1.33, alpha=0.08, mirror_color=(1.0, 0.9, 0.8, 1.0))),
+        ("bl_gs", dict(type="blend_mat", material1="glossy", material2="shiny", blend_value=0.35)),
+        ("bl_gc", dict(type="blend_mat", material1="glass", material2="coated", blend_value=0.6)),
+        ("bl_md", dict(type="blend_mat", material1="gdiff", material2="mirror", blend_value=0.75))],
+    order=["rg", "bl_gs", "coated", "bl_gc", "gdiff", "rg2", "bl_md", "shiny"])
+
 IMAGE_CASES = {
     # BASELINE.json configs[0] (reduced): Cornell box, shinydiffuse + mirror component, area light, directlighting
     "c1_cornell_direct": (scenes.cornell_box, dict(width=64, height=64, spp=4, light_samples=4, mirror_box=True)),
@@ -33,6 +42,12 @@ IMAGE_CASES = {
                    **{"from": (0.5, -0.5, 6.0)})),
         ("s", dict(type="spotlight", to=(0.5, 0.5, 0.5), color=(1.0, 0.9, 0.8, 1.0), power=60.0, cone_angle=30.0, blend=0.3,
                    **{"from": (-3.0, -4.0, 6.0)}))])),
+    # rough_glass (GGX refraction: two-direction sample of recursiveRaytrace) and blend_mat of two leaf materials
+    "c4_roughglass_blend_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_RG_BLEND)),
+    "c4_roughglass_blend_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=5, **_RG_BLEND)),
+    "c4_roughglass_blend_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
+                                                                 integ_params=dict(transpShad=True, shadowDepth=4, bg_transp=True,
+                                                                                   bg_transp_refract=True), **_RG_BLEND)),
     # depth of field with a polygonal lens (perspectiveCam_t::sampleTSD / biasDist)
     "c4_materials_dof_hexagon": (scenes.materials_scene, dict(width=64, height=36, spp=3, integrator="directlighting",
                                                               cam_params=dict(aperture=0.15, dof_distance=10.0, bokeh_type="hexagon",
