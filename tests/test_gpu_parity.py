@@ -32,7 +32,8 @@ def test_image_parity_golden(name):
     # north_star: <= 1 % mean relative error, PSNR >= 40 dB.  The library is built with -fmad=false so device
     # arithmetic rounds like the reference's SSE code; what is left is the summation order of the film atomics.
     # Measured on B200: rel <= 2.2e-7, PSNR 128-164 dB on all ten cases.
-    assert rel <= 1e-5 and psnr >= 100.0 and da <= 1e-5, (rel, psnr, da)
+    bar = cases.GPU_IMAGE_BARS.get(name, cases.GPU_IMAGE_BAR)
+    assert rel <= bar[0] and psnr >= bar[1] and da <= bar[2], (rel, psnr, da)
     st = yi.getStats()
     assert st["kernel_launches"] > 0 and st["rays_closest"] > 0
 
