@@ -71,6 +71,7 @@ _CTX_FUNCS = {
     "create_texture": (HANDLE, [C.c_char_p]),
     "create_volume_region": (HANDLE, [C.c_char_p]),
     "render": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "get_depth": (C.c_int, [C.c_void_p]),
     "abort": (None, []),
     "update_scene": (C.c_int, []),
     "trace_batch": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int]),
@@ -80,6 +81,8 @@ _PRODUCT_ONLY = {
     "render_film": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "render_film_pass": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "film_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "depth_film": (C.c_void_p, []),
+    "depth_resolve": (C.c_int, [C.c_void_p, C.c_void_p]),
     "get_stats": (C.c_int, [C.POINTER(Stats)]),
     "cuda_stream": (C.c_void_p, []),
     "touch_geometry": (None, []),

@@ -152,6 +152,14 @@ int yb200_render(yb200_ctx *ctx, float *rgba, int width, int height, const yb200
     return yb200_film_resolve(ctx, ctx->io.film.p, rgba, 0);
     GUARD_END(0)
 }
+float *yb200_depth_film(yb200_ctx *ctx) { return depth_film_device(CTX); }
+int yb200_depth_resolve(yb200_ctx *ctx, const float *dev_depth_film, float *z)
+{
+    GUARD_BEGIN
+    return depth_resolve_device(CTX, dev_depth_film, z) ? 1 : 0;
+    GUARD_END(0)
+}
+int yb200_get_depth(yb200_ctx *ctx, float *z) { return yb200_depth_resolve(ctx, depth_film_device(CTX), z); }
 void yb200_abort(yb200_ctx *ctx) { CTX.abortFlag = 1; }
 
 int yb200_trace_batch(yb200_ctx *ctx, const float *rays, size_t n, int mode, int shadow_depth, void *out, int on_device)

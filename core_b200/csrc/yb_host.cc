@@ -493,6 +493,12 @@ uintptr_t Context::createLight(const char *name)   // environment.cc:189-216 + l
         l.du = normalize(l.toX); l.dv = cross(l.normal, l.du);
         l.c2 = corner + l.toX; l.c3 = corner + (l.toX + l.toY); l.c4 = corner + l.toY;
         obj = (unsigned)object;
+    } else if (type == "meshlight") {              // meshlight.cc:216-233; geometry is bound at scene update (meshLight_t::init)
+        col3 color(1.f); double power = 1.0; int samples = 4, object = 0; bool ds = false;
+        p.get("object", object); p.getColor("color", color); p.get("power", power); p.get("samples", samples); p.get("double_sided", ds);
+        l.type = LIGHT_MESH; l.samples = samples; l.doubleSided = ds ? 1 : 0;
+        l.color = (color * (float)power) * (float)YB_M_PI;
+        obj = (unsigned)object;
     } else if (type == "directional") {            // directional.cc:52-61,142-160
         v3 from(0.f), dir(0.f, 0.f, 1.f); col3 color(1.f); float power = 1.0f, rad = 1.f; bool inf = true;
         p.getPoint("direction", dir); p.getColor("color", color); p.get("power", power); p.get("infinite", inf);
@@ -530,7 +536,7 @@ uintptr_t Context::createLight(const char *name)   // environment.cc:189-216 + l
         l.invArea = 1.f / l.area;
         if (object != 0) { fail("spherelight '" + std::string(name) + "': binding to a sphere primitive ('object') is not supported (triangle meshes only)"); return 0; }
     } else {
-        fail("Environment: light type '" + type + "' is not supported by the B200 path (supported: pointlight, sunlight, arealight, directional, spotlight, spherelight)");
+        fail("Environment: light type '" + type + "' is not supported by the B200 path (supported: pointlight, sunlight, arealight, meshlight, directional, spotlight, spherelight)");
         return 0;
     }
     lights.push_back(l); lightObj.push_back(obj);
@@ -573,6 +579,7 @@ uintptr_t Context::createCamera(const char *name)   // environment.cc:292-330 + 
     c.camZ = camZ;
     c.near_p = from + camZ * nearClip;
     c.far_p = from + camZ * farClip;
+    c.nearClip = nearClip; c.farClip = farClip;
     c.aspectRatio = aspect_ratio;
     if (ortho) {                                            // orthoCam_t::setAxis (orthographicCamera.cc:36-49)
         const float scale = (float)scale_d;
@@ -721,10 +728,9 @@ bool Context::setupRender(int width, int height)   // environment.cc:596-694 + c
         else { sc.integ.hasBackground = 1; sc.integ.bgColor = bi->second.color; }
     }
     sc.cam = ci->second.cam;
-    int AA_passes = 1, AA_samples = 1, AA_inc = 1; double AA_threshold = 0.05; bool z_chan = false;
+    int AA_passes = 1, AA_samples = 1, AA_inc = 1; double AA_threshold = 0.05; bool z_chan = false, norm_z_chan = true;
     p.get("AA_passes", AA_passes); p.get("AA_minsamples", AA_samples); AA_inc = AA_samples; p.get("AA_inc_samples", AA_inc);
-    p.get("AA_threshold", AA_threshold); p.get("z_channel", z_chan);
-    if (z_chan) return fail("z_channel (depth map output) is not supported yet");
+    p.get("AA_threshold", AA_threshold); p.get("z_channel", z_chan); p.get("normalize_z_channel", norm_z_chan);
     // createImageFilm
     int w = 320, h = 240, xstart = 0, ystart = 0, tileSize = 32; float filt_sz = 1.5f, gamma = 1.f; bool clamp = false, premult = false;
     std::string ftype; bool haveF = p.get("filter_type", ftype);
@@ -751,6 +757,7 @@ bool Context::setupRender(int width, int height)   // environment.cc:596-694 + c
     f.tileSize = tileSize > 0 ? tileSize : 32;
     f.AA_passes = AA_passes; f.n_samples = AA_samples > 0 ? AA_samples : 1; f.pass_offs = 0;
     f.AA_inc_samples = AA_inc; f.AA_threshold = (float)AA_threshold;
+    f.zChan = z_chan ? 1 : 0; f.zNorm = norm_z_chan ? 1 : 0; f.minDepth = 1e38f; f.maxDepth = 0.f;
     return true;
 }
 
@@ -767,6 +774,62 @@ bool Context::ensureDevice()
     if (cudaSetDevice(device) != cudaSuccess) return fail("cudaSetDevice failed");
     if (!stream) { if (cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) != cudaSuccess) return fail("cudaStreamCreate failed"); streamOwned = true; }
 #endif
+    return true;
+}
+
+// Material and light tables -> device.  Mesh lights are bound to their emitter here, as meshLight_t::init does inside
+// scene_t::update (scene.cc:828-835, meshlight.cc:49-76): triangles {a, b, c, normal} and the area cdf of pdf1D_t
+// (sample_utils.h:85-118) go into one light-geometry buffer, and the device pointers are patched into the Light records.
+bool Context::uploadTables()
+{
+    std::vector<f4> ltris; std::vector<float> lcdf;
+    std::vector<size_t> triOff(lights.size(), 0), cdfOff(lights.size(), 0);
+    for (size_t i = 0; i < lights.size(); ++i) {
+        Light &l = lights[i];
+        if (l.type != LIGHT_MESH) continue;
+        std::map<unsigned, MeshObj>::const_iterator it = meshes.find(lightObj[i]);
+        if (it == meshes.end() || it->second.base) return fail("meshlight: object " + std::to_string(lightObj[i]) + " is not a triangle mesh of this scene");
+        const MeshObj &o = it->second;
+        const size_t nt = o.tri_mat.size();
+        if (nt == 0) return fail("meshlight: object " + std::to_string(lightObj[i]) + " has no triangles");
+        triOff[i] = ltris.size(); cdfOff[i] = lcdf.size();
+        std::vector<float> areas(nt);
+        double totalArea = 0.0;
+        for (size_t t = 0; t < nt; ++t) {
+            v3 P[3];
+            for (int c = 0; c < 3; ++c) {
+                const int pi = o.tri_idx[3 * t + c];
+                if (pi < 0 || (size_t)pi >= o.points.size()) return fail("triangle references a vertex that does not exist");
+                P[c] = o.points[pi];
+            }
+            const v3 cr = cross(P[1] - P[0], P[2] - P[0]);
+            const v3 n = normalize(cr);                                  // triangle_t::recNormal (triangle.cc:117-124)
+            areas[t] = (float)(0.5 * (double)length(cr));                // triangle_t::surfaceArea (triangle.cc:144-154)
+            totalArea += areas[t];
+            f4 r; r.x = P[0].x; r.y = P[0].y; r.z = P[0].z; r.w = n.x; ltris.push_back(r);
+            r.x = P[1].x; r.y = P[1].y; r.z = P[1].z; r.w = n.y; ltris.push_back(r);
+            r.x = P[2].x; r.y = P[2].y; r.z = P[2].z; r.w = n.z; ltris.push_back(r);
+        }
+        l.area = (float)totalArea; l.invArea = (float)(1.0 / totalArea); l.meshCount = (int32_t)nt;
+        double c = 0.0; const double delta = 1.0 / (double)nt;          // CumulateStep1dDF
+        std::vector<float> cdf(nt + 1);
+        cdf[0] = 0.f;
+        for (size_t t = 1; t < nt + 1; ++t) { c += (double)areas[t - 1] * delta; cdf[t] = (float)c; }
+        const float integral = (float)c;
+        for (size_t t = 1; t < nt + 1; ++t) cdf[t] /= integral;
+        lcdf.insert(lcdf.end(), cdf.begin(), cdf.end());
+    }
+    try {
+        d_light_tris.reserve(ltris.size() + 1); d_light_cdf.reserve(lcdf.size() + 1);
+        rt_h2d(d_light_tris.p, ltris.data(), ltris.size() * sizeof(f4), stream);
+        rt_h2d(d_light_cdf.p, lcdf.data(), lcdf.size() * sizeof(float), stream);
+        for (size_t i = 0; i < lights.size(); ++i)
+            if (lights[i].type == LIGHT_MESH) { lights[i].meshTris = d_light_tris.p + triOff[i]; lights[i].meshCdf = d_light_cdf.p + cdfOff[i]; }
+        d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
+        rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
+        rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
+        rt_sync(stream);    // the staging vectors above go out of scope
+    } catch (const RtError &e) { return fail(std::string("scene tables upload failed: ") + e.what()); }
     return true;
 }
 
@@ -864,9 +927,7 @@ bool Context::flattenAndBuild()
         rt_sync(stream);
         const auto t2 = std::chrono::steady_clock::now();
         bvh_build(in_v.p, anySmooth ? in_n.p : 0, nTris, d_nodes, d_tri_v, d_tri_n, nNodes, bvhDepth, boundLo, boundHi, bvhScratch, stream);
-        d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
-        rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
-        rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
+        if (!uploadTables()) return false;
         rt_sync(stream);
         if (getenv("YB200_PROFILE_BUILD")) {
             const auto t3 = std::chrono::steady_clock::now();
@@ -895,9 +956,7 @@ bool Context::updateScene()
     if (geomChanged || !sceneReady) { if (!flattenAndBuild()) return false; }
     else {
         try {   // materials / lights may have changed
-            d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
-            rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
-            rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
+            if (!uploadTables()) return false;
             sc.materials = d_materials.p; sc.lights = d_lights.p;
             sc.nLights = (int32_t)lights.size(); sc.nMaterials = (int32_t)materials.size();
         } catch (const RtError &e) { return fail(e.what()); }

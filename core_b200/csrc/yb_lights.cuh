@@ -12,7 +12,8 @@ struct LSample { float s1, s2; col3 col; float pdf; };   // lSample_t fields use
 
 // light_t::diracLight / canIntersect of the six light types
 YB_HD bool light_dirac(const Light &l) { return l.type == LIGHT_POINT || l.type == LIGHT_DIRECTIONAL || (l.type == LIGHT_SPOT && !l.softShadows); }
-YB_HD bool light_canIntersect(const Light &l) { return l.type == LIGHT_SUN || l.type == LIGHT_AREA || (l.type == LIGHT_SPOT && l.softShadows); }
+YB_HD bool light_canIntersect(const Light &l) { return l.type == LIGHT_SUN || l.type == LIGHT_AREA || l.type == LIGHT_MESH || (l.type == LIGHT_SPOT && l.softShadows); }
+YB_HD bool tri_intersect(v3 a, v3 b, v3 c, v3 from, v3 dir, float &t, float &u, float &v);   // yb_trace.cuh
 
 // spot cone falloff (spotlight.cc:117-126,163-172,263-272): smoothstep between cosEnd and cosStart
 YB_HD float spot_falloff(const Light &l, float cosa)
@@ -84,8 +85,48 @@ YB_HD bool sphereIntersect(v3 from, v3 dir, v3 c, float R2, float &d1, float &d2
     return true;
 }
 // sunLight_t::illumSample (sunlight.cc:74-85), areaLight_t::illumSample (arealight.cc:68-96)
-YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s, Ray &wi)
+// meshLight_t::sampleSurface (meshlight.cc:78-96) = pdf1D_t::DSample (sample_utils.h:141-157) + triangle_t::sample (triangle.cc:156-167)
+YB_HD bool mesh_sampleSurface(const Light &l, v3 &p, v3 &n, float s1, float s2)
 {
+    int primNum = 0;
+    if (s1 != 0.f) {
+        int lo = 0, hi = l.meshCount + 1;                 // std::lower_bound(cdf, cdf + count + 1, s1)
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (l.meshCdf[mid] < s1) lo = mid + 1; else hi = mid; }
+        primNum = lo - 1;
+        if (primNum < 0) primNum = 0;
+    }
+    if (primNum >= l.meshCount) return false;             // "MeshLight: Sampling error!"
+    float ss1, delta = l.meshCdf[primNum + 1];
+    if (primNum > 0) { delta -= l.meshCdf[primNum]; ss1 = (s1 - l.meshCdf[primNum]) / delta; }
+    else ss1 = s1 / delta;
+    const f4 A = l.meshTris[3 * primNum], B = l.meshTris[3 * primNum + 1], C = l.meshTris[3 * primNum + 2];
+    const float su1 = fSqrt(ss1), u = 1.f - su1, v = s2 * su1;
+    p = u * v3(A.x, A.y, A.z) + v * v3(B.x, B.y, B.z) + (1.f - u - v) * v3(C.x, C.y, C.z);
+    n = v3(A.w, B.w, C.w);
+    return true;
+}
+template <int EXT> YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s, Ray &wi)
+{
+    if (EXT && l.type == LIGHT_MESH) {           // meshLight_t::illumSample (meshlight.cc:100-137)
+        v3 n(0.f), p(0.f);
+        mesh_sampleSurface(l, p, n, s.s1, s.s2);
+        v3 ldir = p - P;
+        float dist_sqr = dot(ldir, ldir);
+        float dist = fSqrt(dist_sqr);
+        if (dist <= 0.0f) return false;
+        ldir *= 1.f / dist;
+        float cos_angle = -dot(ldir, n);
+        if (cos_angle <= 0) {
+            if (l.doubleSided) cos_angle = -cos_angle;
+            else return false;
+        }
+        wi.tmax = dist;
+        wi.dir = ldir;
+        s.col = l.color;
+        float area_mul_cosangle = l.area * cos_angle;
+        s.pdf = (float)((double)dist_sqr * YB_M_PI / (double)((area_mul_cosangle == 0.f) ? 1e-8f : area_mul_cosangle));
+        return true;
+    }
     if (l.type == LIGHT_SUN) {
         wi.dir = sampleCone(l.direction, l.du, l.dv, (float)l.cosAngle, s.s1, s.s2);
         wi.tmax = -1.f;
@@ -161,8 +202,31 @@ YB_HD bool light_triIntersect(v3 a, v3 b, v3 c, v3 from, v3 dir, float &t)
     return true;
 }
 // sunLight_t::intersect (sunlight.cc:87-95), areaLight_t::intersect (arealight.cc:136-154)
-YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, float &t, col3 &col, float &ipdf)
+template <int EXT> YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, float tmin, float &t, col3 &col, float &ipdf)
 {
+    if (EXT && l.type == LIGHT_MESH) {           // meshLight_t::intersect (meshlight.cc:181-205): closest hit on the emitter's own triangles
+        // (the reference walks a private kd-tree; here the emitter list is tested in order, acceptance rule of kdtree.cc:772,791)
+        float Z = t < 0 ? INFINITY : t;
+        int hit = -1;
+        for (int i = 0; i < l.meshCount; ++i) {
+            const f4 A = l.meshTris[3 * i], B = l.meshTris[3 * i + 1], C = l.meshTris[3 * i + 2];
+            float th, u, v;
+            if (!tri_intersect(v3(A.x, A.y, A.z), v3(B.x, B.y, B.z), v3(C.x, C.y, C.z), from, dir, th, u, v)) continue;
+            if (th < Z && th >= tmin) { Z = th; hit = i; }
+        }
+        if (hit < 0) return false;
+        t = Z;
+        const v3 n(l.meshTris[3 * hit].w, l.meshTris[3 * hit + 1].w, l.meshTris[3 * hit + 2].w);
+        float cos_angle = dot(dir, -n);
+        if (cos_angle <= 0) {
+            if (l.doubleSided) cos_angle = fabsf(cos_angle);
+            else return false;
+        }
+        float idist_sqr = 1.f / (t * t);
+        ipdf = (float)((double)(idist_sqr * l.area * cos_angle) * (1.f / YB_M_PI));
+        col = l.color;
+        return true;
+    }
     if (l.type == LIGHT_SUN) {
         float cosine = dot(dir, l.direction);
         if ((double)cosine < l.cosAngle) return false;

@@ -71,6 +71,8 @@ struct RenderArgs {
     f4 *acc;                // per camera sample: rgb + alpha
     const uint32_t *pix;    // owned pixels: x | y << 16
     float *film;            // (x + w*y)*5: r,g,b,a,weight
+    float *depthT;          // z_channel: per camera sample, c_ray.tmax after integrate() (NaN: no depth sample); 0 = off
+    float *depthFilm;       // z_channel: (x + w*y)*2: sum(depth*w), sum(w)  (gray2DImage_t / pixelGray_t)
     uint32_t sampleBase;    // first global camera-sample index of this batch
     uint32_t outCap, shadowCap;
 };
@@ -121,6 +123,7 @@ YB_KERNEL(k_raygen, RenderArgs)
     // wt == 0 (angular camera outside its circle): the reference adds a black, alpha-0 sample without tracing
     // (integrator.cc:293-297); here the slot keeps a ray that cannot hit (tmin = tmax = 0) and carries zero weights
     if (wt == 0.f) { t.thr = col3(0.f); t.aw = 0.f; }
+    if (a.depthT) a.depthT[tid] = wt == 0.f ? i2f(0x7fc00000) : t.ray.tmax;   // integrator.cc:293-297: no depth sample when wt == 0
     t.bits = task_bits(TASK_INTEGRATE, true, 0, 0);
     t.rayDivision = 1; t.rayOffset = 0; t.dc1 = 0.f; t.dc2 = 0.f; t.pathOffs = 0; t.pad = 0;
     a.tasks[tid] = t;
@@ -282,6 +285,27 @@ YB_KERNEL(k_film, RenderArgs)
             YB_ATOMIC_ADD_F32(px + 2, c.z * filterWt); YB_ATOMIC_ADD_F32(px + 3, c.w * filterWt);
             YB_ATOMIC_ADD_F32(px + 4, filterWt);
         }
+    if (a.depthT) {                                              // integrator.cc:313-334 + imageFilm_t::addDepthSample (imagefilm.cc:513-564)
+        const float tmax = a.depthT[tid];
+        if (tmax == tmax) {
+            float depth = 0.f;
+            if (f.zNorm) { if (tmax > 0.f) depth = 1.f - (tmax - f.minDepth) * f.maxDepth; }
+            else { depth = tmax; if (depth <= 0.f) depth = 99999997952.f; }
+            for (int j = y0; j <= y1; ++j)
+                for (int i = x0; i <= x1; ++i) {
+                    const float filterWt = f.filterTable[yIndex[j - y0] * YB_FILTER_TABLE_SIZE + xIndex[i - x0]];
+                    float *px = a.depthFilm + ((size_t)(i - f.cx0) + (size_t)f.w * (size_t)(j - f.cy0)) * 2;
+                    YB_ATOMIC_ADD_F32(px + 0, depth * filterWt); YB_ATOMIC_ADD_F32(px + 1, filterWt);
+                }
+        }
+    }
+}
+// pixelGray_t::normalized (image_buffers.h:46-57)
+struct DepthResolveArgs { const float *dfilm; float *z; };
+YB_KERNEL(k_resolve_depth, DepthResolveArgs)
+{
+    const float v = a.dfilm[2 * (size_t)tid], w = a.dfilm[2 * (size_t)tid + 1];
+    a.z[tid] = w > 0.f ? v / w : 0.f;
 }
 
 // imageFilm_t::flush (imagefilm.cc:383-443) + pixel_t::normalized (image_buffers.h:32-43), memoryIO_t layout
@@ -355,6 +379,7 @@ struct RenderBuffers {
     DevBuf<f4> acc;
     DevBuf<uint32_t> pix;
     DevBuf<float> film, rgba;
+    DevBuf<float> depthT, depthFilm, depthZ;   // z_channel
     DevBuf<char> io_in, io_out;     // staging for host-pointer ray batches
 };
 void render_release(RenderBuffers *rb) { delete rb; }
@@ -395,6 +420,47 @@ static void trace_tuning(FastJob &j)
     static const uint32_t burst = (uint32_t)env_size("YB200_BURST", 6), idle = (uint32_t)env_size("YB200_REFILL_IDLE", 8);
     j.triThreshold = tri_threshold(); j.oneBits = 0x3F800000u;
     j.burst = burst < 1u ? 1u : burst; j.refillIdle = idle < 1u ? 1u : (idle > 32u ? 32u : idle);
+}
+
+// tiledIntegrator_t::precalcDepths (integrator.cc:99-130): the range the normalised depth channel maps to [0, 1].  Without a
+// far clip the reference shoots one ray per pixel - with row and column swapped, shootRay(i, j) for i < h, j < w, kept here.
+static bool precalc_depths(Context &c, Film &f)
+{
+    const Camera &cam = c.sc.cam;
+    float minDepth = 1e38f, maxDepth = 0.f;
+    if (cam.farClip > -1) { minDepth = cam.nearClip; maxDepth = cam.farClip; }
+    else {
+        const int w = cam.resx, h = cam.resy;
+        const size_t n = (size_t)w * h;
+        std::vector<Ray> rays(n);
+        for (int i = 0; i < h; ++i)
+            for (int j = 0; j < w; ++j) { float wt; rays[(size_t)i * w + j] = cam_shootRay(cam, (float)i, (float)j, 0.5f, 0.5f, wt); }
+        std::vector<ClosestOut> out(n);
+        RenderBuffers &rb = *c.rb;
+        rb.io_in.reserve(n * sizeof(Ray)); rb.io_out.reserve(n * sizeof(ClosestOut));
+        rt_h2d(rb.io_in.p, rays.data(), n * sizeof(Ray), c.stream);
+        trace_batch_device(c, (const float *)rb.io_in.p, n, TRACE_CLOSEST, 0, rb.io_out.p);
+        rt_d2h(out.data(), rb.io_out.p, n * sizeof(ClosestOut), c.stream);
+        for (size_t k = 0; k < n; ++k) {
+            const float tmax = out[k].prim >= 0 ? out[k].t : rays[k].tmax;      // scene_t::intersect writes ray.tmax = Z on a hit
+            if (tmax > maxDepth) maxDepth = tmax;
+            if (tmax < minDepth && tmax >= 0.f) minDepth = tmax;
+        }
+    }
+    if (maxDepth > 0.f) maxDepth = 1.f / (maxDepth - minDepth);
+    f.minDepth = minDepth; f.maxDepth = maxDepth;
+    return true;
+}
+float *depth_film_device(Context &c) { return (c.rb && c.sc.film.zChan) ? c.rb->depthFilm.p : 0; }
+bool depth_resolve_device(Context &c, const float *d_depthFilm, float *z_host)
+{
+    if (!c.rb || !d_depthFilm) return c.fail("depth_resolve: no depth film (render with z_channel = true first)");
+    const size_t npx = (size_t)c.sc.film.w * c.sc.film.h;
+    c.rb->depthZ.reserve(npx + 1);
+    DepthResolveArgs da; da.dfilm = d_depthFilm; da.z = c.rb->depthZ.p;
+    k_resolve_depth((uint32_t)npx, da, c.stream);
+    rt_d2h(z_host, c.rb->depthZ.p, npx * sizeof(float), c.stream);
+    return true;
 }
 
 bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int rank, int world, int onlyPass,
@@ -440,9 +506,18 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         size_t F = (I.type == INTEG_PATH ? (size_t)std::max(1, I.nPaths) : 0) + (anyGlossy ? (anyRoughGlass ? 16 : 8) : 0) + (size_t)specChildren;
         if (F < 1) F = 1;
         size_t S = 0;
+        for (size_t i = 0; i < c.lights.size(); ++i) if (c.lights[i].type == LIGHT_MESH) extShade = true;
         for (size_t i = 0; i < c.lights.size(); ++i) S += light_dirac(c.lights[i]) ? 1 : 2 * (size_t)std::max(1, c.lights[i].samples);
         if (I.type == INTEG_DIRECT && I.useAO) S += (size_t)std::max(1, I.aoSamples);
         if (S < 1) S = 1;
+        // ---- depth channel: own film of this rank, cleared at the start of a frame; normalisation range first
+        Film fz = f;
+        if (f.zChan) {
+            const size_t npx = (size_t)f.w * f.h;
+            rb.depthFilm.reserve(2 * npx + 2);
+            if (onlyPass <= 0) rt_memset(rb.depthFilm.p, 0, 2 * npx * sizeof(float), s);
+            if (f.zNorm) { if (!precalc_depths(c, fz)) return false; }
+        }
         StageTimer tc(s), tsh(s), tsd(s), tf(s);
         uint64_t raysClosest = 0, raysShadow = 0, samplesDone = 0; double msClosest = 0, msShadow = 0, msShade = 0, msFilm = 0;
         const uint64_t launches0 = g_kernel_launches;
@@ -493,12 +568,14 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         rb.poolA.reserve(poolCap); rb.poolB.reserve(poolCap);
         rb.hits.reserve(B); rb.shadow.reserve(shadowCap); rb.counters.reserve(4); rb.acc.reserve(B);
         rb.order.reserve(B); rb.keys.reserve(B); rb.bins.reserve(2 * YB_SHADE_BINS);
+        if (f.zChan) rb.depthT.reserve(B);
         RenderArgs a;
         memset((void *)&a, 0, sizeof(a));
-        a.sc = c.sc; a.sc.film.n_samples = passSamples; a.sc.film.pass_offs = passOffs; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
+        a.sc = c.sc; a.sc.film.minDepth = fz.minDepth; a.sc.film.maxDepth = fz.maxDepth; a.sc.film.n_samples = passSamples; a.sc.film.pass_offs = passOffs; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
         a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
         const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
+        a.depthT = f.zChan ? rb.depthT.p : 0; a.depthFilm = f.zChan ? rb.depthFilm.p : 0;
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
         const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;

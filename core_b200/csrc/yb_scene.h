@@ -98,6 +98,7 @@ struct Context {
     volatile int abortFlag;
     // device-side scene
     DevBuf<BvhNode> d_nodes; DevBuf<f4> d_tri_v; DevBuf<v3> d_tri_n; DevBuf<Material> d_materials; DevBuf<Light> d_lights;
+    DevBuf<f4> d_light_tris; DevBuf<float> d_light_cdf;   // mesh light emitters (yb_host.cc uploadTables)
     DevBuf<uint32_t> d_traceCounter;   // ray-fetch counter of the persistent traversal kernels
     DevBuf<f4> d_in_v; DevBuf<v3> d_in_n;             // flattened geometry in scene order (input of the build)
     HostBuf<f4> h_in_v; HostBuf<v3> h_in_n;           // its pinned host staging
@@ -139,6 +140,7 @@ struct Context {
     bool setupRender(int width, int height);    // renderEnvironment_t::setupScene (environment.cc:596-694) + createImageFilm
     bool updateScene();                          // scene_t::update (scene.cc:748-850): flatten + BVH build
     bool flattenAndBuild();
+    bool uploadTables();
     bool ensureDevice();
 };
 
@@ -156,6 +158,9 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
 bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int rank, int world, int onlyPass,
                         int (*should_abort)(void *), void (*progress)(void *, int, int), void *user);
 void film_resolve_device(Context &c, const float *d_film, float *d_rgba);
+// z_channel: this rank's raw depth film (w*h*2 floats, device; 0 when off) and its normalisation into a HOST buffer of w*h floats
+float *depth_film_device(Context &c);
+bool depth_resolve_device(Context &c, const float *d_depthFilm, float *z_host);
 void render_release(RenderBuffers *rb);
 
 }  // namespace yb

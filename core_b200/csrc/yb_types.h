@@ -15,6 +15,9 @@ enum : uint32_t {
     BSDF_ALL = BSDF_SPECULAR | BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_DISPERSIVE | BSDF_REFLECT | BSDF_TRANSMIT | BSDF_FILTER
 };
 
+struct alignas(16) f4 { float x, y, z, w; };
+struct alignas(16) u4 { uint32_t x, y, z, w; };
+
 enum MatType : int32_t { MAT_SHINYDIFFUSE = 0, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_MIRROR, MAT_NULL, MAT_LIGHT, MAT_ROUGH_GLASS, MAT_BLEND };
 
 // One record per material; the union of the constant parameters of the supported material_t classes
@@ -49,7 +52,7 @@ struct Material {
     float blendVal;
 };
 
-enum LightType : int32_t { LIGHT_POINT = 0, LIGHT_SUN, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE };
+enum LightType : int32_t { LIGHT_POINT = 0, LIGHT_SUN, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE, LIGHT_MESH };
 struct Light {
     int32_t type, samples;
     col3 color;                      // point: col*power; area: col*power*pi; sun: col*power
@@ -65,6 +68,10 @@ struct Light {
     v3 ndir;
     float radius, cosStart, cosEnd, icosDiff, shadowFuzzy, squareRadius, squareRadiusEps;
     int32_t infinite, softShadows, photonOnly;
+    // mesh light (meshlight.cc:32-66): the emitter's triangles as 3 x f4 {a, n.x | b, n.y | c, n.z} and the area cdf of
+    // pdf1D_t (count + 1 floats), both in the scene's light-geometry buffer; area / invArea / color above
+    const f4 *meshTris; const float *meshCdf;
+    int32_t meshCount, doubleSided;
 };
 
 struct Camera {                       // perspectiveCam_t (perspectiveCamera.cc:28-71,127-149; camera.h:41-61)
@@ -80,6 +87,7 @@ struct Camera {                       // perspectiveCam_t (perspectiveCamera.cc:
     int32_t camType, circular;
     v3 opos;
     float horPhi, maxR, aspectRatio;
+    float nearClip, farClip;         // camera_t::getNearClip / getFarClip (camera.h:58-59,77-78)
 };
 enum CamType : int32_t { CAM_PERSPECTIVE = 0, CAM_ORTHO = 1, CAM_ANGULAR = 2 };
 
@@ -111,14 +119,15 @@ struct Film {                         // imageFilm_t (imagefilm.cc:119-165,453-5
     // sampling plan of this render pass (integrator.cc:229-290)
     int32_t AA_passes, n_samples, pass_offs;
     int32_t AA_inc_samples; float AA_threshold;      // adaptive passes (integrator.cc:158-163, imagefilm.cc:226-262)
+    // depth channel (z_channel / normalize_z_channel, environment.cc:661-684; integrator.cc:99-130,313-334)
+    int32_t zChan, zNorm;
+    float minDepth, maxDepth;                        // tiledIntegrator_t::minDepth and the INVERSE range it keeps in maxDepth
 };
 
 // ---- geometry in HBM ------------------------------------------------------------------------------
 // tri_v : 3 x float4 per triangle, in BVH leaf order.  v0.w carries the global primitive index of
 //         scene.cc:760-781 (as int bits), v1.w the material/flags word, v2.w is free.
 // tri_n : 3 x v3 vertex normals per triangle (same order), only when some mesh is smooth.
-struct alignas(16) f4 { float x, y, z, w; };
-struct alignas(16) u4 { uint32_t x, y, z, w; };
 enum : uint32_t {
     TRI_MAT_MASK = 0x000fffffu,
     TRI_SMOOTH = 1u << 20,            // mesh->is_smooth

@@ -135,6 +135,24 @@ class YafrayInterface:
             raise RuntimeError("render failed: " + self.lastError())
         return out
 
+    def getDepth(self, width, height):
+        """Depth channel of the last render (render parameter z_channel = true): what imageFilm_t::flush passes to
+        colorOutput_t::putPixel(..., depth=true, z); returns (H, W) float32."""
+        z = np.zeros((height, width), dtype=np.float32)
+        if not self._call("get_depth", z.ctypes.data):
+            raise RuntimeError("get_depth failed: " + self.lastError())
+        return z
+
+    def depthFilm(self):
+        """Device pointer of this rank's raw depth film (H, W, 2) or None."""
+        return self._call("depth_film")
+
+    def depthResolve(self, depth_film_ptr, width, height):
+        z = np.zeros((height, width), dtype=np.float32)
+        if not self._call("depth_resolve", depth_film_ptr, z.ctypes.data):
+            raise RuntimeError("depth_resolve failed: " + self.lastError())
+        return z
+
     def abort(self): self._call("abort")
     def updateScene(self):
         if not self._call("update_scene"):

@@ -281,7 +281,7 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
 # ----------------------------------------------------------------------------- C4: glossy / coated / glass materials
 def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
                     integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None,
-                    extra_materials=None, order=None, **render_extra):
+                    extra_materials=None, order=None, emitters=None, **render_extra):
     """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
     coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
     shinydiffuse; sun (1 degree, 4 samples) + point + area (8 samples) lights; pathtracing with 8 bounces
@@ -320,6 +320,11 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
         r = 1.0 if i < 4 else 0.9
         V = (v0 * r + np.array([cx, cy, r + 0.02])).astype(np.float32)
         add_mesh(yi, V, f0, M[name], normals=v0.astype(np.float32), smooth_angle=181.0)
+    for e in (emitters or []):              # visible emitter meshes for mesh lights: dict(id, centre, radius, subdiv, material params)
+        M[e["name"]] = create(yi, "material", e["name"], **e["material"])
+        ve, fe = icosphere(e.get("subdiv", 1))
+        sc = np.asarray(e.get("scale", (1.0, 1.0, 1.0)), np.float32)
+        add_mesh(yi, (ve * e["radius"] * sc + np.asarray(e["centre"])).astype(np.float32), fe, M[e["name"]], oid=e["id"])
     yi.endGeometry()
     if lights is None:
         create(yi, "light", "sun", type="sunlight", direction=(0.4, -0.5, 0.8), color=(1.0, 0.95, 0.9, 1.0), power=0.9,

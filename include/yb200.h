@@ -104,6 +104,16 @@ int yb200_render_film_pass(yb200_ctx *c, float *dev_film, const float *dev_film_
                            const yb200_callbacks *cb);
 /* normalise / clamp / gamma / premult exactly like imageFilm_t::flush; dev_film device, rgba HOST or DEVICE */
 int yb200_film_resolve(yb200_ctx *c, const float *dev_film, float *rgba, int rgba_on_device);
+/* Depth channel (render parameters z_channel / normalize_z_channel, environment.cc:661-685): what the reference hands to
+ * colorOutput_t::putPixel(x, y, c, alpha, depth = true, z) (imagefilm.cc:360-362,425-427) - the filtered per-pixel depth of
+ * imageFilm_t::addDepthSample (imagefilm.cc:513-564), normalised to [0, 1] by tiledIntegrator_t::precalcDepths
+ * (integrator.cc:99-130) unless normalize_z_channel is false.  z: HOST buffer of width*height floats, index x + width*y.
+ * yb200_get_depth reads the depth film of the last yb200_render / yb200_render_film of this context; with several ranks,
+ * sum the raw depth films (yb200_depth_film: DEVICE pointer, width*height*2 floats = sum(depth*w), sum(w)) like the colour
+ * film and resolve the sum with yb200_depth_resolve. */
+int    yb200_get_depth(yb200_ctx *c, float *z);
+float *yb200_depth_film(yb200_ctx *c);
+int    yb200_depth_resolve(yb200_ctx *c, const float *dev_depth_film, float *z);
 void yb200_abort(yb200_ctx *c);                              /* yafrayinterface.cc:278 */
 
 /* ---- scene update only (scene_t::update, scene.cc:748-850): flatten + GPU BVH build */

@@ -43,6 +43,7 @@ struct silentBar_t : public yafaray::progressBar_t {
 };
 
 struct yref_ctx {
+    std::vector<float> depth;      // z values the film handed to colorOutput_t::putPixel in the last render (z_channel)
     yafrayInterface_t *yi;
     std::string err;
     std::map<const triangle_t *, int> primIndex;
@@ -138,9 +139,29 @@ uintptr_t yref_create_volume_region(yref_ctx *c, const char *n) { return (uintpt
 
 struct yref_callbacks { void *user; int (*should_abort)(void *); void (*progress)(void *, int, int); };
 
+// memoryIO_t (src/yafraycore/memoryIO.cc:27-43) drops the depth argument of putPixel; this output keeps it
+struct depthIO_t : public colorOutput_t {
+    int w, h; float *mem; std::vector<float> *z;
+    depthIO_t(int w_, int h_, float *m, std::vector<float> *z_) : w(w_), h(h_), mem(m), z(z_) { z->assign((size_t)w * h, 0.f); }
+    virtual bool putPixel(int x, int y, const float *c, bool alpha = true, bool depth = false, float zz = 0.f)
+    {
+        for (int i = 0; i < 4; ++i) mem[(x + w * y) * 4 + i] = (!alpha && i == 3) ? 1.f : c[i];
+        if (depth) (*z)[(size_t)x + (size_t)w * y] = zz;
+        return true;
+    }
+    virtual void flush() {}
+    virtual void flushArea(int, int, int, int) {}
+};
+int yref_get_depth(yref_ctx *c, float *z)
+{
+    if (c->depth.empty()) { c->err = "no depth values (render with z_channel = true first)"; return 0; }
+    memcpy(z, c->depth.data(), c->depth.size() * sizeof(float));
+    return 1;
+}
+
 int yref_render(yref_ctx *c, float *rgba, int w, int h, const yref_callbacks *)
 {
-    memoryIO_t out(w, h, rgba);
+    depthIO_t out(w, h, rgba, &c->depth);
     memset(rgba, 0, sizeof(float) * 4 * (size_t)w * h);
     gTimer.addEvent("yref_render");
     gTimer.start("yref_render");

@@ -13,6 +13,15 @@ _RG_BLEND = dict(
         ("bl_md", dict(type="blend_mat", material1="gdiff", material2="mirror", blend_value=0.75))],
     order=["rg", "bl_gs", "coated", "bl_gc", "gdiff", "rg2", "bl_md", "shiny"])
 
+_MESHLIGHT = dict(
+    emitters=[dict(name="emit1", id=701, centre=(-1.0, -2.5, 3.6), radius=0.5, subdiv=1, scale=(1.6, 1.0, 0.4),
+                   material=dict(type="light_mat", color=(1.0, 0.8, 0.6, 1.0), power=6.0)),
+              dict(name="emit2", id=702, centre=(3.0, 1.0, 3.0), radius=0.35, subdiv=0,
+                   material=dict(type="light_mat", color=(0.6, 0.8, 1.0, 1.0), power=9.0, double_sided=True))],
+    lights=[("ml1", dict(type="meshlight", object=701, color=(1.0, 0.8, 0.6, 1.0), power=6.0, samples=3)),
+            ("ml2", dict(type="meshlight", object=702, color=(0.6, 0.8, 1.0, 1.0), power=9.0, samples=2, double_sided=True)),
+            ("pt", dict(type="pointlight", color=(0.9, 0.9, 1.0, 1.0), power=6.0, **{"from": (-4.0, -3.0, 5.0)}))])
+
 IMAGE_CASES = {
     # BASELINE.json configs[0] (reduced): Cornell box, shinydiffuse + mirror component, area light, directlighting
     "c1_cornell_direct": (scenes.cornell_box, dict(width=64, height=64, spp=4, light_samples=4, mirror_box=True)),
@@ -48,6 +57,11 @@ IMAGE_CASES = {
     "c4_roughglass_blend_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
                                                                  integ_params=dict(transpShad=True, shadowDepth=4, bg_transp=True,
                                                                                    bg_transp_refract=True), **_RG_BLEND)),
+    # meshlight bound to a visible emitter mesh (light_mat): area-cdf sampling + MIS intersect against the emitter triangles
+    "c4_meshlight_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_MESHLIGHT)),
+    # (path case on diffuse-only spheres: with glossy / specular recursion onto VISIBLE emitter geometry the reference's
+    # state.includeLights leaks between sibling calls in traversal order - DESIGN.md section 7, first deviation)
+    "c4_meshlight_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4, order=["gdiff", "ground"] * 4, **_MESHLIGHT)),
     # depth of field with a polygonal lens (perspectiveCam_t::sampleTSD / biasDist)
     "c4_materials_dof_hexagon": (scenes.materials_scene, dict(width=64, height=36, spp=3, integrator="directlighting",
                                                               cam_params=dict(aperture=0.15, dof_distance=10.0, bokeh_type="hexagon",
@@ -76,6 +90,18 @@ IMAGE_CASES = {
 # amplified into a different path for single samples (measured: 5 pixels of 2304, rel 2.9e-6, PSNR 100.7 dB).
 GPU_IMAGE_BAR = (1e-5, 100.0, 1e-5)
 GPU_IMAGE_BARS = {"c4_roughglass_blend_path": (1e-4, 90.0, 1e-4)}
+
+# depth channel (z_channel): the frame AND the z values imageFilm_t::flush hands to colorOutput_t::putPixel
+DEPTH_CASES = {
+    # normalised, no far clip: range from tiledIntegrator_t::precalcDepths' per-pixel rays
+    "z_materials_norm": (scenes.materials_scene, dict(width=64, height=36, spp=2, integrator="directlighting", z_channel=True)),
+    # raw distances; misses read 99999997952
+    "z_field_raw": (scenes.icosphere_field, dict(n_tris=6000, subdiv=1, width=64, height=36, spp=3, integrator="directlighting",
+                                                 z_channel=True, normalize_z_channel=False, filter_type="gauss", pixelwidth=2.0)),
+    # normalised against the camera's clip planes
+    "z_materials_clip": (scenes.materials_scene, dict(width=48, height=27, spp=1, integrator="directlighting", z_channel=True,
+                                                      cam_params=dict(nearClip=6.0, farClip=14.0))),
+}
 
 RAY_CASES = {
     "rays_cornell": (scenes.cornell_box, dict(width=32, height=32, spp=1)),

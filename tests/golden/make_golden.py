@@ -68,6 +68,18 @@ def rays(only=None):
         print(name, "hits", int((closest["prim"] >= 0).sum()), "shadowed", int(shadow.sum()))
 
 
+def depth(only=None):
+    for name, (fn, kw) in cases.DEPTH_CASES.items():
+        if only and name not in only:
+            continue
+        yi = refapi.RefInterface(); yi.setVerbosityMute()
+        fn(yi, threads=1, **kw)
+        img = yi.render(kw["width"], kw["height"])
+        z = yi.getDepth(kw["width"], kw["height"])
+        np.savez_compressed(os.path.join(HERE, "depth_" + name + ".npz"), img=img, z=z)
+        print(name, img.mean(axis=(0, 1)), z.min(), z.max())
+
+
 def images(only=None):
     for name, (fn, kw) in cases.IMAGE_CASES.items():
         if only and name not in only:
@@ -86,3 +98,4 @@ if __name__ == "__main__":
         kat(refapi.ref_lib())
     rays(only)
     images(only)
+    depth(only)

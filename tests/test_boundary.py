@@ -65,11 +65,15 @@ class TestHostLogic:
         yi = refapi.EmuInterface()
         yi.setVerbosityMute()
         yi.startScene(0)
-        for kind, ty in (("material", "blend_mat"), ("material", "rough_glass"), ("light", "ieslight"),
+        for kind, ty in (("material", "translucent"), ("material", "glossy2"), ("light", "ieslight"),
                          ("camera", "equirectangular"), ("background", "sunsky"), ("integrator", "photonmapping")):
             yi.paramsClearAll(); yi.paramsSetString("type", ty)
             assert getattr(yi, "create" + kind.capitalize())("x") == 0
             assert "not supported" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "blend_mat"); yi.paramsSetString("material1", "nope"); yi.paramsSetString("material2", "nope")
+        assert yi.createMaterial("bl") == 0 and "does not exist" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "rough_glass"); yi.paramsSetFloat("dispersion_power", 0.2)
+        assert yi.createMaterial("rgd") == 0 and "dispersion" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat"); yi.paramsSetString("diffuse_shader", "tex")
         assert yi.createMaterial("withnodes") == 0 and "shader" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "glass"); yi.paramsSetFloat("dispersion_power", 0.1)

@@ -25,6 +25,19 @@ def test_image_parity(name):
     assert rel <= 1e-4 and psnr >= 80.0 and da <= 1e-4, (rel, psnr, da)
 
 
+@pytest.mark.parametrize("name", list(cases.DEPTH_CASES))
+def test_depth_channel_parity(name):
+    fn, kw = cases.DEPTH_CASES[name]
+    yi = refapi.EmuInterface()
+    fn(yi, **kw)
+    img = yi.render(kw["width"], kw["height"])
+    z = yi.getDepth(kw["width"], kw["height"])
+    g = np.load(os.path.join(G, "depth_" + name + ".npz"))
+    rel, psnr, da = cases.compare_images(g["img"], img)
+    assert rel <= 1e-4 and psnr >= 80.0, (rel, psnr, da)
+    assert np.allclose(z, g["z"], rtol=2e-5, atol=1e-6), float(np.abs(z - g["z"]).max())
+
+
 @pytest.mark.parametrize("name", list(cases.RAY_CASES))
 def test_ray_parity(name):
     fn, kw = cases.RAY_CASES[name]

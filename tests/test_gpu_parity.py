@@ -38,6 +38,22 @@ def test_image_parity_golden(name):
     assert st["kernel_launches"] > 0 and st["rays_closest"] > 0
 
 
+@pytest.mark.parametrize("name", list(cases.DEPTH_CASES))
+def test_depth_channel_golden(name):
+    fn, kw = cases.DEPTH_CASES[name]
+    yi = YafrayInterface()
+    fn(yi, **kw)
+    img = yi.render(kw["width"], kw["height"])
+    z = yi.getDepth(kw["width"], kw["height"])
+    g = np.load(os.path.join(G, "depth_" + name + ".npz"))
+    rel, psnr, da = cases.compare_images(g["img"], img)
+    assert rel <= 1e-5 and psnr >= 100.0, (rel, psnr, da)
+    assert np.allclose(z, g["z"], rtol=2e-5, atol=1e-6), float(np.abs(z - g["z"]).max())
+    # several ranks: the raw depth films add up like the colour film
+    zr = yi.depthResolve(yi.depthFilm(), kw["width"], kw["height"])
+    assert np.array_equal(zr, z)
+
+
 @pytest.mark.parametrize("name", list(cases.RAY_CASES))
 def test_ray_parity_golden(name):
     fn, kw = cases.RAY_CASES[name]

@@ -63,11 +63,11 @@ def test_xml_reference_digits_close_to_golden(tmp_path):
 @pytest.mark.skipif(not (refapi.have_emu() and os.path.exists(EMU_XML)), reason="emulator xml loader not built")
 def test_xml_unsupported_fails_loudly(tmp_path):
     xml = tmp_path / "bad.xml"
-    xml.write_text('<?xml version="1.0"?>\n<scene type="triangle">\n<material name="m">\n\t<type sval="rough_glass"/>\n'
+    xml.write_text('<?xml version="1.0"?>\n<scene type="triangle">\n<material name="m">\n\t<type sval="translucent"/>\n'
                    '</material>\n<render>\n\t<width ival="8"/>\n\t<height ival="8"/>\n</render>\n</scene>\n')
     r = _run(EMU_XML, str(xml), str(tmp_path / "o.f32"))
     assert r.returncode != 0
-    assert "rough_glass" in r.stderr
+    assert "translucent" in r.stderr
     assert not os.path.exists(tmp_path / "o.f32")
     # malformed document
     xml.write_text("<scene><material name='m'></scene>")
