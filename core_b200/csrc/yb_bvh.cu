@@ -484,4 +484,47 @@ void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &node
     if (2 * maxDepth > YB_STACK_SIZE - 2) throw RtError("bvh_build: tree deeper than the traversal stack");
 }
 
+// ------------------------------------------------------------------------------------------------ ray sorting
+// Coherence sort of one wave of rays (opt-in, YB200_SORT_RAYS): key = Morton code of the ray origin on a 128^3 grid over
+// the scene box (21 bits) followed by the direction octant (3 bits); the traversal kernel then fetches its rays through
+// the sorted index list, so neighbouring lanes start in the same subtree and walk it in the same order.
+struct RayKeyArgs { const char *rays; uint32_t stride; uint32_t *keys, *idx; v3 lo, inv; };
+YB_D uint32_t spread3_10(uint32_t v)
+{
+    v &= 0x3ffu;
+    v = (v | (v << 16)) & 0x030000ffu; v = (v | (v << 8)) & 0x0300f00fu; v = (v | (v << 4)) & 0x030c30c3u; v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+YB_KERNEL(k_ray_keys, RayKeyArgs)
+{
+    const f4 r0 = ld16f(a.rays + (size_t)tid * a.stride), r1 = ld16f(a.rays + (size_t)tid * a.stride + 16);
+    const float fx = fminf_(fmaxf_((r0.x - a.lo.x) * a.inv.x, 0.f), 127.f), fy = fminf_(fmaxf_((r0.y - a.lo.y) * a.inv.y, 0.f), 127.f),
+                fz = fminf_(fmaxf_((r0.z - a.lo.z) * a.inv.z, 0.f), 127.f);
+    const uint32_t m = spread3_10((uint32_t)fx) | (spread3_10((uint32_t)fy) << 1) | (spread3_10((uint32_t)fz) << 2);
+    const uint32_t oct = (r1.x >= 0 ? 1u : 0u) | (r1.y >= 0 ? 2u : 0u) | (r1.z >= 0 ? 4u : 0u);
+    a.keys[tid] = (m << 3) | oct;
+    a.idx[tid] = tid;
+}
+// returns the device array of n sorted ray indices (valid until the next call), or 0 when sorting is not available
+const uint32_t *sort_rays(const char *rays, uint32_t stride, uint32_t n, v3 lo, v3 hi, RaySortScratch &w, rt_stream s)
+{
+#ifdef YB_HOSTEMU
+    (void)rays; (void)stride; (void)n; (void)lo; (void)hi; (void)w; (void)s;
+    return 0;
+#else
+    if (n < 2) return 0;
+    w.keys.reserve(n); w.keys2.reserve(n); w.idx.reserve(n); w.idx2.reserve(n);
+    RayKeyArgs a; a.rays = rays; a.stride = stride; a.keys = w.keys.p; a.idx = w.idx.p; a.lo = lo;
+    const float ext = fmaxf_(fmaxf_(hi.x - lo.x, hi.y - lo.y), fmaxf_(hi.z - lo.z, 1e-20f));
+    a.inv = v3(128.f / ext);
+    k_ray_keys(n, a, s);
+    size_t tmpBytes = 0;
+    YB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, w.keys.p, w.keys2.p, w.idx.p, w.idx2.p, (int)n, 0, 24, s));
+    w.tmp.reserve(tmpBytes + 16);
+    YB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(w.tmp.p, tmpBytes, w.keys.p, w.keys2.p, w.idx.p, w.idx2.p, (int)n, 0, 24, s));
+    g_kernel_launches += 4;
+    return w.idx2.p;
+#endif
+}
+
 }  // namespace yb

@@ -575,6 +575,8 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
         const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
+        // coherence sort of the ray waves: 0 off, 1 closest-hit waves after the camera wave, 2 + shadow waves after the first, 3 all
+        const int sortRays = (int)env_size("YB200_SORT_RAYS", 0);
         a.depthT = f.zChan ? rb.depthT.p : 0; a.depthFilm = f.zChan ? rb.depthFilm.p : 0;
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
@@ -588,6 +590,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
             k_raygen(nb, a, s);
             size_t top = nb;
             bool firstWave = true;      // camera rays come in pixel order: already coherent
+            bool firstShadowWave = true;
             while (top > 0) {
                 size_t M = std::min(top, B);
                 M = std::min(M, shadowCap / S);
@@ -601,6 +604,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 tc.start();
                 if (useFast) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task); j.n = (uint32_t)M;
+                    j.order = (sortRays && !firstWave) ? sort_rays((const char *)a.tasks, sizeof(Task), (uint32_t)M, c.sc.boundLo, c.sc.boundHi, c.raySort, s) : 0;
                     j.counter = rb.counters.p + 2; j.out = a.hits; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j);
                     launch_trace_fast<false, OUT_HITS>(j, s);
                 } else
@@ -618,11 +622,13 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 tsh.start();
                 if (useFast && !I.trShad) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask); j.n = cnt[1];
+                    j.order = (sortRays >= 2 && (!firstShadowWave || sortRays >= 3)) ? sort_rays((const char *)a.shadow, sizeof(ShadowTask), cnt[1], c.sc.boundLo, c.sc.boundHi, c.raySort, s) : 0;
                     j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j);
                     launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
                 } else
                     k_trace_shadow(cnt[1], a, s);
                 tsh.stop();
+                firstShadowWave = false;
                 raysClosest += M; raysShadow += cnt[1];
                 if (logWaves) fprintf(stderr, "yb200 wave: batch %d closest %zu shadow %u children %u\n", b, M, cnt[1], cnt[0]);
                 msClosest += tc.ms(); msShade += tsd.ms(); if (cnt[1]) msShadow += tsh.ms();
@@ -668,7 +674,7 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
         if (useFast && mode != TRACE_TSHADOW) {
             c.d_traceCounter.reserve(4);
             FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)(ta.rays + o); j.stride = sizeof(Ray); j.n = m;
-            j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; trace_tuning(j);
+            j.order = 0; j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; trace_tuning(j);
             if (mode == TRACE_CLOSEST) { j.out = (ClosestOut *)d_out + o; launch_trace_fast<false, OUT_CLOSEST_PRIM>(j, c.stream); }
             else { j.out = (int32_t *)d_out + o; launch_trace_fast<true, OUT_SHADOW_FLAG>(j, c.stream); }
             continue;

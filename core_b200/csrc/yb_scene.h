@@ -73,6 +73,8 @@ struct BvhScratch {
     DevBuf<uint64_t> qa, qb;          // collapse work items (2 x int32 each)
 };
 
+struct RaySortScratch { DevBuf<uint32_t> keys, keys2, idx, idx2; DevBuf<char> tmp; };
+
 struct Context {
     std::string err;
     int verbosity;
@@ -103,6 +105,7 @@ struct Context {
     DevBuf<f4> d_in_v; DevBuf<v3> d_in_n;             // flattened geometry in scene order (input of the build)
     HostBuf<f4> h_in_v; HostBuf<v3> h_in_n;           // its pinned host staging
     BvhScratch bvhScratch;
+    RaySortScratch raySort;
     uint32_t nTris, nNodes, bvhDepth; bool haveNormals;
     v3 boundLo, boundHi;
     SceneDev sc;                     // filled by updateScene / setupRender
@@ -150,6 +153,8 @@ static const uintptr_t HANDLE_MAT_TAG = 0x4d000000u;
 // ---- GPU stages
 void bvh_build(const f4 *in_v, const v3 *in_n, uint32_t n, DevBuf<BvhNode> &nodes, DevBuf<f4> &out_v, DevBuf<v3> &out_n,
                uint32_t &nNodes, uint32_t &maxDepth, v3 &boundLo, v3 &boundHi, BvhScratch &w, rt_stream s);
+// coherence sort of a wave of rays (yb_bvh.cu): sorted ray indices on the device, or 0
+const uint32_t *sort_rays(const char *rays, uint32_t stride, uint32_t n, v3 lo, v3 hi, RaySortScratch &w, rt_stream s);
 // rays/out are DEVICE pointers; mode = TRACE_*; out layout as documented in include/yb200.h
 void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int shadow_depth, void *d_out);
 // accumulate the tiles of (rank, world) of one frame into d_film (w*h*5 floats, raw sums)

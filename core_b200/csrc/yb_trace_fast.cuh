@@ -89,6 +89,7 @@ struct FastJob {
     const f4 *tri_v;
     const char *rays;        // ray records {from, tmin, dir, tmax} at offset 0 of each `stride`-byte record
     uint32_t stride, n;
+    const uint32_t *order;   // optional: fetch order of the rays (coherence sort); results still go to the ray's own slot
     uint32_t *counter;       // zeroed by the host before launch
     void *out;               // OUT_HITS: Hit[n]; OUT_SHADOW_FLAG: int32[n]; OUT_CLOSEST_PRIM: {prim,t,b1,b2}[n]
     f4 *acc;                 // OUT_SHADOW_ACC: ShadowTask{ray, c, sid}: acc[sid].rgb += c when unoccluded
@@ -145,8 +146,9 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                 if ((int)lane == leader) base = atomicAdd(job.counter, (uint32_t)nIdle);
                 base = __shfl_sync(FULL, base, leader);
                 if (!active) {
-                    const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                    uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
                     if (i < job.n) {
+                        if (job.order) i = __ldg(job.order + i);
                         const float4 r0 = __ldg((const float4 *)(job.rays + (size_t)i * job.stride));
                         const float4 r1 = __ldg((const float4 *)(job.rays + (size_t)i * job.stride + 16));
                         rayIdx = i;
