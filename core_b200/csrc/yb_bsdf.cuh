@@ -8,6 +8,7 @@
 // that look like bugs are kept on purpose: W = |wi.N|/(0.99 pdf + 0.01), no 1/pi, ...
 #pragma once
 #include "yb_types.h"
+#include "yb_nodes.cuh"
 
 namespace yb {
 
@@ -1051,6 +1052,36 @@ template <int EXT> YB_HD float mat_getAlpha(const Material &m, const MatDat &d, 
     leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);
     float al1 = leaf_getAlpha(blend_m1(m), d1, sp, wo), al2 = leaf_getAlpha(blend_m2(m), d2, sp, wo);
     return fminf_(al1, al2);
+}
+
+// ================================================================== node materials: constants <- shader nodes
+// Evaluates the material's nodes for this surface point and returns a Material whose constants are the node outputs
+// (EXT >= 2 builds only; materials without nodes, and every material in the other builds, come back untouched).
+// Slot use per material: shinydiffuse.cc:82-98,242-256,305-329,407,427,447-453; glossy.cc:93,164-169; coatedglossy.cc:115,186-190;
+// glass.cc:123,168,240; roughglass.cc:132.
+template <int EXT> YB_HD const Material &mat_resolve(const SceneDev &sc, const Material &m, v3 P, v3 Ng, const TexPoint &tp, Material &tmp)
+{
+    if (EXT < 2 || m.nNodes <= 0) return m;
+    NodeRes st[YB_MAX_NODES];
+    for (int i = 0; i < m.nNodes && i < YB_MAX_NODES; ++i) node_eval(sc.shaderNodes[m.nodeBase + i], sc.textures, P, Ng, tp, st, i);
+    tmp = m;
+    tmp.nNodes = 0;
+    int s;
+    if ((s = m.slot[SLOT_DIFFUSE]) >= 0) {
+        const col3 c(st[s].r, st[s].g, st[s].b);
+        if (m.type == MAT_SHINYDIFFUSE) { tmp.diffuseColor = c; tmp.emitColor = c * m.emitStrength; }
+        else tmp.diffColor = c;
+    }
+    if ((s = m.slot[SLOT_MIRROR_COLOR]) >= 0) {
+        const col3 c(st[s].r, st[s].g, st[s].b);
+        if (m.type == MAT_SHINYDIFFUSE) tmp.mirrorColor = c; else tmp.specRefCol = c;       // glass / rough_glass: mirColS
+    }
+    if ((s = m.slot[SLOT_MIRROR]) >= 0) tmp.mirrorStrength = st[s].f;
+    if ((s = m.slot[SLOT_TRANSPARENCY]) >= 0) tmp.transparencyStrength = st[s].f;
+    if ((s = m.slot[SLOT_TRANSLUCENCY]) >= 0) tmp.translucencyStrength = st[s].f;
+    if ((s = m.slot[SLOT_GLOSSY]) >= 0) tmp.glossColor = col3(st[s].r, st[s].g, st[s].b);
+    if ((s = m.slot[SLOT_GLOSSY_REFLECT]) >= 0) tmp.reflectivity = st[s].f;
+    return tmp;
 }
 
 }  // namespace yb

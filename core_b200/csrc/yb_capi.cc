@@ -98,7 +98,7 @@ yb200_handle yb200_create_material(yb200_ctx *ctx, const char *n) { return CTX.c
 yb200_handle yb200_create_camera(yb200_ctx *ctx, const char *n) { return CTX.createCamera(n); }
 yb200_handle yb200_create_background(yb200_ctx *ctx, const char *n) { return CTX.createBackground(n); }
 yb200_handle yb200_create_integrator(yb200_ctx *ctx, const char *n) { return CTX.createIntegrator(n); }
-yb200_handle yb200_create_texture(yb200_ctx *ctx, const char *n) { CTX.fail(std::string("createTexture('") + n + "'): textures / shader nodes are not supported by the B200 path"); return 0; }
+yb200_handle yb200_create_texture(yb200_ctx *ctx, const char *n) { GUARD_BEGIN return CTX.createTexture(n); GUARD_END(0) }
 yb200_handle yb200_create_volume_region(yb200_ctx *ctx, const char *n) { CTX.fail(std::string("createVolumeRegion('") + n + "'): participating media are not supported by the B200 path"); return 0; }
 
 int yb200_update_scene(yb200_ctx *ctx)

@@ -79,7 +79,7 @@ void Context::info(const std::string &msg) { if (verbosity >= 3) fprintf(stderr,
 void Context::clearAll()   // yafrayinterface.cc:47-64
 {
     params.clear(); eparams.clear(); cparams = &params;
-    materials.clear(); materialNames.clear(); lights.clear(); lightNames.clear(); lightObj.clear();
+    materials.clear(); materialNames.clear(); textures.clear(); textureNames.clear(); shaderNodes.clear(); lights.clear(); lightNames.clear(); lightObj.clear();
     cameras.clear(); backgrounds.clear(); integrators.clear();
     meshes.clear(); curObj = 0; stateStack.clear(); stateStack.push_back(ST_READY);
     nextFreeID = INT_MAX; geomChanged = true; sceneReady = false; sceneStarted = false;
@@ -179,17 +179,18 @@ bool Context::addTriangle(int a, int b, int c, uintptr_t mat)   // scene.cc:585-
     o.tri_mat.push_back((uint32_t)((mat & 0xffffffu) - 1));
     return true;
 }
-bool Context::addTriangleUV(int a, int b, int c, int, int, int, uintptr_t mat)   // scene.cc:628-646
+bool Context::addTriangleUV(int a, int b, int c, int uv_a, int uv_b, int uv_c, uintptr_t mat)   // scene.cc:628-646
 {
     if (!addTriangle(a, b, c, mat)) return false;
-    curObj->n_uv_offsets += 3;      // UV sets are accepted and ignored: no supported material reads sp.U/V (textures are rejected)
+    curObj->n_uv_offsets += 3;
+    curObj->uv_offsets.push_back(uv_a); curObj->uv_offsets.push_back(uv_b); curObj->uv_offsets.push_back(uv_c);
     return true;
 }
-int Context::addUV(float, float)
+int Context::addUV(float u, float v)   // scene.cc:648-662
 {
     if (stateStack.back() != ST_OBJECT) return 0;
-    static int counter = 0;
-    return counter++;
+    curObj->uv_values.push_back(u); curObj->uv_values.push_back(v);
+    return (int)(curObj->uv_values.size() / 2) - 1;
 }
 bool Context::addInstance(unsigned baseId, const float m[16])   // scene.cc:983-1008
 {
@@ -309,15 +310,201 @@ static bool has_shader_params(const ParaMap &p, const std::list<ParaMap> &ep, st
     return false;
 }
 
+// ------------------------------------------------------------------------------------------------ textures + shader nodes
+uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 + src/textures/basictex.cc factories
+{
+    std::string type;
+    if (!params.get("type", type)) { fail(std::string("Environment: Type of texture not specified for ") + name); return 0; }
+    if (textureNames.count(name)) { warn(std::string("Environment: Sorry, texture already in table: ") + name); return 0; }
+    const ParaMap &p = params;
+    Texture t;
+    memset((void *)&t, 0, sizeof(t));
+    t.color1 = col3(0.f); t.color2 = col3(1.f); t.depth = 2; t.size = 1.f; t.turb = 1.f; t.sharpness = 1.f;
+    std::string ntype, s;
+    if (p.get("noise_type", ntype) && ntype != "newperlin" && ntype != "")
+        // newNoise (basictex.cc:26-50): anything but blender / stdperlin / voronoi_* / cellnoise means newPerlin_t
+        if (ntype == "blender" || ntype == "stdperlin" || ntype == "cellnoise" || ntype.find("voronoi") != std::string::npos) {
+            fail("texture '" + std::string(name) + "': noise_type '" + ntype + "' is not supported (newperlin only)"); return 0;
+        }
+    if (type == "rgb_cube") t.type = TEX_RGB_CUBE;
+    else if (type == "blend") t.type = TEX_BLEND;
+    else if (type == "clouds") {                     // basictex.cc:82-98
+        bool hard = false;
+        t.type = TEX_CLOUDS;
+        p.getColor("color1", t.color1); p.getColor("color2", t.color2); p.get("depth", t.depth); p.get("size", t.size); p.get("hard", hard);
+        t.hard = hard;
+        if (p.get("bias", s)) t.bias = s == "positive" ? 1 : (s == "negative" ? 2 : 0);
+    } else if (type == "marble" || type == "wood") { // basictex.cc:132-152,200-224
+        bool hard = false; float shp = 1.f;
+        t.type = type == "marble" ? TEX_MARBLE : TEX_WOOD;
+        p.getColor("color1", t.color1); p.getColor("color2", t.color2); p.get("depth", t.depth); p.get("turbulence", t.turb); p.get("size", t.size);
+        p.get("hard", hard); t.hard = hard;
+        if (t.type == TEX_MARBLE) { p.get("sharpness", shp); if (shp > 1) t.sharpness = (float)(1.0 / (double)shp); }
+        else if (p.get("wood_type", s)) t.rings = s == "rings";
+        if (p.get("shape", s)) t.wshape = s == "saw" ? 1 : (s == "tri" ? 2 : 0);
+    } else {
+        fail("Environment: texture type '" + type + "' is not supported by the B200 path (supported: rgb_cube, blend, clouds, marble, wood)");
+        return 0;
+    }
+    textures.push_back(t);
+    textureNames[name] = (int)textures.size() - 1;
+    return 0x54000000u | (uintptr_t)textures.size();
+}
+
+// nodeMaterial_t::loadNodes + parseNodes + solveNodesOrder (nodematerial.cc:77-243) for the node types of yb_types.h.  The
+// material's nodes are appended to the scene's node table in evaluation order; m.slot[] gets the index of each bound root.
+bool Context::loadMaterialNodes(const char *name, Material &m, const char *const *slotKeys, const int *slotIds, int nSlots)
+{
+    m.nodeBase = (int32_t)shaderNodes.size(); m.nNodes = 0;
+    for (int i = 0; i < SLOT_COUNT + 1 && i < 8; ++i) m.slot[i] = -1;
+    if (params.has("bump_shader")) return fail("material '" + std::string(name) + "': bump_shader (bump / normal mapping) is not supported");
+    if (eparams.empty()) {
+        for (int k = 0; k < nSlots; ++k) { std::string nm; if (params.get(slotKeys[k], nm)) warn("Shader node " + std::string(slotKeys[k]) + " '" + nm + "' does not exist!"); }
+        return true;
+    }
+    struct Raw { ShaderNode n; std::string name, in1, in2, factor, input, upper; };
+    std::vector<Raw> raw;
+    std::map<std::string, int> table;
+    for (std::list<ParaMap>::const_iterator it = eparams.begin(); it != eparams.end(); ++it) {
+        const ParaMap &p = *it;
+        std::string element, nname, type;
+        if (p.get("element", element) && element != "shader_node") continue;
+        if (!p.get("name", nname)) return fail("NodeMaterial: Name of shader node not specified!");
+        if (table.count(nname)) return fail("NodeMaterial: Multiple nodes with identically names!");
+        if (!p.get("type", type)) return fail("NodeMaterial: Type of shader node not specified!");
+        Raw r;
+        memset((void *)&r.n, 0, sizeof(r.n));
+        r.name = nname;
+        ShaderNode &n = r.n;
+        n.in1 = n.in2 = n.inFactor = n.input = n.upper = -1;
+        if (type == "texture_mapper") {                 // basicnodes.cc:236-304
+            std::string texname, opt;
+            if (!p.get("texture", texname)) return fail("TextureMapper: No texture given for texture mapper!");
+            std::map<std::string, int>::const_iterator ti = textureNames.find(texname);
+            if (ti == textureNames.end()) return fail("TextureMapper: texture '" + texname + "' does not exist!");
+            n.type = NODE_TEXMAP; n.tex = ti->second; n.texCoords = TXC_GLOB;
+            if (p.get("texco", opt)) {
+                if (opt == "uv") n.texCoords = TXC_UV;
+                else if (opt == "orco") n.texCoords = TXC_ORCO;
+                else if (opt == "transformed") n.texCoords = TXC_TRAN;
+                else if (opt == "window") return fail("TextureMapper: texco 'window' is not supported");
+                else n.texCoords = TXC_GLOB;             // normal / reflect / stick / stress / tangent fall back to global (basicnodes.cc:139-146)
+            }
+            float bump = 1.f; bool scalar = true; int map[3] = {1, 2, 3}; v3 offset(0.f), scale(1.f);
+            p.getPoint("scale", scale); p.getPoint("offset", offset); p.get("do_scalar", scalar); p.get("bump_strength", bump);
+            p.get("proj_x", map[0]); p.get("proj_y", map[1]); p.get("proj_z", map[2]);
+            for (int i = 0; i < 3; ++i) map[i] = std::min(3, std::max(0, map[i]));
+            n.mapX = map[0]; n.mapY = map[1]; n.mapZ = map[2]; n.scale = scale; n.offset = 2.f * offset; n.doScalar = scalar;
+            const float ident[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+            memcpy(n.mtx, ident, sizeof(ident));
+            std::map<std::string, std::vector<float> >::const_iterator mi = p.mdicc.find("transform");
+            if (mi != p.mdicc.end() && mi->second.size() >= 12) memcpy(n.mtx, mi->second.data(), 12 * sizeof(float));
+        } else if (type == "value") {                   // basicnodes.cc:322-333
+            col3 col(1.f); float alpha = 1.f, val = 1.f;
+            p.getColor("color", col); p.get("alpha", alpha); p.get("scalar", val);
+            n.type = NODE_VALUE; n.col1[0] = col.x; n.col1[1] = col.y; n.col1[2] = col.z; n.col1[3] = alpha; n.val1 = val;
+        } else if (type == "mix") {                     // basicnodes.cc:383-436,580-600
+            float val = 0.5f; int mode = 0;
+            p.get("cfactor", val); p.get("mode", mode);
+            n.type = NODE_MIX; n.mode = mode; n.cfactor = (mode == 0 || mode == 5 || mode < 0 || mode > 9) ? val : 0.f;   // subclasses start from cfactor(0)
+            std::map<std::string, Param>::const_iterator ci;
+            if (!p.get("input1", r.in1)) {
+                ci = p.dicc.find("color1");
+                if (ci == p.dicc.end() || ci->second.type != Param::T_COLOR) return fail("MixNode: Color1 not set");
+                for (int k = 0; k < 4; ++k) n.col1[k] = ci->second.v[k];
+            }
+            if (!p.get("input2", r.in2)) {
+                ci = p.dicc.find("color2");
+                if (ci == p.dicc.end() || ci->second.type != Param::T_COLOR) return fail("MixNode: Color2 not set");
+                for (int k = 0; k < 4; ++k) n.col2[k] = ci->second.v[k];
+            }
+            if (!p.get("factor", r.factor)) { if (!p.get("value", n.cfactor)) return fail("MixNode: Value not set"); }
+            // val1 / val2 (the scalars of constant inputs) are never initialised by the reference: 0 here
+        } else if (type == "layer") {                   // layernode.cc:190-225
+            col3 def_col(1.f); bool do_color = true, do_scalar = false, color_input = true, use_alpha = false, stencil = false, noRGB = false, negative = false;
+            double def_val = 1.0, colfac = 1.0, valfac = 1.0; int mode = 0;
+            p.get("mode", mode); p.getColor("def_col", def_col); p.get("colfac", colfac); p.get("def_val", def_val); p.get("valfac", valfac);
+            p.get("do_color", do_color); p.get("do_scalar", do_scalar); p.get("color_input", color_input); p.get("use_alpha", use_alpha);
+            p.get("noRGB", noRGB); p.get("stencil", stencil); p.get("negative", negative);
+            n.type = NODE_LAYER; n.mode = mode;
+            n.texflag = (noRGB ? TXF_RGBTOINT : 0u) | (stencil ? TXF_STENCIL : 0u) | (negative ? TXF_NEGATIVE : 0u) | (use_alpha ? TXF_ALPHAMIX : 0u);
+            n.colfac = (float)colfac; n.valfac = (float)valfac; n.defVal = (float)def_val; n.defCol = def_col;
+            n.doColor = do_color; n.doScalarL = do_scalar; n.colorInput = color_input; n.useAlpha = use_alpha;
+            if (!p.get("input", r.input)) return fail("LayerNode: input not set");
+            if (!p.get("upper_layer", r.upper)) {
+                std::map<std::string, Param>::const_iterator ci = p.dicc.find("upper_color");
+                if (ci != p.dicc.end() && ci->second.type == Param::T_COLOR) for (int k = 0; k < 4; ++k) n.upperCol[k] = ci->second.v[k];
+                else { n.upperCol[0] = n.upperCol[1] = n.upperCol[2] = 0.f; n.upperCol[3] = 1.f; }
+                float uv = 0.f; p.get("upper_value", uv); n.upperVal = uv;
+            }
+        } else return fail("NodeMaterial: Don't know how to create shader node of type '" + type + "'!");
+        table[nname] = (int)raw.size();
+        raw.push_back(r);
+    }
+    // configInputs: names -> raw indices
+    std::vector<std::vector<int> > deps(raw.size());
+    auto link = [&](const std::string &nm, int &dst, size_t self, const char *what) -> bool {
+        if (nm.empty()) return true;
+        std::map<std::string, int>::const_iterator i = table.find(nm);
+        if (i == table.end()) { fail(std::string(what) + ": Couldn't get input " + nm); return false; }
+        dst = i->second; deps[self].push_back(i->second);
+        return true;
+    };
+    for (size_t i = 0; i < raw.size(); ++i) {
+        Raw &r = raw[i];
+        // dependency order of getDependencies: mix = input1, input2, factor; layer = input, upper layer
+        if (!link(r.in1, r.n.in1, i, "MixNode") || !link(r.in2, r.n.in2, i, "MixNode") || !link(r.factor, r.n.inFactor, i, "MixNode")) return false;
+        if (!link(r.input, r.n.input, i, "LayerNode") || !link(r.upper, r.n.upper, i, "LayerNode")) return false;
+    }
+    // roots in the order of the material's nodeList map (std::map<std::string, ...>: alphabetical by slot key), then
+    // recursiveSolver: depth-first, dependencies before the node
+    std::vector<std::pair<std::string, int> > roots;   // (slot key, raw index)
+    std::vector<int> rootSlot;
+    {
+        std::vector<std::pair<std::string, int> > keys;
+        for (int k = 0; k < nSlots; ++k) keys.push_back(std::make_pair(std::string(slotKeys[k]), slotIds[k]));
+        std::sort(keys.begin(), keys.end());
+        for (size_t k = 0; k < keys.size(); ++k) {
+            std::string nm;
+            if (!params.get(keys[k].first, nm)) continue;
+            std::map<std::string, int>::const_iterator i = table.find(nm);
+            if (i == table.end()) { warn("Shader node " + keys[k].first + " '" + nm + "' does not exist!"); continue; }
+            roots.push_back(std::make_pair(keys[k].first, i->second)); rootSlot.push_back(keys[k].second);
+        }
+    }
+    std::vector<int> order, newIndex(raw.size(), -1);
+    std::vector<char> seen(raw.size(), 0);
+    struct Rec { static void go(int n, const std::vector<std::vector<int> > &deps, std::vector<char> &seen, std::vector<int> &order) {
+        if (seen[n]) return; seen[n] = 1;
+        for (size_t k = 0; k < deps[n].size(); ++k) if (!seen[deps[n][k]]) go(deps[n][k], deps, seen, order);
+        order.push_back(n); } };
+    for (size_t k = 0; k < roots.size(); ++k) Rec::go(roots[k].second, deps, seen, order);
+    if (order.size() != raw.size()) warn("NodeMaterial: Unreachable nodes!");
+    if (order.size() > YB_MAX_NODES) return fail("material '" + std::string(name) + "': more than " + std::to_string(YB_MAX_NODES) + " shader nodes are not supported");
+    for (size_t k = 0; k < order.size(); ++k) newIndex[order[k]] = (int)k;
+    for (size_t k = 0; k < order.size(); ++k) {
+        ShaderNode n = raw[order[k]].n;
+        if (n.in1 >= 0) n.in1 = newIndex[n.in1];
+        if (n.in2 >= 0) n.in2 = newIndex[n.in2];
+        if (n.inFactor >= 0) n.inFactor = newIndex[n.inFactor];
+        if (n.input >= 0) n.input = newIndex[n.input];
+        if (n.upper >= 0) n.upper = newIndex[n.upper];
+        shaderNodes.push_back(n);
+    }
+    m.nNodes = (int32_t)order.size();
+    for (size_t k = 0; k < roots.size(); ++k) m.slot[rootSlot[k]] = newIndex[roots[k].second];
+    return true;
+}
+
 uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 + the plugins' factory()
 {
     std::string type;
     if (!params.get("type", type)) { fail(std::string("Environment: Type of material not specified for ") + name); return 0; }
     if (materialNames.count(name)) { warn(std::string("Environment: Sorry, material already in table: ") + name); return 0; }
-    std::string which;
-    if (has_shader_params(params, eparams, which)) { fail("material '" + std::string(name) + "': shader nodes / textures are not supported (" + which + ")"); return 0; }
     Material m;
-    memset(&m, 0, sizeof(m));
+    memset((void *)&m, 0, sizeof(m));
+    for (int i = 0; i < 8; ++i) m.slot[i] = -1;
+    const size_t nodesBefore = shaderNodes.size();
     const ParaMap &p = params;
     if (type == "shinydiffusemat") {              // shinydiffuse.cc:470-515 + ctor :5-14 + config :32-80
         col3 diffuseColor(1.f), mirrorColor(1.f);
@@ -343,19 +530,26 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
             m.orenB = (float)(0.45 * s2 / (s2 + 0.09));
             m.useOrenNayar = 1;
         }
-        // config()
+        m.emitStrength = emit;
+        {
+            static const char *const keys[] = {"diffuse_shader", "mirror_color_shader", "mirror_shader", "transparency_shader", "translucency_shader"};
+            static const int ids[] = {SLOT_DIFFUSE, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY};
+            if (!loadMaterialNodes(name, m, keys, ids, 5)) { shaderNodes.resize(nodesBefore); return 0; }
+        }
+        const bool shMirror = m.slot[SLOT_MIRROR] >= 0, shTransp = m.slot[SLOT_TRANSPARENCY] >= 0, shTransl = m.slot[SLOT_TRANSLUCENCY] >= 0;
+        // config() (shinydiffuse.cc:27-73): a bound shader switches the component on and leaves `acc` alone
         float acc = 1.f; int n = 0;
-        if (m.mirrorStrength > 0.00001f) {
+        if (m.mirrorStrength > 0.00001f || shMirror) {
             m.isMirror = 1;
-            if (!m.hasFresnel) acc = 1.f - m.mirrorStrength;
+            if (shMirror) {} else if (!m.hasFresnel) acc = 1.f - m.mirrorStrength;
             m.bsdfFlags |= BSDF_SPECULAR | BSDF_REFLECT; m.cFlags[n] = BSDF_SPECULAR | BSDF_REFLECT; m.cIndex[n] = 0; ++n;
         }
-        if (m.transparencyStrength * acc > 0.00001f) {
-            m.isTransparent = 1; acc *= 1.f - m.transparencyStrength;
+        if (m.transparencyStrength * acc > 0.00001f || shTransp) {
+            m.isTransparent = 1; if (!shTransp) acc *= 1.f - m.transparencyStrength;
             m.bsdfFlags |= BSDF_TRANSMIT | BSDF_FILTER; m.cFlags[n] = BSDF_TRANSMIT | BSDF_FILTER; m.cIndex[n] = 1; ++n;
         }
-        if (m.translucencyStrength * acc > 0.00001f) {
-            m.isTranslucent = 1; acc *= 1.f - m.transparencyStrength;   // sic (shinydiffuse.cc:57)
+        if (m.translucencyStrength * acc > 0.00001f || shTransl) {
+            m.isTranslucent = 1; if (!shTransl) acc *= 1.f - m.transparencyStrength;   // sic (shinydiffuse.cc:57)
             m.bsdfFlags |= BSDF_DIFFUSE | BSDF_TRANSMIT; m.cFlags[n] = BSDF_DIFFUSE | BSDF_TRANSMIT; m.cIndex[n] = 2; ++n;
         }
         if (m.diffuseStrength * acc > 0.00001f) {
@@ -386,6 +580,11 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
             m.orenB = (float)(0.45 * s2 / (s2 + 0.09));
             m.orenNayar = 1;
         }
+        {
+            static const char *const keys[] = {"diffuse_shader", "glossy_shader", "glossy_reflect_shader"};
+            static const int ids[] = {SLOT_DIFFUSE, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT};
+            if (!loadMaterialNodes(name, m, keys, ids, 3)) { shaderNodes.resize(nodesBefore); return 0; }
+        }
         const uint32_t glossyFlags = as_diff ? (BSDF_DIFFUSE | BSDF_REFLECT) : (BSDF_GLOSSY | BSDF_REFLECT);
         if (coated) {
             m.cFlags[0] = BSDF_SPECULAR | BSDF_REFLECT; m.cFlags[1] = glossyFlags;
@@ -403,6 +602,11 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         p.get("dispersion_power", disp_power); p.get("fake_shadows", fake);
         if (disp_power > 0.0) { fail("glass '" + std::string(name) + "': dispersion is not supported"); return 0; }
         if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
+        {
+            static const char *const keys[] = {"mirror_color_shader"};
+            static const int ids[] = {SLOT_MIRROR_COLOR};
+            if (!loadMaterialNodes(name, m, keys, ids, 1)) { shaderNodes.resize(nodesBefore); return 0; }
+        }
         m.type = MAT_GLASS;
         m.ior = (float)IOR;
         m.filterCol = (float)filt * filtCol + col3((float)(1.f - filt));
@@ -416,6 +620,11 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         if (disp_power > 0.0) { fail("rough_glass '" + std::string(name) + "': dispersion is not supported"); return 0; }
         if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("rough_glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
         alpha = std::max(1e-4f, std::min(alpha * 0.5f, 1.f));
+        {
+            static const char *const keys[] = {"mirror_color_shader"};
+            static const int ids[] = {SLOT_MIRROR_COLOR};
+            if (!loadMaterialNodes(name, m, keys, ids, 1)) { shaderNodes.resize(nodesBefore); return 0; }
+        }
         m.type = MAT_ROUGH_GLASS;
         m.ior = IOR; m.rgAlpha2 = alpha * alpha;
         m.filterCol = filt * filtCol + col3(1.f - filt);
@@ -428,6 +637,7 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         std::map<std::string, int>::const_iterator i1 = materialNames.find(n1), i2 = materialNames.find(n2);
         if (i1 == materialNames.end() || i2 == materialNames.end()) { fail("blend_mat '" + std::string(name) + "': material '" + (i1 == materialNames.end() ? n1 : n2) + "' does not exist"); return 0; }
         if (p.has("mask")) { fail("blend_mat '" + std::string(name) + "': a blend mask shader node is not supported (constant blend_value only)"); return 0; }
+        if (materials[i1->second].nNodes > 0 || materials[i2->second].nNodes > 0) { fail("blend_mat '" + std::string(name) + "': blending materials with shader nodes is not supported"); return 0; }
         if (materials[i1->second].type == MAT_BLEND || materials[i2->second].type == MAT_BLEND) { fail("blend_mat '" + std::string(name) + "': blending a blend_mat is not supported (one level only)"); return 0; }
         p.get("blend_value", blend_val);
         const int self = (int)materials.size();
@@ -828,6 +1038,10 @@ bool Context::uploadTables()
         d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
         rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
         rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
+        d_textures.reserve(textures.size() + 1); d_shaderNodes.reserve(shaderNodes.size() + 1);
+        rt_h2d(d_textures.p, textures.data(), textures.size() * sizeof(Texture), stream);
+        rt_h2d(d_shaderNodes.p, shaderNodes.data(), shaderNodes.size() * sizeof(ShaderNode), stream);
+        sc.textures = d_textures.p; sc.shaderNodes = d_shaderNodes.p;
         rt_sync(stream);    // the staging vectors above go out of scope
     } catch (const RtError &e) { return fail(std::string("scene tables upload failed: ") + e.what()); }
     return true;
@@ -849,6 +1063,20 @@ bool Context::flattenAndBuild()
         if (o.is_smooth || (o.base && o.normals_exported)) anySmooth = true;
     }
     if (ntri >= 0x7fffffffu / 3) return fail("scene has too many triangles for 32-bit indexing");
+    // texture coordinates are only flattened when some material has shader nodes (nothing else reads sp.U/V or sp.orcoP)
+    bool anyNodes = false, anyUV = false, anyOrco = false;
+    for (size_t i = 0; i < materials.size(); ++i) if (materials[i].nNodes > 0) anyNodes = true;
+    if (anyNodes)
+        for (std::map<unsigned, MeshObj>::iterator i = meshes.begin(); i != meshes.end(); ++i) {
+            MeshObj &o = i->second;
+            if (!o.visible || o.is_base) continue;
+            const MeshObj &g = o.base ? *o.base : o;
+            if (g.has_uv && g.uv_offsets.size() == 3 * g.tri_mat.size()) anyUV = true;
+            if (g.has_orco) anyOrco = true;
+        }
+    std::vector<float> h_uv; std::vector<v3> h_orco;
+    if (anyUV) h_uv.assign(6 * ntri, 0.f);
+    if (anyOrco) h_orco.assign(3 * ntri, v3(0.f));
     h_in_v.reserve(3 * ntri + 1); if (anySmooth) h_in_n.reserve(3 * ntri + 1);
     f4 *hv = h_in_v.p; v3 *hn = h_in_n.p;
     // work list: (object, first global triangle) in scene order, cut into chunks that host threads fill in parallel
@@ -901,6 +1129,24 @@ bool Context::flattenAndBuild()
                         hn[3 * k + c] = nn;
                     }
                 }
+                if (anyUV && g.has_uv && g.uv_offsets.size() == 3 * g.tri_mat.size()) {   // triangle.cc:50-58
+                    bool ok = true;
+                    for (int c = 0; c < 3; ++c) {
+                        const int ui = g.uv_offsets[3 * t + c];
+                        if (ui < 0 || 2 * (size_t)ui + 1 >= g.uv_values.size()) { ok = false; break; }
+                        h_uv[6 * k + 2 * c] = g.uv_values[2 * (size_t)ui]; h_uv[6 * k + 2 * c + 1] = g.uv_values[2 * (size_t)ui + 1];
+                    }
+                    if (!ok) { bad = 3; return; }
+                    info |= TRI_HAS_UV;
+                }
+                if (anyOrco && g.has_orco) {                                             // triangle.cc:28-41: orco of vertex p is points[p + 1]
+                    for (int c = 0; c < 3; ++c) {
+                        const size_t pi = (size_t)g.tri_idx[3 * t + c] + 1;
+                        if (pi >= g.points.size()) { bad = 1; return; }
+                        h_orco[3 * k + c] = g.points[pi];
+                    }
+                    info |= TRI_HAS_ORCO;
+                }
                 hv[3 * k].w = i2f((int32_t)k);
                 hv[3 * k + 1].w = i2f((int32_t)info);
             }
@@ -916,6 +1162,7 @@ bool Context::flattenAndBuild()
     }
     if (bad == 1) return fail("triangle references a vertex that does not exist");
     if (bad == 2) return fail("triangle references a normal that does not exist");
+    if (bad == 3) return fail("triangle references a UV value that does not exist");
     nTris = (uint32_t)ntri; haveNormals = anySmooth;
     const auto t1 = std::chrono::steady_clock::now();
     // upload + build
@@ -924,6 +1171,9 @@ bool Context::flattenAndBuild()
         in_v.reserve(3 * ntri + 1);
         rt_h2d(in_v.p, hv, 3 * ntri * sizeof(f4), stream);
         if (anySmooth) { in_n.reserve(3 * ntri + 1); rt_h2d(in_n.p, hn, 3 * ntri * sizeof(v3), stream); }
+        sc.prim_uv = 0; sc.prim_orco = 0;
+        if (anyUV) { d_prim_uv.reserve(h_uv.size() + 1); rt_h2d(d_prim_uv.p, h_uv.data(), h_uv.size() * sizeof(float), stream); sc.prim_uv = d_prim_uv.p; }
+        if (anyOrco) { d_prim_orco.reserve(h_orco.size() + 1); rt_h2d(d_prim_orco.p, h_orco.data(), h_orco.size() * sizeof(v3), stream); sc.prim_orco = d_prim_orco.p; }
         rt_sync(stream);
         const auto t2 = std::chrono::steady_clock::now();
         bvh_build(in_v.p, anySmooth ? in_n.p : 0, nTris, d_nodes, d_tri_v, d_tri_n, nNodes, bvhDepth, boundLo, boundHi, bvhScratch, stream);

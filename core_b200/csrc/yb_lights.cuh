@@ -356,4 +356,23 @@ YB_HD void tri_getSurface(const SceneDev &sc, int tri, v3 hitP, float b1, float 
     createCS(sp.N, sp.NU, sp.NV);
 }
 
+// the texture-coordinate part of triangle_t::getSurface (triangle.cc:28-64): orco point / normal and interpolated UV
+YB_HD void tri_getTexPoint(const SceneDev &sc, int tri, v3 hitP, float b1, float b2, v3 Ng, TexPoint &tp)
+{
+    const uint32_t info = (uint32_t)f2i(sc.tri_v[3 * tri + 1].w);
+    const int prim = f2i(sc.tri_v[3 * tri].w);
+    const float u = 1 - b1 - b2, v = b1, w = b2;
+    if ((info & TRI_HAS_ORCO) && sc.prim_orco) {
+        const v3 p0 = sc.prim_orco[3 * (size_t)prim], p1 = sc.prim_orco[3 * (size_t)prim + 1], p2 = sc.prim_orco[3 * (size_t)prim + 2];
+        tp.orcoP = u * p0 + v * p1 + w * p2;
+        tp.orcoNg = normalize(cross(p1 - p0, p2 - p0));
+    } else { tp.orcoP = hitP; tp.orcoNg = Ng; }
+    tp.U = 0.f; tp.V = 0.f;                              // left uninitialised by the reference without UVs (triangle.cc:85-90)
+    if ((info & TRI_HAS_UV) && sc.prim_uv) {
+        const float *q = sc.prim_uv + 6 * (size_t)prim;
+        tp.U = u * q[0] + v * q[2] + w * q[4];
+        tp.V = u * q[1] + v * q[3] + w * q[5];
+    }
+}
+
 }  // namespace yb

@@ -1,0 +1,238 @@
+// yb_nodes.cuh — device restatement of the shader-node tree of nodeMaterial_t for the node and texture types listed in
+// yb_types.h:
+//   textureMapper_t / valueNode_t / mixNode_t family   src/textures/basicnodes.cc:96-160,312-600
+//   layerNode_t                                        src/textures/layernode.cc:12-110, include/core_api/shader.h:112-225
+//   rgbCube_t / textureBlend_t / textureClouds_t / textureMarble_t / textureWood_t   src/textures/basictex.cc:44-244,478-502
+//   newPerlin_t + turbulence                           src/textures/noise.cc:161-183,757-769, include/textures/noise.h:46-53
+// Every supported node is view independent, so a material's nodes are evaluated once per surface point (what initBSDF does
+// with allViewindep, e.g. shinydiffuse.cc:159-161) and the results replace the constants of a LOCAL copy of the Material
+// record (mat_resolve at the end of yb_bsdf.cuh); the BSDF code then runs unchanged.  Bump mapping is rejected at creation.
+#pragma once
+#include "yb_types.h"
+
+namespace yb {
+
+#if defined(__CUDACC__) && !defined(YB_HOSTEMU)
+#define YB_NTABLE static __device__ __constant__
+#else
+#define YB_NTABLE static
+#endif
+#include "yb_noise_tab.inc"
+
+struct NodeRes { float r, g, b, a, f; };          // nodeResult_t: colorA_t + scalar (shader.h:32-38)
+struct TexPoint { float U, V; v3 orcoP, orcoNg; };   // the surfacePoint_t fields texture_mapper reads besides P / Ng
+
+// ---- noise ------------------------------------------------------------------------------------------
+YB_HD int nperm(int i) { return (int)yb_noise_perm[i & 255]; }     // hash[512] holds the permutation twice
+YB_HD float np_fade(float t) { return t * t * t * (t * (t * 6 - 15) + 10); }
+YB_HD float np_grad(int hash, float x, float y, float z)
+{
+    int h = hash & 15;
+    float u = h < 8 ? x : y, v = h < 4 ? y : (h == 12 || h == 14) ? x : z;
+    return ((h & 1) == 0 ? u : -u) + ((h & 2) == 0 ? v : -v);
+}
+YB_HD float np_lerp(float t, float a, float b) { return a + t * (b - a); }
+YB_HD float newPerlin(v3 pt)
+{
+    float x = pt.x, y = pt.y, z = pt.z;
+    float u = floorf(x), v = floorf(y), w = floorf(z);
+    int X = ((int)u) & 255, Y = ((int)v) & 255, Z = ((int)w) & 255;
+    x -= u; y -= v; z -= w;
+    u = np_fade(x); v = np_fade(y); w = np_fade(z);
+    int A = nperm(X) + Y, AA = nperm(A) + Z, AB = nperm(A + 1) + Z, B = nperm(X + 1) + Y, BA = nperm(B) + Z, BB = nperm(B + 1) + Z;
+    float nv = np_lerp(w, np_lerp(v, np_lerp(u, np_grad(nperm(AA), x, y, z), np_grad(nperm(BA), x - 1, y, z)),
+                                     np_lerp(u, np_grad(nperm(AB), x, y - 1, z), np_grad(nperm(BB), x - 1, y - 1, z))),
+                          np_lerp(v, np_lerp(u, np_grad(nperm(AA + 1), x, y, z - 1), np_grad(nperm(BA + 1), x - 1, y, z - 1)),
+                                     np_lerp(u, np_grad(nperm(AB + 1), x, y - 1, z - 1), np_grad(nperm(BB + 1), x - 1, y - 1, z - 1))));
+    return (float)(0.5 + 0.5 * (double)nv);
+}
+YB_HD float turbulence(v3 pt, int oct, float size, bool hard)
+{
+    float val, amp = 1, sum = 0;
+    v3 tp = pt * size;
+    for (int i = 0; i <= oct; i++, amp *= 0.5f, tp *= 2.0f) {
+        val = newPerlin(tp);
+        if (hard) val = fabsf((float)(2.0 * (double)val - 1.0));
+        sum += amp * val;
+    }
+    return sum * ((float)(1 << oct) / (float)((1 << (oct + 1)) - 1));
+}
+YB_HD float wave_shape(int wshape, float w)             // the shape switch of marble / wood (basictex.cc:112-124,180-192)
+{
+    if (wshape == 1) { w *= (float)(0.5 * YB_M_1_PI); w -= floorf(w); return w; }
+    if (wshape == 2) { w *= (float)(0.5 * YB_M_1_PI); return fabsf(2.0f * (w - floorf(w)) - 1.0f); }
+    return 0.5f + 0.5f * fSin(w);
+}
+
+// ---- textures: texture_t::getFloat / getColor --------------------------------------------------------
+YB_HD float tex_getFloat(const Texture &t, v3 p)
+{
+    switch (t.type) {
+        case TEX_RGB_CUBE: {
+            const float r = clamp01f(p.x), g = clamp01f(p.y), b = clamp01f(p.z);
+            return (r + g + b) * 0.333333f;                                  // color_t::energy
+        }
+        case TEX_BLEND: {
+            float blend = (float)(0.5 * ((double)p.x + 1.));
+            return fmaxf_(0.f, fminf_(blend, 1.f));
+        }
+        case TEX_CLOUDS: {
+            float v = turbulence(p, t.depth, t.size, t.hard != 0);
+            if (t.bias) { v *= v; if (t.bias == 1) return -v; }
+            return v;
+        }
+        case TEX_MARBLE: {
+            float w = (float)((double)(p.x + p.y + p.z) * 5.0 + ((t.turb == 0.0f) ? 0.0 : (double)(t.turb * turbulence(p, t.depth, t.size, t.hard != 0))));
+            return fPow(wave_shape(t.wshape, w), t.sharpness);
+        }
+        default: {                                                           // TEX_WOOD
+            float w;
+            if (t.rings) w = (float)((double)fSqrt(p.x * p.x + p.y * p.y + p.z * p.z) * 20.0);
+            else w = (float)((double)(p.x + p.y + p.z) * 10.0);
+            w += (t.turb == 0.0f) ? 0.0f : t.turb * turbulence(p, t.depth, t.size, t.hard != 0);
+            return wave_shape(t.wshape, w);
+        }
+    }
+}
+YB_HD void tex_getColor(const Texture &t, v3 p, float *c)
+{
+    if (t.type == TEX_RGB_CUBE) { c[0] = clamp01f(p.x); c[1] = clamp01f(p.y); c[2] = clamp01f(p.z); c[3] = 1.f; return; }
+    if (t.type == TEX_BLEND) { c[0] = c[1] = c[2] = c[3] = 1.f; return; }
+    const float f = tex_getFloat(t, p);                                      // color1 + getFloat(p) * (color2 - color1), alpha 1
+    c[0] = t.color1.x + f * (t.color2.x - t.color1.x); c[1] = t.color1.y + f * (t.color2.y - t.color1.y);
+    c[2] = t.color1.z + f * (t.color2.z - t.color1.z); c[3] = 1.f;
+}
+
+// ---- nodes ---------------------------------------------------------------------------------------------
+YB_HD float col2bri(const float *c) { return 0.2126f * c[0] + 0.7152f * c[1] + 0.0722f * c[2]; }   // color.h:79-80
+// texture_rgb_blend / texture_value_blend (shader.h:112-225); blend types: mix_modes of shader.h:62
+YB_HD void texture_rgb_blend(const float *tex, const float *out, float fact, float facg, int mode, float *res)
+{
+    for (int k = 0; k < 3; ++k) {
+        const float t = tex[k], o = out[k];
+        float f = fact, r;
+        switch (mode) {
+            case 2: f *= facg; r = ((1.f - facg) + f * t) * o; break;                                    // MN_MULT
+            case 4: f *= facg; r = 1.f - ((1.f - facg) + f * (1.f - t)) * (1.f - o); break;              // MN_SCREEN
+            case 3: f = -f; f *= facg; r = f * t + o; break;                                             // MN_SUB
+            case 1: f *= facg; r = f * t + o; break;                                                     // MN_ADD
+            case 5: { f *= facg; const float it = t == 0.f ? 0.f : 1.f / t; r = (1.f - f) * o + f * o * it; break; }   // MN_DIV (invertRGB, color.h)
+            case 6: f *= facg; r = (1.f - f) * o + f * fabsf(t - o); break;                              // MN_DIFF
+            case 7: { f *= facg; const float c = f * t; r = c < o ? c : o; break; }                      // MN_DARK (darkenRGB)
+            case 8: { f *= facg; const float c = f * t; r = c > o ? c : o; break; }                      // MN_LIGHT (lightenRGB)
+            default: f *= facg; r = f * t + (1.f - f) * o; break;                                        // MN_MIX
+        }
+        res[k] = r;
+    }
+}
+YB_HD float texture_value_blend(float tex, float out, float fact, float facg, int mode, bool flip)
+{
+    fact *= facg;
+    float facm = 1.f - fact;
+    if (flip) { const float t = fact; fact = facm; facm = t; }
+    switch (mode) {
+        case 2: facm = 1.f - facg; return (facm + fact * tex) * out;
+        case 4: facm = 1.f - facg; return 1.f - (facm + fact * (1.f - tex)) * (1.f - out);
+        case 3: fact = -fact; return fact * tex + out;
+        case 1: return fact * tex + out;
+        case 5: if (tex == 0.f) return 0.f; return facm * out + fact * out / tex;
+        case 6: return facm * out + fact * fabsf(tex - out);
+        case 7: { const float c = fact * tex; return c < out ? c : out; }
+        case 8: { const float c = fact * tex; return c > out ? c : out; }
+        default: return fact * tex + facm * out;
+    }
+}
+
+YB_HD void node_eval(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, const TexPoint &tp, NodeRes *st, int self)
+{
+    NodeRes r; r.r = r.g = r.b = r.a = r.f = 0.f;
+    if (n.type == NODE_TEXMAP) {                      // textureMapper_t::getCoords + doMapping + eval
+        v3 texpt;
+        switch (n.texCoords) {
+            case TXC_UV: texpt = v3(tp.U, tp.V, 0.f); break;
+            case TXC_ORCO: texpt = tp.orcoP; break;
+            case TXC_TRAN: texpt = v3(n.mtx[0] * P.x + n.mtx[1] * P.y + n.mtx[2] * P.z + n.mtx[3], n.mtx[4] * P.x + n.mtx[5] * P.y + n.mtx[6] * P.z + n.mtx[7],
+                                      n.mtx[8] * P.x + n.mtx[9] * P.y + n.mtx[10] * P.z + n.mtx[11]); break;
+            default: texpt = P; break;
+        }
+        if (n.texCoords == TXC_UV) texpt = v3(2.0f * texpt.x - 1.0f, 2.0f * texpt.y - 1.0f, texpt.z);
+        const float texmap[4] = {0.f, texpt.x, texpt.y, texpt.z};
+        texpt = v3(texmap[n.mapX], texmap[n.mapY], texmap[n.mapZ]);
+        // tube / sphere / cube projections apply to discrete (image) textures only (basicnodes.cc:270): none supported yet
+        texpt = mul(texpt, n.scale) + n.offset;
+        const Texture &t = textures[n.tex];
+        float c[4];
+        tex_getColor(t, texpt, c);
+        r.r = c[0]; r.g = c[1]; r.b = c[2]; r.a = c[3];
+        r.f = n.doScalar ? tex_getFloat(t, texpt) : 0.f;
+    } else if (n.type == NODE_VALUE) {
+        r.r = n.col1[0]; r.g = n.col1[1]; r.b = n.col1[2]; r.a = n.col1[3]; r.f = n.val1;
+    } else if (n.type == NODE_MIX) {                  // mixNode_t::getInputs + the eval of the selected subclass
+        const float f2 = n.inFactor >= 0 ? st[n.inFactor].f : n.cfactor, f1 = 1.f - f2;
+        float c1[4], c2[4], fin1, fin2;
+        if (n.in1 >= 0) { c1[0] = st[n.in1].r; c1[1] = st[n.in1].g; c1[2] = st[n.in1].b; c1[3] = st[n.in1].a; fin1 = st[n.in1].f; }
+        else { c1[0] = n.col1[0]; c1[1] = n.col1[1]; c1[2] = n.col1[2]; c1[3] = n.col1[3]; fin1 = n.val1; }
+        if (n.in2 >= 0) { c2[0] = st[n.in2].r; c2[1] = st[n.in2].g; c2[2] = st[n.in2].b; c2[3] = st[n.in2].a; fin2 = st[n.in2].f; }
+        else { c2[0] = n.col2[0]; c2[1] = n.col2[1]; c2[2] = n.col2[2]; c2[3] = n.col2[3]; fin2 = n.val2; }
+        float o[4], of;
+        switch (n.mode) {
+            case 1: for (int k = 0; k < 4; ++k) o[k] = c1[k] + f2 * c2[k]; of = fin1 + f2 * fin2; break;                    // add
+            case 2: for (int k = 0; k < 4; ++k) o[k] = c1[k] * (f1 + f2 * c2[k]); of = fin1; break;                          // mult (sic: scalar = fin1)
+            case 3: for (int k = 0; k < 4; ++k) o[k] = c1[k] - f2 * c2[k]; of = fin1 - f2 * fin2; break;                    // sub
+            case 4: for (int k = 0; k < 4; ++k) o[k] = 1.f - (f1 + f2 * (1.f - c2[k])) * (1.f - c1[k]);
+                    of = (float)(1.0 - (double)((f1 + f2 * (1.f - fin2)) * (1.f - fin1))); break;                           // screen
+            case 6: for (int k = 0; k < 4; ++k) o[k] = f1 * c1[k] + f2 * fabsf(c1[k] - c2[k]); of = f1 * fin1 + f2 * fabsf(fin1 - fin2); break;   // diff
+            case 7: for (int k = 0; k < 4; ++k) { const float x = c2[k] * f2; o[k] = x < c1[k] ? x : c1[k]; }
+                    { const float x = fin2 * f2; of = x < fin1 ? x : fin1; } break;                                         // dark
+            case 8: for (int k = 0; k < 4; ++k) { const float x = c2[k] * f2; o[k] = x > c1[k] ? x : c1[k]; }
+                    { const float x = fin2 * f2; of = x > fin1 ? x : fin1; } break;                                         // light
+            case 9: for (int k = 0; k < 4; ++k)
+                        o[k] = (c1[k] < 0.5f) ? c1[k] * (f1 + 2.0f * f2 * c2[k]) : (float)(1.0 - ((double)f1 + (double)(2.0f * f2) * (1.0 - (double)c2[k])) * (1.0 - (double)c1[k]));
+                    of = (fin1 < 0.5f) ? fin1 * (f1 + 2.0f * f2 * fin2) : (float)(1.0 - ((double)f1 + (double)(2.0f * f2) * (1.0 - (double)fin2)) * (1.0 - (double)fin1));
+                    break;                                                                                                  // overlay
+            default: for (int k = 0; k < 4; ++k) o[k] = f1 * c1[k] + f2 * c2[k]; of = f1 * fin1 + f2 * fin2; break;         // mix (also mode 5: no case in the factory)
+        }
+        r.r = o[0]; r.g = o[1]; r.b = o[2]; r.a = o[3]; r.f = of;
+    } else {                                          // layerNode_t::eval (layernode.cc:12-110)
+        float rcol[4], texcolor[4] = {0.f, 0.f, 0.f, 0.f};
+        float rval, Tin = 0.f, Ta = 1.f, stencilTin;
+        if (n.upper >= 0) { rcol[0] = st[n.upper].r; rcol[1] = st[n.upper].g; rcol[2] = st[n.upper].b; rcol[3] = st[n.upper].a; rval = st[n.upper].f; }
+        else { rcol[0] = n.upperCol[0]; rcol[1] = n.upperCol[1]; rcol[2] = n.upperCol[2]; rcol[3] = n.upperCol[3]; rval = n.upperVal; }
+        stencilTin = rcol[3];
+        bool TEX_RGB = n.colorInput != 0;
+        if (n.colorInput) { texcolor[0] = st[n.input].r; texcolor[1] = st[n.input].g; texcolor[2] = st[n.input].b; texcolor[3] = st[n.input].a; Ta = texcolor[3]; }
+        else Tin = st[n.input].f;
+        if (n.texflag & TXF_RGBTOINT) { Tin = col2bri(texcolor); TEX_RGB = false; }
+        if (n.texflag & TXF_NEGATIVE) {
+            if (TEX_RGB) for (int k = 0; k < 4; ++k) texcolor[k] = 1.f - texcolor[k];
+            Tin = 1.f - Tin;
+        }
+        if (n.texflag & TXF_STENCIL) {
+            float fact;
+            if (TEX_RGB) { fact = Ta; Ta *= stencilTin; stencilTin *= fact; }
+            else { fact = Tin; Tin *= stencilTin; stencilTin *= fact; }
+        }
+        if (n.doColor) {
+            if (!TEX_RGB) { texcolor[0] = n.defCol.x; texcolor[1] = n.defCol.y; texcolor[2] = n.defCol.z; texcolor[3] = 1.f; }
+            else Tin = Ta;
+            Tin = Tin > 1.f ? 1.f : (Tin < 0.f ? 0.f : Tin);               // inRange(1, 0, Tin)
+            float res[3];
+            texture_rgb_blend(texcolor, rcol, Tin, stencilTin * n.colfac, n.mode, res);
+            rcol[0] = fmaxf_(0.f, res[0]); rcol[1] = fmaxf_(0.f, res[1]); rcol[2] = fmaxf_(0.f, res[2]);   // clampRGB0; alpha of the blend is 1 (color_t -> colorA_t)
+            rcol[3] = 1.f;
+        }
+        if (n.doScalarL) {
+            if (TEX_RGB) {
+                if (n.useAlpha) { Tin = Ta; if (n.texflag & TXF_NEGATIVE) Tin = 1.f - Tin; }
+                else Tin = col2bri(texcolor);
+            }
+            rval = texture_value_blend(n.defVal, rval, Tin, stencilTin * n.valfac, n.mode, !n.doScalarL);
+            if (rval < 0.f) rval = 0.f;
+        }
+        rcol[3] = stencilTin;
+        r.r = rcol[0]; r.g = rcol[1]; r.b = rcol[2]; r.a = rcol[3]; r.f = rval;
+    }
+    st[self] = r;
+}
+
+}  // namespace yb

@@ -189,6 +189,11 @@ YB_D int pick_one_light(int n, int lightNum)
 #include "yb_shade.inc"
 #undef YB_SHADE_NS
 #undef YB_EXT
+#define YB_SHADE_NS shade_nodes
+#define YB_EXT 2
+#include "yb_shade.inc"
+#undef YB_SHADE_NS
+#undef YB_EXT
 
 // ---- shading order.  After the first wave the tasks of one warp take very different code paths (hit / miss, the
 // light estimateOneDirectLight picks): measured 8 of 32 lanes active.  Tasks are binned by a small key so that warps
@@ -491,12 +496,13 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 }
         }
         // ---- worst-case fan-out per task, from the integrator and the materials present
-        bool anyGlossy = false, anyRoughGlass = false, extShade = false; int specChildren = 0;
+        bool anyGlossy = false, anyRoughGlass = false, extShade = false, nodeShade = false; int specChildren = 0;
         for (size_t i = 0; i < c.materials.size(); ++i) {
             const Material &m = c.materials[i];
             if (m.bsdfFlags & BSDF_GLOSSY) anyGlossy = true;
             if (m.type == MAT_ROUGH_GLASS) anyRoughGlass = true;     // two children per glossy sample
             if (m.type == MAT_ROUGH_GLASS || m.type == MAT_BLEND) extShade = true;
+            if (m.nNodes > 0) nodeShade = true;
             int sc_ = 0;
             if (m.type == MAT_GLASS || m.type == MAT_BLEND) sc_ = 2;
             else if (m.type == MAT_SHINYDIFFUSE) sc_ = (m.isMirror ? 1 : 0) + (m.isTransparent ? 1 : 0);
@@ -613,7 +619,9 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 tsd.start();
                 a.order = 0;
                 if (binShade && !firstWave) { bin_tasks((uint32_t)M, a, s); a.order = rb.order.p; }
-                if (extShade) shade_ext::k_shade((uint32_t)M, a, s); else shade_base::k_shade((uint32_t)M, a, s);
+                if (nodeShade) shade_nodes::k_shade((uint32_t)M, a, s);
+                else if (extShade) shade_ext::k_shade((uint32_t)M, a, s);
+                else shade_base::k_shade((uint32_t)M, a, s);
                 tsd.stop();
                 firstWave = false;
                 uint32_t cnt[4];

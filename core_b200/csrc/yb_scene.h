@@ -39,6 +39,8 @@ struct MeshObj {
     std::vector<int32_t> tri_idx;    // 3 per triangle: pa, pb, pc (already doubled for orco)
     std::vector<int32_t> tri_nidx;   // 3 per triangle: na, nb, nc (-1 = none)
     std::vector<uint32_t> tri_mat;   // material index per triangle
+    std::vector<float> uv_values;    // uv_t pairs (scene.cc:648-662)
+    std::vector<int32_t> uv_offsets; // 3 per triangle (scene.cc:628-646)
     bool has_orco, has_uv, is_smooth, normals_exported, visible, is_base;
     int n_uv_offsets;
     // instance (scene.cc:983-1008): base != 0 -> triangles come from *base transformed by objToWorld
@@ -85,6 +87,8 @@ struct Context {
     ParaMap params; std::list<ParaMap> eparams; ParaMap *cparams;
     // environment tables (environment.cc:189-479)
     std::vector<Material> materials; std::map<std::string, int> materialNames;
+    std::vector<Texture> textures; std::map<std::string, int> textureNames;
+    std::vector<ShaderNode> shaderNodes;
     std::vector<Light> lights; std::map<std::string, int> lightNames; std::vector<unsigned> lightObj;
     std::map<std::string, CameraDesc> cameras;
     std::map<std::string, BackgroundDesc> backgrounds;
@@ -100,6 +104,7 @@ struct Context {
     volatile int abortFlag;
     // device-side scene
     DevBuf<BvhNode> d_nodes; DevBuf<f4> d_tri_v; DevBuf<v3> d_tri_n; DevBuf<Material> d_materials; DevBuf<Light> d_lights;
+    DevBuf<Texture> d_textures; DevBuf<ShaderNode> d_shaderNodes; DevBuf<float> d_prim_uv; DevBuf<v3> d_prim_orco;
     DevBuf<f4> d_light_tris; DevBuf<float> d_light_cdf;   // mesh light emitters (yb_host.cc uploadTables)
     DevBuf<uint32_t> d_traceCounter;   // ray-fetch counter of the persistent traversal kernels
     DevBuf<f4> d_in_v; DevBuf<v3> d_in_n;             // flattened geometry in scene order (input of the build)
@@ -136,6 +141,8 @@ struct Context {
     // factories
     uintptr_t createLight(const char *name);
     uintptr_t createMaterial(const char *name);
+    uintptr_t createTexture(const char *name);
+    bool loadMaterialNodes(const char *name, Material &m, const char *const *slotKeys, const int *slotIds, int nSlots);
     uintptr_t createCamera(const char *name);
     uintptr_t createBackground(const char *name);
     uintptr_t createIntegrator(const char *name);

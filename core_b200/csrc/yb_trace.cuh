@@ -157,7 +157,10 @@ YB_HD bool bvh_traverse(const SceneDev &sc, v3 from, v3 dir, float tlo, float th
                     if (depth >= maxDepth) return true;
                     Surf sps;
                     tri_getSurface(sc, (int)ti, from + t * dir, u, v, sps);
-                    filt *= mat_getTransparency<1>(m, sps, dir);
+                    Material rmat;                      // shinydiffuse.cc:435-455 evaluates the nodes itself for shadow rays
+                    const Material *mp = &m;
+                    if (m.nNodes > 0) { TexPoint tp; tri_getTexPoint(sc, (int)ti, sps.P, u, v, sps.Ng, tp); mp = &mat_resolve<2>(sc, m, sps.P, sps.Ng, tp, rmat); }
+                    filt *= mat_getTransparency<1>(*mp, sps, dir);
                     ++depth;
                 }
             }

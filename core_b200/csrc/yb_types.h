@@ -50,6 +50,47 @@ struct Material {
     //     material table (sub-materials are leaf materials: a blend of blends is rejected at creation)
     int32_t blendOff1, blendOff2;
     float blendVal;
+    // --- nodeMaterial_t (nodematerial.cc:77-243): the material's shader nodes in evaluation order (allSorted) live at
+    //     [nodeBase, nodeBase + nNodes) of the scene's node table; slot[s] = index (relative to nodeBase) of the node bound to
+    //     shader slot s, -1 = the constant above is used.  emitStrength: shinydiffuse.cc:251-257 scales the diffuse NODE colour
+    int32_t nodeBase, nNodes;
+    int32_t slot[8];
+    float emitStrength;
+};
+enum ShaderSlot : int32_t { SLOT_DIFFUSE = 0, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT, SLOT_COUNT };
+#define YB_MAX_NODES 8               // nodes per material (creation fails beyond)
+
+// texture_t implementations evaluated on the device (src/textures/basictex.cc): rgb_cube, blend, clouds, marble, wood with the
+// default noise generator (newPerlin_t, noise.cc:161-183)
+enum TexType : int32_t { TEX_RGB_CUBE = 0, TEX_BLEND, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD };
+struct Texture {
+    int32_t type;
+    int32_t depth, hard, bias, wshape, rings;   // wshape: 0 sin, 1 saw, 2 tri
+    float size, turb, sharpness;
+    col3 color1, color2;
+};
+// shaderNode_t implementations (src/textures/basicnodes.cc, layernode.cc)
+enum NodeType : int32_t { NODE_TEXMAP = 0, NODE_VALUE, NODE_MIX, NODE_LAYER };
+enum : int32_t { TXC_UV = 0, TXC_GLOB, TXC_ORCO, TXC_TRAN };                     // texture_mapper texco (window / normal / ... rejected)
+enum : uint32_t { TXF_RGBTOINT = 1, TXF_STENCIL = 2, TXF_NEGATIVE = 4, TXF_ALPHAMIX = 8 };   // layernode.h:11
+struct ShaderNode {
+    int32_t type;
+    // texture_mapper (basicnodes.cc:96-160,236-304)
+    int32_t tex, texCoords, mapX, mapY, mapZ, doScalar;
+    v3 scale, offset;
+    float mtx[12];                   // first three rows of the 'transform' matrix (texco = transformed)
+    // value (col1, val1) and the mix family (basicnodes.cc:312-600): inputs are node indices relative to nodeBase or -1
+    float col1[4], col2[4];
+    float val1, val2, cfactor;
+    int32_t in1, in2, inFactor, mode;
+    // layer (layernode.cc:12-110,190-225): input / upper layer, flags and factors
+    int32_t input, upper;
+    uint32_t texflag;
+    int32_t doColor, doScalarL, colorInput, useAlpha;
+    float colfac, valfac, defVal;
+    col3 defCol;
+    float upperCol[4];
+    float upperVal;
 };
 
 enum LightType : int32_t { LIGHT_POINT = 0, LIGHT_SUN, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE, LIGHT_MESH };
@@ -132,6 +173,7 @@ enum : uint32_t {
     TRI_MAT_MASK = 0x000fffffu,
     TRI_SMOOTH = 1u << 20,            // mesh->is_smooth
     TRI_HAS_NA = 1u << 21, TRI_HAS_NB = 1u << 22, TRI_HAS_NC = 1u << 23,   // na/nb/nc >= 0 (triangle.cc:20-22)
+    TRI_HAS_UV = 1u << 24, TRI_HAS_ORCO = 1u << 25,                        // mesh->has_uv / has_orco (triangle.cc:28-48)
 };
 
 // 8-wide BVH node with child boxes quantised to 8 bits on a per-node power-of-two grid (80 B = 5 x 16 B).
@@ -154,6 +196,12 @@ struct SceneDev {
     const v3 *tri_n;                  // may be null
     const Material *materials;
     const Light *lights;
+    // textures / shader nodes; per-primitive texture coordinates in the ORIGINAL primitive order of scene.cc:760-781
+    // (tri_v[3 t].w): prim_uv = 6 floats {u1,v1,u2,v2,u3,v3}, prim_orco = the three orco points; null when no mesh has them
+    const Texture *textures;
+    const ShaderNode *shaderNodes;
+    const float *prim_uv;
+    const v3 *prim_orco;
     int32_t nLights, nMaterials;
     uint32_t nTris, nNodes;
     v3 boundLo, boundHi;

@@ -51,11 +51,20 @@ def _set(yi, k, v):
         raise TypeError(f"param {k}: {v!r}")
 
 
-def create(yi, kind, name, **params):
-    """kind in light|material|camera|background|integrator; colours are 4-tuples, points 3-tuples."""
+def create(yi, kind, name, nodes=None, **params):
+    """kind in light|material|texture|camera|background|integrator; colours are 4-tuples, points 3-tuples.
+    nodes: list of shader-node parameter dicts (each with name / type / ...), sent as the material's parameter list
+    (paramsPushList per node + paramsEndList, what the XML <list_element> children become)."""
     yi.paramsClearAll()
     for k, v in params.items():
         _set(yi, k, v)
+    if nodes:                                   # like the exporters: one paramsPushList per node (paramsStartList on an empty
+        for nd in nodes:                        # list dereferences eparams->back() in the reference, yafrayinterface.cc:230-235)
+            yi.paramsPushList()
+            _set(yi, "element", "shader_node")
+            for k, v in nd.items():
+                _set(yi, k, v)
+        yi.paramsEndList()
     h = getattr(yi, "create" + kind.capitalize())(name)
     if not h:
         raise RuntimeError(f"create{kind.capitalize()}({name!r}, {params.get('type')!r}) failed")
@@ -77,6 +86,23 @@ def add_mesh(yi, verts, tris, mat, normals=None, smooth_angle=None, oid=None, bu
                 yi.addNormal(*[float(x) for x in normals[i]])
         for t in tris:
             assert yi.addTriangle(int(t[0]), int(t[1]), int(t[2]), mat)
+    assert yi.endTriMesh()
+    if smooth_angle is not None:
+        assert yi.smoothMesh(oid, smooth_angle)
+    return oid
+
+
+def add_mesh_uv_orco(yi, verts, tris, mat, orco, uv, normals=None, smooth_angle=None, oid=None):
+    """Mesh with original coordinates (has_orco) and one UV value per vertex (has_uv), through the single-item calls."""
+    oid = yi.getNextFreeID() if oid is None else oid
+    assert yi.startTriMesh(oid, len(verts), len(tris), True, True, 0)
+    for i, v in enumerate(verts):
+        yi.addVertex(float(v[0]), float(v[1]), float(v[2]), float(orco[i][0]), float(orco[i][1]), float(orco[i][2]))
+        if normals is not None:
+            yi.addNormal(*[float(x) for x in normals[i]])
+    ids = [yi.addUV(float(u), float(v)) for u, v in uv]
+    for t in tris:
+        assert yi.addTriangle(int(t[0]), int(t[1]), int(t[2]), ids[int(t[0])], ids[int(t[1])], ids[int(t[2])], mat)
     assert yi.endTriMesh()
     if smooth_angle is not None:
         assert yi.smoothMesh(oid, smooth_angle)
@@ -281,7 +307,7 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
 # ----------------------------------------------------------------------------- C4: glossy / coated / glass materials
 def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
                     integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None,
-                    extra_materials=None, order=None, emitters=None, **render_extra):
+                    extra_materials=None, order=None, emitters=None, textures=None, uv_orco=False, **render_extra):
     """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
     coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
     shinydiffuse; sun (1 degree, 4 samples) + point + area (8 samples) lights; pathtracing with 8 bounces
@@ -307,7 +333,9 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     M["shiny"] = create(yi, "material", "shiny", type="shinydiffusemat", color=(0.3, 0.5, 0.9, 1.0), diffuse_reflect=0.7,
                         specular_reflect=0.3, transparency=0.4, transmit_filter=0.8, fresnel_effect=True, IOR=1.6,
                         mirror_color=(1.0, 0.95, 0.9, 1.0), diffuse_brdf="oren_nayar", sigma=0.25)
-    for mname, mp in (extra_materials or []):   # e.g. rough_glass, blend_mat of two of the above
+    for tname, tp in (textures or []):          # textures must exist before the texture_mapper nodes that name them
+        create(yi, "texture", tname, **tp)
+    for mname, mp in (extra_materials or []):   # e.g. rough_glass, blend_mat of two of the above, node materials
         M[mname] = create(yi, "material", mname, **mp)
     order = order or ["glossy", "aniso", "coated", "glass", "gdiff", "glass2", "mirror", "shiny"]
     v0, f0 = icosphere(subdiv)
@@ -319,7 +347,12 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
         cy = 0.0 if i < 4 else 3.2
         r = 1.0 if i < 4 else 0.9
         V = (v0 * r + np.array([cx, cy, r + 0.02])).astype(np.float32)
-        add_mesh(yi, V, f0, M[name], normals=v0.astype(np.float32), smooth_angle=181.0)
+        if uv_orco:                             # orco = unit-sphere position, UV = longitude / latitude of the vertex
+            uv = np.stack([np.arctan2(v0[:, 1], v0[:, 0]) / (2 * np.pi) + 0.5, np.arccos(np.clip(v0[:, 2], -1, 1)) / np.pi], 1)
+            add_mesh_uv_orco(yi, V, f0, M[name], orco=v0.astype(np.float32), uv=uv.astype(np.float32),
+                             normals=v0.astype(np.float32), smooth_angle=181.0)
+        else:
+            add_mesh(yi, V, f0, M[name], normals=v0.astype(np.float32), smooth_angle=181.0)
     for e in (emitters or []):              # visible emitter meshes for mesh lights: dict(id, centre, radius, subdiv, material params)
         M[e["name"]] = create(yi, "material", e["name"], **e["material"])
         ve, fe = icosphere(e.get("subdiv", 1))

@@ -22,6 +22,54 @@ _MESHLIGHT = dict(
             ("ml2", dict(type="meshlight", object=702, color=(0.6, 0.8, 1.0, 1.0), power=9.0, samples=2, double_sided=True)),
             ("pt", dict(type="pointlight", color=(0.9, 0.9, 1.0, 1.0), power=6.0, **{"from": (-4.0, -3.0, 5.0)}))])
 
+def _mapper(name, tex, texco="orco", scale=(1.0, 1.0, 1.0), offset=(0.0, 0.0, 0.0), **kw):
+    return dict(name=name, type="texture_mapper", texture=tex, texco=texco, scale=scale, offset=offset, **kw)
+
+
+# procedural textures (newperlin noise) through texture_mapper / value / mix / layer nodes on every node slot of the materials
+_TEXTURED = dict(
+    uv_orco=True,
+    textures=[("tclouds", dict(type="clouds", depth=3, size=2.5, color1=(0.9, 0.3, 0.1, 1.0), color2=(0.1, 0.3, 0.9, 1.0))),
+              ("tclouds_hard", dict(type="clouds", depth=2, size=4.0, hard=True, bias="negative")),
+              ("tmarble", dict(type="marble", depth=2, size=1.5, turbulence=4.0, sharpness=2.5, shape="saw",
+                               color1=(0.95, 0.95, 0.9, 1.0), color2=(0.2, 0.25, 0.3, 1.0))),
+              ("twood", dict(type="wood", depth=2, size=3.0, turbulence=2.0, wood_type="rings", shape="tri",
+                             color1=(0.55, 0.35, 0.15, 1.0), color2=(0.25, 0.12, 0.05, 1.0))),
+              ("tcube", dict(type="rgb_cube")),
+              ("tblend", dict(type="blend"))],
+    extra_materials=[
+        ("m_clouds", dict(type="shinydiffusemat", color=(1.0, 1.0, 1.0, 1.0), diffuse_reflect=0.9, diffuse_shader="map",
+                          nodes=[_mapper("map", "tclouds", "orco", scale=(1.5, 1.5, 1.5))])),
+        ("m_layer", dict(type="shinydiffusemat", color=(0.8, 0.8, 0.8, 1.0), diffuse_reflect=0.8, specular_reflect=0.1,
+                         mirror_color=(1.0, 0.9, 0.8, 1.0), diffuse_shader="lay2", mirror_shader="mir", mirror_color_shader="mcol",
+                         nodes=[_mapper("marb", "tmarble", "global", scale=(0.7, 0.7, 0.7), offset=(0.1, 0.2, 0.3)),
+                                dict(name="lay1", type="layer", input="marb", mode=0, colfac=0.85, upper_color=(0.8, 0.2, 0.2, 1.0),
+                                     upper_value=0.3, do_color=True, do_scalar=True, valfac=0.6, def_val=0.9),
+                                _mapper("cl", "tclouds_hard", "orco", scale=(2.0, 2.0, 2.0)),
+                                dict(name="lay2", type="layer", input="cl", upper_layer="lay1", mode=2, colfac=0.7, color_input=False,
+                                     def_col=(0.2, 0.8, 0.3, 1.0), stencil=True, negative=True),
+                                _mapper("mir", "twood", "orco", scale=(1.2, 1.2, 1.2)),
+                                dict(name="mcol", type="value", color=(0.9, 0.8, 0.5, 1.0), alpha=1.0, scalar=0.4)])),
+        ("m_glossy", dict(type="glossy", color=(0.9, 0.6, 0.3, 1.0), diffuse_color=(0.5, 0.2, 0.1, 1.0), diffuse_reflect=0.5,
+                          glossy_reflect=0.7, exponent=60.0, as_diffuse=False, glossy_shader="gmix", diffuse_shader="dwood",
+                          glossy_reflect_shader="grefl",
+                          nodes=[_mapper("cube", "tcube", "uv"),
+                                 dict(name="gmix", type="mix", mode=2, input1="cube", color2=(0.9, 0.8, 0.3, 1.0), value=0.6),
+                                 _mapper("dwood", "twood", "global", scale=(0.5, 0.5, 0.5), proj_x=2, proj_y=3, proj_z=1),
+                                 _mapper("grefl", "tblend", "uv")])),
+        ("m_coated", dict(type="coated_glossy", color=(0.8, 0.2, 0.2, 1.0), diffuse_color=(0.6, 0.1, 0.1, 1.0), diffuse_reflect=0.5,
+                          glossy_reflect=0.6, exponent=80.0, IOR=1.4, as_diffuse=False, diffuse_shader="ov",
+                          nodes=[_mapper("a", "tmarble", "orco"), _mapper("b", "tclouds", "uv", scale=(3.0, 3.0, 1.0)),
+                                 dict(name="ov", type="mix", mode=9, input1="a", input2="b", value=0.7)])),
+        ("m_glass", dict(type="glass", IOR=1.5, filter_color=(0.8, 1.0, 0.9, 1.0), transmit_filter=0.6, fake_shadows=True,
+                         mirror_color_shader="mc", nodes=[_mapper("mc", "tclouds", "orco", scale=(2.0, 2.0, 2.0))])),
+        ("m_transp", dict(type="shinydiffusemat", color=(0.9, 0.7, 0.3, 1.0), diffuse_reflect=0.6, transparency=0.2, transmit_filter=0.7,
+                          transparency_shader="tr", translucency_shader="tl", translucency=0.1,
+                          nodes=[_mapper("tr", "tblend", "uv", scale=(2.0, 1.0, 1.0)),
+                                 _mapper("c2", "tclouds_hard", "orco"),
+                                 dict(name="tl", type="mix", mode=6, input1="c2", color2=(0.5, 0.5, 0.5, 1.0), factor="tr")]))],
+    order=["m_clouds", "m_layer", "m_glossy", "m_glass", "m_coated", "m_transp", "mirror", "gdiff"])
+
 IMAGE_CASES = {
     # BASELINE.json configs[0] (reduced): Cornell box, shinydiffuse + mirror component, area light, directlighting
     "c1_cornell_direct": (scenes.cornell_box, dict(width=64, height=64, spp=4, light_samples=4, mirror_box=True)),
@@ -62,6 +110,11 @@ IMAGE_CASES = {
     # (path case on diffuse-only spheres: with glossy / specular recursion onto VISIBLE emitter geometry the reference's
     # state.includeLights leaks between sibling calls in traversal order - DESIGN.md section 7, first deviation)
     "c4_meshlight_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4, order=["gdiff", "ground"] * 4, **_MESHLIGHT)),
+    # shader nodes + procedural textures on UV / orco / global coordinates
+    "c4_textured_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_TEXTURED)),
+    "c4_textured_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4, **_TEXTURED)),
+    "c4_textured_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
+                                                         integ_params=dict(transpShad=True, shadowDepth=4), **_TEXTURED)),
     # depth of field with a polygonal lens (perspectiveCam_t::sampleTSD / biasDist)
     "c4_materials_dof_hexagon": (scenes.materials_scene, dict(width=64, height=36, spp=3, integrator="directlighting",
                                                               cam_params=dict(aperture=0.15, dof_distance=10.0, bokeh_type="hexagon",

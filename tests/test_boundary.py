@@ -74,10 +74,19 @@ class TestHostLogic:
         assert yi.createMaterial("bl") == 0 and "does not exist" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "rough_glass"); yi.paramsSetFloat("dispersion_power", 0.2)
         assert yi.createMaterial("rgd") == 0 and "dispersion" in yi.lastError()
-        yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat"); yi.paramsSetString("diffuse_shader", "tex")
-        assert yi.createMaterial("withnodes") == 0 and "shader" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat"); yi.paramsSetString("bump_shader", "tex")
+        assert yi.createMaterial("withbump") == 0 and "bump" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat"); yi.paramsSetString("diffuse_shader", "n")
+        yi.paramsPushList(); yi.paramsSetString("element", "shader_node"); yi.paramsSetString("name", "n")
+        yi.paramsSetString("type", "texture_mapper"); yi.paramsSetString("texture", "missing"); yi.paramsEndList()
+        assert yi.createMaterial("withnodes") == 0 and "does not exist" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "voronoi")
+        assert yi.createTexture("vor") == 0 and "not supported" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "clouds"); yi.paramsSetString("noise_type", "blender")
+        assert yi.createTexture("cl") == 0 and "noise_type" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "glass"); yi.paramsSetFloat("dispersion_power", 0.1)
         assert yi.createMaterial("disp") == 0
+        yi.paramsClearAll()
         assert yi.createTexture("t") == 0 and yi.createVolumeRegion("v") == 0
         yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat")
         assert yi.createMaterial("dup") != 0 and yi.createMaterial("dup") == 0     # name clash (environment.cc:226)
