@@ -49,6 +49,8 @@ class XmlWriter:
     def startTriMesh(self, id, vertices, triangles, hasOrco, hasUV=False, type=0):
         self._cur_mat = None
         self._mesh_has_uv = bool(hasUV)
+        self._n_uv = 0          # addUV returns the index of the value inside the mesh (scene.cc:648-662)
+        self._n_vert = 0
         self._f.write('\n<mesh id="%d" vertices="%d" faces="%d" has_orco="%s" has_uv="%s" type="%d">\n' % (
             id, vertices, triangles, "true" if hasOrco else "false", "true" if hasUV else "false", type))
         return True
@@ -86,7 +88,8 @@ class XmlWriter:
 
     def addUV(self, u, v):
         self._f.write('\t<uv u="%s" v="%s"/>\n' % (self._n(u), self._n(v)))
-        return 0
+        self._n_uv += 1
+        return self._n_uv - 1
 
     def addVertices(self, xyz, normals=None):
         xyz = np.asarray(xyz, dtype=np.float32)

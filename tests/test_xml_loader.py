@@ -14,7 +14,7 @@ from core_b200.xmlwriter import XmlWriter
 ROOT = refapi.ROOT
 EMU_XML = os.path.join(ROOT, "tests", "emu", "yb200-xml-emu")
 GPU_XML = os.path.join(ROOT, "core_b200", "bin", "yb200-xml")
-NAMES = ["c1_cornell_direct", "c2_field_flat_direct", "c4_materials_path"]
+NAMES = ["c1_cornell_direct", "c2_field_flat_direct", "c4_materials_path", "c4_textured_direct", "c4_meshlight_direct"]
 
 
 def _write_scene(name, path, digits=None):
