@@ -1059,10 +1059,22 @@ template <int EXT> YB_HD float mat_getAlpha(const Material &m, const MatDat &d, 
 // (EXT >= 2 builds only; materials without nodes, and every material in the other builds, come back untouched).
 // Slot use per material: shinydiffuse.cc:82-98,242-256,305-329,407,427,447-453; glossy.cc:93,164-169; coatedglossy.cc:115,186-190;
 // glass.cc:123,168,240; roughglass.cc:132.
-template <int EXT> YB_HD const Material &mat_resolve(const SceneDev &sc, const Material &m, v3 P, v3 Ng, const TexPoint &tp, Material &tmp)
+// sp != 0: the call stands for initBSDF, which first bumps the shading frame (nodeMaterial_t::evalBump, nodematerial.cc:132-139 +
+// material_t::applyBump, material.cc:68-75); getTransparency for shadow rays (sp == 0) does not.
+template <int EXT> YB_HD const Material &mat_resolve(const SceneDev &sc, const Material &m, v3 P, v3 Ng, const TexPoint &tp, Material &tmp, Surf *sp = 0)
 {
     if (EXT < 2 || m.nNodes <= 0) return m;
     NodeRes st[YB_MAX_NODES];
+    if (sp && m.slot[SLOT_BUMP] >= 0) {
+        for (int i = 0; i < m.nNodes && i < YB_MAX_NODES; ++i)
+            if (m.bumpMask & (1u << i)) node_evalDerivative(sc.shaderNodes[m.nodeBase + i], sc.textures, P, sp->NU, sp->NV, tp, st, i);
+        const float du = st[m.slot[SLOT_BUMP]].r, dv = st[m.slot[SLOT_BUMP]].g;
+        sp->NU += du * sp->N;
+        sp->NV += dv * sp->N;
+        sp->N = normalize(cross(sp->NU, sp->NV));
+        sp->NU = normalize(sp->NU);
+        sp->NV = normalize(cross(sp->N, sp->NU));
+    }
     for (int i = 0; i < m.nNodes && i < YB_MAX_NODES; ++i) node_eval(sc.shaderNodes[m.nodeBase + i], sc.textures, P, Ng, tp, st, i);
     tmp = m;
     tmp.nNodes = 0;

@@ -356,8 +356,8 @@ uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 +
 bool Context::loadMaterialNodes(const char *name, Material &m, const char *const *slotKeys, const int *slotIds, int nSlots)
 {
     m.nodeBase = (int32_t)shaderNodes.size(); m.nNodes = 0;
-    for (int i = 0; i < SLOT_COUNT + 1 && i < 8; ++i) m.slot[i] = -1;
-    if (params.has("bump_shader")) return fail("material '" + std::string(name) + "': bump_shader (bump / normal mapping) is not supported");
+    for (int i = 0; i < 8; ++i) m.slot[i] = -1;
+    m.bumpMask = 0;
     if (eparams.empty()) {
         for (int k = 0; k < nSlots; ++k) { std::string nm; if (params.get(slotKeys[k], nm)) warn("Shader node " + std::string(slotKeys[k]) + " '" + nm + "' does not exist!"); }
         return true;
@@ -395,6 +395,8 @@ bool Context::loadMaterialNodes(const char *name, Material &m, const char *const
             p.get("proj_x", map[0]); p.get("proj_y", map[1]); p.get("proj_z", map[2]);
             for (int i = 0; i < 3; ++i) map[i] = std::min(3, std::max(0, map[i]));
             n.mapX = map[0]; n.mapY = map[1]; n.mapZ = map[2]; n.scale = scale; n.offset = 2.f * offset; n.doScalar = scalar;
+            n.dU = n.dV = 0.0002f;                                           // setup(): procedural textures step
+            n.bumpStr = (bump / length(scale)) / 100.0f;
             const float ident[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
             memcpy(n.mtx, ident, sizeof(ident));
             std::map<std::string, std::vector<float> >::const_iterator mi = p.mdicc.find("transform");
@@ -493,6 +495,15 @@ bool Context::loadMaterialNodes(const char *name, Material &m, const char *const
     }
     m.nNodes = (int32_t)order.size();
     for (size_t k = 0; k < roots.size(); ++k) m.slot[rootSlot[k]] = newIndex[roots[k].second];
+    if (m.slot[SLOT_BUMP] >= 0) {           // getNodeList(bumpS, bumpNodes): the bump root and everything it depends on
+        std::vector<int> todo(1, order[m.slot[SLOT_BUMP]]);
+        while (!todo.empty()) {
+            const int n = todo.back(); todo.pop_back();
+            if (m.bumpMask & (1u << newIndex[n])) continue;
+            m.bumpMask |= 1u << newIndex[n];
+            for (size_t k = 0; k < deps[n].size(); ++k) todo.push_back(deps[n][k]);
+        }
+    }
     return true;
 }
 
@@ -532,9 +543,9 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         }
         m.emitStrength = emit;
         {
-            static const char *const keys[] = {"diffuse_shader", "mirror_color_shader", "mirror_shader", "transparency_shader", "translucency_shader"};
-            static const int ids[] = {SLOT_DIFFUSE, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY};
-            if (!loadMaterialNodes(name, m, keys, ids, 5)) { shaderNodes.resize(nodesBefore); return 0; }
+            static const char *const keys[] = {"diffuse_shader", "mirror_color_shader", "mirror_shader", "transparency_shader", "translucency_shader", "bump_shader"};
+            static const int ids[] = {SLOT_DIFFUSE, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY, SLOT_BUMP};
+            if (!loadMaterialNodes(name, m, keys, ids, 6)) { shaderNodes.resize(nodesBefore); return 0; }
         }
         const bool shMirror = m.slot[SLOT_MIRROR] >= 0, shTransp = m.slot[SLOT_TRANSPARENCY] >= 0, shTransl = m.slot[SLOT_TRANSLUCENCY] >= 0;
         // config() (shinydiffuse.cc:27-73): a bound shader switches the component on and leaves `acc` alone
@@ -581,9 +592,9 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
             m.orenNayar = 1;
         }
         {
-            static const char *const keys[] = {"diffuse_shader", "glossy_shader", "glossy_reflect_shader"};
-            static const int ids[] = {SLOT_DIFFUSE, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT};
-            if (!loadMaterialNodes(name, m, keys, ids, 3)) { shaderNodes.resize(nodesBefore); return 0; }
+            static const char *const keys[] = {"diffuse_shader", "glossy_shader", "glossy_reflect_shader", "bump_shader"};
+            static const int ids[] = {SLOT_DIFFUSE, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT, SLOT_BUMP};
+            if (!loadMaterialNodes(name, m, keys, ids, 4)) { shaderNodes.resize(nodesBefore); return 0; }
         }
         const uint32_t glossyFlags = as_diff ? (BSDF_DIFFUSE | BSDF_REFLECT) : (BSDF_GLOSSY | BSDF_REFLECT);
         if (coated) {
@@ -603,9 +614,9 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         if (disp_power > 0.0) { fail("glass '" + std::string(name) + "': dispersion is not supported"); return 0; }
         if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
         {
-            static const char *const keys[] = {"mirror_color_shader"};
-            static const int ids[] = {SLOT_MIRROR_COLOR};
-            if (!loadMaterialNodes(name, m, keys, ids, 1)) { shaderNodes.resize(nodesBefore); return 0; }
+            static const char *const keys[] = {"mirror_color_shader", "bump_shader"};
+            static const int ids[] = {SLOT_MIRROR_COLOR, SLOT_BUMP};
+            if (!loadMaterialNodes(name, m, keys, ids, 2)) { shaderNodes.resize(nodesBefore); return 0; }
         }
         m.type = MAT_GLASS;
         m.ior = (float)IOR;
@@ -621,9 +632,9 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("rough_glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
         alpha = std::max(1e-4f, std::min(alpha * 0.5f, 1.f));
         {
-            static const char *const keys[] = {"mirror_color_shader"};
-            static const int ids[] = {SLOT_MIRROR_COLOR};
-            if (!loadMaterialNodes(name, m, keys, ids, 1)) { shaderNodes.resize(nodesBefore); return 0; }
+            static const char *const keys[] = {"mirror_color_shader", "bump_shader"};
+            static const int ids[] = {SLOT_MIRROR_COLOR, SLOT_BUMP};
+            if (!loadMaterialNodes(name, m, keys, ids, 2)) { shaderNodes.resize(nodesBefore); return 0; }
         }
         m.type = MAT_ROUGH_GLASS;
         m.ior = IOR; m.rgAlpha2 = alpha * alpha;

@@ -16,9 +16,18 @@
 #if defined(__CUDACC__) && !defined(YB_HOSTEMU)
 #define YB_HD __host__ __device__ __forceinline__
 #define YB_D __device__ __forceinline__
+// large device functions shared by several call sites of the shade kernel.  Out-of-line (-DYB_OUTLINE) shrinks k_shade from
+// 70 k to 44 k SASS instructions but was measured 5x SLOWER on B200 (shade 108 -> 590 ms per frame: the call ABI pins the
+// surface point, material data and sample state in local memory), so everything stays inlined.
+#ifdef YB_OUTLINE
+#define YB_D_BIG static __device__ __noinline__
+#else
+#define YB_D_BIG __device__ __forceinline__
+#endif
 #else
 #define YB_HD inline
 #define YB_D inline
+#define YB_D_BIG inline
 #endif
 
 namespace yb {

@@ -143,23 +143,53 @@ YB_HD float texture_value_blend(float tex, float out, float fact, float facg, in
     }
 }
 
+// textureMapper_t::getCoords (basicnodes.cc:121-139) and doMapping (:96-119)
+YB_HD v3 texmap_coords(const ShaderNode &n, v3 P, const TexPoint &tp)
+{
+    switch (n.texCoords) {
+        case TXC_UV: return v3(tp.U, tp.V, 0.f);
+        case TXC_ORCO: return tp.orcoP;
+        case TXC_TRAN: return v3(n.mtx[0] * P.x + n.mtx[1] * P.y + n.mtx[2] * P.z + n.mtx[3], n.mtx[4] * P.x + n.mtx[5] * P.y + n.mtx[6] * P.z + n.mtx[7],
+                                 n.mtx[8] * P.x + n.mtx[9] * P.y + n.mtx[10] * P.z + n.mtx[11]);
+        default: return P;
+    }
+}
+YB_HD v3 texmap_doMapping(const ShaderNode &n, v3 texpt)
+{
+    if (n.texCoords == TXC_UV) texpt = v3(2.0f * texpt.x - 1.0f, 2.0f * texpt.y - 1.0f, texpt.z);
+    const float texmap[4] = {0.f, texpt.x, texpt.y, texpt.z};
+    texpt = v3(texmap[n.mapX], texmap[n.mapY], texmap[n.mapZ]);
+    // tube / sphere / cube projections apply to discrete (image) textures only (basicnodes.cc:270): none supported yet
+    return mul(texpt, n.scale) + n.offset;
+}
+// shaderNode_t::evalDerivative for bump mapping: texture_mapper on a procedural (non-discrete) texture (basicnodes.cc:218-232),
+// layer (layernode.cc:118-146); every other node type keeps the base-class zero (shader.h:83-84)
+YB_HD void node_evalDerivative(const ShaderNode &n, const Texture *textures, v3 P, v3 NU, v3 NV, const TexPoint &tp, NodeRes *st, int self)
+{
+    NodeRes r; r.r = r.g = r.b = r.a = r.f = 0.f;
+    if (n.type == NODE_TEXMAP) {
+        const v3 texpt = texmap_coords(n, P, tp);
+        const Texture &t = textures[n.tex];
+        const v3 i0 = texmap_doMapping(n, texpt - n.dU * NU), i1 = texmap_doMapping(n, texpt + n.dU * NU);
+        const v3 j0 = texmap_doMapping(n, texpt - n.dV * NV), j1 = texmap_doMapping(n, texpt + n.dV * NV);
+        float du = (tex_getFloat(t, i0) - tex_getFloat(t, i1)) / n.dU;
+        float dv = (tex_getFloat(t, j0) - tex_getFloat(t, j1)) / n.dV;
+        r.r = du * n.bumpStr; r.g = dv * n.bumpStr;
+    } else if (n.type == NODE_LAYER) {
+        float rdu = 0.f, rdv = 0.f, stencilTin = 1.f;
+        if (n.upper >= 0) { rdu = st[n.upper].r; rdv = st[n.upper].g; stencilTin = st[n.upper].a; }
+        float tdu = st[n.input].r, tdv = st[n.input].g;
+        if (n.texflag & TXF_NEGATIVE) { tdu = -tdu; tdv = -tdv; }
+        r.r = rdu + tdu; r.g = rdv + tdv; r.a = stencilTin;
+    }
+    st[self] = r;
+}
+
 YB_HD void node_eval(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, const TexPoint &tp, NodeRes *st, int self)
 {
     NodeRes r; r.r = r.g = r.b = r.a = r.f = 0.f;
-    if (n.type == NODE_TEXMAP) {                      // textureMapper_t::getCoords + doMapping + eval
-        v3 texpt;
-        switch (n.texCoords) {
-            case TXC_UV: texpt = v3(tp.U, tp.V, 0.f); break;
-            case TXC_ORCO: texpt = tp.orcoP; break;
-            case TXC_TRAN: texpt = v3(n.mtx[0] * P.x + n.mtx[1] * P.y + n.mtx[2] * P.z + n.mtx[3], n.mtx[4] * P.x + n.mtx[5] * P.y + n.mtx[6] * P.z + n.mtx[7],
-                                      n.mtx[8] * P.x + n.mtx[9] * P.y + n.mtx[10] * P.z + n.mtx[11]); break;
-            default: texpt = P; break;
-        }
-        if (n.texCoords == TXC_UV) texpt = v3(2.0f * texpt.x - 1.0f, 2.0f * texpt.y - 1.0f, texpt.z);
-        const float texmap[4] = {0.f, texpt.x, texpt.y, texpt.z};
-        texpt = v3(texmap[n.mapX], texmap[n.mapY], texmap[n.mapZ]);
-        // tube / sphere / cube projections apply to discrete (image) textures only (basicnodes.cc:270): none supported yet
-        texpt = mul(texpt, n.scale) + n.offset;
+    if (n.type == NODE_TEXMAP) {                      // textureMapper_t::eval
+        const v3 texpt = texmap_doMapping(n, texmap_coords(n, P, tp));
         const Texture &t = textures[n.tex];
         float c[4];
         tex_getColor(t, texpt, c);

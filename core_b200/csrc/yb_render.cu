@@ -153,14 +153,19 @@ YB_KERNEL(k_trace_shadow, RenderArgs)
 }
 
 // ------------------------------------------------------------------------------------------------ queues
-YB_D void push_shadow(const RenderArgs &a, const Ray &r, col3 c, uint32_t sid)
+// the shadow queue as three words, so that out-of-line functions take it by value instead of a reference to the kernel's
+// parameter block (a reference would make every thread copy the 2 KB RenderArgs to local memory)
+struct ShadowQ { ShadowTask *shadow; uint32_t *counters; uint32_t shadowCap; };
+YB_D ShadowQ shadow_q(const RenderArgs &a) { ShadowQ q; q.shadow = a.shadow; q.counters = a.counters; q.shadowCap = a.shadowCap; return q; }
+YB_D void push_shadow(const ShadowQ q, const Ray &r, col3 c, uint32_t sid)
 {
     if (isBlack(c)) return;                                   // contributes nothing either way
-    const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + 1, 1u);
-    if (i >= a.shadowCap) return;                             // cannot happen: the host sizes chunks for the worst case
+    const uint32_t i = YB_ATOMIC_ADD_U32(q.counters + 1, 1u);
+    if (i >= q.shadowCap) return;                             // cannot happen: the host sizes chunks for the worst case
     ShadowTask st; st.ray = r; st.c = c; st.sid = sid;
-    a.shadow[i] = st;
+    q.shadow[i] = st;
 }
+YB_D void push_shadow(const RenderArgs &a, const Ray &r, col3 c, uint32_t sid) { push_shadow(shadow_q(a), r, c, sid); }
 YB_D void push_task(const RenderArgs &a, const Task &t)
 {
     const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + 0, 1u);

@@ -56,8 +56,9 @@ struct Material {
     int32_t nodeBase, nNodes;
     int32_t slot[8];
     float emitStrength;
+    uint32_t bumpMask;               // nodes of the bump_shader tree (nodeMaterial_t::bumpNodes), bit i = node i of this material
 };
-enum ShaderSlot : int32_t { SLOT_DIFFUSE = 0, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT, SLOT_COUNT };
+enum ShaderSlot : int32_t { SLOT_DIFFUSE = 0, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT, SLOT_BUMP, SLOT_COUNT };
 #define YB_MAX_NODES 8               // nodes per material (creation fails beyond)
 
 // texture_t implementations evaluated on the device (src/textures/basictex.cc): rgb_cube, blend, clouds, marble, wood with the
@@ -78,6 +79,7 @@ struct ShaderNode {
     // texture_mapper (basicnodes.cc:96-160,236-304)
     int32_t tex, texCoords, mapX, mapY, mapZ, doScalar;
     v3 scale, offset;
+    float bumpStr, dU, dV;           // textureMapper_t::setup (basicnodes.cc:12-38): step 0.0002, bump_strength / |scale| / 100
     float mtx[12];                   // first three rows of the 'transform' matrix (texco = transformed)
     // value (col1, val1) and the mix family (basicnodes.cc:312-600): inputs are node indices relative to nodeBase or -1
     float col1[4], col2[4];
