@@ -74,8 +74,9 @@ class TestHostLogic:
         assert yi.createMaterial("bl") == 0 and "does not exist" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "rough_glass"); yi.paramsSetFloat("dispersion_power", 0.2)
         assert yi.createMaterial("rgd") == 0 and "dispersion" in yi.lastError()
-        yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat"); yi.paramsSetString("bump_shader", "tex")
-        assert yi.createMaterial("withbump") == 0 and "bump" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "blend_mat"); yi.paramsSetString("material1", "m1"); yi.paramsSetString("material2", "m1")
+        yi.paramsSetString("mask", "node")
+        assert yi.createMaterial("masked") == 0
         yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat"); yi.paramsSetString("diffuse_shader", "n")
         yi.paramsPushList(); yi.paramsSetString("element", "shader_node"); yi.paramsSetString("name", "n")
         yi.paramsSetString("type", "texture_mapper"); yi.paramsSetString("texture", "missing"); yi.paramsEndList()
