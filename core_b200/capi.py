@@ -81,6 +81,7 @@ _PRODUCT_ONLY = {
     "render_film": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "render_film_pass": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "film_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "register_image": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "depth_film": (C.c_void_p, []),
     "depth_resolve": (C.c_int, [C.c_void_p, C.c_void_p]),
     "get_stats": (C.c_int, [C.POINTER(Stats)]),

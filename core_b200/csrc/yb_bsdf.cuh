@@ -1067,7 +1067,7 @@ template <int EXT> YB_HD const Material &mat_resolve(const SceneDev &sc, const M
     NodeRes st[YB_MAX_NODES];
     if (sp && m.slot[SLOT_BUMP] >= 0) {
         for (int i = 0; i < m.nNodes && i < YB_MAX_NODES; ++i)
-            if (m.bumpMask & (1u << i)) node_evalDerivative(sc.shaderNodes[m.nodeBase + i], sc.textures, P, sp->NU, sp->NV, tp, st, i);
+            if (m.bumpMask & (1u << i)) node_evalDerivative(sc.shaderNodes[m.nodeBase + i], sc.textures, P, Ng, sp->NU, sp->NV, tp, st, i);
         const float du = st[m.slot[SLOT_BUMP]].r, dv = st[m.slot[SLOT_BUMP]].g;
         sp->NU += du * sp->N;
         sp->NV += dv * sp->N;

@@ -98,6 +98,12 @@ yb200_handle yb200_create_material(yb200_ctx *ctx, const char *n) { return CTX.c
 yb200_handle yb200_create_camera(yb200_ctx *ctx, const char *n) { return CTX.createCamera(n); }
 yb200_handle yb200_create_background(yb200_ctx *ctx, const char *n) { return CTX.createBackground(n); }
 yb200_handle yb200_create_integrator(yb200_ctx *ctx, const char *n) { return CTX.createIntegrator(n); }
+int yb200_register_image(yb200_ctx *ctx, const char *file_name, const float *rgba, int width, int height, int is_hdr)
+{
+    GUARD_BEGIN
+    return CTX.registerImage(file_name, rgba, width, height, is_hdr != 0) ? 1 : 0;
+    GUARD_END(0)
+}
 yb200_handle yb200_create_texture(yb200_ctx *ctx, const char *n) { GUARD_BEGIN return CTX.createTexture(n); GUARD_END(0) }
 yb200_handle yb200_create_volume_region(yb200_ctx *ctx, const char *n) { CTX.fail(std::string("createVolumeRegion('") + n + "'): participating media are not supported by the B200 path"); return 0; }
 

@@ -79,7 +79,7 @@ void Context::info(const std::string &msg) { if (verbosity >= 3) fprintf(stderr,
 void Context::clearAll()   // yafrayinterface.cc:47-64
 {
     params.clear(); eparams.clear(); cparams = &params;
-    materials.clear(); materialNames.clear(); textures.clear(); textureNames.clear(); shaderNodes.clear(); lights.clear(); lightNames.clear(); lightObj.clear();
+    materials.clear(); materialNames.clear(); textures.clear(); textureNames.clear(); texPixels.clear(); texPixOffset.clear(); shaderNodes.clear(); lights.clear(); lightNames.clear(); lightObj.clear();
     cameras.clear(); backgrounds.clear(); integrators.clear();
     meshes.clear(); curObj = 0; stateStack.clear(); stateStack.push_back(ST_READY);
     nextFreeID = INT_MAX; geomChanged = true; sceneReady = false; sceneStarted = false;
@@ -310,6 +310,67 @@ static bool has_shader_params(const ParaMap &p, const std::list<ParaMap> &ep, st
     return false;
 }
 
+// ------------------------------------------------------------------------------------------------ image textures
+// The reference decodes image files in its image-handler plugins (src/image_handlers/*, a loader subsystem outside this path) and
+// textureImage_t only calls imageHandler_t::getPixel.  Here the decoded pixels come in through yb200_register_image (what a plugin
+// living inside the reference passes on from its handler); files are only read for the one self-contained format, TGA.
+bool Context::registerImage(const char *fileName, const float *rgba, int w, int h, bool hdr)
+{
+    if (!fileName || !rgba || w <= 0 || h <= 0) return fail("register_image: bad arguments");
+    HostImage &im = images[fileName];
+    im.w = w; im.h = h; im.hdr = hdr;
+    im.px.resize((size_t)w * h);
+    memcpy((void *)im.px.data(), rgba, (size_t)w * h * sizeof(f4));
+    return true;
+}
+// tgaHandler_t::loadFromFile (src/image_handlers/tgaHandler.cc:433-581) for true-colour 24 / 32 bit and 8-bit grey images,
+// uncompressed or RLE, any origin; colour-mapped and 15 / 16 bit files are not read here.
+bool Context::loadTga(const std::string &fileName, HostImage &img)
+{
+    FILE *fp = fopen(fileName.c_str(), "rb");
+    if (!fp) return fail("TGAHandler: Cannot open file " + fileName);
+    unsigned char hd[18];
+    if (fread(hd, 1, 18, fp) != 18) { fclose(fp); return fail("TGAHandler: truncated file " + fileName); }
+    const int idLength = hd[0], cmType = hd[1], imageType = hd[2], width = hd[12] | (hd[13] << 8), height = hd[14] | (hd[15] << 8), bitDepth = hd[16], desc = hd[17];
+    const bool isRLE = imageType == 10 || imageType == 11, isGray = imageType == 3 || imageType == 11;
+    const bool trueCol = imageType == 2 || imageType == 10;
+    if (cmType != 0 || !(trueCol || isGray) || !((trueCol && (bitDepth == 24 || bitDepth == 32)) || (isGray && bitDepth == 8)) || width <= 0 || height <= 0) {
+        fclose(fp);
+        return fail("TGAHandler: " + fileName + ": only 24/32-bit true-colour and 8-bit grey TGA files are read by the B200 path (pass other images through yb200_register_image)");
+    }
+    fseek(fp, idLength, SEEK_CUR);
+    const bool fromTop = ((desc & 0x20) >> 5) != 0, fromLeft = ((desc & 0x10) >> 4) != 0;   // sic: the reference mirrors in x when bit 4 is set
+    img.w = width; img.h = height; img.hdr = false;
+    img.px.assign((size_t)width * height, f4{0.f, 0.f, 0.f, 0.f});
+    const int bpp = bitDepth / 8;
+    long x = fromLeft ? width - 1 : 0, y = fromTop ? 0 : height - 1;
+    const long minX = x, maxX = fromLeft ? -1 : width, stepX = fromLeft ? -1 : 1, maxY = fromTop ? height : -1, stepY = fromTop ? 1 : -1;
+    const double inv255 = 0.00392156862745098039;
+    auto put = [&](const unsigned char *c) {
+        f4 p;
+        if (bpp == 1) { p.x = p.y = p.z = p.w = (float)(c[0] * inv255); }                   // colorA_t(float): all four channels
+        else { p.z = (float)(c[0] * inv255); p.y = (float)(c[1] * inv255); p.x = (float)(c[2] * inv255); p.w = bpp == 4 ? (float)(c[3] * inv255) : 1.f; }
+        img.px[(size_t)y * width + x] = p;
+        x += stepX;
+        if (x == maxX) { x = minX; y += stepY; }
+    };
+    unsigned char c[4] = {0, 0, 0, 0};
+    if (!isRLE) {
+        for (size_t i = 0; i < (size_t)width * height && y != maxY; ++i) { if (fread(c, 1, bpp, fp) != (size_t)bpp) break; put(c); }
+    } else {
+        while (!feof(fp) && y != maxY) {
+            unsigned char pack = 0;
+            if (fread(&pack, 1, 1, fp) != 1) break;
+            const bool rlePack = (pack & 0x80) != 0;
+            const int rep = (int)(pack & 0x7f) + 1;
+            if (rlePack && fread(c, 1, bpp, fp) != (size_t)bpp) break;
+            for (int i = 0; i < rep && y != maxY; ++i) { if (!rlePack && fread(c, 1, bpp, fp) != (size_t)bpp) break; put(c); }
+        }
+    }
+    fclose(fp);
+    return true;
+}
+
 // ------------------------------------------------------------------------------------------------ textures + shader nodes
 uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 + src/textures/basictex.cc factories
 {
@@ -342,10 +403,42 @@ uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 +
         if (t.type == TEX_MARBLE) { p.get("sharpness", shp); if (shp > 1) t.sharpness = (float)(1.0 / (double)shp); }
         else if (p.get("wood_type", s)) t.rings = s == "rings";
         if (p.get("shape", s)) t.wshape = s == "saw" ? 1 : (s == "tri" ? 2 : 0);
+    } else if (type == "image") {                    // imagetex.cc:241-340
+        std::string fname, intpstr, clip;
+        double gamma = 1.0, minx = 0.0, miny = 0.0, maxx = 1.0, maxy = 1.0, cdist = 0.0; bool normalmap = false, rot90 = false, even = false, odd = true;
+        int xrep = 1, yrep = 1;
+        if (!p.get("filename", fname)) { fail("ImageTexture: Required argument filename not found for image texture"); return 0; }
+        std::map<std::string, HostImage>::iterator ii = images.find(fname);
+        if (ii == images.end()) {
+            std::string ext = fname.substr(fname.rfind('.') + 1);
+            for (size_t i = 0; i < ext.size(); ++i) ext[i] = (char)tolower(ext[i]);
+            if (ext != "tga" && ext != "tpic") {
+                fail("ImageTexture: '" + fname + "': only TGA files are decoded by the B200 path; register the decoded pixels with yb200_register_image");
+                return 0;
+            }
+            HostImage im;
+            if (!loadTga(fname, im)) return 0;
+            ii = images.insert(std::make_pair(fname, im)).first;
+        }
+        const HostImage &im = ii->second;
+        p.get("interpolate", intpstr); p.get("gamma", gamma); p.get("normalmap", normalmap);
+        p.get("xrepeat", xrep); p.get("yrepeat", yrep); p.get("cropmin_x", minx); p.get("cropmin_y", miny); p.get("cropmax_x", maxx); p.get("cropmax_y", maxy);
+        p.get("rot90", rot90); p.get("clipping", clip); p.get("even_tiles", even); p.get("odd_tiles", odd); p.get("checker_dist", cdist);
+        t.type = TEX_IMAGE; t.resx = im.w; t.resy = im.h; t.isHDR = im.hdr; t.normalmap = normalmap;
+        t.intp = intpstr == "none" ? 0 : (intpstr == "bicubic" ? 2 : 1);
+        t.gamma = (float)gamma; t.xrepeat = xrep; t.yrepeat = yrep; t.rot90 = rot90;
+        t.cropminx = (float)minx; t.cropmaxx = (float)maxx; t.cropminy = (float)miny; t.cropmaxy = (float)maxy;
+        t.cropx = (t.cropminx != 0.0f) || (t.cropmaxx != 1.0f); t.cropy = (t.cropminy != 0.0f) || (t.cropmaxy != 1.0f);
+        t.clipmode = clip == "extend" ? TCL_EXTEND : (clip == "clip" ? TCL_CLIP : (clip == "clipcube" ? TCL_CLIPCUBE : (clip == "checker" ? TCL_CHECKER : TCL_REPEAT)));
+        t.checkerEven = even; t.checkerOdd = odd; t.checkerDist = (float)cdist;
+        texPixOffset.resize(textures.size() + 1, (size_t)-1);
+        texPixOffset[textures.size()] = texPixels.size();
+        texPixels.insert(texPixels.end(), im.px.begin(), im.px.end());
     } else {
-        fail("Environment: texture type '" + type + "' is not supported by the B200 path (supported: rgb_cube, blend, clouds, marble, wood)");
+        fail("Environment: texture type '" + type + "' is not supported by the B200 path (supported: rgb_cube, blend, clouds, marble, wood, image)");
         return 0;
     }
+    texPixOffset.resize(textures.size() + 1, (size_t)-1);
     textures.push_back(t);
     textureNames[name] = (int)textures.size() - 1;
     return 0x54000000u | (uintptr_t)textures.size();
@@ -395,8 +488,13 @@ bool Context::loadMaterialNodes(const char *name, Material &m, const char *const
             p.get("proj_x", map[0]); p.get("proj_y", map[1]); p.get("proj_z", map[2]);
             for (int i = 0; i < 3; ++i) map[i] = std::min(3, std::max(0, map[i]));
             n.mapX = map[0]; n.mapY = map[1]; n.mapZ = map[2]; n.scale = scale; n.offset = 2.f * offset; n.doScalar = scalar;
-            n.dU = n.dV = 0.0002f;                                           // setup(): procedural textures step
-            n.bumpStr = (bump / length(scale)) / 100.0f;
+            const Texture &tx = textures[n.tex];
+            n.mapType = TXP_PLAIN;
+            if (p.get("mapping", opt) && tx.type == TEX_IMAGE) n.mapType = opt == "cube" ? TXP_CUBE : (opt == "tube" ? TXP_TUBE : (opt == "sphere" ? TXP_SPHERE : TXP_PLAIN));
+            if (tx.type == TEX_IMAGE) { n.dU = 1.f / (float)tx.resx; n.dV = 1.f / (float)tx.resy; }   // setup() (basicnodes.cc:12-38)
+            else n.dU = n.dV = 0.0002f;
+            n.bumpStr = bump / length(scale);
+            if (!(tx.type == TEX_IMAGE && tx.normalmap)) n.bumpStr /= 100.0f;
             const float ident[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
             memcpy(n.mtx, ident, sizeof(ident));
             std::map<std::string, std::vector<float> >::const_iterator mi = p.mdicc.find("transform");
@@ -1049,6 +1147,10 @@ bool Context::uploadTables()
         d_materials.reserve(materials.size() + 1); d_lights.reserve(lights.size() + 1);
         rt_h2d(d_materials.p, materials.data(), materials.size() * sizeof(Material), stream);
         rt_h2d(d_lights.p, lights.data(), lights.size() * sizeof(Light), stream);
+        d_tex_pixels.reserve(texPixels.size() + 1);
+        rt_h2d(d_tex_pixels.p, texPixels.data(), texPixels.size() * sizeof(f4), stream);
+        for (size_t i = 0; i < textures.size(); ++i)
+            textures[i].pixels = (i < texPixOffset.size() && texPixOffset[i] != (size_t)-1) ? d_tex_pixels.p + texPixOffset[i] : 0;
         d_textures.reserve(textures.size() + 1); d_shaderNodes.reserve(shaderNodes.size() + 1);
         rt_h2d(d_textures.p, textures.data(), textures.size() * sizeof(Texture), stream);
         rt_h2d(d_shaderNodes.p, shaderNodes.data(), shaderNodes.size() * sizeof(ShaderNode), stream);

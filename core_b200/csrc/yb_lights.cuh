@@ -356,11 +356,13 @@ YB_HD void tri_getSurface(const SceneDev &sc, int tri, v3 hitP, float b1, float 
     createCS(sp.N, sp.NU, sp.NV);
 }
 
-// the texture-coordinate part of triangle_t::getSurface (triangle.cc:28-64): orco point / normal and interpolated UV
-YB_HD void tri_getTexPoint(const SceneDev &sc, int tri, v3 hitP, float b1, float b2, v3 Ng, TexPoint &tp)
+// the texture-coordinate part of triangle_t::getSurface (triangle.cc:28-105): orco point / normal, interpolated UV and - when
+// the shading frame is given (bump mapping from image textures) - dPdU / dPdV brought into shading space
+YB_HD void tri_getTexPoint(const SceneDev &sc, int tri, v3 hitP, float b1, float b2, v3 Ng, TexPoint &tp, const Surf *sp = 0)
 {
-    const uint32_t info = (uint32_t)f2i(sc.tri_v[3 * tri + 1].w);
-    const int prim = f2i(sc.tri_v[3 * tri].w);
+    const f4 A = sc.tri_v[3 * tri], B = sc.tri_v[3 * tri + 1], C = sc.tri_v[3 * tri + 2];
+    const uint32_t info = (uint32_t)f2i(B.w);
+    const int prim = f2i(A.w);
     const float u = 1 - b1 - b2, v = b1, w = b2;
     if ((info & TRI_HAS_ORCO) && sc.prim_orco) {
         const v3 p0 = sc.prim_orco[3 * (size_t)prim], p1 = sc.prim_orco[3 * (size_t)prim + 1], p2 = sc.prim_orco[3 * (size_t)prim + 2];
@@ -368,10 +370,26 @@ YB_HD void tri_getTexPoint(const SceneDev &sc, int tri, v3 hitP, float b1, float
         tp.orcoNg = normalize(cross(p1 - p0, p2 - p0));
     } else { tp.orcoP = hitP; tp.orcoNg = Ng; }
     tp.U = 0.f; tp.V = 0.f;                              // left uninitialised by the reference without UVs (triangle.cc:85-90)
+    const v3 p0(A.x, A.y, A.z), p1(B.x, B.y, B.z), p2(C.x, C.y, C.z);
+    v3 dPdU = p1 - p0, dPdV = p2 - p1;                   // implicit mapping (triangle.cc:78-90)
     if ((info & TRI_HAS_UV) && sc.prim_uv) {
         const float *q = sc.prim_uv + 6 * (size_t)prim;
         tp.U = u * q[0] + v * q[2] + w * q[4];
         tp.V = u * q[1] + v * q[3] + w * q[5];
+        const float du1 = q[0] - q[4], du2 = q[2] - q[4], dv1 = q[1] - q[5], dv2 = q[3] - q[5];
+        const float det = du1 * dv2 - dv1 * du2;
+        if (fabsf(det) > 1e-30f) {
+            const float invdet = 1.f / det;
+            const v3 dp1 = p0 - p2, dp2 = p1 - p2;
+            dPdU = (dv2 * dp1 - dv1 * dp2) * invdet;
+            dPdV = (du1 * dp2 - du2 * dp1) * invdet;
+        }
+    }
+    tp.dSdU = tp.dSdV = v3(0.f);
+    if (sp) {
+        dPdU = normalize(dPdU); dPdV = normalize(dPdV);
+        tp.dSdU = v3(dot(sp->NU, dPdU), dot(sp->NV, dPdU), dot(sp->N, dPdU));
+        tp.dSdV = v3(dot(sp->NU, dPdV), dot(sp->NV, dPdV), dot(sp->N, dPdV));
     }
 }
 

@@ -20,7 +20,7 @@ namespace yb {
 #include "yb_noise_tab.inc"
 
 struct NodeRes { float r, g, b, a, f; };          // nodeResult_t: colorA_t + scalar (shader.h:32-38)
-struct TexPoint { float U, V; v3 orcoP, orcoNg; };   // the surfacePoint_t fields texture_mapper reads besides P / Ng
+struct TexPoint { float U, V; v3 orcoP, orcoNg, dSdU, dSdV; };   // the surfacePoint_t fields texture_mapper reads besides P / Ng / NU / NV
 
 // ---- noise ------------------------------------------------------------------------------------------
 YB_HD int nperm(int i) { return (int)yb_noise_perm[i & 255]; }     // hash[512] holds the permutation twice
@@ -64,6 +64,92 @@ YB_HD float wave_shape(int wshape, float w)             // the shape switch of m
     return 0.5f + 0.5f * fSin(w);
 }
 
+// ---- image texture (imagetex.cc:44-107 interpolateImage, :152-218 doMapping, :109-126 getColor / getNoGammaColor) -------
+struct C4 { float r, g, b, a; };
+YB_HD C4 c4(f4 p) { C4 c; c.r = p.x; c.g = p.y; c.b = p.z; c.a = p.w; return c; }
+YB_HD C4 operator+(C4 a, C4 b) { C4 c; c.r = a.r + b.r; c.g = a.g + b.g; c.b = a.b + b.b; c.a = a.a + b.a; return c; }
+YB_HD C4 operator-(C4 a, C4 b) { C4 c; c.r = a.r - b.r; c.g = a.g - b.g; c.b = a.b - b.b; c.a = a.a - b.a; return c; }
+YB_HD C4 operator*(C4 a, C4 b) { C4 c; c.r = a.r * b.r; c.g = a.g * b.g; c.b = a.b * b.b; c.a = a.a * b.a; return c; }
+YB_HD C4 operator*(C4 a, float f) { C4 c; c.r = a.r * f; c.g = a.g * f; c.b = a.b * f; c.a = a.a * f; return c; }
+YB_HD C4 operator*(float f, C4 a) { return a * f; }
+YB_HD C4 img_px(const Texture &t, int x, int y) { return c4(t.pixels[(size_t)y * (size_t)t.resx + (size_t)x]); }
+YB_HD C4 cubicInterpolate(C4 y0, C4 y1, C4 y2, C4 y3, double mu)          // interpolation.h:47-61 with T = colorA_t
+{
+    const float m = (float)mu, m2 = (float)(mu * mu);
+    C4 mu2; mu2.r = mu2.g = mu2.b = mu2.a = m2;
+    const C4 a0 = y3 - y2 - y0 + y1, a1 = y0 - y1 - a0, a2 = y2 - y0, a3 = y1;
+    return (a0 * m * mu2 + a1 * mu2 + a2 * m + a3);
+}
+YB_HD C4 img_interpolate(const Texture &t, v3 p)
+{
+    const int resx = t.resx, resy = t.resy;
+    float xf = ((float)resx * (p.x - floorf(p.x)));
+    float yf = ((float)resy * (p.y - floorf(p.y)));
+    if (t.intp != 0) { xf -= 0.5f; yf -= 0.5f; }
+    int x = (int)xf; x = x > resx - 1 ? resx - 1 : x; x = x < 0 ? 0 : x;
+    int y = (int)yf; y = y > resy - 1 ? resy - 1 : y; y = y < 0 ? 0 : y;
+    const C4 c1 = img_px(t, x, y);
+    if (t.intp == 0) return c1;
+    const int x2 = x + 1 < resx - 1 ? x + 1 : resx - 1, y2 = y + 1 < resy - 1 ? y + 1 : resy - 1;
+    const C4 c2 = img_px(t, x2, y), c3 = img_px(t, x, y2), c4_ = img_px(t, x2, y2);
+    const float dx = xf - floorf(xf), dy = yf - floorf(yf);
+    if (t.intp == 1) {
+        const float w0 = (1 - dx) * (1 - dy), w1 = (1 - dx) * dy, w2 = dx * (1 - dy), w3 = dx * dy;
+        return (w0 * c1) + (w1 * c3) + (w2 * c2) + (w3 * c4_);
+    }
+    const int x0 = x - 1 > 0 ? x - 1 : 0, x3 = x2 + 1 < resx - 1 ? x2 + 1 : resx - 1;
+    const int y0 = y - 1 > 0 ? y - 1 : 0, y3 = y2 + 1 < resy - 1 ? y2 + 1 : resy - 1;
+    C4 c0 = cubicInterpolate(img_px(t, x0, y0), img_px(t, x, y0), img_px(t, x2, y0), img_px(t, x3, y0), dx);
+    C4 c8 = cubicInterpolate(img_px(t, x0, y), c1, c2, img_px(t, x3, y), dx);
+    C4 cA = cubicInterpolate(img_px(t, x0, y2), c3, c4_, img_px(t, x3, y2), dx);
+    C4 cC = cubicInterpolate(img_px(t, x0, y3), img_px(t, x, y3), img_px(t, x2, y3), img_px(t, x3, y3), dx);
+    return cubicInterpolate(c0, c8, cA, cC, dy);
+}
+YB_HD bool img_doMapping(const Texture &t, v3 &texpt)
+{
+    bool outside = false;
+    texpt = 0.5f * texpt + v3(0.5f);
+    if (t.clipmode == TCL_REPEAT) {
+        if (t.xrepeat > 1) { texpt.x *= (float)t.xrepeat; if (texpt.x > 1.0f) texpt.x -= (float)(int)texpt.x; else if (texpt.x < 0.0f) texpt.x += (float)(1 - (int)texpt.x); }
+        if (t.yrepeat > 1) { texpt.y *= (float)t.yrepeat; if (texpt.y > 1.0f) texpt.y -= (float)(int)texpt.y; else if (texpt.y < 0.0f) texpt.y += (float)(1 - (int)texpt.y); }
+    }
+    if (t.cropx) texpt.x = t.cropminx + texpt.x * (t.cropmaxx - t.cropminx);
+    if (t.cropy) texpt.y = t.cropminy + texpt.y * (t.cropmaxy - t.cropminy);
+    if (t.rot90) { const float tmp = texpt.x; texpt.x = texpt.y; texpt.y = tmp; }
+    int mode = t.clipmode;
+    if (mode == TCL_CLIPCUBE) {
+        if ((texpt.x < 0) || (texpt.x > 1) || (texpt.y < 0) || (texpt.y > 1) || (texpt.z < -1) || (texpt.z > 1)) outside = true;
+        return outside;
+    }
+    if (mode == TCL_CHECKER) {
+        const int xs = (int)floorf(texpt.x), ys = (int)floorf(texpt.y);
+        texpt.x -= (float)xs; texpt.y -= (float)ys;
+        if (!t.checkerOdd && !((xs + ys) & 1)) return true;
+        if (!t.checkerEven && ((xs + ys) & 1)) return true;
+        if (t.checkerDist < 1.0f) {
+            texpt.x = (float)(((double)texpt.x - 0.5) / (1.0 - (double)t.checkerDist) + 0.5);
+            texpt.y = (float)(((double)texpt.y - 0.5) / (1.0 - (double)t.checkerDist) + 0.5);
+        }
+        mode = TCL_CLIP;                                    // falls through
+    }
+    if (mode == TCL_CLIP) {
+        if ((texpt.x < 0) || (texpt.x > 1) || (texpt.y < 0) || (texpt.y > 1)) outside = true;
+        return outside;
+    }
+    if (mode == TCL_EXTEND) {
+        if (texpt.x > 0.99999f) texpt.x = 0.99999f; else if (texpt.x < 0) texpt.x = 0;
+        if (texpt.y > 0.99999f) texpt.y = 0.99999f; else if (texpt.y < 0) texpt.y = 0;
+    }
+    return false;
+}
+YB_HD C4 img_getNoGammaColor(const Texture &t, v3 p)
+{
+    v3 p1(p.x, -p.y, p.z);
+    C4 ret; ret.r = ret.g = ret.b = ret.a = 0.f;
+    if (img_doMapping(t, p1)) return ret;
+    return img_interpolate(t, p1);
+}
+
 // ---- textures: texture_t::getFloat / getColor --------------------------------------------------------
 YB_HD float tex_getFloat(const Texture &t, v3 p)
 {
@@ -72,6 +158,7 @@ YB_HD float tex_getFloat(const Texture &t, v3 p)
             const float r = clamp01f(p.x), g = clamp01f(p.y), b = clamp01f(p.z);
             return (r + g + b) * 0.333333f;                                  // color_t::energy
         }
+        case TEX_IMAGE: { const C4 c = img_getNoGammaColor(t, p); return 0.2126f * c.r + 0.7152f * c.g + 0.0722f * c.b; }   // texture.h:38: col2bri of the NO-gamma colour
         case TEX_BLEND: {
             float blend = (float)(0.5 * ((double)p.x + 1.));
             return fmaxf_(0.f, fminf_(blend, 1.f));
@@ -98,6 +185,12 @@ YB_HD void tex_getColor(const Texture &t, v3 p, float *c)
 {
     if (t.type == TEX_RGB_CUBE) { c[0] = clamp01f(p.x); c[1] = clamp01f(p.y); c[2] = clamp01f(p.z); c[3] = 1.f; return; }
     if (t.type == TEX_BLEND) { c[0] = c[1] = c[2] = c[3] = 1.f; return; }
+    if (t.type == TEX_IMAGE) {
+        C4 r = img_getNoGammaColor(t, p);
+        if (t.gamma != 1.f && !t.isHDR) { r.r = fPow(r.r, t.gamma); r.g = fPow(r.g, t.gamma); r.b = fPow(r.b, t.gamma); }
+        c[0] = r.r; c[1] = r.g; c[2] = r.b; c[3] = r.a;
+        return;
+    }
     const float f = tex_getFloat(t, p);                                      // color1 + getFloat(p) * (color2 - color1), alpha 1
     c[0] = t.color1.x + f * (t.color2.x - t.color1.x); c[1] = t.color1.y + f * (t.color2.y - t.color1.y);
     c[2] = t.color1.z + f * (t.color2.z - t.color1.z); c[3] = 1.f;
@@ -154,27 +247,81 @@ YB_HD v3 texmap_coords(const ShaderNode &n, v3 P, const TexPoint &tp)
         default: return P;
     }
 }
-YB_HD v3 texmap_doMapping(const ShaderNode &n, v3 texpt)
+// tubemap / spheremap / cubemap of basicnodes.cc:41-91 (discrete textures only, :270)
+YB_HD v3 texmap_doMapping(const ShaderNode &n, v3 texpt, v3 N)
 {
     if (n.texCoords == TXC_UV) texpt = v3(2.0f * texpt.x - 1.0f, 2.0f * texpt.y - 1.0f, texpt.z);
     const float texmap[4] = {0.f, texpt.x, texpt.y, texpt.z};
     texpt = v3(texmap[n.mapX], texmap[n.mapY], texmap[n.mapZ]);
-    // tube / sphere / cube projections apply to discrete (image) textures only (basicnodes.cc:270): none supported yet
+    if (n.mapType == TXP_TUBE) {
+        const v3 p = texpt; v3 res(0.f, p.z, 0.f);
+        const float d = p.x * p.x + p.y * p.y;
+        if (d > 0) { res.z = (float)(1.0 / (double)fSqrt(d)); res.x = (float)((double)(-atan2f(p.x, p.y)) * YB_M_1_PI); }
+        texpt = res;
+    } else if (n.mapType == TXP_SPHERE) {
+        const v3 p = texpt; v3 res(0.f);
+        const float d = p.x * p.x + p.y * p.y + p.z * p.z;
+        if (d > 0) {
+            res.z = fSqrt(d);
+            if ((p.x != 0) && (p.y != 0)) res.x = (float)((double)(-atan2f(p.x, p.y)) * YB_M_1_PI);
+            res.y = (float)(1.0 - 2.0 * ((double)fAcos(p.z / res.z) * YB_M_1_PI));
+        }
+        texpt = res;
+    } else if (n.mapType == TXP_CUBE) {
+        int axis;
+        if (fabsf(N.z) >= fabsf(N.x) && fabsf(N.z) >= fabsf(N.y)) axis = 2;
+        else if (fabsf(N.y) >= fabsf(N.x) && fabsf(N.y) >= fabsf(N.z)) axis = 1;
+        else axis = 0;
+        const v3 p = texpt;
+        texpt = axis == 0 ? v3(p.y, p.z, p.x) : (axis == 1 ? v3(p.x, p.z, p.y) : p);
+    }
     return mul(texpt, n.scale) + n.offset;
+}
+YB_HD v3 texmap_Ng(const ShaderNode &n, v3 Ng, const TexPoint &tp)        // the normal getCoords pairs with the coordinates
+{
+    if (n.texCoords == TXC_ORCO) return tp.orcoNg;
+    if (n.texCoords == TXC_TRAN) return v3(n.mtx[0] * Ng.x + n.mtx[1] * Ng.y + n.mtx[2] * Ng.z, n.mtx[4] * Ng.x + n.mtx[5] * Ng.y + n.mtx[6] * Ng.z,
+                                            n.mtx[8] * Ng.x + n.mtx[9] * Ng.y + n.mtx[10] * Ng.z);
+    return Ng;
 }
 // shaderNode_t::evalDerivative for bump mapping: texture_mapper on a procedural (non-discrete) texture (basicnodes.cc:218-232),
 // layer (layernode.cc:118-146); every other node type keeps the base-class zero (shader.h:83-84)
-YB_HD void node_evalDerivative(const ShaderNode &n, const Texture *textures, v3 P, v3 NU, v3 NV, const TexPoint &tp, NodeRes *st, int self)
+YB_HD void node_evalDerivative(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, v3 NU, v3 NV, const TexPoint &tp, NodeRes *st, int self)
 {
     NodeRes r; r.r = r.g = r.b = r.a = r.f = 0.f;
     if (n.type == NODE_TEXMAP) {
-        const v3 texpt = texmap_coords(n, P, tp);
+        v3 texpt = texmap_coords(n, P, tp);
+        const v3 mNg = texmap_Ng(n, Ng, tp);
         const Texture &t = textures[n.tex];
-        const v3 i0 = texmap_doMapping(n, texpt - n.dU * NU), i1 = texmap_doMapping(n, texpt + n.dU * NU);
-        const v3 j0 = texmap_doMapping(n, texpt - n.dV * NV), j1 = texmap_doMapping(n, texpt + n.dV * NV);
-        float du = (tex_getFloat(t, i0) - tex_getFloat(t, i1)) / n.dU;
-        float dv = (tex_getFloat(t, j0) - tex_getFloat(t, j1)) / n.dV;
-        r.r = du * n.bumpStr; r.g = dv * n.bumpStr;
+        float du = 0.f, dv = 0.f;
+        if (t.type == TEX_IMAGE) {                     // discrete texture (basicnodes.cc:173-216)
+            texpt = texmap_doMapping(n, texpt, mNg);
+            v3 norm(0.f);
+            if (t.normalmap) {
+                const C4 color = img_getNoGammaColor(t, texpt);
+                norm = 2.f * v3(color.r, color.g, color.b) - v3(1.f);
+                du = dot(norm, tp.dSdU); dv = dot(norm, tp.dSdV);          // overwritten below, as in the reference
+            } else {
+                const v3 pDU(n.dU, 0.f, 0.f), pDV(0.f, n.dV, 0.f);
+                const float dfdu = (tex_getFloat(t, texpt - pDU) - tex_getFloat(t, texpt + pDU)) / n.dU;
+                const float dfdv = (tex_getFloat(t, texpt - pDV) - tex_getFloat(t, texpt + pDV)) / n.dV;
+                v3 vecU = tp.dSdU, vecV = tp.dSdV;
+                vecU.z = dfdu; vecV.z = dfdv;
+                norm = cross(vecU, vecV);
+            }
+            norm = normalize(norm);
+            if (fabsf(norm.z) > 1e-30f) {
+                const float NF = (float)(1.0 / (double)norm.z * (double)n.bumpStr);
+                du = norm.x * NF; dv = norm.y * NF;
+            } else du = dv = 0.f;
+        } else {
+            const v3 i0 = texmap_doMapping(n, texpt - n.dU * NU, mNg), i1 = texmap_doMapping(n, texpt + n.dU * NU, mNg);
+            const v3 j0 = texmap_doMapping(n, texpt - n.dV * NV, mNg), j1 = texmap_doMapping(n, texpt + n.dV * NV, mNg);
+            du = (tex_getFloat(t, i0) - tex_getFloat(t, i1)) / n.dU;
+            dv = (tex_getFloat(t, j0) - tex_getFloat(t, j1)) / n.dV;
+            du *= n.bumpStr; dv *= n.bumpStr;
+        }
+        r.r = du; r.g = dv;
     } else if (n.type == NODE_LAYER) {
         float rdu = 0.f, rdv = 0.f, stencilTin = 1.f;
         if (n.upper >= 0) { rdu = st[n.upper].r; rdv = st[n.upper].g; stencilTin = st[n.upper].a; }
@@ -189,7 +336,7 @@ YB_HD void node_eval(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, 
 {
     NodeRes r; r.r = r.g = r.b = r.a = r.f = 0.f;
     if (n.type == NODE_TEXMAP) {                      // textureMapper_t::eval
-        const v3 texpt = texmap_doMapping(n, texmap_coords(n, P, tp));
+        const v3 texpt = texmap_doMapping(n, texmap_coords(n, P, tp), texmap_Ng(n, Ng, tp));
         const Texture &t = textures[n.tex];
         float c[4];
         tex_getColor(t, texpt, c);

@@ -88,6 +88,11 @@ struct Context {
     // environment tables (environment.cc:189-479)
     std::vector<Material> materials; std::map<std::string, int> materialNames;
     std::vector<Texture> textures; std::map<std::string, int> textureNames;
+    // image textures: decoded pixels (RGBA float, row 0 on top) by file name - registered through the C ABI or read from a TGA file;
+    // texPixels = pool of the pixels of all image textures, texPixOffset[i] = first pixel of texture i (or npos)
+    struct HostImage { int w, h; bool hdr; std::vector<f4> px; };
+    std::map<std::string, HostImage> images;
+    std::vector<f4> texPixels; std::vector<size_t> texPixOffset;
     std::vector<ShaderNode> shaderNodes;
     std::vector<Light> lights; std::map<std::string, int> lightNames; std::vector<unsigned> lightObj;
     std::map<std::string, CameraDesc> cameras;
@@ -104,6 +109,7 @@ struct Context {
     volatile int abortFlag;
     // device-side scene
     DevBuf<BvhNode> d_nodes; DevBuf<f4> d_tri_v; DevBuf<v3> d_tri_n; DevBuf<Material> d_materials; DevBuf<Light> d_lights;
+    DevBuf<f4> d_tex_pixels;
     DevBuf<Texture> d_textures; DevBuf<ShaderNode> d_shaderNodes; DevBuf<float> d_prim_uv; DevBuf<v3> d_prim_orco;
     DevBuf<f4> d_light_tris; DevBuf<float> d_light_cdf;   // mesh light emitters (yb_host.cc uploadTables)
     DevBuf<uint32_t> d_traceCounter;   // ray-fetch counter of the persistent traversal kernels
@@ -142,6 +148,8 @@ struct Context {
     uintptr_t createLight(const char *name);
     uintptr_t createMaterial(const char *name);
     uintptr_t createTexture(const char *name);
+    bool registerImage(const char *fileName, const float *rgba, int w, int h, bool hdr);
+    bool loadTga(const std::string &fileName, HostImage &img);
     bool loadMaterialNodes(const char *name, Material &m, const char *const *slotKeys, const int *slotIds, int nSlots);
     uintptr_t createCamera(const char *name);
     uintptr_t createBackground(const char *name);

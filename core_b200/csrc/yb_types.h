@@ -63,12 +63,19 @@ enum ShaderSlot : int32_t { SLOT_DIFFUSE = 0, SLOT_MIRROR_COLOR, SLOT_MIRROR, SL
 
 // texture_t implementations evaluated on the device (src/textures/basictex.cc): rgb_cube, blend, clouds, marble, wood with the
 // default noise generator (newPerlin_t, noise.cc:161-183)
-enum TexType : int32_t { TEX_RGB_CUBE = 0, TEX_BLEND, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD };
+enum TexType : int32_t { TEX_RGB_CUBE = 0, TEX_BLEND, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD, TEX_IMAGE };
+enum : int32_t { TCL_EXTEND = 0, TCL_CLIP, TCL_CLIPCUBE, TCL_REPEAT, TCL_CHECKER };   // imagetex.h:31-38
+enum : int32_t { TXP_PLAIN = 0, TXP_CUBE, TXP_TUBE, TXP_SPHERE };                 // basicnodes.h texture_mapper projection
 struct Texture {
     int32_t type;
     int32_t depth, hard, bias, wshape, rings;   // wshape: 0 sin, 1 saw, 2 tri
     float size, turb, sharpness;
     col3 color1, color2;
+    // textureImage_t (src/textures/imagetex.cc:27-240): pixels = resx*resy RGBA floats of the image handler, row 0 on top
+    const f4 *pixels;
+    int32_t resx, resy, intp, isHDR, normalmap;          // intp: 0 none, 1 bilinear, 2 bicubic
+    int32_t xrepeat, yrepeat, rot90, cropx, cropy, clipmode, checkerOdd, checkerEven;
+    float gamma, cropminx, cropmaxx, cropminy, cropmaxy, checkerDist;
 };
 // shaderNode_t implementations (src/textures/basicnodes.cc, layernode.cc)
 enum NodeType : int32_t { NODE_TEXMAP = 0, NODE_VALUE, NODE_MIX, NODE_LAYER };
@@ -77,7 +84,7 @@ enum : uint32_t { TXF_RGBTOINT = 1, TXF_STENCIL = 2, TXF_NEGATIVE = 4, TXF_ALPHA
 struct ShaderNode {
     int32_t type;
     // texture_mapper (basicnodes.cc:96-160,236-304)
-    int32_t tex, texCoords, mapX, mapY, mapZ, doScalar;
+    int32_t tex, texCoords, mapX, mapY, mapZ, doScalar, mapType;
     v3 scale, offset;
     float bumpStr, dU, dV;           // textureMapper_t::setup (basicnodes.cc:12-38): step 0.0002, bump_strength / |scale| / 100
     float mtx[12];                   // first three rows of the 'transform' matrix (texco = transformed)

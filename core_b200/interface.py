@@ -123,6 +123,11 @@ class YafrayInterface:
     def createCamera(self, name): return self._call("create_camera", _b(name))
     def createBackground(self, name): return self._call("create_background", _b(name))
     def createIntegrator(self, name): return self._call("create_integrator", _b(name))
+    def registerImage(self, file_name, rgba, is_hdr=False):
+        """Decoded pixels (H, W, 4) float32, row 0 on top, for image textures whose `filename` parameter is file_name."""
+        rgba = np.ascontiguousarray(rgba, dtype=np.float32)
+        return bool(self._call("register_image", _b(file_name), rgba.ctypes.data, rgba.shape[1], rgba.shape[0], int(is_hdr)))
+
     def createTexture(self, name): return self._call("create_texture", _b(name))
     def createVolumeRegion(self, name): return self._call("create_volume_region", _b(name))
 

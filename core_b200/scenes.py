@@ -109,6 +109,42 @@ def add_mesh_uv_orco(yi, verts, tris, mat, orco, uv, normals=None, smooth_angle=
     return oid
 
 
+def test_image(w, h, seed=5):
+    """Deterministic RGBA8 test picture (H, W, 4) uint8: colour gradients, a checker and an alpha ramp."""
+    y, x = np.mgrid[0:h, 0:w]
+    rng = np.random.Generator(np.random.PCG64(seed))
+    r = (255 * x / max(1, w - 1)).astype(np.uint8)
+    g = (255 * y / max(1, h - 1)).astype(np.uint8)
+    b = ((((x // 4) + (y // 4)) & 1) * 200 + rng.integers(0, 56, (h, w))).astype(np.uint8)
+    a = (64 + 191 * ((x + y) % 16) / 15).astype(np.uint8)
+    return np.stack([r, g, b, a], 2)
+
+
+def write_tga(path, img, top=False, rle=False, gray=False):
+    """Write (H, W, 4) uint8 as a TGA file: 32-bit BGRA (24-bit if the alpha is all 255, 8-bit grey if gray), bottom or
+    top origin, optionally run-length encoded with raw packets only."""
+    import os
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    h, w = img.shape[:2]
+    has_alpha = bool((img[..., 3] != 255).any()) and not gray
+    bpp = 1 if gray else (4 if has_alpha else 3)
+    rows = img if top else img[::-1]
+    px = rows[..., :1] if gray else (rows[..., [2, 1, 0, 3]] if has_alpha else rows[..., [2, 1, 0]])
+    data = np.ascontiguousarray(px).reshape(-1, bpp)
+    itype = (3 if gray else 2) + (8 if rle else 0)
+    hdr = bytes([0, 0, itype, 0, 0, 0, 0, 0, 0, 0, 0, 0, w & 255, w >> 8, h & 255, h >> 8, 8 * bpp, (0x20 if top else 0) | (8 if has_alpha else 0)])
+    with open(path, "wb") as f:
+        f.write(hdr)
+        if not rle:
+            f.write(data.tobytes())
+        else:
+            for i in range(0, len(data), 128):
+                chunk = data[i:i + 128]
+                f.write(bytes([len(chunk) - 1]))
+                f.write(chunk.tobytes())
+    return path
+
+
 def quad(p0, p1, p2, p3):
     return np.array([p0, p1, p2, p3], dtype=np.float32), np.array([[0, 1, 2], [0, 2, 3]], dtype=np.int32)
 
@@ -307,7 +343,7 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
 # ----------------------------------------------------------------------------- C4: glossy / coated / glass materials
 def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
                     integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None,
-                    extra_materials=None, order=None, emitters=None, textures=None, uv_orco=False, **render_extra):
+                    extra_materials=None, order=None, emitters=None, textures=None, uv_orco=False, image_files=None, **render_extra):
     """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
     coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
     shinydiffuse; sun (1 degree, 4 samples) + point + area (8 samples) lights; pathtracing with 8 bounces
@@ -333,6 +369,9 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     M["shiny"] = create(yi, "material", "shiny", type="shinydiffusemat", color=(0.3, 0.5, 0.9, 1.0), diffuse_reflect=0.7,
                         specular_reflect=0.3, transparency=0.4, transmit_filter=0.8, fresnel_effect=True, IOR=1.6,
                         mirror_color=(1.0, 0.95, 0.9, 1.0), diffuse_brdf="oren_nayar", sigma=0.25)
+    for path, spec in (image_files or []):      # TGA files the image textures below name
+        write_tga(path, test_image(spec["w"], spec["h"], spec.get("seed", 5)), top=spec.get("top", False), rle=spec.get("rle", False),
+                  gray=spec.get("gray", False))
     for tname, tp in (textures or []):          # textures must exist before the texture_mapper nodes that name them
         create(yi, "texture", tname, **tp)
     for mname, mp in (extra_materials or []):   # e.g. rough_glass, blend_mat of two of the above, node materials

@@ -72,7 +72,12 @@ yb200_handle yb200_create_material  (yb200_ctx *c, const char *name);  /* shinyd
 yb200_handle yb200_create_camera    (yb200_ctx *c, const char *name);  /* perspective | architect | orthographic | angular */
 yb200_handle yb200_create_background(yb200_ctx *c, const char *name);  /* constant */
 yb200_handle yb200_create_integrator(yb200_ctx *c, const char *name);  /* directlighting | pathtracing | none (volume) */
-yb200_handle yb200_create_texture   (yb200_ctx *c, const char *name);  /* always fails: shader nodes/textures unsupported */
+yb200_handle yb200_create_texture   (yb200_ctx *c, const char *name);  /* rgb_cube | blend | clouds | marble | wood | image (basictex.cc, imagetex.cc) */
+/* Decoded pixels for an image texture, keyed by the `filename` the texture's parameters name: what imageHandler_t::getPixel
+ * (include/core_api/imagehandler.h:44) returns for that file - width*height RGBA floats, row 0 on top, index x + width*y;
+ * is_hdr = imageHandler_t::isHDR (no gamma).  The reference decodes files in its image-handler plugins; this library only
+ * reads TGA (24/32-bit true colour, 8-bit grey) itself, every other format has to be registered before yb200_create_texture. */
+int yb200_register_image(yb200_ctx *c, const char *file_name, const float *rgba, int width, int height, int is_hdr);
 yb200_handle yb200_create_volume_region(yb200_ctx *c, const char *name); /* always fails */
 
 /* ---- render: yafrayInterface_t::render + scene_t::render + imageFilm_t::flush

@@ -91,6 +91,39 @@ _BUMPED = dict(
                          nodes=[_mapper("bg", "tclouds", "uv", scale=(4.0, 4.0, 1.0), bump_strength=2.0)]))],
     order=["b_sd", "b_glossy", "b_coated", "b_glass", "gdiff", "b_sd", "mirror", "b_glossy"])
 
+# image textures (TGA files written by the scene builder): interpolation / clipping / repeat / crop modes, the cube / tube /
+# sphere projections of texture_mapper, bump and normal maps from images
+import os as _os
+import tempfile as _tempfile
+_TEXDIR = _os.path.join(_tempfile.gettempdir(), "yb200_tex")
+_IMG_A, _IMG_B, _IMG_C = (_os.path.join(_TEXDIR, n) for n in ("a32.tga", "b24_top_rle.tga", "c8.tga"))
+_IMAGED = dict(
+    uv_orco=True,
+    image_files=[(_IMG_A, dict(w=32, h=16, seed=5)), (_IMG_B, dict(w=20, h=24, seed=6, top=True, rle=True)),
+                 (_IMG_C, dict(w=16, h=16, seed=7, gray=True))],
+    textures=[("ia", dict(type="image", filename=_IMG_A, gamma=2.2)),
+              ("ia_none", dict(type="image", filename=_IMG_A, interpolate="none", clipping="checker", even_tiles=True, odd_tiles=False,
+                               checker_dist=0.2, xrepeat=1, yrepeat=1)),
+              ("ib_cubic", dict(type="image", filename=_IMG_B, interpolate="bicubic", clipping="repeat", xrepeat=3, yrepeat=2, rot90=True)),
+              ("ib_clip", dict(type="image", filename=_IMG_B, clipping="clip", cropmin_x=0.1, cropmax_x=0.8, cropmin_y=0.2, cropmax_y=0.9)),
+              ("ic", dict(type="image", filename=_IMG_C, clipping="extend")),
+              ("inorm", dict(type="image", filename=_IMG_A, normalmap=True))],
+    extra_materials=[
+        ("i_uv", dict(type="shinydiffusemat", color=(1.0, 1.0, 1.0, 1.0), diffuse_reflect=0.9, diffuse_shader="m",
+                      nodes=[_mapper("m", "ia", "uv")])),
+        ("i_checker", dict(type="shinydiffusemat", color=(0.8, 0.8, 0.8, 1.0), diffuse_reflect=0.9, diffuse_shader="lay",
+                           nodes=[_mapper("m", "ia_none", "uv", scale=(4.0, 4.0, 1.0)),
+                                  dict(name="lay", type="layer", input="m", mode=0, upper_color=(0.9, 0.9, 0.2, 1.0), use_alpha=True)])),
+        ("i_cube", dict(type="glossy", color=(0.9, 0.6, 0.3, 1.0), diffuse_color=(0.5, 0.2, 0.1, 1.0), diffuse_reflect=0.6, glossy_reflect=0.5,
+                        exponent=60.0, as_diffuse=False, diffuse_shader="m", bump_shader="bm",
+                        nodes=[_mapper("m", "ib_cubic", "orco", mapping="cube"), _mapper("bm", "ic", "uv", scale=(2.0, 2.0, 1.0), bump_strength=2.0)])),
+        ("i_tube", dict(type="shinydiffusemat", color=(0.8, 0.8, 0.8, 1.0), diffuse_reflect=0.9, diffuse_shader="m", transparency_shader="t",
+                        transmit_filter=0.5, nodes=[_mapper("m", "ib_clip", "orco", mapping="tube"), _mapper("t", "ic", "orco", mapping="sphere")])),
+        ("i_normal", dict(type="coated_glossy", color=(0.8, 0.2, 0.2, 1.0), diffuse_color=(0.6, 0.1, 0.1, 1.0), diffuse_reflect=0.5,
+                          glossy_reflect=0.6, exponent=80.0, IOR=1.4, as_diffuse=False, bump_shader="nm",
+                          nodes=[_mapper("nm", "inorm", "uv", bump_strength=0.5)]))],
+    order=["i_uv", "i_checker", "i_cube", "i_tube", "i_normal", "i_uv", "mirror", "i_cube"])
+
 IMAGE_CASES = {
     # BASELINE.json configs[0] (reduced): Cornell box, shinydiffuse + mirror component, area light, directlighting
     "c1_cornell_direct": (scenes.cornell_box, dict(width=64, height=64, spp=4, light_samples=4, mirror_box=True)),
@@ -138,6 +171,8 @@ IMAGE_CASES = {
                                                          integ_params=dict(transpShad=True, shadowDepth=4), **_TEXTURED)),
     "c4_bump_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_BUMPED)),
     "c4_bump_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=3, **_BUMPED)),
+    "c4_imagetex_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_IMAGED)),
+    "c4_imagetex_path": (scenes.materials_scene, dict(width=64, height=36, spp=1, bounces=3, **_IMAGED)),
     # depth of field with a polygonal lens (perspectiveCam_t::sampleTSD / biasDist)
     "c4_materials_dof_hexagon": (scenes.materials_scene, dict(width=64, height=36, spp=3, integrator="directlighting",
                                                               cam_params=dict(aperture=0.15, dof_distance=10.0, bokeh_type="hexagon",

@@ -81,6 +81,10 @@ class TestHostLogic:
         yi.paramsPushList(); yi.paramsSetString("element", "shader_node"); yi.paramsSetString("name", "n")
         yi.paramsSetString("type", "texture_mapper"); yi.paramsSetString("texture", "missing"); yi.paramsEndList()
         assert yi.createMaterial("withnodes") == 0 and "does not exist" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "image"); yi.paramsSetString("filename", "/nonexistent/picture.png")
+        assert yi.createTexture("png") == 0 and "register" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "image"); yi.paramsSetString("filename", "/nonexistent/picture.tga")
+        assert yi.createTexture("tga") == 0 and "Cannot open" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "voronoi")
         assert yi.createTexture("vor") == 0 and "not supported" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "clouds"); yi.paramsSetString("noise_type", "blender")
@@ -91,6 +95,36 @@ class TestHostLogic:
         assert yi.createTexture("t") == 0 and yi.createVolumeRegion("v") == 0
         yi.paramsClearAll(); yi.paramsSetString("type", "shinydiffusemat")
         assert yi.createMaterial("dup") != 0 and yi.createMaterial("dup") == 0     # name clash (environment.cc:226)
+
+    def test_registered_image_equals_tga_file(self, tmp_path):
+        """yb200_register_image (decoded pixels handed over by the caller) and the built-in TGA reader feed the same texture."""
+        import numpy as np
+        from core_b200 import scenes as sc
+        img8 = sc.test_image(24, 12, seed=9)
+        path = sc.write_tga(str(tmp_path / "t.tga"), img8, top=False, rle=True)
+        frames = []
+        for registered in (False, True):
+            yi = refapi.EmuInterface(); yi.setVerbosityMute()
+            name = path if not registered else "memory://picture.png"
+            if registered:
+                px = (img8.astype(np.float64) * 0.00392156862745098039).astype(np.float32)
+                assert yi.registerImage(name, px)
+            yi.startScene(0)
+            sc.create(yi, "texture", "pic", type="image", filename=name, interpolate="bicubic")
+            m = sc.create(yi, "material", "m", type="shinydiffusemat", color=(1.0, 1.0, 1.0, 1.0), diffuse_shader="map",
+                          nodes=[dict(name="map", type="texture_mapper", texture="pic", texco="global", scale=(0.5, 0.5, 0.5))])
+            yi.startGeometry()
+            sc.add_mesh(yi, *sc.quad((-2, -2, 0), (2, -2, 0), (2, 2, 0), (-2, 2, 0)), m, bulk=False)
+            yi.endGeometry()
+            sc.create(yi, "light", "pt", type="pointlight", color=(1.0, 1.0, 1.0, 1.0), power=30.0, **{"from": (0.5, 0.3, 3.0)})
+            sc.create(yi, "camera", "cam", type="perspective", to=(0.0, 0.0, 0.0), up=(0.0, 1.0, 5.0), resx=24, resy=24, focal=1.0,
+                      **{"from": (0.0, 0.0, 5.0)})
+            sc.create(yi, "background", "bg", type="constant", color=(0.0, 0.0, 0.0, 1.0))
+            sc.create(yi, "integrator", "default", type="directlighting")
+            sc.std_volintegr(yi)
+            sc.set_render(yi, 24, 24, spp=1)
+            frames.append(yi.render(24, 24))
+        assert frames[0][..., :3].std() > 0.01 and np.array_equal(frames[0], frames[1])
 
     def test_render_requires_volume_integrator_none(self):
         yi = refapi.EmuInterface()
