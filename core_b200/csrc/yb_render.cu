@@ -63,14 +63,24 @@ YB_KERNEL(k_trace_shadow, RenderArgs)
 // ---- shading order.  After the first wave the tasks of one warp take very different code paths (hit / miss, the
 // light estimateOneDirectLight picks): measured 8 of 32 lanes active.  Tasks are binned by a small key so that warps
 // of the shade kernel are homogeneous; the kernel then gathers its task through `order`.
-#define YB_SHADE_BINS 8
+#define YB_SHADE_BINS 32
+// key: 0 = miss; 1..7 = integrate() task by material type of the hit (the BSDF code of the material classes shares nothing, and
+// recursiveRaytrace children of a glossy / specular surface land on every material: 1080p materials scene, shade 14.4 s -> see
+// profiles/); 8..31 = path vertex by (light estimateOneDirectLight picks: 0, 1, 2+) x (material type)
 YB_D uint32_t shade_key(const RenderArgs &a, uint32_t t)
 {
-    if (a.hits[t].tri < 0) return 0u;
+    const int tri = a.hits[t].tri;
+    if (tri < 0) return 0u;
     const uint32_t bits = a.tasks[t].bits;
-    if (task_kind(bits) == TASK_INTEGRATE) return 1u;
+    if (task_kind(bits) == TASK_INTEGRATE) {
+        const uint32_t info = (uint32_t)f2i(a.sc.tri_v[3 * (size_t)tri + 1].w);
+        const uint32_t ty = (uint32_t)a.sc.materials[info & TRI_MAT_MASK].type;
+        return 1u + (ty < 6u ? ty : 6u);
+    }
+    const uint32_t info = (uint32_t)f2i(a.sc.tri_v[3 * (size_t)tri + 1].w);
+    const uint32_t ty = (uint32_t)a.sc.materials[info & TRI_MAT_MASK].type;
     const int l = pick_one_light((int)a.tasks[t].pathOffs, a.sc.nLights);
-    return 2u + (uint32_t)(l < YB_SHADE_BINS - 3 ? l : YB_SHADE_BINS - 3);
+    return 8u + 8u * (uint32_t)(l < 2 ? l : 2) + (ty < 7u ? ty : 7u);
 }
 #ifndef YB_HOSTEMU
 __global__ void __launch_bounds__(256) k_bin_count_kernel(uint32_t n, const RenderArgs a)
