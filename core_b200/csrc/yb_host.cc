@@ -372,6 +372,17 @@ bool Context::loadTga(const std::string &fileName, HostImage &img)
 }
 
 // ------------------------------------------------------------------------------------------------ textures + shader nodes
+// newNoise (basictex.cc:26-50): generator id of yb_types.h for a noise_type string; anything unknown means newPerlin_t
+static bool noise_kind(const std::string &ntype, int &kind)
+{
+    kind = 0;
+    if (ntype == "blender") kind = 1;
+    else if (ntype == "stdperlin") kind = 9;
+    else if (ntype.find("voronoi") != std::string::npos)
+        kind = ntype == "voronoi_f2" ? 4 : (ntype == "voronoi_f3" ? 5 : (ntype == "voronoi_f4" ? 6 : (ntype == "voronoi_f2f1" ? 7 : (ntype == "voronoi_crackle" ? 8 : 3))));
+    else if (ntype == "cellnoise") kind = 2;
+    return true;
+}
 uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 + src/textures/basictex.cc factories
 {
     std::string type;
@@ -382,11 +393,7 @@ uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 +
     memset((void *)&t, 0, sizeof(t));
     t.color1 = col3(0.f); t.color2 = col3(1.f); t.depth = 2; t.size = 1.f; t.turb = 1.f; t.sharpness = 1.f;
     std::string ntype, s;
-    if (p.get("noise_type", ntype) && ntype != "newperlin" && ntype != "")
-        // newNoise (basictex.cc:26-50): anything but blender / stdperlin / voronoi_* / cellnoise means newPerlin_t
-        if (ntype == "blender" || ntype == "stdperlin" || ntype == "cellnoise" || ntype.find("voronoi") != std::string::npos) {
-            fail("texture '" + std::string(name) + "': noise_type '" + ntype + "' is not supported (newperlin only)"); return 0;
-        }
+    if (p.get("noise_type", ntype) && !noise_kind(ntype, t.noiseType)) { fail("texture '" + std::string(name) + "': noise_type 'stdperlin' is not supported"); return 0; }
     if (type == "rgb_cube") t.type = TEX_RGB_CUBE;
     else if (type == "blend") t.type = TEX_BLEND;
     else if (type == "clouds") {                     // basictex.cc:82-98
@@ -403,6 +410,31 @@ uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 +
         if (t.type == TEX_MARBLE) { p.get("sharpness", shp); if (shp > 1) t.sharpness = (float)(1.0 / (double)shp); }
         else if (p.get("wood_type", s)) t.rings = s == "rings";
         if (p.get("shape", s)) t.wshape = s == "saw" ? 1 : (s == "tri" ? 2 : 0);
+    } else if (type == "voronoi") {                  // basictex.cc:320-344
+        std::string cltype, dname; float fw1 = 1, fw2 = 0, fw3 = 0, fw4 = 0, mex = 2.5f, isc = 1, sz = 1;
+        p.getColor("color1", t.color1); p.getColor("color2", t.color2);
+        if (p.get("color_type", cltype)) t.coltype = cltype == "col1" ? 1 : (cltype == "col2" ? 2 : (cltype == "col3" ? 3 : 0));
+        p.get("weight1", fw1); p.get("weight2", fw2); p.get("weight3", fw3); p.get("weight4", fw4);
+        p.get("mk_exponent", mex); p.get("intensity", isc); p.get("size", sz); p.get("distance_metric", dname);
+        t.type = TEX_VORONOI; t.size = sz; t.mkExp = mex;
+        t.distMetric = (dname == "squared" || dname == "manhattan") ? 1 : (dname == "chebychev" ? 2 : (dname == "minkovsky_half" ? 3 : (dname == "minkovsky_four" ? 4 : (dname == "minkovsky" ? 5 : 0))));
+        t.vw[0] = fw1; t.vw[1] = fw2; t.vw[2] = fw3; t.vw[3] = fw4;
+        for (int k = 0; k < 4; ++k) t.vaw[k] = fabsf(t.vw[k]);
+        t.iscale = t.vaw[0] + t.vaw[1] + t.vaw[2] + t.vaw[3];
+        if (t.iscale != 0) t.iscale = isc / t.iscale;
+    } else if (type == "musgrave") {                 // basictex.cc:385-407
+        std::string mtype; float H = 1, lacu = 2, octs = 2, offs = 1, gain = 1, size = 1, iscale = 1;
+        p.getColor("color1", t.color1); p.getColor("color2", t.color2); p.get("musgrave_type", mtype);
+        p.get("H", H); p.get("lacunarity", lacu); p.get("octaves", octs); p.get("offset", offs); p.get("gain", gain); p.get("size", size); p.get("intensity", iscale);
+        t.type = TEX_MUSGRAVE; t.size = size; t.iscale = iscale;
+        t.musType = mtype == "multifractal" ? 1 : (mtype == "heteroterrain" ? 2 : (mtype == "hybridmf" ? 3 : (mtype == "ridgedmf" ? 4 : 0)));
+        t.musH = H; t.musLacu = lacu; t.musOcts = octs; t.musOffs = offs; t.musGain = gain;
+    } else if (type == "distorted_noise") {          // basictex.cc:443-458
+        std::string n1, n2; float dist = 1, size = 1; int k1 = 0, k2 = 0;
+        p.getColor("color1", t.color1); p.getColor("color2", t.color2); p.get("distort", dist); p.get("size", size);
+        if (p.get("noise_type1", n1) && !noise_kind(n1, k1)) { fail("texture '" + std::string(name) + "': noise_type1 'stdperlin' is not supported"); return 0; }
+        if (p.get("noise_type2", n2) && !noise_kind(n2, k2)) { fail("texture '" + std::string(name) + "': noise_type2 'stdperlin' is not supported"); return 0; }
+        t.type = TEX_DISTNOISE; t.size = size; t.distort = dist; t.noiseType = k1; t.noiseType2 = k2;
     } else if (type == "image") {                    // imagetex.cc:241-340
         std::string fname, intpstr, clip;
         double gamma = 1.0, minx = 0.0, miny = 0.0, maxx = 1.0, maxy = 1.0, cdist = 0.0; bool normalmap = false, rot90 = false, even = false, odd = true;
@@ -435,7 +467,7 @@ uintptr_t Context::createTexture(const char *name)   // environment.cc:252-290 +
         texPixOffset[textures.size()] = texPixels.size();
         texPixels.insert(texPixels.end(), im.px.begin(), im.px.end());
     } else {
-        fail("Environment: texture type '" + type + "' is not supported by the B200 path (supported: rgb_cube, blend, clouds, marble, wood, image)");
+        fail("Environment: texture type '" + type + "' is not supported by the B200 path (supported: rgb_cube, blend, clouds, marble, wood, voronoi, musgrave, distorted_noise, image)");
         return 0;
     }
     texPixOffset.resize(textures.size() + 1, (size_t)-1);

@@ -18,6 +18,13 @@ namespace yb {
 #define YB_NTABLE static
 #endif
 #include "yb_noise_tab.inc"
+// texture / node evaluation is called from many places of the (fully inlined) shade kernel with small by-value arguments:
+// out of line it keeps the EXT = 2 build at a compilable size (-DYB_INLINE_NODES restores inlining for A/B runs)
+#if defined(__CUDACC__) && !defined(YB_HOSTEMU) && !defined(YB_INLINE_NODES)
+#define YB_HD_NODE static __host__ __device__ __noinline__
+#else
+#define YB_HD_NODE YB_HD
+#endif
 
 struct NodeRes { float r, g, b, a, f; };          // nodeResult_t: colorA_t + scalar (shader.h:32-38)
 struct TexPoint { float U, V; v3 orcoP, orcoNg, dSdU, dSdV; };   // the surfacePoint_t fields texture_mapper reads besides P / Ng / NU / NV
@@ -46,16 +53,205 @@ YB_HD float newPerlin(v3 pt)
                                      np_lerp(u, np_grad(nperm(AB + 1), x, y - 1, z - 1), np_grad(nperm(BB + 1), x - 1, y - 1, z - 1))));
     return (float)(0.5 + 0.5 * (double)nv);
 }
-YB_HD float turbulence(v3 pt, int oct, float size, bool hard)
+// blenderNoise_t (noise.cc:373-447)
+YB_HD float blenderNoise(v3 pt)
+{
+    float cn1, cn2, cn3, cn4, cn5, cn6, i;
+    const float *h;
+    float ox, oy, oz, jx, jy, jz;
+    float n = 0.5f;
+    int ix, iy, iz, b00, b01, b10, b11, b20, b21;
+    const float x = pt.x, y = pt.y, z = pt.z;
+    ox = (x - (float)(ix = (int)floorf(x)));
+    oy = (y - (float)(iy = (int)floorf(y)));
+    oz = (z - (float)(iz = (int)floorf(z)));
+    jx = ox - 1; jy = oy - 1; jz = oz - 1;
+    cn1 = ox * ox; cn2 = oy * oy; cn3 = oz * oz;
+    cn4 = jx * jx; cn5 = jy * jy; cn6 = jz * jz;
+    cn1 = (float)(1.0 - 3.0 * (double)cn1 + 2.0 * (double)cn1 * (double)ox);
+    cn2 = (float)(1.0 - 3.0 * (double)cn2 + 2.0 * (double)cn2 * (double)oy);
+    cn3 = (float)(1.0 - 3.0 * (double)cn3 + 2.0 * (double)cn3 * (double)oz);
+    cn4 = (float)(1.0 - 3.0 * (double)cn4 - 2.0 * (double)cn4 * (double)jx);
+    cn5 = (float)(1.0 - 3.0 * (double)cn5 - 2.0 * (double)cn5 * (double)jy);
+    cn6 = (float)(1.0 - 3.0 * (double)cn6 - 2.0 * (double)cn6 * (double)jz);
+    b00 = nperm(nperm(ix & 255) + (iy & 255));
+    b10 = nperm(nperm((ix + 1) & 255) + (iy & 255));
+    b01 = nperm(nperm(ix & 255) + ((iy + 1) & 255));
+    b11 = nperm(nperm((ix + 1) & 255) + ((iy + 1) & 255));
+    b20 = iz & 255; b21 = (iz + 1) & 255;
+    i = (cn1 * cn2 * cn3); h = yb_noise_vect + 3 * nperm(b20 + b00); n += i * (h[0] * ox + h[1] * oy + h[2] * oz);
+    i = (cn1 * cn2 * cn6); h = yb_noise_vect + 3 * nperm(b21 + b00); n += i * (h[0] * ox + h[1] * oy + h[2] * jz);
+    i = (cn1 * cn5 * cn3); h = yb_noise_vect + 3 * nperm(b20 + b01); n += i * (h[0] * ox + h[1] * jy + h[2] * oz);
+    i = (cn1 * cn5 * cn6); h = yb_noise_vect + 3 * nperm(b21 + b01); n += i * (h[0] * ox + h[1] * jy + h[2] * jz);
+    i = cn4 * cn2 * cn3; h = yb_noise_vect + 3 * nperm(b20 + b10); n += i * (h[0] * jx + h[1] * oy + h[2] * oz);
+    i = cn4 * cn2 * cn6; h = yb_noise_vect + 3 * nperm(b21 + b10); n += i * (h[0] * jx + h[1] * oy + h[2] * jz);
+    i = cn4 * cn5 * cn3; h = yb_noise_vect + 3 * nperm(b20 + b11); n += i * (h[0] * jx + h[1] * jy + h[2] * oz);
+    i = (cn4 * cn5 * cn6); h = yb_noise_vect + 3 * nperm(b21 + b11); n += i * (h[0] * jx + h[1] * jy + h[2] * jz);
+    if (n < 0.0f) n = 0.0f; else if (n > 1.0f) n = 1.0f;
+    return n;
+}
+// distance metrics of voronoi_t (noise.cc:335-370)
+YB_HD float voronoi_dist(int dm, float x, float y, float z, float e)
+{
+    switch (dm) {
+        case 1: return x * x + y * y + z * z;
+        case 2: { x = fabsf(x); y = fabsf(y); z = fabsf(z); const float t = (x > y) ? x : y; return (z > t) ? z : t; }
+        case 3: { const float d = fSqrt(fabsf(x)) + fSqrt(fabsf(y)) + fSqrt(fabsf(z)); return d * d; }
+        case 4: { x *= x; y *= y; z *= z; return fSqrt(fSqrt(x * x + y * y + z * z)); }
+        case 5: return fPow(fPow(fabsf(x), e) + fPow(fabsf(y), e) + fPow(fabsf(z), e), 1.0f / e);
+        default: return fSqrt(x * x + y * y + z * z);
+    }
+}
+// voronoi_t::getFeatures (noise.cc:498-541): the four nearest feature points and their distances
+YB_HD void voronoi_features(v3 pt, int dm, float mex, float *da, v3 *pa)
+{
+    const float x = pt.x, y = pt.y, z = pt.z;
+    const int xi = (int)floorf(x), yi = (int)floorf(y), zi = (int)floorf(z);
+    da[0] = da[1] = da[2] = da[3] = 1e10f;
+    pa[0] = pa[1] = pa[2] = pa[3] = v3(0.f);
+    for (int xx = xi - 1; xx <= xi + 1; xx++)
+        for (int yy = yi - 1; yy <= yi + 1; yy++)
+            for (int zz = zi - 1; zz <= zi + 1; zz++) {
+                const float *p = yb_noise_pnt + 3 * nperm(nperm(nperm(zz & 255) + yy) + xx);   // HASHPNT (noise.cc:6)
+                const float xd = x - (p[0] + (float)xx), yd = y - (p[1] + (float)yy), zd = z - (p[2] + (float)zz);
+                const float d = voronoi_dist(dm, xd, yd, zd, mex);
+                const v3 q(p[0] + (float)xx, p[1] + (float)yy, p[2] + (float)zz);
+                if (d < da[0]) { da[3] = da[2]; da[2] = da[1]; da[1] = da[0]; da[0] = d; pa[3] = pa[2]; pa[2] = pa[1]; pa[1] = pa[0]; pa[0] = q; }
+                else if (d < da[1]) { da[3] = da[2]; da[2] = da[1]; da[1] = d; pa[3] = pa[2]; pa[2] = pa[1]; pa[1] = q; }
+                else if (d < da[2]) { da[3] = da[2]; da[2] = d; pa[3] = pa[2]; pa[2] = q; }
+                else if (d < da[3]) { da[3] = d; pa[3] = q; }
+            }
+}
+// voronoi_t::operator() as a noise basis: real distance (noise.cc:543-565)
+YB_HD float voronoiNoise(v3 pt, int vType)
+{
+    float da[4]; v3 pa[4];
+    voronoi_features(pt, 0, 2.5f, da, pa);
+    switch (vType) {
+        case 1: return da[1];
+        case 2: return da[2];
+        case 3: return da[3];
+        case 4: return da[1] - da[0];
+        case 5: { const float t = (float)(10.0 * (double)(da[1] - da[0])); return (t > 1.0f) ? 1.0f : t; }
+        default: return da[0];
+    }
+}
+YB_HD float cellNoise(v3 pt)                             // noise.cc:568-576
+{
+    const int xi = (int)floorf(pt.x), yi = (int)floorf(pt.y), zi = (int)floorf(pt.z);
+    unsigned int n = (unsigned int)(xi + yi * 1301 + zi * 314159);
+    n ^= (n << 13);
+    return (float)((double)(float)(n * (n * n * 15731u + 789221u) + 1376312589u) / 4294967296.0);
+}
+// stdPerlin_t (noise.cc:289-345)
+YB_HD void stdp_setup(float v, int &b0, int &b1, float &r0, float &r1)
+{
+    const float t = (float)((double)v + 10000.0);
+    b0 = ((int)t) & 255; b1 = (b0 + 1) & 255;
+    r0 = t - (float)(int)t; r1 = (float)((double)r0 - 1.0);
+}
+YB_HD float stdp_surve(float t) { return (float)((double)t * (double)t * (3.0 - 2.0 * (double)t)); }
+YB_HD float stdp_at(int gi, float rx, float ry, float rz) { const float *q = yb_stdp_g + 3 * gi; return rx * q[0] + ry * q[1] + rz * q[2]; }
+YB_HD float stdPerlin(v3 pt)
+{
+    int bx0, bx1, by0, by1, bz0, bz1;
+    float rx0, rx1, ry0, ry1, rz0, rz1;
+    stdp_setup(pt.x, bx0, bx1, rx0, rx1); stdp_setup(pt.y, by0, by1, ry0, ry1); stdp_setup(pt.z, bz0, bz1, rz0, rz1);
+    const int i = yb_stdp_p[bx0], j = yb_stdp_p[bx1];
+    const int b00 = yb_stdp_p[i + by0], b10 = yb_stdp_p[j + by0], b01 = yb_stdp_p[i + by1], b11 = yb_stdp_p[j + by1];
+    const float sx = stdp_surve(rx0), sy = stdp_surve(ry0), sz = stdp_surve(rz0);
+    float u, v, a, b;
+    u = stdp_at(b00 + bz0, rx0, ry0, rz0); v = stdp_at(b10 + bz0, rx1, ry0, rz0); a = np_lerp(sx, u, v);
+    u = stdp_at(b01 + bz0, rx0, ry1, rz0); v = stdp_at(b11 + bz0, rx1, ry1, rz0); b = np_lerp(sx, u, v);
+    const float c = np_lerp(sy, a, b);
+    u = stdp_at(b00 + bz1, rx0, ry0, rz1); v = stdp_at(b10 + bz1, rx1, ry0, rz1); a = np_lerp(sx, u, v);
+    u = stdp_at(b01 + bz1, rx0, ry1, rz1); v = stdp_at(b11 + bz1, rx1, ry1, rz1); b = np_lerp(sx, u, v);
+    const float d = np_lerp(sy, a, b);
+    return (float)(0.5 + 0.75 * (double)np_lerp(sz, c, d));
+}
+YB_HD float noise_gen(int noiseType, v3 p)
+{
+    if (noiseType == 0) return newPerlin(p);
+    if (noiseType == 1) return blenderNoise(p);
+    if (noiseType == 2) return cellNoise(p);
+    if (noiseType == 9) return stdPerlin(p);
+    return voronoiNoise(p, noiseType - 3);
+}
+YB_HD float turbulence(int noiseType, v3 pt, int oct, float size, bool hard)
 {
     float val, amp = 1, sum = 0;
-    v3 tp = pt * size;
+    v3 tp = (noiseType == 1 ? pt + v3(1.0f) : pt) * size;      // only blenderNoise_t::offset adds (1, 1, 1)
     for (int i = 0; i <= oct; i++, amp *= 0.5f, tp *= 2.0f) {
-        val = newPerlin(tp);
+        val = noise_gen(noiseType, tp);
         if (hard) val = fabsf((float)(2.0 * (double)val - 1.0));
         sum += amp * val;
     }
     return sum * ((float)(1 << oct) / (float)((1 << (oct + 1)) - 1));
+}
+YB_HD float signedNoise(int nt, v3 p) { return 2.0f * noise_gen(nt, p) - 1.0f; }          // noise.h:259-262
+// the five musgrave generators (noise.cc:594-745)
+YB_HD float musgrave(const Texture &t, v3 pt)
+{
+    const int nt = t.noiseType;
+    const float H = t.musH, lacunarity = t.musLacu, octaves = t.musOcts, offset = t.musOffs, gain = t.musGain;
+    const float pwHL = fPow(lacunarity, -H);
+    v3 tp = pt;
+    const float rmd = octaves - floorf(octaves);
+    if (t.musType == 1) {                       // mFractal_t
+        float value = 1, pwr = 1;
+        for (int i = 0; i < (int)octaves; i++) { value *= (pwr * signedNoise(nt, tp) + 1.0f); pwr *= pwHL; tp *= lacunarity; }
+        if (rmd != 0.0f) value *= (rmd * signedNoise(nt, tp) * pwr + 1.0f);
+        return value;
+    }
+    if (t.musType == 2) {                       // heteroTerrain_t
+        float pwr = pwHL;
+        float value = offset + signedNoise(nt, tp);
+        tp *= lacunarity;
+        for (int i = 1; i < (int)octaves; i++) { const float increment = (signedNoise(nt, tp) + offset) * pwr * value; value += increment; pwr *= pwHL; tp *= lacunarity; }
+        if (rmd != 0.0f) { const float increment = (signedNoise(nt, tp) + offset) * pwr * value; value += rmd * increment; }
+        return value;
+    }
+    if (t.musType == 3) {                       // hybridMFractal_t
+        float pwr = pwHL;
+        float result = signedNoise(nt, tp) + offset;
+        float weight = gain * result;
+        tp *= lacunarity;
+        for (int i = 1; (weight > 0.001f) && (i < (int)octaves); i++) {
+            if (weight > 1.0f) weight = 1.0f;
+            const float signal = (signedNoise(nt, tp) + offset) * pwr;
+            pwr *= pwHL;
+            result += weight * signal;
+            weight *= gain * signal;
+            tp *= lacunarity;
+        }
+        if (rmd != 0.0f) result += rmd * ((signedNoise(nt, tp) + offset) * pwr);
+        return result;
+    }
+    if (t.musType == 4) {                       // ridgedMFractal_t
+        float pwr = pwHL;
+        float signal = offset - fabsf(signedNoise(nt, tp));
+        signal *= signal;
+        float result = signal, weight = 1.0f;
+        for (int i = 1; i < (int)octaves; i++) {
+            tp *= lacunarity;
+            weight = signal * gain;
+            if (weight > 1.0f) weight = 1.0f; else if (weight < 0.0f) weight = 0.0f;
+            signal = offset - fabsf(signedNoise(nt, tp));
+            signal *= signal;
+            signal *= weight;
+            result += signal * pwr;
+            pwr *= pwHL;
+        }
+        return result;
+    }
+    float value = 0, pwr = 1;                   // fBm_t
+    for (int i = 0; i < (int)octaves; i++) { value += signedNoise(nt, tp) * pwr; pwr *= pwHL; tp *= lacunarity; }
+    if (rmd != 0.f) value += rmd * signedNoise(nt, tp) * pwr;
+    return value;
+}
+YB_HD float voronoi_intensity(const Texture &t, const float *da)
+{
+    return t.iscale * fabsf(t.vw[0] * da[0] + t.vw[1] * da[1] + t.vw[2] * da[2] + t.vw[3] * da[3]);
 }
 YB_HD float wave_shape(int wshape, float w)             // the shape switch of marble / wood (basictex.cc:112-124,180-192)
 {
@@ -142,7 +338,7 @@ YB_HD bool img_doMapping(const Texture &t, v3 &texpt)
     }
     return false;
 }
-YB_HD C4 img_getNoGammaColor(const Texture &t, v3 p)
+YB_HD_NODE C4 img_getNoGammaColor(const Texture &t, v3 p)
 {
     v3 p1(p.x, -p.y, p.z);
     C4 ret; ret.r = ret.g = ret.b = ret.a = 0.f;
@@ -151,7 +347,7 @@ YB_HD C4 img_getNoGammaColor(const Texture &t, v3 p)
 }
 
 // ---- textures: texture_t::getFloat / getColor --------------------------------------------------------
-YB_HD float tex_getFloat(const Texture &t, v3 p)
+YB_HD_NODE float tex_getFloat(const Texture &t, v3 p)
 {
     switch (t.type) {
         case TEX_RGB_CUBE: {
@@ -159,32 +355,61 @@ YB_HD float tex_getFloat(const Texture &t, v3 p)
             return (r + g + b) * 0.333333f;                                  // color_t::energy
         }
         case TEX_IMAGE: { const C4 c = img_getNoGammaColor(t, p); return 0.2126f * c.r + 0.7152f * c.g + 0.0722f * c.b; }   // texture.h:38: col2bri of the NO-gamma colour
+        case TEX_VORONOI: { float da[4]; v3 pa[4]; voronoi_features(p * t.size, t.distMetric, t.mkExp, da, pa); return voronoi_intensity(t, da); }
+        case TEX_MUSGRAVE: return t.iscale * musgrave(t, p * t.size);
+        case TEX_DISTNOISE: {                                                // basictex.cc:427-435
+            const v3 ofs(13.5f, 13.5f, 13.5f);
+            const v3 tp = p * t.size;
+            const v3 rv(signedNoise(t.noiseType, tp + ofs), signedNoise(t.noiseType, tp), signedNoise(t.noiseType, tp - ofs));
+            return signedNoise(t.noiseType2, tp + rv * t.distort);
+        }
         case TEX_BLEND: {
             float blend = (float)(0.5 * ((double)p.x + 1.));
             return fmaxf_(0.f, fminf_(blend, 1.f));
         }
         case TEX_CLOUDS: {
-            float v = turbulence(p, t.depth, t.size, t.hard != 0);
+            float v = turbulence(t.noiseType, p, t.depth, t.size, t.hard != 0);
             if (t.bias) { v *= v; if (t.bias == 1) return -v; }
             return v;
         }
         case TEX_MARBLE: {
-            float w = (float)((double)(p.x + p.y + p.z) * 5.0 + ((t.turb == 0.0f) ? 0.0 : (double)(t.turb * turbulence(p, t.depth, t.size, t.hard != 0))));
+            float w = (float)((double)(p.x + p.y + p.z) * 5.0 + ((t.turb == 0.0f) ? 0.0 : (double)(t.turb * turbulence(t.noiseType, p, t.depth, t.size, t.hard != 0))));
             return fPow(wave_shape(t.wshape, w), t.sharpness);
         }
         default: {                                                           // TEX_WOOD
             float w;
             if (t.rings) w = (float)((double)fSqrt(p.x * p.x + p.y * p.y + p.z * p.z) * 20.0);
             else w = (float)((double)(p.x + p.y + p.z) * 10.0);
-            w += (t.turb == 0.0f) ? 0.0f : t.turb * turbulence(p, t.depth, t.size, t.hard != 0);
+            w += (t.turb == 0.0f) ? 0.0f : t.turb * turbulence(t.noiseType, p, t.depth, t.size, t.hard != 0);
             return wave_shape(t.wshape, w);
         }
     }
 }
-YB_HD void tex_getColor(const Texture &t, v3 p, float *c)
+YB_HD_NODE void tex_getColor(const Texture &t, v3 p, float *c)
 {
     if (t.type == TEX_RGB_CUBE) { c[0] = clamp01f(p.x); c[1] = clamp01f(p.y); c[2] = clamp01f(p.z); c[3] = 1.f; return; }
     if (t.type == TEX_BLEND) { c[0] = c[1] = c[2] = c[3] = 1.f; return; }
+    if (t.type == TEX_VORONOI) {                                             // basictex.cc:288-318
+        float da[4]; v3 pa[4];
+        voronoi_features(p * t.size, t.distMetric, t.mkExp, da, pa);
+        const float inte = voronoi_intensity(t, da);
+        if (!t.coltype) { c[0] = c[1] = c[2] = c[3] = inte; return; }
+        float col[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int k = 0; k < 4; ++k) {                                        // aw_k * cellNoiseColor(pa[k]) (noise.cc:748-755), alpha 1
+            const int xi = (int)floorf(pa[k].x), yi = (int)floorf(pa[k].y), zi = (int)floorf(pa[k].z);
+            const float *cl = yb_noise_pnt + 3 * nperm(nperm(nperm(zi & 255) + yi) + xi);
+            col[0] += t.vaw[k] * cl[0]; col[1] += t.vaw[k] * cl[1]; col[2] += t.vaw[k] * cl[2]; col[3] += t.vaw[k] * 1.0f;
+        }
+        float mulv = t.iscale;
+        if (t.coltype >= 2) {
+            float t1 = (float)((double)(da[1] - da[0]) * 10.0);
+            if (t1 > 1) t1 = 1;
+            if (t.coltype == 3) t1 *= inte; else t1 *= t.iscale;
+            mulv = t1;
+        }
+        c[0] = col[0] * mulv; c[1] = col[1] * mulv; c[2] = col[2] * mulv; c[3] = col[3] * mulv;
+        return;
+    }
     if (t.type == TEX_IMAGE) {
         C4 r = img_getNoGammaColor(t, p);
         if (t.gamma != 1.f && !t.isHDR) { r.r = fPow(r.r, t.gamma); r.g = fPow(r.g, t.gamma); r.b = fPow(r.b, t.gamma); }
@@ -286,7 +511,7 @@ YB_HD v3 texmap_Ng(const ShaderNode &n, v3 Ng, const TexPoint &tp)        // the
 }
 // shaderNode_t::evalDerivative for bump mapping: texture_mapper on a procedural (non-discrete) texture (basicnodes.cc:218-232),
 // layer (layernode.cc:118-146); every other node type keeps the base-class zero (shader.h:83-84)
-YB_HD void node_evalDerivative(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, v3 NU, v3 NV, const TexPoint &tp, NodeRes *st, int self)
+YB_HD_NODE void node_evalDerivative(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, v3 NU, v3 NV, const TexPoint &tp, NodeRes *st, int self)
 {
     NodeRes r; r.r = r.g = r.b = r.a = r.f = 0.f;
     if (n.type == NODE_TEXMAP) {
@@ -332,7 +557,7 @@ YB_HD void node_evalDerivative(const ShaderNode &n, const Texture *textures, v3 
     st[self] = r;
 }
 
-YB_HD void node_eval(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, const TexPoint &tp, NodeRes *st, int self)
+YB_HD_NODE void node_eval(const ShaderNode &n, const Texture *textures, v3 P, v3 Ng, const TexPoint &tp, NodeRes *st, int self)
 {
     NodeRes r; r.r = r.g = r.b = r.a = r.f = 0.f;
     if (n.type == NODE_TEXMAP) {                      // textureMapper_t::eval

@@ -62,15 +62,24 @@ enum ShaderSlot : int32_t { SLOT_DIFFUSE = 0, SLOT_MIRROR_COLOR, SLOT_MIRROR, SL
 #define YB_MAX_NODES 8               // nodes per material (creation fails beyond)
 
 // texture_t implementations evaluated on the device (src/textures/basictex.cc): rgb_cube, blend, clouds, marble, wood with the
-// default noise generator (newPerlin_t, noise.cc:161-183)
-enum TexType : int32_t { TEX_RGB_CUBE = 0, TEX_BLEND, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD, TEX_IMAGE };
+// noise generators newPerlin_t (default), blenderNoise_t, voronoi_t (real distance), cellNoise_t (noise.cc)
+enum TexType : int32_t { TEX_RGB_CUBE = 0, TEX_BLEND, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD, TEX_IMAGE, TEX_VORONOI, TEX_MUSGRAVE, TEX_DISTNOISE };
 enum : int32_t { TCL_EXTEND = 0, TCL_CLIP, TCL_CLIPCUBE, TCL_REPEAT, TCL_CHECKER };   // imagetex.h:31-38
 enum : int32_t { TXP_PLAIN = 0, TXP_CUBE, TXP_TUBE, TXP_SPHERE };                 // basicnodes.h texture_mapper projection
 struct Texture {
     int32_t type;
     int32_t depth, hard, bias, wshape, rings;   // wshape: 0 sin, 1 saw, 2 tri
+    int32_t noiseType;                          // newNoise (basictex.cc:26-50): 0 newperlin, 1 blender, 2 cellnoise, 3..8 voronoi f1 f2 f3 f4 f2f1 crackle, 9 stdperlin
     float size, turb, sharpness;
     col3 color1, color2;
+    // textureVoronoi_t (basictex.cc:250-318): weights, |weights|, intensity scale, colour type, distance metric (0 real, 1 squared -
+    // also what 'manhattan' selects, noise.cc:453-456 -, 2 chebychev, 3 minkovsky 1/2, 4 minkovsky 4, 5 minkovsky e) and exponent
+    float vw[4], vaw[4], iscale, mkExp;
+    int32_t coltype, distMetric;
+    // textureMusgrave_t (basictex.cc:346-383; 0 fBm, 1 multifractal, 2 heteroterrain, 3 hybridmf, 4 ridgedmf) and
+    // textureDistortedNoise_t (:409-441: second noise basis, distortion)
+    int32_t musType, noiseType2;
+    float musH, musLacu, musOcts, musOffs, musGain, distort;
     // textureImage_t (src/textures/imagetex.cc:27-240): pixels = resx*resy RGBA floats of the image handler, row 0 on top
     const f4 *pixels;
     int32_t resx, resy, intp, isHDR, normalmap;          // intp: 0 none, 1 bilinear, 2 bicubic

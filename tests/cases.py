@@ -70,6 +70,46 @@ _TEXTURED = dict(
                                  dict(name="tl", type="mix", mode=6, input1="c2", color2=(0.5, 0.5, 0.5, 1.0), factor="tr")]))],
     order=["m_clouds", "m_layer", "m_glossy", "m_glass", "m_coated", "m_transp", "mirror", "gdiff"])
 
+# the other noise bases of newNoise (blender = Blender's default basis, voronoi f1..crackle, cellnoise) under clouds / marble / wood
+_NOISES = dict(
+    uv_orco=True,
+    textures=[("n_blender", dict(type="clouds", noise_type="blender", depth=3, size=3.0, color1=(0.9, 0.3, 0.1, 1.0), color2=(0.1, 0.3, 0.9, 1.0))),
+              ("n_blender_hard", dict(type="marble", noise_type="blender", depth=2, size=2.0, turbulence=5.0, hard=True, sharpness=3.0, shape="tri")),
+              ("n_vf1", dict(type="clouds", noise_type="voronoi_f1", depth=1, size=4.0)),
+              ("n_vf2f1", dict(type="wood", noise_type="voronoi_f2f1", depth=1, size=3.0, turbulence=3.0)),
+              ("n_crackle", dict(type="clouds", noise_type="voronoi_crackle", depth=0, size=5.0, color1=(1.0, 1.0, 0.8, 1.0), color2=(0.2, 0.1, 0.0, 1.0))),
+              ("n_cell", dict(type="clouds", noise_type="cellnoise", depth=0, size=6.0)),
+              ("n_vf3", dict(type="marble", noise_type="voronoi_f3", depth=1, size=2.0, turbulence=2.0)),
+              ("n_vf4", dict(type="clouds", noise_type="voronoi_f4", depth=0, size=3.0, bias="positive")),
+              ("n_std", dict(type="clouds", noise_type="stdperlin", depth=2, size=3.0, color1=(0.1, 0.5, 0.2, 1.0), color2=(1.0, 0.9, 0.7, 1.0)))],
+    extra_materials=[(("mn%d" % i), dict(type="shinydiffusemat", color=(1.0, 1.0, 1.0, 1.0), diffuse_reflect=0.9, diffuse_shader="m",
+                                         nodes=[_mapper("m", t, "orco" if i % 2 == 0 else "global", scale=(1.3, 1.3, 1.3))]))
+                     for i, t in enumerate(["n_blender", "n_blender_hard", "n_vf1", "n_vf2f1", "n_crackle", "n_cell", "n_vf3", "n_std"])],
+    order=["mn%d" % i for i in range(8)])
+
+# voronoi (every distance metric and colour type), musgrave (five generators) and distorted-noise textures
+_PROCS = dict(
+    uv_orco=True,
+    textures=[("v_int", dict(type="voronoi", size=3.0, weight1=1.0, weight2=0.5, intensity=1.2)),
+              ("v_col1", dict(type="voronoi", size=4.0, color_type="col1", weight1=0.7, weight2=-0.3, weight3=0.2, distance_metric="manhattan")),
+              ("v_col2", dict(type="voronoi", size=3.5, color_type="col2", weight1=1.0, weight4=0.4, distance_metric="chebychev")),
+              ("v_col3", dict(type="voronoi", size=2.5, color_type="col3", weight1=1.0, weight2=1.0, distance_metric="minkovsky", mk_exponent=3.0)),
+              ("v_mh", dict(type="voronoi", size=3.0, weight2=1.0, weight1=0.0, distance_metric="minkovsky_half")),
+              ("v_m4", dict(type="voronoi", size=3.0, weight1=1.0, distance_metric="minkovsky_four", intensity=0.8)),
+              ("m_fbm", dict(type="musgrave", musgrave_type="fBm", H=0.8, lacunarity=2.1, octaves=3.5, size=2.0, intensity=0.7,
+                             color1=(0.1, 0.2, 0.5, 1.0), color2=(1.0, 0.9, 0.6, 1.0))),
+              ("m_mf", dict(type="musgrave", musgrave_type="multifractal", noise_type="blender", H=0.9, lacunarity=2.0, octaves=3.0, size=1.5, intensity=0.5)),
+              ("m_ht", dict(type="musgrave", musgrave_type="heteroterrain", H=1.0, lacunarity=2.0, octaves=2.5, offset=0.8, size=2.0, intensity=0.4)),
+              ("m_hy", dict(type="musgrave", musgrave_type="hybridmf", noise_type="voronoi_f1", H=0.3, lacunarity=2.2, octaves=4.0, offset=0.7, gain=1.2,
+                            size=1.5, intensity=0.6)),
+              ("m_rd", dict(type="musgrave", musgrave_type="ridgedmf", H=1.0, lacunarity=2.0, octaves=4.0, offset=1.0, gain=2.0, size=1.5, intensity=0.5)),
+              ("dn", dict(type="distorted_noise", noise_type1="blender", noise_type2="cellnoise", distort=1.5, size=3.0,
+                          color1=(0.9, 0.9, 0.2, 1.0), color2=(0.2, 0.1, 0.6, 1.0))),
+              ("dn2", dict(type="distorted_noise", distort=0.8, size=2.0))],
+    extra_materials=[(("mp%d" % i), dict(type="shinydiffusemat", color=(1.0, 1.0, 1.0, 1.0), diffuse_reflect=0.9, diffuse_shader="m",
+                                         nodes=[_mapper("m", t, "orco" if i % 2 == 0 else "global", scale=(1.2, 1.2, 1.2))]))
+                     for i, t in enumerate(["v_int", "v_col1", "v_col2", "v_col3", "v_mh", "v_m4", "m_fbm", "m_mf", "m_ht", "m_hy", "m_rd", "dn", "dn2"])])
+
 # bump mapping from procedural textures (textureMapper_t::evalDerivative, layer derivative chain, material_t::applyBump)
 _BUMPED = dict(
     uv_orco=True,
@@ -169,6 +209,11 @@ IMAGE_CASES = {
     "c4_textured_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4, **_TEXTURED)),
     "c4_textured_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
                                                          integ_params=dict(transpShad=True, shadowDepth=4), **_TEXTURED)),
+    "c4_noises_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_NOISES)),
+    "c4_procs_a_direct": (scenes.materials_scene, dict(width=80, height=45, spp=1, integrator="directlighting",
+                                                       order=["mp%d" % i for i in range(8)], **_PROCS)),
+    "c4_procs_b_direct": (scenes.materials_scene, dict(width=80, height=45, spp=1, integrator="directlighting",
+                                                       order=["mp%d" % i for i in (8, 9, 10, 11, 12, 0, 3, 6)], **_PROCS)),
     "c4_bump_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_BUMPED)),
     "c4_bump_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=3, **_BUMPED)),
     "c4_imagetex_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_IMAGED)),

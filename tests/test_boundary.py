@@ -85,10 +85,8 @@ class TestHostLogic:
         assert yi.createTexture("png") == 0 and "register" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "image"); yi.paramsSetString("filename", "/nonexistent/picture.tga")
         assert yi.createTexture("tga") == 0 and "Cannot open" in yi.lastError()
-        yi.paramsClearAll(); yi.paramsSetString("type", "voronoi")
-        assert yi.createTexture("vor") == 0 and "not supported" in yi.lastError()
-        yi.paramsClearAll(); yi.paramsSetString("type", "clouds"); yi.paramsSetString("noise_type", "blender")
-        assert yi.createTexture("cl") == 0 and "noise_type" in yi.lastError()
+        yi.paramsClearAll(); yi.paramsSetString("type", "fractal_flames")
+        assert yi.createTexture("ff") == 0 and "not supported" in yi.lastError()
         yi.paramsClearAll(); yi.paramsSetString("type", "glass"); yi.paramsSetFloat("dispersion_power", 0.1)
         assert yi.createMaterial("disp") == 0
         yi.paramsClearAll()
