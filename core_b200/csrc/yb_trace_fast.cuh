@@ -115,7 +115,7 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
 // encodes 0x3F800000 as the immediate and re-materialises the selector in a register before each of the 48 PRMTs.
 __device__ __forceinline__ float plane_f(uint32_t w, uint32_t one, uint32_t sel) { return __uint_as_float(__byte_perm(w, one, sel)); }
 
-template <bool ANYHIT, int OUT>
+template <bool ANYHIT, int OUT, bool SORTED>
 __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
 {
     __shared__ uint2 sstack[YB_SSTACK][YB_TB];
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                 if (!active) {
                     uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
                     if (i < job.n) {
-                        if (job.order) i = __ldg(job.order + i);
+                        if (SORTED) i = __ldg(job.order + i);          // coherence-sorted fetch order (opt-in, measured slower: DESIGN.md)
                         const float4 r0 = __ldg((const float4 *)(job.rays + (size_t)i * job.stride));
                         const float4 r1 = __ldg((const float4 *)(job.rays + (size_t)i * job.stride + 16));
                         rayIdx = i;
@@ -313,7 +313,7 @@ static void launch_trace_fast(const FastJob &job, rt_stream s)
     g_stat_rays += job.n;
 #endif
     *job.counter = 0;
-    k_trace_fast<ANYHIT, OUT>(job);
+    if (job.order) k_trace_fast<ANYHIT, OUT, true>(job); else k_trace_fast<ANYHIT, OUT, false>(job);
     g_kernel_launches++;
     return;
 #else
@@ -324,7 +324,8 @@ static void launch_trace_fast(const FastJob &job, rt_stream s)
     uint32_t blocks = (uint32_t)sms * 6u;
     const uint32_t need = (job.n + YB_TB - 1) / YB_TB;
     if (blocks > need) blocks = need;
-    k_trace_fast<ANYHIT, OUT><<<blocks, YB_TB, 0, s>>>(job);
+    if (job.order) k_trace_fast<ANYHIT, OUT, true><<<blocks, YB_TB, 0, s>>>(job);
+    else k_trace_fast<ANYHIT, OUT, false><<<blocks, YB_TB, 0, s>>>(job);
     YB_CUDA_CHECK(cudaGetLastError());
     g_kernel_launches++;
 #endif

@@ -25,7 +25,14 @@ CONFIGS = {
            scenes.terrain, dict(grid=5000, width=3840, height=2160, spp=64, bounces=4), 1),
 }
 
-for key in (sys.argv[1:] or list(CONFIGS)):
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import cases  # noqa: E402  (the textured / bumped material sets of the parity cases, at full resolution)
+CONFIGS["c4tex"] = ("materials scene with procedural textures + shader nodes on every slot (tests/cases.py _TEXTURED), pathtracing 4 bounces, 1080p, 16 spp",
+                    scenes.materials_scene, dict(width=1920, height=1080, spp=16, bounces=4, **cases._TEXTURED), 2)
+CONFIGS["c4img"] = ("materials scene with image textures, projections, bump and normal maps (tests/cases.py _IMAGED), pathtracing 4 bounces, 1080p, 16 spp",
+                    scenes.materials_scene, dict(width=1920, height=1080, spp=16, bounces=4, **cases._IMAGED), 2)
+
+for key in (sys.argv[1:] or ["c1", "c2", "c3", "c4", "c5"]):
     desc, fn, kw, reps = CONFIGS[key]
     yi = YafrayInterface(device=0)
     t0 = time.time()
