@@ -455,6 +455,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         a.sc = c.sc; a.sc.film.minDepth = fz.minDepth; a.sc.film.maxDepth = fz.maxDepth; a.sc.film.n_samples = passSamples; a.sc.film.pass_offs = passOffs; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
         a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
         const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
+        const bool binFirst = env_size("YB200_BIN_FIRST", 0) != 0;      // also bin the camera wave (pixel order is already coherent)
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
         // coherence sort of the ray waves: 0 off, 1 closest-hit waves after the camera wave, 2 + shadow waves after the first, 3 all
         const int sortRays = (int)env_size("YB200_SORT_RAYS", 0);
@@ -493,7 +494,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 tc.stop();
                 tsd.start();
                 a.order = 0;
-                if (binShade && !firstWave) { bin_tasks((uint32_t)M, a, s); a.order = rb.order.p; }
+                if (binShade && (!firstWave || binFirst)) { bin_tasks((uint32_t)M, a, s); a.order = rb.order.p; }
                 if (nodeShade) launch_shade_nodes((uint32_t)M, a, s);
                 else if (extShade) launch_shade_ext((uint32_t)M, a, s);
                 else launch_shade_base((uint32_t)M, a, s);
