@@ -15,7 +15,10 @@ from core_b200.interface import YafrayInterface  # noqa: E402
 
 spp = int(os.environ.get("YB_PROFILE_SPP", "4"))
 yi = YafrayInterface(device=0)
-scenes.icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=spp, bounces=4)
+if os.environ.get("YB_PROFILE_SCENE", "c2") == "c4":      # BASELINE configs[3]: materials scene, pathtracing 8 bounces
+    scenes.materials_scene(yi, width=1920, height=1080, spp=spp, bounces=8)
+else:
+    scenes.icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=spp, bounces=4)
 yi.render(1920, 1080)
 torch.cuda.synchronize()
 torch.cuda.profiler.start()
