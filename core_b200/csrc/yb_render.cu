@@ -80,7 +80,7 @@ YB_D uint32_t shade_key(const RenderArgs &a, uint32_t t)
     const uint32_t info = (uint32_t)f2i(a.sc.tri_v[3 * (size_t)tri + 1].w);
     const uint32_t ty = (uint32_t)a.sc.materials[info & TRI_MAT_MASK].type;
     const int l = pick_one_light((int)a.tasks[t].pathOffs, a.sc.nLights);
-    return 8u + 8u * (uint32_t)(l < 2 ? l : 2) + (ty < 7u ? ty : 7u);
+    return 8u + 8u * (uint32_t)(l < 0 ? 0 : (l < 2 ? l : 2)) + (ty < 7u ? ty : 7u);      // l = -1 without lights
 }
 #ifndef YB_HOSTEMU
 __global__ void __launch_bounds__(256) k_bin_count_kernel(uint32_t n, const RenderArgs a)
