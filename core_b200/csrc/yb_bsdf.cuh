@@ -4,7 +4,8 @@
 //   coatedGlossyMat_t  src/materials/coatedglossy.cc:104-418
 //   glassMat_t/mirrorMat_t/nullMat_t  src/materials/glass.cc:84-253,336-390
 //   lightMat_t         src/materials/simple.cc:54-75
-// Constant-parameter forms only (shader nodes are rejected at creation).  The reference's behaviours
+// The BSDF code reads constants only: shader nodes are evaluated first and written over the constants of a local copy of the
+// record (mat_resolve at the end of this file).  The reference's behaviours
 // that look like bugs are kept on purpose: W = |wi.N|/(0.99 pdf + 0.01), no 1/pi, ...
 #pragma once
 #include "yb_types.h"

@@ -6,7 +6,7 @@
 //   newPerlin_t + turbulence                           src/textures/noise.cc:161-183,757-769, include/textures/noise.h:46-53
 // Every supported node is view independent, so a material's nodes are evaluated once per surface point (what initBSDF does
 // with allViewindep, e.g. shinydiffuse.cc:159-161) and the results replace the constants of a LOCAL copy of the Material
-// record (mat_resolve at the end of yb_bsdf.cuh); the BSDF code then runs unchanged.  Bump mapping is rejected at creation.
+// record (mat_resolve at the end of yb_bsdf.cuh); the BSDF code then runs unchanged.  Bump and normal mapping: node_evalDerivative + the frame update in mat_resolve.
 #pragma once
 #include "yb_types.h"
 

@@ -21,7 +21,7 @@ struct alignas(16) u4 { uint32_t x, y, z, w; };
 enum MatType : int32_t { MAT_SHINYDIFFUSE = 0, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_MIRROR, MAT_NULL, MAT_LIGHT, MAT_ROUGH_GLASS, MAT_BLEND };
 
 // One record per material; the union of the constant parameters of the supported material_t classes
-// (shader-node inputs are rejected at creation).  ~260 B, read through the read-only cache.
+// (shader-node inputs: the node table below + mat_resolve in yb_bsdf.cuh).  ~350 B, read through the read-only cache.
 struct Material {
     int32_t type;
     uint32_t bsdfFlags;

@@ -5,7 +5,7 @@
  * reference tree).  Plain pointers and sizes only; no C++/torch types cross this boundary.
  * All functions returning int return 1 on success and 0 on failure (the reference's `bool`);
  * on failure yb200_last_error() holds a "Y_ERROR"-style message.  Unsupported features
- * (materials, lights, volumes, universal scene mode, shader nodes ...) FAIL — there is no
+ * (unknown materials / lights, volumes, universal scene mode, photon maps ...) FAIL — there is no
  * CPU fallback anywhere in this library.
  */
 #ifndef YB200_H
@@ -67,8 +67,8 @@ void yb200_params_push_list (yb200_ctx *c);
 void yb200_params_end_list  (yb200_ctx *c);
 
 /* ---- factories: renderEnvironment_t::create* (src/yafraycore/environment.cc:189-479) keyed by "type" */
-yb200_handle yb200_create_light     (yb200_ctx *c, const char *name);  /* pointlight | sunlight | arealight | directional | spotlight | spherelight */
-yb200_handle yb200_create_material  (yb200_ctx *c, const char *name);  /* shinydiffusemat | glossy | coated_glossy | glass | mirror | null | light_mat */
+yb200_handle yb200_create_light     (yb200_ctx *c, const char *name);  /* pointlight | sunlight | arealight | meshlight | directional | spotlight | spherelight */
+yb200_handle yb200_create_material  (yb200_ctx *c, const char *name);  /* shinydiffusemat | glossy | coated_glossy | glass | rough_glass | blend_mat | mirror | null | light_mat; shader nodes = the parameter list */
 yb200_handle yb200_create_camera    (yb200_ctx *c, const char *name);  /* perspective | architect | orthographic | angular */
 yb200_handle yb200_create_background(yb200_ctx *c, const char *name);  /* constant */
 yb200_handle yb200_create_integrator(yb200_ctx *c, const char *name);  /* directlighting | pathtracing | none (volume) */
