@@ -38,6 +38,20 @@ def test_image_parity_golden(name):
     assert st["kernel_launches"] > 0 and st["rays_closest"] > 0
 
 
+def test_opt_in_knobs_keep_the_image(monkeypatch):
+    """The measured-and-rejected variants stay selectable: coherence-sorted ray fetch, camera-wave binning."""
+    name = "c2_field_path"
+    fn, kw = cases.IMAGE_CASES[name]
+    ref = np.load(os.path.join(G, "img_" + name + ".npz"))["img"]
+    for var, val in (("YB200_SORT_RAYS", "3"), ("YB200_BIN_FIRST", "1"), ("YB200_BIN_SHADE", "0")):
+        monkeypatch.setenv(var, val)
+        yi = YafrayInterface()
+        fn(yi, **kw)
+        rel, psnr, da = cases.compare_images(ref, yi.render(kw["width"], kw["height"]))
+        monkeypatch.delenv(var)
+        assert rel <= 1e-5 and psnr >= 100.0, (var, rel, psnr)
+
+
 @pytest.mark.parametrize("name", list(cases.DEPTH_CASES))
 def test_depth_channel_golden(name):
     fn, kw = cases.DEPTH_CASES[name]
