@@ -133,7 +133,7 @@ static void bin_tasks(uint32_t n, const RenderArgs &a, rt_stream s)
 
 // ------------------------------------------------------------------------------------------------ film
 // imageFilm_t::addSample (imagefilm.cc:453-511); film layout (x + w*y)*5 = r,g,b,a,weight (pixel_t)
-YB_KERNEL(k_film, RenderArgs)
+YB_D void film_splat_sample(const RenderArgs &a, uint32_t tid)
 {
     const Film &f = a.sc.film;
     const SampleId id = sample_id(a, tid);
@@ -180,6 +180,94 @@ YB_KERNEL(k_film, RenderArgs)
         }
     }
 }
+YB_KERNEL(k_film, RenderArgs) { film_splat_sample(a, tid); }
+#ifndef YB_HOSTEMU
+// Warp-aggregated form of the splat for the common case (no premult, footprint inside the 3x3 neighbourhood of the pixel: box /
+// gauss filters up to AA_pixelwidth 2): consecutive lanes hold consecutive samples of the same pixel, so the 3x3 x 5 partial sums
+// are reduced over each run of equal pixels with shuffles and only the run's first lane touches the film - 45 atomics per pixel
+// and warp instead of 20 per sample.  Anything else (wide filters, premult, the depth channel) takes k_film's per-sample path.
+__global__ void __launch_bounds__(256) k_film_fast_kernel(uint32_t n, const RenderArgs a)
+{
+    const Film &f = a.sc.film;
+    const unsigned lane = threadIdx.x & 31u;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+        const uint32_t tid = base + threadIdx.x;
+        const bool valid = tid < n;
+        bool fits = false;
+        int x = 0, y = 0, dx0 = 0, dx1 = -1, dy0 = 0, dy1 = -1;
+        int xIndex[3] = {0, 0, 0}, yIndex[3] = {0, 0, 0};
+        f4 c; c.x = c.y = c.z = c.w = 0.f;
+        uint32_t key = 0xffffffffu - lane;                        // invalid lanes: runs of their own
+        if (valid) {
+            const SampleId id = sample_id(a, tid);
+            float dx, dy;
+            sample_dxdy(f, id, dx, dy);
+            c = a.acc[tid];
+            if (f.clamp) {
+                c.x = c.x < 0.f ? 0.f : (c.x > 1.f ? 1.f : c.x); c.y = c.y < 0.f ? 0.f : (c.y > 1.f ? 1.f : c.y); c.z = c.z < 0.f ? 0.f : (c.z > 1.f ? 1.f : c.z);
+            }
+            x = id.x; y = id.y;
+            dx0 = Round2Int((double)dx - f.filterw); dx1 = Round2Int((double)dx + f.filterw - 1.0);
+            dy0 = Round2Int((double)dy - f.filterw); dy1 = Round2Int((double)dy + f.filterw - 1.0);
+            if (dx0 < f.cx0 - x) dx0 = f.cx0 - x;
+            if (dx1 > f.cx1 - x - 1) dx1 = f.cx1 - x - 1;
+            if (dy0 < f.cy0 - y) dy0 = f.cy0 - y;
+            if (dy1 > f.cy1 - y - 1) dy1 = f.cy1 - y - 1;
+            fits = dx0 >= -1 && dx1 <= 1 && dy0 >= -1 && dy1 <= 1;
+            if (fits) {
+                const double x_offs = dx - 0.5, y_offs = dy - 0.5;
+                for (int i = dx0; i <= dx1; ++i) xIndex[i + 1] = Floor2Int(fabs(((double)i - x_offs) * f.tableScale));
+                for (int i = dy0; i <= dy1; ++i) yIndex[i + 1] = Floor2Int(fabs(((double)i - y_offs) * f.tableScale));
+            }
+            key = (a.sampleBase + tid) / (uint32_t)f.n_samples;  // pixel slot: equal for the samples of one pixel
+        }
+        const bool fast = __all_sync(0xffffffffu, !valid || fits) && !f.premult;
+        if (!fast) { if (valid) film_splat_sample(a, tid); continue; }
+        float v[45];
+        uint32_t cover = 0u;
+#pragma unroll
+        for (int j = -1; j <= 1; ++j)
+#pragma unroll
+            for (int i = -1; i <= 1; ++i) {
+                const int cell = (j + 1) * 3 + (i + 1);
+                const bool in = valid && i >= dx0 && i <= dx1 && j >= dy0 && j <= dy1;
+                const float wgt = in ? f.filterTable[yIndex[j + 1] * YB_FILTER_TABLE_SIZE + xIndex[i + 1]] : 0.f;
+                if (in) cover |= 1u << cell;
+                v[5 * cell + 0] = c.x * wgt; v[5 * cell + 1] = c.y * wgt; v[5 * cell + 2] = c.z * wgt; v[5 * cell + 3] = c.w * wgt; v[5 * cell + 4] = wgt;
+            }
+        // segmented reduction over runs of equal keys (runs are contiguous: samples of a pixel are consecutive)
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t k2 = __shfl_down_sync(0xffffffffu, key, off);
+            const uint32_t c2 = __shfl_down_sync(0xffffffffu, cover, off);
+            const bool take = (lane + off < 32u) && k2 == key;
+            if (take) cover |= c2;
+#pragma unroll
+            for (int q = 0; q < 45; ++q) { const float t = __shfl_down_sync(0xffffffffu, v[q], off); if (take) v[q] += t; }
+        }
+        const uint32_t kprev = __shfl_up_sync(0xffffffffu, key, 1);
+        if (valid && (lane == 0u || kprev != key)) {
+#pragma unroll
+            for (int cell = 0; cell < 9; ++cell)
+                if (cover & (1u << cell)) {
+                    const int i = cell % 3 - 1, j = cell / 3 - 1;
+                    float *px = a.film + ((size_t)(x + i - f.cx0) + (size_t)f.w * (size_t)(y + j - f.cy0)) * 5;
+                    atomicAdd(px + 0, v[5 * cell + 0]); atomicAdd(px + 1, v[5 * cell + 1]); atomicAdd(px + 2, v[5 * cell + 2]);
+                    atomicAdd(px + 3, v[5 * cell + 3]); atomicAdd(px + 4, v[5 * cell + 4]);
+                }
+        }
+    }
+}
+static void k_film_fast(uint32_t n, const RenderArgs &a, rt_stream s)
+{
+    if (n == 0) return;
+    uint32_t blocks = (n + 255u) / 256u;
+    if (blocks > 148u * 32u) blocks = 148u * 32u;
+    k_film_fast_kernel<<<blocks, 256, 0, s>>>(n, a);
+    YB_CUDA_CHECK(cudaGetLastError());
+    g_kernel_launches++;
+}
+#endif
 // pixelGray_t::normalized (image_buffers.h:46-57)
 struct DepthResolveArgs { const float *dfilm; float *z; };
 YB_KERNEL(k_resolve_depth, DepthResolveArgs)
@@ -455,7 +543,9 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         a.sc = c.sc; a.sc.film.minDepth = fz.minDepth; a.sc.film.maxDepth = fz.maxDepth; a.sc.film.n_samples = passSamples; a.sc.film.pass_offs = passOffs; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
         a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
         const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
-        const bool binFirst = env_size("YB200_BIN_FIRST", 0) != 0;      // also bin the camera wave (pixel order is already coherent)
+        const bool binFirst = env_size("YB200_BIN_FIRST", 0) != 0;
+        const bool filmFast = env_size("YB200_FILM_FAST", 1) != 0;       // warp-aggregated film splat (k_film_fast_kernel)
+        (void)filmFast;      // also bin the camera wave (pixel order is already coherent)
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
         // coherence sort of the ray waves: 0 off, 1 closest-hit waves after the camera wave, 2 + shadow waves after the first, 3 all
         const int sortRays = (int)env_size("YB200_SORT_RAYS", 0);
@@ -524,7 +614,12 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 }
             }
             a.tasks = pool;
-            tf.start(); k_film(nb, a, s); tf.stop();
+            tf.start();
+#ifndef YB_HOSTEMU
+            if (filmFast && !a.depthT) k_film_fast(nb, a, s); else
+#endif
+            k_film(nb, a, s);
+            tf.stop();
             rt_sync(s);
             msFilm += tf.ms();
             if (progress) progress(user, pass * nBatches + b + 1, nPasses * nBatches);
