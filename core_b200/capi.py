@@ -87,6 +87,7 @@ _PRODUCT_ONLY = {
     "get_stats": (C.c_int, [C.POINTER(Stats)]),
     "cuda_stream": (C.c_void_p, []),
     "touch_geometry": (None, []),
+    "trace_batch_static": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int]),
 }
 EXPORTED_SYMBOLS = (["create", "version"] + sorted(_CTX_FUNCS) + sorted(_PRODUCT_ONLY))
 

@@ -1,18 +1,11 @@
 // yb_capi.cc — the C ABI of include/yb200.h over yb::Context.  Plain pointers and sizes only.
 #include "../../include/yb200.h"
-#include "yb_scene.h"
+#include "yb_ctx.h"
 #include "yb_trace.cuh"
 #include <new>
 #include <chrono>
 
 using namespace yb;
-
-namespace yb {
-struct RenderBuffers;
-// small accessors implemented in yb_render.cu would need the full type; the staging buffers live here instead
-struct IoBuffers { DevBuf<char> in, out; DevBuf<float> film, rgba; };
-}
-struct yb200_ctx { Context c; IoBuffers io; };
 
 #define CTX (ctx->c)
 #define GUARD_BEGIN try {

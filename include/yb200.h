@@ -139,6 +139,23 @@ enum { YB200_TRACE_CLOSEST = 0, YB200_TRACE_SHADOW = 1, YB200_TRACE_TSHADOW = 2 
 int yb200_trace_batch(yb200_ctx *c, const float *rays, size_t n, int mode, int shadow_depth,
                       void *out, int on_device);
 
+/* Allocation-free form of yb200_trace_batch for callers that must not allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same rays / out records / modes as yb200_trace_batch, except YB200_TRACE_TSHADOW (rejected).  The entry
+ * point calls no cudaMalloc / cudaFree or allocating library routine: the ray-fetch counter of the traversal kernel and,
+ * for HOST pointers, the device staging of rays and results live in one file-scope device array of
+ * YB200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ * Limits (a larger n fails with a message in yb200_last_error, nothing is traced):
+ *   on_device == 0: n <= YB200_STATIC_MAX_RAYS_HOST (the staging area); copies in, traces, copies out, waits;
+ *   on_device != 0: n <= YB200_STATIC_MAX_RAYS_DEVICE (one launch of the 32-bit counter); asynchronous on the context stream.
+ * Needs a scene already on the device (yb200_update_scene / a render - those do allocate).  The array is shared by every
+ * call on that GPU and keeps the last call's contents; the counter is cleared on the stream before each launch.  Calls that
+ * overlap on the GPU (other streams, contexts or threads) race on it: serialise them. */
+#define YB200_STATIC_MAX_RAYS_HOST   65536u
+#define YB200_STATIC_MAX_RAYS_DEVICE (1u << 30)
+#define YB200_STATIC_SCRATCH_BYTES   (256u + YB200_STATIC_MAX_RAYS_HOST * (32u + 16u))
+int yb200_trace_batch_static(yb200_ctx *c, const float *rays, size_t n, int mode, void *out, int on_device);
+
 /* ---- counters (new: the reference has none) */
 typedef struct yb200_stats {
     uint64_t n_triangles, n_bvh_nodes;
