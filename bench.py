@@ -145,15 +145,16 @@ def cpu_reference_run(wl, steps, warmup, threads=-1):
     yi.updateScene()                       # kd-tree build (scene.cc:782), reported separately
     kd_s = time.time() - t0
     times = []
+    frame = None
     for i in range(warmup + steps):
         t = time.time()
-        yi.render(kw["width"], kw["height"])
+        frame = yi.render(kw["width"], kw["height"])
         if i >= warmup:
             times.append(time.time() - t)
     rays = None
     if os.path.exists(RAYS_JSON):
         rays = json.load(open(RAYS_JSON)).get(wl)
-    return dict(n_tris=n_tris, kw=kw, sec=float(np.mean(times)), kd_s=kd_s, rays=rays, cores=os.cpu_count())
+    return dict(n_tris=n_tris, kw=kw, sec=float(np.mean(times)), kd_s=kd_s, rays=rays, cores=os.cpu_count(), frame=frame)
 
 
 def main():
@@ -186,6 +187,11 @@ def main():
             print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libyref.so missing (build it with make -C oracle ref)"}))
             return 0
         config["n_triangles"] = r["n_tris"]
+        # what this arm really renders: a bounded sample of the workload, compared per ray
+        config["full_config"] = {"resolution": config["resolution"], "spp": config["spp"]}
+        config["resolution"] = [r["kw"]["width"], r["kw"]["height"]]
+        config["spp"] = r["kw"]["spp"]
+        config["note"] = "CPU arm renders the same 1M-triangle scene / integrator at the reduced resolution and spp stated here; Mrays/s is per ray"
         sample = "same scene, %dx%d, %d spp, threads=%d (kd-tree build %.1f s not included)" % (
             r["kw"]["width"], r["kw"]["height"], r["kw"]["spp"], r["cores"], r["kd_s"])
         rays = r["rays"]
@@ -224,22 +230,31 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    def reduce_film():
+        # NCCL runs on its own stream and only torch's current stream waits for it: order the library's (non-blocking)
+        # stream after the reduce before anything on it reads the film
+        dist.reduce(film, 0)
+        ext.wait_stream(torch.cuda.current_stream())
+
     def frame_resident():
         film.zero_()
         torch.cuda.synchronize()
         yi.renderFilm(film, rank, world)
         if world > 1:
-            dist.reduce(film, 0)
+            reduce_film()
         if rank == 0:
             yi._call("film_resolve", film.data_ptr(), rgba_dev.data_ptr(), 1)
 
     def frame_e2e(host_out):
         yi.touchGeometry()                 # re-flatten + H2D of the geometry + BVH build inside the step
+        if world == 1:                     # the reference-facing call itself: yafrayInterface_t::render -> yb200_render, host buffer out
+            if not yi._call("render", host_out.ctypes.data, W, H, None):
+                raise RuntimeError(yi.lastError())
+            return
         film.zero_()
         torch.cuda.synchronize()
         yi.renderFilm(film, rank, world)
-        if world > 1:
-            dist.reduce(film, 0)
+        reduce_film()
         if rank == 0:
             yi._call("film_resolve", film.data_ptr(), host_out.ctypes.data, 0)   # D2H of the float RGBA frame
 
@@ -280,7 +295,7 @@ def main():
     frame_e2e(host_out)
     barrier()
     t0 = time.time()
-    e2e_steps = max(1, min(args.steps, 3))
+    e2e_steps = args.steps
     for _ in range(e2e_steps):
         frame_e2e(host_out)
     barrier()
@@ -294,6 +309,19 @@ def main():
     h2d = int(st["tri_bytes"]) * world
     d2h = W * H * 16
 
+    frame_check = None
+    if world > 1:
+        # the reduced N-rank frame (host_out on rank 0, from the last e2e step) against a 1-rank render of the same frame
+        if rank == 0:
+            import cases
+            film.zero_()
+            torch.cuda.synchronize()
+            yi.renderFilm(film, 0, 1)
+            one = yi.filmResolve(film, W, H)
+            rel, psnr, da = cases.compare_images(one, host_out)
+            frame_check = {"rel": float(rel), "psnr": float(psnr), "max_alpha_diff": float(da),
+                           "what": "frame reduced over %d ranks (NCCL) vs the same frame rendered by rank 0 alone" % world}
+        barrier()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -321,14 +349,44 @@ def main():
                 "grays_per_s_in_trace_kernels": rays_rank / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else None,
                 "kernel_ms_per_step": {"trace_closest": float(ktime[0]) / args.steps, "trace_shadow": float(ktime[1]) / args.steps,
                                        "shade": float(ktime[2]) / args.steps, "film": float(ktime[3]) / args.steps}}
+    # the other two bounds of SURVEY 8(d) / VERDICT: dependent-load latency (pointer chase measured now) and instruction issue
+    # (thread instructions per ray from the ncu capture recorded in profiles/)
+    R = math.ceil(math.log(max(n_tris / 4.0, 1.0), 8)) + 1
+    try:
+        t_miss = yi.probeLatency(1 << 30, 20000)
+        t_hit = yi.probeLatency(16 << 20, 20000)
+    except Exception:
+        t_miss = t_hit = None
+    clk_summary = clk.summary()
+    sm_hz = (clk_summary["sm_mhz"] or 1965.0) * 1e6
+    roofline["t_l2miss_ns"] = t_miss
+    roofline["t_l2hit_ns"] = t_hit
+    roofline["dependent_fetch_rounds"] = R
+    if t_miss:
+        roofline["latency_bound_grays"] = 148 * 64 * 32 / (R * t_miss * 1e-9) / 1e9          # all 64 warps per SM resident
+        roofline["latency_bound_grays_at_kernel_occupancy"] = 148 * 6 * 128 / (R * t_miss * 1e-9) / 1e9   # k_trace_fast: 6 x 128 threads per SM
+    roofline["hbm_bound_grays"] = peak / A
+    ifiles = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if "trace_inst" in f and f.endswith(".json"))
+    if ifiles and args.workload == "c2_field_1M_1080p_64spp":
+        ij = json.load(open(os.path.join(ROOT, "profiles", ifiles[-1])))
+        roofline["thread_inst_per_ray"] = ij["thread_inst_per_ray"]
+        roofline["lanes_active"] = ij["lanes_active"]
+        roofline["issue_bound_grays"] = 148 * 4 * 32 * sm_hz / ij["thread_inst_per_ray"] / 1e9
+        roofline["issue_note"] = "148 SM x 4 schedulers x 32 lanes x SM clock / thread instructions per ray (ncu, profiles/%s)" % ifiles[-1]
+        roofline["binding_bound"] = "issue"
+        roofline["frac_of_issue_bound"] = roofline["grays_per_s_in_trace_kernels"] / roofline["issue_bound_grays"] if roofline["grays_per_s_in_trace_kernels"] else None
     line = {"metric": metric, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "sec_per_frame": ms_per_step * 1e-3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
             "rays_per_frame": rays_per_frame, "camera_samples_per_frame": float(cnt[3]) / args.steps, "wall_ms_per_step": wall_ms / args.steps,
-            "bvh_build_ms": build_ms, "gpu_launches": int(cnt[2]), "clocks": clk.summary(),
+            "bvh_build_ms": build_ms, "gpu_launches": int(cnt[2]), "clocks": clk_summary,
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "sec_per_frame": e2e_s, "includes": "flatten + H2D geometry + BVH build + render + film reduce + D2H frame"},
+                    "sec_per_frame": e2e_s, "steps": e2e_steps,
+                    "call": "yb200_render (yafrayInterface_t::render) with a host RGBA buffer" if world == 1 else "yb200_render_film + NCCL reduce + yb200_film_resolve to a host buffer",
+                    "includes": "flatten + H2D geometry + BVH build + render + film reduce + D2H frame"},
             "roofline": roofline}
+    if frame_check:
+        line["frame_check"] = frame_check
 
     # the reference's CPU path on this box's host cores, bounded sample (rank 0, N = 1 only)
     if world == 1 and not args.no_cpu_baseline:
@@ -345,6 +403,17 @@ def main():
                 json.dump(d, open(os.path.join(ROOT, "gpurun_out", "cpu_sample_rays.json"), "w"), indent=1)
             y2.close()
         r = cpu_reference_run(wl, 1, 1)
+        if r is not None and r.get("frame") is not None:
+            # the frame the reference just rendered against a GPU render of the same sample (after all timed regions)
+            import cases
+            y3 = YafrayInterface(device=local)
+            build_scene(y3, wl, **CPU_SAMPLE)
+            g = y3.render(CPU_SAMPLE["width"], CPU_SAMPLE["height"])
+            y3.close()
+            rel, psnr, da = cases.compare_images(r["frame"], g)
+            line["parity"] = {"rel": float(rel), "psnr": float(psnr), "max_alpha_diff": float(da),
+                              "sample": "reference frame of the cpu_baseline leg (%dx%d, %d spp, 1M triangles) vs the CUDA path on the same sample" % (
+                                  r["kw"]["width"], r["kw"]["height"], r["kw"]["spp"])}
         if r is not None and r["rays"]:
             line["cpu_baseline"] = {"value": r["rays"] / r["sec"] / 1e6, "unit": "Mrays/s", "cores": r["cores"], "kind": "reference",
                                     "sample": "same scene, %dx%d, %d spp, threads=%d; kd-tree build %.1f s excluded" % (

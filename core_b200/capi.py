@@ -88,6 +88,8 @@ _PRODUCT_ONLY = {
     "cuda_stream": (C.c_void_p, []),
     "touch_geometry": (None, []),
     "trace_batch_static": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int]),
+    "selftest": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "probe_latency": (C.c_int, [C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
 }
 EXPORTED_SYMBOLS = (["create", "version"] + sorted(_CTX_FUNCS) + sorted(_PRODUCT_ONLY))
 

@@ -222,77 +222,86 @@ static inline float sinFromVectors(v3 a, v3 b)   // vector3d.h:263-268
     if (ret < -1.f) ret = -1.f;
     return asinf(ret);
 }
-bool Context::smoothMesh(unsigned id, double angle_)   // scene.cc:362-520
+// scene_t::smoothMesh (scene.cc:362-520), restated over a corner table.
+//
+// A "corner" is (triangle t, slot c) -> vertex tri_idx[3t+c]; corner id = 3t+c.  The corners are grouped by vertex with a
+// counting sort (ascending corner id inside a group - the order in which the reference meets the faces of a vertex, which
+// fixes the float summation order and therefore the normals bit for bit).  Per corner the interior angle weight is
+// asin(|e1 x e2| / |e1||e2|) (vector3d.h:263-268).
+//   angle >= 180 : one normal per vertex = normalised sum of weight * face normal over the vertex' corners;
+//   0.1 < angle  : one normal per smoothing group: a corner takes its own face plus every other face at the vertex whose
+//                  normal is within `angle` (dot > fCos(angle)); corners without such a neighbour keep the flat normal
+//                  (index -1); groups of one vertex whose normals agree to dot > 0.999 share the first one created.
+bool Context::smoothMesh(unsigned id, double angle_)
 {
     if (stateStack.back() != ST_GEOMETRY) return false;
-    const float angle = (float)angle_;
-    MeshObj *o;
+    MeshObj *o = curObj;
     if (id) {
         std::map<unsigned, MeshObj>::iterator it = meshes.find(id);
         if (it == meshes.end()) return false;
         o = &it->second;
-    } else { o = curObj; if (!o) return false; }
-    if (o->base) return false;
+    }
+    if (!o || o->base) return false;
     if (o->normals_exported && o->points.size() == o->normals.size()) { o->is_smooth = true; return true; }
-    const size_t points = o->points.size(), ntri = o->tri_mat.size();
-    std::vector<v3> &normals = o->normals;
-    normals.resize(points, v3(0.f));
-    const std::vector<v3> &vertices = o->points;
-    if (angle >= 180) {
-        for (size_t t = 0; t < ntri; ++t) {
-            const int pa = o->tri_idx[3 * t], pb = o->tri_idx[3 * t + 1], pc = o->tri_idx[3 * t + 2];
-            v3 n = tri_rec_normal(*o, t);
-            float alpha = sinFromVectors(vertices[pb] - vertices[pa], vertices[pc] - vertices[pa]);
-            normals[pa] += n * alpha;
-            alpha = sinFromVectors(vertices[pa] - vertices[pb], vertices[pc] - vertices[pb]);
-            normals[pb] += n * alpha;
-            alpha = sinFromVectors(vertices[pa] - vertices[pc], vertices[pb] - vertices[pc]);
-            normals[pc] += n * alpha;
-            o->tri_nidx[3 * t] = pa; o->tri_nidx[3 * t + 1] = pb; o->tri_nidx[3 * t + 2] = pc;
+    const float angle = (float)angle_;
+    const size_t nPoints = o->points.size(), nCorners = 3 * o->tri_mat.size();
+    o->normals.resize(nPoints, v3(0.f));
+    if (angle > 0.1f) {
+        for (size_t k = 0; k < nCorners; ++k)
+            if (o->tri_idx[k] < 0 || (size_t)o->tri_idx[k] >= nPoints) { fail("smoothMesh: triangle references a vertex that does not exist"); return false; }
+        // corner table: cornersOf[first[v] .. first[v + 1]) = the corners at vertex v
+        std::vector<uint32_t> first(nPoints + 1, 0u), cornersOf(nCorners);
+        for (size_t k = 0; k < nCorners; ++k) first[(size_t)o->tri_idx[k] + 1]++;
+        for (size_t v = 0; v < nPoints; ++v) first[v + 1] += first[v];
+        {
+            std::vector<uint32_t> fill(first.begin(), first.end() - 1);
+            for (size_t k = 0; k < nCorners; ++k) cornersOf[fill[(size_t)o->tri_idx[k]]++] = (uint32_t)k;
         }
-        for (size_t i = 0; i < normals.size(); ++i) normals[i] = normalize(normals[i]);
-    } else if (angle > 0.1) {
-        const float thresh = fCos((float)(angle * 0.01745329251994329576922));
-        std::vector<std::vector<size_t> > vface(points);
-        std::vector<std::vector<float> > alphas(points);
-        for (size_t t = 0; t < ntri; ++t) {
-            const int pa = o->tri_idx[3 * t], pb = o->tri_idx[3 * t + 1], pc = o->tri_idx[3 * t + 2];
-            alphas[pa].push_back(sinFromVectors(vertices[pb] - vertices[pa], vertices[pc] - vertices[pa])); vface[pa].push_back(t);
-            alphas[pb].push_back(sinFromVectors(vertices[pa] - vertices[pb], vertices[pc] - vertices[pb])); vface[pb].push_back(t);
-            alphas[pc].push_back(sinFromVectors(vertices[pa] - vertices[pc], vertices[pb] - vertices[pc])); vface[pc].push_back(t);
+        std::vector<float> weight(nCorners);
+        std::vector<v3> faceN(nCorners / 3);
+        for (size_t t = 0; t < nCorners / 3; ++t) {
+            faceN[t] = tri_rec_normal(*o, t);
+            const v3 P[3] = {o->points[o->tri_idx[3 * t]], o->points[o->tri_idx[3 * t + 1]], o->points[o->tri_idx[3 * t + 2]]};
+            // edges in the reference's order: from the corner to the remaining two vertices, lower slot first
+            weight[3 * t + 0] = sinFromVectors(P[1] - P[0], P[2] - P[0]);
+            weight[3 * t + 1] = sinFromVectors(P[0] - P[1], P[2] - P[1]);
+            weight[3 * t + 2] = sinFromVectors(P[0] - P[2], P[1] - P[2]);
         }
-        std::vector<v3> fn(ntri);
-        for (size_t t = 0; t < ntri; ++t) fn[t] = tri_rec_normal(*o, t);
-        std::vector<v3> vnormals; std::vector<int> vn_index;
-        for (int i = 0; i < (int)vface.size(); ++i) {
-            std::vector<size_t> &tris = vface[i];
-            for (size_t j = 0; j < tris.size(); ++j) {
-                const size_t f = tris[j];
-                bool smooth = false;
-                v3 fnorm = fn[f];
-                v3 vnorm = fnorm * alphas[i][j];
-                for (size_t k = 0; k < tris.size(); ++k) {
-                    const size_t f2 = tris[k];
-                    if (f == f2) continue;          // triangle_t::operator== compares selfIndex (triangle.h:68-71)
-                    v3 f2norm = fn[f2];
-                    if (dot(fnorm, f2norm) > thresh) { smooth = true; vnorm += f2norm * alphas[i][k]; }
-                }
-                int n_idx = -1;
-                if (smooth) {
-                    vnorm = normalize(vnorm);
-                    for (size_t l = 0; l < vnormals.size(); ++l)
-                        if (dot(vnorm, vnormals[l]) > 0.999) { n_idx = vn_index[l]; break; }
-                    if (n_idx == -1) {
-                        n_idx = (int)normals.size();
-                        vnormals.push_back(vnorm); vn_index.push_back(n_idx); normals.push_back(vnorm);
-                    }
-                }
-                if (o->tri_idx[3 * f] == i) o->tri_nidx[3 * f] = n_idx;
-                else if (o->tri_idx[3 * f + 1] == i) o->tri_nidx[3 * f + 1] = n_idx;
-                else if (o->tri_idx[3 * f + 2] == i) o->tri_nidx[3 * f + 2] = n_idx;
-                else { fail("Scene: Mesh smoothing error!"); return false; }
+        if (angle >= 180.f) {
+            for (size_t v = 0; v < nPoints; ++v) {
+                v3 sum = o->normals[v];
+                for (uint32_t q = first[v]; q < first[v + 1]; ++q) sum += faceN[cornersOf[q] / 3] * weight[cornersOf[q]];
+                o->normals[v] = normalize(sum);
             }
-            vnormals.clear(); vn_index.clear();
+            for (size_t k = 0; k < nCorners; ++k) o->tri_nidx[k] = o->tri_idx[k];
+        } else {
+            const float thresh = fCos((float)(angle * 0.01745329251994329576922));
+            std::vector<int> groupIdx;                               // normals created for the current vertex
+            for (size_t v = 0; v < nPoints; ++v) {
+                groupIdx.clear();
+                for (uint32_t q = first[v]; q < first[v + 1]; ++q) {
+                    const uint32_t k = cornersOf[q];
+                    // a triangle that names the vertex twice: the reference resolves both visits to the first slot holding it
+                    uint32_t slot = 3 * (k / 3);
+                    while (o->tri_idx[slot] != (int32_t)v) ++slot;
+                    const v3 own = faceN[k / 3];
+                    v3 sum = own * weight[k];
+                    bool grouped = false;
+                    for (uint32_t r = first[v]; r < first[v + 1]; ++r) {
+                        const uint32_t k2 = cornersOf[r];
+                        if (k2 / 3 == k / 3) continue;               // triangle_t::operator== is identity of the face (triangle.h:68-71)
+                        if (dot(own, faceN[k2 / 3]) > thresh) { grouped = true; sum += faceN[k2 / 3] * weight[k2]; }
+                    }
+                    int n = -1;
+                    if (grouped) {
+                        sum = normalize(sum);
+                        for (size_t g = 0; g < groupIdx.size() && n < 0; ++g)
+                            if (dot(sum, o->normals[groupIdx[g]]) > 0.999) n = groupIdx[g];
+                        if (n < 0) { n = (int)o->normals.size(); o->normals.push_back(sum); groupIdx.push_back(n); }
+                    }
+                    o->tri_nidx[slot] = n;
+                }
+            }
         }
     }
     o->is_smooth = true;
@@ -1219,7 +1228,11 @@ bool Context::flattenAndBuild()
             if (g.has_uv && g.uv_offsets.size() == 3 * g.tri_mat.size()) anyUV = true;
             if (g.has_orco) anyOrco = true;
         }
-    std::vector<float> h_uv; std::vector<v3> h_orco;
+    bool anyInst = false;
+    for (std::map<unsigned, MeshObj>::iterator i = meshes.begin(); i != meshes.end(); ++i)
+        if (i->second.visible && !i->second.is_base && i->second.base) anyInst = true;
+    std::vector<float> h_uv; std::vector<v3> h_orco, h_ng;
+    if (anyInst) h_ng.assign(ntri, v3(0.f));
     if (anyUV) h_uv.assign(6 * ntri, 0.f);
     if (anyOrco) h_orco.assign(3 * ntri, v3(0.f));
     h_in_v.reserve(3 * ntri + 1); if (anySmooth) h_in_n.reserve(3 * ntri + 1);
@@ -1292,6 +1305,11 @@ bool Context::flattenAndBuild()
                     }
                     info |= TRI_HAS_ORCO;
                 }
+                if (inst) {      // triangleInstance_t::getNormal (triangle_inline.h:183-186): objToWorld * (base triangle's recNormal), normalised
+                    const v3 bn = tri_rec_normal(g, t);
+                    h_ng[k] = normalize(v3(m[0] * bn.x + m[1] * bn.y + m[2] * bn.z, m[4] * bn.x + m[5] * bn.y + m[6] * bn.z, m[8] * bn.x + m[9] * bn.y + m[10] * bn.z));
+                    info |= TRI_EXPLICIT_NG;
+                }
                 hv[3 * k].w = i2f((int32_t)k);
                 hv[3 * k + 1].w = i2f((int32_t)info);
             }
@@ -1316,7 +1334,8 @@ bool Context::flattenAndBuild()
         in_v.reserve(3 * ntri + 1);
         rt_h2d(in_v.p, hv, 3 * ntri * sizeof(f4), stream);
         if (anySmooth) { in_n.reserve(3 * ntri + 1); rt_h2d(in_n.p, hn, 3 * ntri * sizeof(v3), stream); }
-        sc.prim_uv = 0; sc.prim_orco = 0;
+        sc.prim_uv = 0; sc.prim_orco = 0; sc.prim_ng = 0;
+        if (anyInst) { d_prim_ng.reserve(h_ng.size() + 1); rt_h2d(d_prim_ng.p, h_ng.data(), h_ng.size() * sizeof(v3), stream); sc.prim_ng = d_prim_ng.p; }
         if (anyUV) { d_prim_uv.reserve(h_uv.size() + 1); rt_h2d(d_prim_uv.p, h_uv.data(), h_uv.size() * sizeof(float), stream); sc.prim_uv = d_prim_uv.p; }
         if (anyOrco) { d_prim_orco.reserve(h_orco.size() + 1); rt_h2d(d_prim_orco.p, h_orco.data(), h_orco.size() * sizeof(v3), stream); sc.prim_orco = d_prim_orco.p; }
         rt_sync(stream);

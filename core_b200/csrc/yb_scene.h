@@ -110,7 +110,7 @@ struct Context {
     // device-side scene
     DevBuf<BvhNode> d_nodes; DevBuf<f4> d_tri_v; DevBuf<v3> d_tri_n; DevBuf<Material> d_materials; DevBuf<Light> d_lights;
     DevBuf<f4> d_tex_pixels;
-    DevBuf<Texture> d_textures; DevBuf<ShaderNode> d_shaderNodes; DevBuf<float> d_prim_uv; DevBuf<v3> d_prim_orco;
+    DevBuf<Texture> d_textures; DevBuf<ShaderNode> d_shaderNodes; DevBuf<float> d_prim_uv; DevBuf<v3> d_prim_orco, d_prim_ng;
     DevBuf<f4> d_light_tris; DevBuf<float> d_light_cdf;   // mesh light emitters (yb_host.cc uploadTables)
     DevBuf<uint32_t> d_traceCounter;   // ray-fetch counter of the persistent traversal kernels
     DevBuf<f4> d_in_v; DevBuf<v3> d_in_n;             // flattened geometry in scene order (input of the build)

@@ -192,6 +192,7 @@ enum : uint32_t {
     TRI_SMOOTH = 1u << 20,            // mesh->is_smooth
     TRI_HAS_NA = 1u << 21, TRI_HAS_NB = 1u << 22, TRI_HAS_NC = 1u << 23,   // na/nb/nc >= 0 (triangle.cc:20-22)
     TRI_HAS_UV = 1u << 24, TRI_HAS_ORCO = 1u << 25,                        // mesh->has_uv / has_orco (triangle.cc:28-48)
+    TRI_EXPLICIT_NG = 1u << 26,       // instance triangle: Ng = normalize(objToWorld * base normal) in prim_ng (triangle_inline.h:183-186)
 };
 
 // 8-wide BVH node with child boxes quantised to 8 bits on a per-node power-of-two grid (80 B = 5 x 16 B).
@@ -220,6 +221,7 @@ struct SceneDev {
     const ShaderNode *shaderNodes;
     const float *prim_uv;
     const v3 *prim_orco;
+    const v3 *prim_ng;      // geometric normal of instance triangles (TRI_EXPLICIT_NG), by primitive index; null without instances
     int32_t nLights, nMaterials;
     uint32_t nTris, nNodes;
     v3 boundLo, boundHi;

@@ -205,6 +205,13 @@ class YafrayInterface:
         self._call("get_stats", C.byref(s))
         return {k: getattr(s, k) for k, _ in capi.Stats._fields_}
 
+    def probeLatency(self, nbytes, steps=20000):
+        """ns per dependent load through a random cycle over nbytes (yb200_probe_latency)."""
+        ns = C.c_double(0.0)
+        if not self._call("probe_latency", int(nbytes), int(steps), C.byref(ns)):
+            raise RuntimeError("probe_latency failed: " + self.lastError())
+        return ns.value
+
     def touchGeometry(self):
         self._call("touch_geometry")
 

@@ -232,7 +232,7 @@ def cornell_box(yi, width=512, height=512, spp=16, integrator="directlighting", 
 
 # ----------------------------------------------------------------------------- C2: icosphere field
 def icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=64, bounces=4, seed=1,
-                    subdiv=3, smooth=True, threads=1, integrator="pathtracing", integ_params=None,
+                    subdiv=3, smooth=True, threads=1, integrator="pathtracing", integ_params=None, cam_res=None,
                     **render_extra):
     """Subdivided icospheres (1280 tris each at subdiv=3) on a jittered grid over a ground quad;
     sun + point light; pathtracing (BASELINE.json configs[1])."""
@@ -270,7 +270,7 @@ def icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=64, bounc
     create(yi, "light", "pt", type="pointlight", **{"from": (0.0, 0.0, 6.0)}, color=(0.8, 0.85, 1.0, 1.0), power=30.0)
     d = 0.55 * ext
     create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -d * 1.6, d * 0.9)}, to=(0.0, 0.0, 0.5),
-           up=(0.0, -d * 1.6, d * 0.9 + 1.0), resx=width, resy=height, focal=1.1)
+           up=(0.0, -d * 1.6, d * 0.9 + 1.0), resx=cam_res[0] if cam_res else width, resy=cam_res[1] if cam_res else height, focal=1.1)
     create(yi, "background", "bg", type="constant", color=(0.5, 0.6, 0.8, 1.0))
     ip = dict(type=integrator, raydepth=5)
     if integrator == "pathtracing":
@@ -294,7 +294,7 @@ def soup_mesh(n_tris, seed=2):
 
 
 def triangle_soup(yi, n_tris=10_000_000, width=512, height=512, spp=1, ao_samples=32, ao_distance=0.1,
-                  seed=2, threads=1, **render_extra):
+                  seed=2, threads=1, cam_res=None, **render_extra):
     """Random triangles: centres uniform in [-1,1]^3, edges N(0, 0.01^2); directlighting with AO —
     the IntersectS any-hit stress (BASELINE.json configs[2])."""
     V, F = soup_mesh(n_tris, seed)
@@ -305,7 +305,7 @@ def triangle_soup(yi, n_tris=10_000_000, width=512, height=512, spp=1, ao_sample
     yi.endGeometry()
     create(yi, "light", "pt", type="pointlight", **{"from": (0.0, -3.0, 3.0)}, color=(1.0, 1.0, 1.0, 1.0), power=20.0)
     create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -3.2, 0.4)}, to=(0.0, 0.0, 0.0),
-           up=(0.0, -3.2, 1.4), resx=width, resy=height, focal=1.2)
+           up=(0.0, -3.2, 1.4), resx=cam_res[0] if cam_res else width, resy=cam_res[1] if cam_res else height, focal=1.2)
     create(yi, "background", "bg", type="constant", color=(0.1, 0.1, 0.1, 1.0))
     create(yi, "integrator", "default", type="directlighting", raydepth=2, do_AO=True, AO_samples=ao_samples,
            AO_distance=float(ao_distance), AO_color=(0.9, 0.9, 0.9, 1.0))
@@ -422,6 +422,88 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     return len(order) * len(f0) + 4
 
 
+# ----------------------------------------------------------------------------- instances + angle smoothing
+def capped_cylinder(n=12, r=1.0, h=1.0):
+    """Closed cylinder with shared vertices between side and caps: with smoothMesh(angle ~ 45) the side is smooth
+    (360/n degrees between neighbouring faces) while the rim stays sharp (90 degrees) - both branches of the
+    per-corner grouping of scene_t::smoothMesh (scene.cc:425-515) at every rim vertex."""
+    a = np.arange(n) * (2 * np.pi / n)
+    ring = np.stack([r * np.cos(a), r * np.sin(a)], 1)
+    V = np.concatenate([np.c_[ring, np.zeros(n)], np.c_[ring, np.full(n, h)], [[0, 0, 0], [0, 0, h]]]).astype(np.float32)
+    F = []
+    for i in range(n):
+        j = (i + 1) % n
+        F += [(i, j, n + j), (i, n + j, n + i), (2 * n, j, i), (2 * n + 1, n + i, n + j)]
+    return V, np.asarray(F, np.int32)
+
+
+def _xform(scale=(1.0, 1.0, 1.0), rot_z=0.0, rot_x=0.0, shear_xy=0.0, translate=(0.0, 0.0, 0.0)):
+    cz, sz, cx, sx = np.cos(rot_z), np.sin(rot_z), np.cos(rot_x), np.sin(rot_x)
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1.0]])
+    Rx = np.array([[1.0, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Sh = np.array([[1.0, shear_xy, 0], [0, 1, 0], [0, 0, 1]])
+    m = np.eye(4)
+    m[:3, :3] = Rz @ Rx @ Sh @ np.diag(scale)
+    m[:3, 3] = translate
+    return m.astype(np.float32)
+
+
+def instanced_scene(yi, width=96, height=54, spp=2, integrator="directlighting", bounces=3, threads=1, smooth_angle=45.0,
+                    integ_params=None, **render_extra):
+    """scene_t::addInstance (scene.cc:983-1008, triangleInstance_t) and angle-dependent scene_t::smoothMesh (scene.cc:425-515):
+    an invisible BASEMESH icosphere with exported normals and an angle-smoothed cylinder, each instanced under rigid, uniformly
+    scaled and non-uniformly scaled / sheared transforms, plus directly placed angle-smoothed cylinders."""
+    yi.startScene(0)
+    ground = create(yi, "material", "ground", type="shinydiffusemat", color=(0.6, 0.6, 0.55, 1.0), diffuse_reflect=0.9)
+    red = create(yi, "material", "red", type="shinydiffusemat", color=(0.8, 0.25, 0.2, 1.0), diffuse_reflect=0.9)
+    blue = create(yi, "material", "blue", type="glossy", color=(0.5, 0.6, 0.9, 1.0), diffuse_color=(0.2, 0.3, 0.6, 1.0),
+                  diffuse_reflect=0.6, glossy_reflect=0.5, exponent=40.0, as_diffuse=True)
+    shiny = create(yi, "material", "shiny", type="shinydiffusemat", color=(0.7, 0.7, 0.3, 1.0), diffuse_reflect=0.7,
+                   specular_reflect=0.25, mirror_color=(1.0, 1.0, 1.0, 1.0))
+    v0, f0 = icosphere(2)
+    vc, fc = capped_cylinder(12, 0.8, 1.6)
+    BASEMESH = 0x0200
+    yi.startGeometry()
+    add_mesh(yi, *quad((-8, -5, 0), (8, -5, 0), (8, 8, 0), (-8, 8, 0)), ground, bulk=False)
+    # base objects: not rendered themselves (scene.cc:768)
+    assert yi.startTriMesh(50, len(v0), len(f0), False, False, BASEMESH)
+    for v in v0:
+        yi.addVertex(float(v[0]), float(v[1]), float(v[2])); yi.addNormal(float(v[0]), float(v[1]), float(v[2]))
+    for t in f0:
+        assert yi.addTriangle(int(t[0]), int(t[1]), int(t[2]), red)
+    assert yi.endTriMesh() and yi.smoothMesh(50, 181.0)
+    assert yi.startTriMesh(51, len(vc), len(fc), False, False, BASEMESH)
+    for v in vc:
+        yi.addVertex(float(v[0]), float(v[1]), float(v[2]))
+    for t in fc:
+        assert yi.addTriangle(int(t[0]), int(t[1]), int(t[2]), blue)
+    assert yi.endTriMesh() and yi.smoothMesh(51, smooth_angle)
+    # directly placed cylinders: one angle-smoothed, one smoothed with a small angle (every corner keeps the flat normal)
+    add_mesh(yi, vc * np.float32(0.9) + np.array([-4.5, 1.0, 0.01], np.float32), fc, shiny, smooth_angle=smooth_angle, oid=60, bulk=False)
+    add_mesh(yi, vc * np.float32(0.7) + np.array([4.6, -1.5, 0.01], np.float32), fc, red, smooth_angle=5.0, oid=61, bulk=False)
+    yi.endGeometry()
+    for base, m in ((50, _xform(translate=(-2.2, 0.5, 1.0), rot_z=0.7, rot_x=0.4)),                       # rigid
+                    (50, _xform(scale=(0.6, 0.6, 0.6), translate=(0.0, -2.0, 0.6))),                      # uniform scale
+                    (50, _xform(scale=(1.6, 0.7, 0.45), rot_z=-0.5, translate=(2.4, 1.2, 0.45))),         # non-uniform scale
+                    (51, _xform(rot_x=0.5, rot_z=1.1, translate=(0.2, 2.6, 0.6))),
+                    (51, _xform(scale=(0.6, 1.4, 0.8), shear_xy=0.4, translate=(-2.0, -2.4, 0.013)))):    # sheared (cap not coplanar with the ground: t-ties)
+        assert yi.addInstance(base, m)
+    create(yi, "light", "sun", type="sunlight", direction=(0.35, -0.45, 0.8), color=(1.0, 0.95, 0.9, 1.0), power=1.0,
+           angle=1.0, samples=2)
+    create(yi, "light", "pt", type="pointlight", **{"from": (-3.0, -3.0, 5.0)}, color=(0.9, 0.9, 1.0, 1.0), power=25.0)
+    create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -9.0, 4.5)}, to=(0.0, 0.5, 0.6), up=(0.0, -9.0, 5.5),
+           resx=width, resy=height, focal=1.25)
+    create(yi, "background", "bg", type="constant", color=(0.4, 0.5, 0.7, 1.0))
+    ip = dict(type=integrator, raydepth=4)
+    if integrator == "pathtracing":
+        ip.update(bounces=bounces, path_samples=1)
+    ip.update(integ_params or {})
+    create(yi, "integrator", "default", **ip)
+    std_volintegr(yi)
+    set_render(yi, width, height, spp=spp, threads=threads, **render_extra)
+    return len(f0) * 3 + len(fc) * 4 + 2
+
+
 # ----------------------------------------------------------------------------- C5: tessellated terrain
 def _hash2(ix, iy, seed):
     """Integer lattice hash -> [0, 1) (uint32 arithmetic, identical on every machine)."""
@@ -470,7 +552,7 @@ def terrain_mesh(grid, extent=100.0, **kw):
 
 
 def terrain(yi, grid=5000, width=3840, height=2160, spp=1024, bounces=4, extent=100.0, seed=3, threads=1,
-            integrator="pathtracing", **render_extra):
+            integrator="pathtracing", cam_res=None, **render_extra):
     """Tessellated fBm terrain, 2*grid^2 triangles (grid=5000 -> 50 M), sun + constant background,
     pathtracing (BASELINE.json configs[4])."""
     V, F, _ = terrain_mesh(grid, extent, seed=seed)
@@ -482,7 +564,7 @@ def terrain(yi, grid=5000, width=3840, height=2160, spp=1024, bounces=4, extent=
     create(yi, "light", "sun", type="sunlight", direction=(0.4, -0.3, 0.6), color=(1.0, 0.96, 0.9, 1.0), power=1.5, angle=0.6, samples=2)
     e = extent
     create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -0.62 * e, 0.35 * e)}, to=(0.0, 0.0, 0.02 * e),
-           up=(0.0, -0.62 * e, 0.35 * e + 1.0), resx=width, resy=height, focal=1.0)
+           up=(0.0, -0.62 * e, 0.35 * e + 1.0), resx=cam_res[0] if cam_res else width, resy=cam_res[1] if cam_res else height, focal=1.0)
     create(yi, "background", "bg", type="constant", color=(0.55, 0.65, 0.85, 1.0))
     ip = dict(type=integrator, raydepth=3)
     if integrator == "pathtracing":

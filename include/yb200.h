@@ -156,6 +156,25 @@ int yb200_trace_batch(yb200_ctx *c, const float *rays, size_t n, int mode, int s
 #define YB200_STATIC_SCRATCH_BYTES   (256u + YB200_STATIC_MAX_RAYS_HOST * (32u + 16u))
 int yb200_trace_batch_static(yb200_ctx *c, const float *rays, size_t n, int mode, void *out, int on_device);
 
+/* ---- device known-answer hook (TEST INFRASTRUCTURE, no counterpart in the reference's interface): one GPU thread
+ * per record runs the device functions the path is built from, so tests can compare them with vectors generated by the compiled
+ * reference.  in / out are HOST buffers.
+ *  YB200_KAT_QMC : in n x {uint32 kind, a, b, c}, out n x double.  kind 0 scrHalton(dim a, n b) (scr_halton.h:47-69); 1 RI_vdC(a, b);
+ *                  2 RI_S(a, b); 3 RI_LP(a, b) (mcqmc.h:100-122); 4 fnv_32a_buf(a) (mcqmc.h:155-168); 5 Halton(base a in {2,3,5})
+ *                  .setStart(b), value of call c + 1 of getNext() (mcqmc.h:29-94)
+ *  YB200_KAT_MATH: in n x {uint32 fn, float x, float y, pad}, out n x float.  fn 0 fSin, 1 fCos, 2 fPow(x, y), 3 fExp, 4 fLog, 5 fSqrt
+ *                  (mathOptimizations.h:100-296)
+ *  YB200_KAT_BSDF: needs an updated scene.  in n x 16 words {uint32 material index (creation order), float N.xyz, Ng.xyz, wo.xyz,
+ *                  wi.xyz, s1, s2, uint32 bsdf flags}; out n x 16 floats {eval.rgb, pdf, sample(): wi.xyz, colour.rgb, W, s.pdf,
+ *                  uint32 sampledFlags, uint32 flags of initBSDF, 0, 0}  (material_t::initBSDF / eval / pdf / sample, material.h:91-192) */
+enum { YB200_KAT_QMC = 0, YB200_KAT_MATH = 1, YB200_KAT_BSDF = 2 };
+int yb200_selftest(yb200_ctx *c, int what, const void *in, size_t n, void *out);
+
+/* Dependent-load latency of this GPU (measurement hook for the latency roofline of SURVEY §8d; no reference counterpart): one
+ * thread walks a random cycle through bytes / 128 cache lines (ld.global.cg) for `steps` loads.  bytes well above the L2 size
+ * gives the L2-miss (HBM) latency t_L2miss, a few MB the L2-hit latency.  Allocates and frees `bytes` of device memory. */
+int yb200_probe_latency(yb200_ctx *c, size_t bytes, int steps, double *ns_per_load);
+
 /* ---- counters (new: the reference has none) */
 typedef struct yb200_stats {
     uint64_t n_triangles, n_bvh_nodes;

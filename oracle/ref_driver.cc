@@ -248,6 +248,41 @@ float yref_fpow(float a, float b) { return fPow(a, b); }
 float yref_fexp(float a) { return fExp(a); }
 float yref_flog(float a) { return fLog(a); }
 float yref_fsqrt(float a) { return fSqrt(a); }
+// BSDF known answers: initBSDF + eval + pdf + sample of a material created through the interface, at a surface point with the
+// given shading / geometric normal (the record layout of yb200_selftest's YB200_KAT_BSDF table; word 0 is ignored here)
+int yref_bsdf_kat(yref_ctx *c, const char *matName, const float *in, size_t n, float *out)
+{
+    const material_t *mat = c->yi->env->getMaterial(matName);
+    if (!mat) { c->err = std::string("no material ") + matName; return 0; }
+    for (size_t i = 0; i < n; ++i) {
+        const float *f = in + 16 * i;
+        float *o = out + 16 * i;
+        surfacePoint_t sp;
+        memset((void *)&sp, 0, sizeof(sp));
+        sp.material = mat;
+        sp.N = vector3d_t(f[1], f[2], f[3]); sp.Ng = vector3d_t(f[4], f[5], f[6]);
+        sp.orcoNg = sp.Ng;
+        createCS(sp.N, sp.NU, sp.NV);
+        const vector3d_t wo(f[7], f[8], f[9]), wl(f[10], f[11], f[12]);
+        uint32_t flags; memcpy(&flags, f + 15, 4);
+        renderState_t state;
+        unsigned char udat[USER_DATA_SIZE + 8];
+        state.userdata = udat;
+        state.includeLights = true;
+        BSDF_t bsdfs = 0;
+        mat->initBSDF(state, sp, bsdfs);
+        const color_t ev = mat->eval(state, sp, wo, wl, (BSDF_t)flags);
+        const float pdf = mat->pdf(state, sp, wo, wl, (BSDF_t)flags);
+        sample_t s(f[13], f[14], (BSDF_t)flags);
+        vector3d_t wi(0.f, 0.f, 0.f); float W = 0.f;
+        const color_t sc = mat->sample(state, sp, wo, wi, s, W);
+        o[0] = ev.R; o[1] = ev.G; o[2] = ev.B; o[3] = pdf;
+        o[4] = wi.x; o[5] = wi.y; o[6] = wi.z; o[7] = sc.R; o[8] = sc.G; o[9] = sc.B; o[10] = W; o[11] = s.pdf;
+        uint32_t sf = (uint32_t)s.sampledFlags, bf = (uint32_t)bsdfs;
+        memcpy(o + 12, &sf, 4); memcpy(o + 13, &bf, 4); o[14] = 0.f; o[15] = 0.f;
+    }
+    return 1;
+}
 int   yref_faure(int dim, int *out) { int b = prims[dim]; for (int i = 0; i < b; ++i) out[i] = faure[dim][i]; return b; }
 
 } // extern "C"

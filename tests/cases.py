@@ -236,6 +236,20 @@ IMAGE_CASES = {
                                                        AA_inc_samples=3, AA_threshold=0.02)),
     "c4_materials_adaptive": (scenes.materials_scene, dict(width=80, height=45, spp=1, integrator="directlighting", passes=2,
                                                            AA_inc_samples=2, AA_threshold=0.1)),
+    # scene_t::addInstance (rigid / uniform / non-uniform / sheared objToWorld) + angle-dependent smoothMesh
+    "inst_smooth_direct": (scenes.instanced_scene, dict(width=96, height=54, spp=2)),
+    "inst_smooth_path": (scenes.instanced_scene, dict(width=64, height=36, spp=2, integrator="pathtracing", bounces=3, smooth_angle=35.0)),
+    # the other reconstruction filters (imagefilm.cc:119-165) and film options: premultiplied alpha, clamp_rgb, a cropped window
+    "c1_cornell_mitchell": (scenes.cornell_box, dict(width=48, height=48, spp=3, light_samples=2, mirror_box=False,
+                                                     filter_type="mitchell", pixelwidth=3.0)),
+    "c1_cornell_lanczos": (scenes.cornell_box, dict(width=48, height=48, spp=3, light_samples=2, mirror_box=True,
+                                                    filter_type="lanczos", pixelwidth=4.0)),
+    "c1_cornell_gauss_wide": (scenes.cornell_box, dict(width=48, height=48, spp=2, light_samples=2, mirror_box=False,
+                                                       filter_type="gauss", pixelwidth=6.0)),
+    "c4_materials_premult_clamp": (scenes.materials_scene, dict(width=64, height=36, spp=2, integrator="directlighting",
+                                                                premult=True, clamp_rgb=True)),
+    "c2_field_crop": (scenes.icosphere_field, dict(n_tris=6000, subdiv=1, width=40, height=24, spp=2, bounces=3,
+                                                   xstart=17, ystart=9, cam_res=(96, 54))),
     # configs[4] (reduced): tessellated fBm terrain, sun + sky, pathtracing 4 bounces
     "c5_terrain_path": (scenes.terrain, dict(grid=60, width=64, height=36, spp=2, bounces=4)),
 }

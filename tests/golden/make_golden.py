@@ -54,6 +54,57 @@ def kat(lib):
                         hal_starts=starts, hal=hal, trig_x=x, fsin=fsin, fcos=fcos, pow_a=pa, pow_b=pb, fpow=fpow)
 
 
+BSDF_MATERIALS = ["ground", "glossy", "aniso", "gdiff", "coated", "glass", "glass2", "mirror", "shiny"]    # creation order of scenes.materials_scene
+
+
+def bsdf_queries(n_per=96, seed=21):
+    """Seeded surface frames / directions / sample values for the BSDF known answers: record layout of yb200_selftest
+    (include/yb200.h): {material index, N, Ng, wo, wi, s1, s2, flags}.  Directions cover both hemispheres; Ng = N for half of
+    the records and a tilted geometric normal otherwise; flags cycle through BSDF_ALL and single-component masks."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    BSDF_SPECULAR, BSDF_GLOSSY, BSDF_DIFFUSE, BSDF_REFLECT, BSDF_TRANSMIT = 0x1, 0x2, 0x4, 0x10, 0x20
+    ALL = 0x1 | 0x2 | 0x4 | 0x8 | 0x10 | 0x20 | 0x40            # BSDF_ALL (material.h:62)
+    masks = [ALL, ALL, BSDF_DIFFUSE | BSDF_REFLECT, BSDF_GLOSSY | BSDF_REFLECT, BSDF_SPECULAR | BSDF_REFLECT | BSDF_TRANSMIT,
+             BSDF_GLOSSY | BSDF_DIFFUSE | BSDF_REFLECT | BSDF_TRANSMIT]
+
+    def unit(v):
+        return v / np.linalg.norm(v, axis=-1, keepdims=True)
+    recs = []
+    for mi in range(len(BSDF_MATERIALS)):
+        N = unit(rng.normal(size=(n_per, 3)))
+        Ng = np.where(rng.uniform(size=(n_per, 1)) < 0.5, N, unit(N + 0.3 * rng.normal(size=(n_per, 3))))
+        wo = unit(N * rng.uniform(0.05, 1.0, (n_per, 1)) + 0.7 * rng.normal(size=(n_per, 3)))
+        wi = unit(N * rng.uniform(-0.3, 1.0, (n_per, 1)) + 0.7 * rng.normal(size=(n_per, 3)))
+        r = np.zeros((n_per, 16), np.float32)
+        r[:, 1:4] = N; r[:, 4:7] = Ng; r[:, 7:10] = wo; r[:, 10:13] = wi
+        r[:, 13] = rng.uniform(0, 1, n_per); r[:, 14] = rng.uniform(0, 1, n_per)
+        w = r.view(np.uint32)
+        w[:, 0] = mi
+        w[:, 15] = np.array([masks[k % len(masks)] for k in range(n_per)], np.uint32)
+        recs.append(r)
+    return np.concatenate(recs)
+
+
+def bsdf_kat(lib):
+    """material_t::initBSDF / eval / pdf / sample of the nine materials of scenes.materials_scene, called on the compiled reference."""
+    from core_b200 import scenes
+    yi = refapi.RefInterface(); yi.setVerbosityMute()
+    scenes.materials_scene(yi, width=8, height=8, spp=1)
+    q = bsdf_queries()
+    out = np.zeros_like(q)
+    L = lib.lib
+    L.yref_bsdf_kat.restype = C.c_int
+    L.yref_bsdf_kat.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    mi = q.view(np.uint32)[:, 0]
+    for k, name in enumerate(BSDF_MATERIALS):
+        sel = np.nonzero(mi == k)[0]
+        qi = np.ascontiguousarray(q[sel]); oi = np.zeros_like(qi)
+        assert L.yref_bsdf_kat(yi._c, name.encode(), qi.ctypes.data, len(qi), oi.ctypes.data) == 1
+        out[sel] = oi
+    np.savez_compressed(os.path.join(HERE, "bsdf_kat.npz"), q=q, out=out, materials=np.array(BSDF_MATERIALS))
+    print("bsdf_kat", len(q), "records; non-black eval", int((out[:, :3].sum(1) > 0).sum()), "non-zero sample pdf", int((out[:, 11] > 0).sum()))
+
+
 def rays(only=None):
     for name, (fn, kw) in cases.RAY_CASES.items():
         if only and name not in only:
@@ -96,6 +147,8 @@ if __name__ == "__main__":
     only = set(sys.argv[1:])      # optional: regenerate just the named cases (fixtures are deterministic)
     if not only:
         kat(refapi.ref_lib())
+    if not only or "bsdf_kat" in only:
+        bsdf_kat(refapi.ref_lib())
     rays(only)
     images(only)
     depth(only)

@@ -10,7 +10,9 @@ from core_b200.interface import YafrayInterface
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libyref.so")
 EMU_SO = os.path.join(ROOT, "tests", "emu", "libyb200_emu.so")
+REF_STRICT_SO = os.path.join(ROOT, "oracle", "_ref", "strict", "libyref.so")    # same sources without -ffast-math (oracle/Makefile)
 _ref = None
+_ref_strict = None
 _emu = None
 
 
@@ -27,6 +29,32 @@ def ref_lib():
 
 def RefInterface():
     return YafrayInterface(clib=ref_lib())
+
+
+def have_ref_strict():
+    return os.path.exists(REF_STRICT_SO)
+
+
+def StrictRefInterface():
+    """The reference compiled without -ffast-math: separates the release build's own float noise from real differences."""
+    global _ref_strict
+    if _ref_strict is None:
+        _ref_strict = capi.CLib(REF_STRICT_SO, prefix="yref_", product=False)
+    return YafrayInterface(clib=_ref_strict)
+
+
+def render_in_subprocess(which, builder, **kw):
+    """Frame of core_b200.scenes.<builder>(**kw) rendered by the `release` or the `strict` build of the reference in its own
+    process (tests/ref_subprocess.py)."""
+    import json
+    import sys
+    import tempfile
+    import numpy as np
+    with tempfile.TemporaryDirectory() as d:
+        out = os.path.join(d, "frame.npy")
+        subprocess.run([sys.executable, os.path.join(ROOT, "tests", "ref_subprocess.py"), which, builder, json.dumps(kw), out],
+                       check=True, stdout=subprocess.DEVNULL)
+        return np.load(out)
 
 
 def have_emu():

@@ -77,9 +77,10 @@ def test_ray_parity_golden(name):
     g = np.load(os.path.join(G, name + ".npz"))
     got = yi.traceBatch(g["rays"], 0)
     bad, terr, berr, ntie = cases.compare_hits(g["closest"], got)
-    assert bad <= 1e-3 and terr <= 1e-5 and berr <= 1e-4, (bad, terr, berr, ntie)   # north_star: IDs exact except t-ties, t/bary 1e-5
+    # north_star: ids exact except t-ties, t and barycentrics to 1e-5; shadow flags equal
+    assert bad == 0 and terr <= 1e-5 and berr <= 1e-5, (bad, terr, berr, ntie)
     sh = yi.traceBatch(g["rays"], 1)
-    assert np.mean(sh != g["shadow"]) <= 1e-3
+    assert np.count_nonzero(sh != g["shadow"]) == 0
 
 
 def test_against_bruteforce_oracle_fresh_rays():
@@ -102,7 +103,7 @@ def test_against_live_reference_medium_scene():
     yi = YafrayInterface(); scenes.icosphere_field(yi, **kw)
     b = yi.render(160, 90)
     rel, psnr, da = cases.compare_images(a, b)
-    assert rel <= 1e-3 and psnr >= 60.0, (rel, psnr, da)
+    assert rel <= 1e-5 and psnr >= 100.0, (rel, psnr, da)
 
 
 def test_full_size_properties_1m_triangles():
@@ -221,3 +222,49 @@ def test_full_size_terrain_50m_triangles():
     assert np.all(yi.traceBatch(up, 0)["prim"] < 0)
     img = yi.render(160, 90)
     assert np.isfinite(img).all() and img[..., :3].mean() > 0.05
+
+
+def test_russian_roulette_extension_is_unbiased_gpu():
+    """north_star names Russian roulette; the reference path tracer has none (SURVEY.md discrepancy 1), so it is an opt-in
+    extension that is OFF in every parity case and validated statistically when ON: same image mean within noise."""
+    out = []
+    for rr in (False, True):
+        yi = YafrayInterface()
+        scenes.cornell_box(yi, 64, 64, spp=64, light_samples=1, mirror_box=False, integrator="pathtracing",
+                           integ_params=dict(bounces=8, path_samples=1, russian_roulette=rr))
+        img = yi.render(64, 64)
+        assert np.isfinite(img).all()
+        out.append((img[..., :3].mean(axis=(0, 1)), yi.getStats()["rays_closest"]))
+    (m0, r0), (m1, r1) = out
+    assert np.all(np.abs(m0 - m1) / m0 < 0.01), (m0, m1)
+    assert r1 < r0                                   # roulette really terminates paths
+
+
+def test_abort_mid_frame(monkeypatch):
+    """scene_t::abort (scene.cc:71-85) polled between batches: through the should_abort callback and through yb200_abort
+    called from the progress callback.  The frame so far is still resolved (imageFilm_t::flush after an aborted render)."""
+    import ctypes as C
+    from core_b200 import capi
+    monkeypatch.setenv("YB200_BATCH_SAMPLES", "2048")        # 48 x 32 x 8 spp = 6 batches
+    kw = dict(width=48, height=32, spp=8, light_samples=2)
+    yi = YafrayInterface(); scenes.cornell_box(yi, **kw)
+    full = yi.render(48, 32)
+    for how in ("callback", "yb200_abort"):
+        yi = YafrayInterface(); scenes.cornell_box(yi, **kw)
+        seen = []
+
+        def progress(user, done, total):
+            seen.append((done, total))
+            if how == "yb200_abort" and done == 2:
+                yi.abort()
+        cb = capi.Callbacks(None, C.CFUNCTYPE(C.c_int, C.c_void_p)(lambda u: 1 if (how == "callback" and len(seen) >= 2) else 0),
+                            C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int)(progress))
+        out = np.zeros((32, 48, 4), np.float32)
+        assert yi._call("render", out.ctypes.data, 48, 32, C.byref(cb)) == 1, yi.lastError()
+        assert seen and seen[-1][0] == 2 and seen[-1][1] == 6, (how, seen)
+        done = (out != 0).any(axis=2)                     # pixels that received a splat (weight > 0; rays that leave the box have alpha 0)
+        assert 0.2 < done.mean() < 0.5, done.mean()
+        inner = done & np.roll(done, 1, 0) & np.roll(done, -1, 0) & np.roll(done, 1, 1) & np.roll(done, -1, 1)
+        inner[-1] = False                                 # splats of the next (aborted) row never arrived at the last finished row
+        assert np.allclose(out[inner], full[inner], rtol=1e-5, atol=1e-6)
+        assert np.all(out[~done] == 0.0)

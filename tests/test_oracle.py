@@ -64,10 +64,12 @@ def test_bruteforce_against_golden_kdtree_results(name):
     g = np.load(os.path.join(G, name + ".npz"))
     got, ties = op.closest(tris, g["rays"])
     bad, terr, berr, ntie = cases.compare_hits(g["closest"], got)
-    assert bad <= 1e-3, (bad, ntie)           # kd-tree vs brute force: only edge/tie cases may differ
-    assert terr <= 1e-5 and berr <= 1e-4
+    # north_star: ids exact except t-ties, t and barycentrics to 1e-5 (the brute force runs the reference's own Moeller-Trumbore
+    # arithmetic, so t / u / v are in fact bit-identical wherever the ids agree)
+    assert bad == 0, (bad, ntie)
+    assert terr <= 1e-5 and berr <= 1e-5, (terr, berr)
     sh = op.shadow(tris, g["rays"])
-    assert np.mean(sh != g["shadow"]) <= 1e-3
+    assert np.count_nonzero(sh != g["shadow"]) == 0
 
 
 @pytest.mark.skipif(not refapi.have_ref(), reason="oracle/_ref not built")
