@@ -370,9 +370,13 @@ def main():
     if ifiles and args.workload == "c2_field_1M_1080p_64spp":
         ij = json.load(open(os.path.join(ROOT, "profiles", ifiles[-1])))
         roofline["thread_inst_per_ray"] = ij["thread_inst_per_ray"]
+        roofline["warp_inst_per_ray"] = ij["warp_inst_per_ray"]
         roofline["lanes_active"] = ij["lanes_active"]
-        roofline["issue_bound_grays"] = 148 * 4 * 32 * sm_hz / ij["thread_inst_per_ray"] / 1e9
-        roofline["issue_note"] = "148 SM x 4 schedulers x 32 lanes x SM clock / thread instructions per ray (ncu, profiles/%s)" % ifiles[-1]
+        # what binds (ncu: issue slots ~70 % busy, DRAM < 5 %): 4 warp instructions per SM and clock
+        roofline["issue_bound_grays"] = 148 * 4 * sm_hz / ij["warp_inst_per_ray"] / 1e9
+        roofline["issue_bound_grays_all_lanes_active"] = 148 * 4 * 32 * sm_hz / ij["thread_inst_per_ray"] / 1e9
+        roofline["issue_note"] = ("148 SM x 4 schedulers x SM clock / warp instructions per ray at the measured lane efficiency; "
+                                  "the second figure assumes 32 of 32 lanes active (ncu, profiles/%s)" % ifiles[-1])
         roofline["binding_bound"] = "issue"
         roofline["frac_of_issue_bound"] = roofline["grays_per_s_in_trace_kernels"] / roofline["issue_bound_grays"] if roofline["grays_per_s_in_trace_kernels"] else None
     line = {"metric": metric, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

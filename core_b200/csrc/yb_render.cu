@@ -86,6 +86,7 @@ YB_D uint32_t shade_key(const RenderArgs &a, uint32_t t)
 __global__ void __launch_bounds__(256) k_bin_count_kernel(uint32_t n, const RenderArgs a)
 {
     __shared__ uint32_t h[YB_SHADE_BINS];
+    if (a.nPtr) n = min(n, *a.nPtr);
     if (threadIdx.x < YB_SHADE_BINS) h[threadIdx.x] = 0u;
     __syncthreads();
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
@@ -99,6 +100,8 @@ __global__ void __launch_bounds__(256) k_bin_count_kernel(uint32_t n, const Rend
 __global__ void __launch_bounds__(256) k_bin_scatter_kernel(uint32_t n, const RenderArgs a)
 {
     __shared__ uint32_t h[YB_SHADE_BINS], base[YB_SHADE_BINS];
+    if (a.nPtr) n = min(n, *a.nPtr);
+    if (blockIdx.x * blockDim.x >= n) return;
     if (threadIdx.x < YB_SHADE_BINS) h[threadIdx.x] = 0u;
     __syncthreads();
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -123,6 +126,7 @@ static void bin_tasks(uint32_t n, const RenderArgs &a, rt_stream s)
     k_bin_scatter_kernel<<<blocks, 256, 0, s>>>(n, a);
     YB_CUDA_CHECK(cudaGetLastError());
 #else
+    if (a.nPtr && *a.nPtr < n) n = *a.nPtr;
     for (uint32_t t = 0; t < n; ++t) { a.keys[t] = (unsigned char)shade_key(a, t); a.bins[a.keys[t]]++; }
     uint32_t base[YB_SHADE_BINS], acc = 0;
     for (int b = 0; b < YB_SHADE_BINS; ++b) { base[b] = acc; acc += a.bins[b]; }
@@ -342,7 +346,16 @@ struct RenderBuffers {
     DevBuf<Task> poolA, poolB;
     DevBuf<Hit> hits;
     DevBuf<ShadowTask> shadow;
-    DevBuf<uint32_t> counters, order, bins;
+    DevBuf<uint32_t> counters, order, bins, waveCnt;
+#ifndef YB_HOSTEMU
+    std::vector<cudaEvent_t> events;     // per-wave stage timers of the device-counted wave loop, read once per batch
+    ~RenderBuffers() { for (size_t i = 0; i < events.size(); ++i) cudaEventDestroy(events[i]); }
+    cudaEvent_t event(size_t i)
+    {
+        while (events.size() <= i) { cudaEvent_t e; YB_CUDA_CHECK(cudaEventCreate(&e)); events.push_back(e); }
+        return events[i];
+    }
+#endif
     DevBuf<unsigned char> keys, aaFlags;
     DevBuf<f4> acc;
     DevBuf<uint32_t> pix;
@@ -553,6 +566,10 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
         const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;
+        // longest chain of tasks one camera sample can spawn when every task has at most one child: the camera task, one path
+        // vertex per bounce, one specular child per recursion level (raylevel is capped at rDepth, mcintegrator.cc:428,588)
+        const int maxChain = 1 + (I.type == INTEG_PATH ? std::max(0, I.maxBounces) : 0) + (specChildren ? std::max(0, I.rDepth) + 1 : 0);
+        const bool deviceWaves = F <= 1 && useFast && !I.trShad && !sortRays && !logWaves && env_size("YB200_DEVICE_WAVES", 1) != 0;
         const int nBatches = (int)((totalSamples + B - 1) / B);
         for (int b = 0; b < nBatches; ++b) {
             if (c.abortFlag || (should_abort && should_abort(user))) break;
@@ -563,6 +580,74 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
             size_t top = nb;
             bool firstWave = true;      // camera rays come in pixel order: already coherent
             bool firstShadowWave = true;
+            // ---- device-counted waves.  With a fan-out of at most one child per task the pool never outgrows the batch, every
+            //      wave consumes the whole pool and ping-pongs to the other one - so the host does not need the counts to plan
+            //      the next wave: each kernel reads its task / ray count from the counter block the previous kernel filled, and
+            //      the host reads all counters and stage timers ONCE per batch instead of blocking three times per wave
+            //      (160 waves per frame of the benchmark scene).
+            if (deviceWaves) {
+                uint32_t pending = nb;
+                while (pending > 0) {
+                    const size_t nSlots = (size_t)maxChain + 1;
+                    rb.waveCnt.reserve(4 * nSlots);
+                    rt_memset(rb.waveCnt.p, 0, 4 * nSlots * sizeof(uint32_t), s);
+                    rt_h2d(rb.waveCnt.p, &pending, sizeof(uint32_t), s);          // slot 0: input count of the first wave
+                    for (int w = 0; w < maxChain; ++w) {
+                        a.tasks = pool; a.out_tasks = alt; a.outCap = (uint32_t)std::min<size_t>(poolCap, 0xffffffffu);
+                        a.nPtr = rb.waveCnt.p + 4 * (size_t)w;
+                        a.counters = rb.waveCnt.p + 4 * (size_t)(w + 1);
+#ifndef YB_HOSTEMU
+                        YB_CUDA_CHECK(cudaEventRecord(rb.event(4 * (size_t)w + 0), s));
+#endif
+                        {
+                            FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task);
+                            j.n = pending; j.nPtr = a.nPtr; j.order = 0; j.counter = a.counters + 2; j.out = a.hits; j.acc = a.acc;
+                            j.nNodes = c.sc.nNodes; trace_tuning(j); j.counterZeroed = true;
+                            launch_trace_fast<false, OUT_HITS>(j, s);
+                        }
+#ifndef YB_HOSTEMU
+                        YB_CUDA_CHECK(cudaEventRecord(rb.event(4 * (size_t)w + 1), s));
+#endif
+                        a.order = 0;
+                        if (binShade && (!firstWave || binFirst)) { bin_tasks(pending, a, s); a.order = rb.order.p; }
+                        if (nodeShade) launch_shade_nodes(pending, a, s);
+                        else if (extShade) launch_shade_ext(pending, a, s);
+                        else launch_shade_base(pending, a, s);
+#ifndef YB_HOSTEMU
+                        YB_CUDA_CHECK(cudaEventRecord(rb.event(4 * (size_t)w + 2), s));
+#endif
+                        firstWave = false;
+                        {
+                            FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask);
+                            j.n = (uint32_t)std::min<size_t>((size_t)pending * S, 0xffffffffu); j.nPtr = a.counters + 1; j.order = 0;
+                            j.counter = a.counters + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j); j.counterZeroed = true;
+                            launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
+                        }
+#ifndef YB_HOSTEMU
+                        YB_CUDA_CHECK(cudaEventRecord(rb.event(4 * (size_t)w + 3), s));
+#endif
+                        std::swap(pool, alt);
+                    }
+                    std::vector<uint32_t> hc(4 * nSlots);
+                    rt_d2h(hc.data(), rb.waveCnt.p, hc.size() * sizeof(uint32_t), s);      // waits for the waves above
+                    for (int w = 0; w < maxChain; ++w) {
+                        const uint32_t nIn = hc[4 * (size_t)w], nChildren = hc[4 * (size_t)(w + 1)], nShadow = hc[4 * (size_t)(w + 1) + 1];
+                        if (nChildren > poolCap || nShadow > shadowCap || nChildren > nIn) throw RtError("render: internal queue overflow");
+                        raysClosest += nIn; raysShadow += nShadow;
+#ifndef YB_HOSTEMU
+                        if (nIn) {
+                            float m = 0.f;
+                            cudaEventElapsedTime(&m, rb.events[4 * (size_t)w + 0], rb.events[4 * (size_t)w + 1]); msClosest += m;
+                            cudaEventElapsedTime(&m, rb.events[4 * (size_t)w + 1], rb.events[4 * (size_t)w + 2]); msShade += m;
+                            if (nShadow) { cudaEventElapsedTime(&m, rb.events[4 * (size_t)w + 2], rb.events[4 * (size_t)w + 3]); msShadow += m; }
+                        }
+#endif
+                    }
+                    pending = hc[4 * (size_t)maxChain];      // tasks still alive after maxChain waves (none unless the bound below is too low)
+                }
+                top = 0;
+                a.nPtr = 0; a.counters = rb.counters.p;
+            }
             while (top > 0) {
                 size_t M = std::min(top, B);
                 M = std::min(M, shadowCap / S);
@@ -575,7 +660,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 rt_memset(rb.counters.p, 0, 4 * sizeof(uint32_t), s);
                 tc.start();
                 if (useFast) {
-                    FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task); j.n = (uint32_t)M;
+                    FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task); j.n = (uint32_t)M; j.nPtr = 0; j.counterZeroed = false;
                     j.order = (sortRays && !firstWave) ? sort_rays((const char *)a.tasks, sizeof(Task), (uint32_t)M, c.sc.boundLo, c.sc.boundHi, c.raySort, s) : 0;
                     j.counter = rb.counters.p + 2; j.out = a.hits; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j);
                     launch_trace_fast<false, OUT_HITS>(j, s);
@@ -595,7 +680,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 if (cnt[0] > a.outCap || cnt[1] > a.shadowCap) throw RtError("render: internal queue overflow");
                 tsh.start();
                 if (useFast && !I.trShad) {
-                    FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask); j.n = cnt[1];
+                    FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask); j.n = cnt[1]; j.nPtr = 0; j.counterZeroed = false;
                     j.order = (sortRays >= 2 && (!firstShadowWave || sortRays >= 3)) ? sort_rays((const char *)a.shadow, sizeof(ShadowTask), cnt[1], c.sc.boundLo, c.sc.boundHi, c.raySort, s) : 0;
                     j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j);
                     launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
@@ -653,7 +738,7 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
         if (useFast && mode != TRACE_TSHADOW) {
             c.d_traceCounter.reserve(4);
             FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)(ta.rays + o); j.stride = sizeof(Ray); j.n = m;
-            j.order = 0; j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; trace_tuning(j);
+            j.order = 0; j.nPtr = 0; j.counterZeroed = false; j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; trace_tuning(j);
             if (mode == TRACE_CLOSEST) { j.out = (ClosestOut *)d_out + o; launch_trace_fast<false, OUT_CLOSEST_PRIM>(j, c.stream); }
             else { j.out = (int32_t *)d_out + o; launch_trace_fast<true, OUT_SHADOW_FLAG>(j, c.stream); }
             continue;

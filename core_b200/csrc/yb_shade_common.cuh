@@ -56,6 +56,7 @@ struct RenderArgs {
     Task *out_tasks;        // children appended here
     ShadowTask *shadow;     // shadow rays appended here
     uint32_t *counters;     // [0] out_tasks count, [1] shadow count
+    const uint32_t *nPtr;   // optional: the number of tasks of this wave lives in device memory (the launch's n is an upper bound)
     const uint32_t *order;  // shading order of this wave (0 = identity): tasks binned by shade_key
     uint32_t *orderOut; unsigned char *keys; uint32_t *bins;   // binning scratch: bins[0..7] counts, bins[8..15] cursors
     f4 *acc;                // per camera sample: rgb + alpha

@@ -88,9 +88,11 @@ struct FastJob {
     const BvhNode *nodes;
     const f4 *tri_v;
     const char *rays;        // ray records {from, tmin, dir, tmax} at offset 0 of each `stride`-byte record
-    uint32_t stride, n;
+    uint32_t stride, n;      // n: number of rays, or - with nPtr - an upper bound that only sizes the grid
+    const uint32_t *nPtr;    // optional: the ray count lives in device memory (written by the kernel that filled the queue)
     const uint32_t *order;   // optional: fetch order of the rays (coherence sort); results still go to the ray's own slot
-    uint32_t *counter;       // zeroed by the host before launch
+    uint32_t *counter;       // ray-fetch counter; cleared on the stream by the launcher unless counterZeroed
+    bool counterZeroed;
     void *out;               // OUT_HITS: Hit[n]; OUT_SHADOW_FLAG: int32[n]; OUT_CLOSEST_PRIM: {prim,t,b1,b2}[n]
     f4 *acc;                 // OUT_SHADOW_ACC: ShadowTask{ray, c, sid}: acc[sid].rgb += c when unoccluded
     uint32_t nNodes;
@@ -123,6 +125,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
     const unsigned lane = threadIdx.x & 31u;   // 0 in the emulator
     const unsigned FULL = YB_FULLMASK;
     const uint32_t one = job.oneBits;
+    const uint32_t nRays = job.nPtr ? __ldg(job.nPtr) : job.n;
 
     bool active = false, exhausted = false;
     uint32_t rayIdx = 0;
@@ -147,7 +150,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                 base = __shfl_sync(FULL, base, leader);
                 if (!active) {
                     uint32_t i = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
-                    if (i < job.n) {
+                    if (i < nRays) {
                         if (SORTED) i = __ldg(job.order + i);          // coherence-sorted fetch order (opt-in, measured slower: DESIGN.md)
                         const float4 r0 = __ldg((const float4 *)(job.rays + (size_t)i * job.stride));
                         const float4 r1 = __ldg((const float4 *)(job.rays + (size_t)i * job.stride + 16));
@@ -179,7 +182,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                         }
                     }
                 }
-                if (base + (uint32_t)nIdle >= job.n) exhausted = true;
+                if (base + (uint32_t)nIdle >= nRays) exhausted = true;
             }
             if (__ballot_sync(FULL, active) == 0u) { if (exhausted) break; else continue; }
         }
@@ -312,12 +315,12 @@ static void launch_trace_fast(const FastJob &job, rt_stream s)
 #ifdef YB_TRACE_STATS
     g_stat_rays += job.n;
 #endif
-    *job.counter = 0;
+    if (!job.counterZeroed) *job.counter = 0;
     if (job.order) k_trace_fast<ANYHIT, OUT, true>(job); else k_trace_fast<ANYHIT, OUT, false>(job);
     g_kernel_launches++;
     return;
 #else
-    YB_CUDA_CHECK(cudaMemsetAsync(job.counter, 0, sizeof(uint32_t), s));
+    if (!job.counterZeroed) YB_CUDA_CHECK(cudaMemsetAsync(job.counter, 0, sizeof(uint32_t), s));
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

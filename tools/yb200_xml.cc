@@ -9,8 +9,31 @@
 //   <smooth ID angle>; <instance base_object_id><transform m00..m33/></instance>; <render> parameter map.
 // SAX events come from expat (libxml2 is what the reference uses; it is not needed for this dialect).
 //
-// usage: yb200-xml [-o out.(tga|pfm|f32)] [-dev N] [-vl 0..3] [-w W -h H] scene.xml
+// usage: yb200-xml [-o out.(tga|pfm|f32)] [-z depth.f32] [-dev N] [-vl 0..3] [-w W -h H] scene.xml
+//
+// Second build, -DYB200_XML_REFERENCE_HEADER (oracle/Makefile -> oracle/_ref/yb200-xml-refhdr, test infrastructure): the same
+// loader compiled ONLY against the reference's own headers (include/interface/yafrayinterface.h, core_api/output.h,
+// core_api/matrix4.h, yafraycore/monitor.h) - no header of this repository - that obtains its interface object from
+// `getYafray()` of the library named with -lib.  It is what an existing exporter / binding binary is: with
+// -lib core_b200/libyb200_yafray.so it proves that the vtable of include/yb200_interface.hpp is binary-compatible
+// (tests/test_reference_header_client.py); with -lib oracle/_ref/libyafarayplugin.so -plugins oracle/_ref/plugins the very
+// same binary drives the reference itself.
+#ifdef YB200_XML_REFERENCE_HEADER
+#include <interface/yafrayinterface.h>
+#include <core_api/output.h>
+#include <core_api/matrix4.h>
+#include <yafraycore/monitor.h>
+#include <dlfcn.h>
+#include <cstring>
+namespace yb200 {
+using yafaray::yafrayInterface_t; using yafaray::material_t; using yafaray::colorOutput_t; using yafaray::progressBar_t;
+using yafaray::matrix4x4_t;
+}
+#define YI_ERR(yi) "(the interface of the reference has no lastError: see the log above)"
+#else
 #include "../include/yb200_interface.hpp"
+#define YI_ERR(yi) (yi).lastError()
+#endif
 #include <expat.h>
 #include <cstdio>
 #include <cstdlib>
@@ -102,7 +125,7 @@ struct Loader {
             {
                 int type = 0;
                 for (int n = 0; at[n]; n += 2) if (!strcmp(at[n], "type") && !strcmp(at[n + 1], "universal")) type = 1;
-                if (!yi.startScene(type)) error(std::string("startScene failed: ") + yi.lastError());
+                if (!yi.startScene(type)) error(std::string("startScene failed: ") + YI_ERR(yi));
             }
             push(SCENE);
             break;
@@ -117,10 +140,11 @@ struct Loader {
         case INSTANCE:
             if (e == "transform") {
                 yb200::matrix4x4_t m;
+                for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) m[i][j] = i == j ? 1.f : 0.f;
                 for (int n = 0; at[n]; n += 2)
                     if (at[n][0] == 'm' && at[n][1] >= '0' && at[n][1] <= '3' && at[n][2] >= '0' && at[n][2] <= '3' && !at[n][3])
                         m[at[n][1] - '0'][at[n][2] - '0'] = (float)atof(at[n + 1]);
-                if (!yi.addInstance(instanceBase, m)) error(std::string("addInstance failed: ") + yi.lastError());
+                if (!yi.addInstance(instanceBase, m)) error(std::string("addInstance failed: ") + YI_ERR(yi));
             }
             push(SKIP);
             break;
@@ -167,7 +191,7 @@ struct Loader {
             }
             if (!yi.startGeometry()) error("invalid scene state on startGeometry()");
             unsigned uid = id == -1 ? yi.getNextFreeID() : (unsigned)id;
-            if (!yi.startTriMesh(uid, vertices, faces, meshOrco, meshUV, type)) error(std::string("startTriMesh failed: ") + yi.lastError());
+            if (!yi.startTriMesh(uid, vertices, faces, meshOrco, meshUV, type)) error(std::string("startTriMesh failed: ") + YI_ERR(yi));
             push(MESH);
         } else if (e == "smooth") {
             unsigned id = 0; double angle = 181;
@@ -221,7 +245,7 @@ struct Loader {
                 else if (!strcmp(k, "uv_c")) uc = atoi(at[n + 1]);
             }
             bool ok = meshUV ? yi.addTriangle(a, b, c, ua, ub, uc, meshMat) : yi.addTriangle(a, b, c, meshMat);
-            if (!ok) error(std::string("addTriangle failed: ") + yi.lastError());
+            if (!ok) error(std::string("addTriangle failed: ") + YI_ERR(yi));
         } else if (e == "uv") {
             float u = 0, v = 0;
             for (int n = 0; at[n]; n += 2) { if (at[n][0] == 'u') u = (float)atof(at[n + 1]); else if (at[n][0] == 'v') v = (float)atof(at[n + 1]); }
@@ -247,7 +271,7 @@ struct Loader {
         else if (elemKind == "background") ok = yi.createBackground(n) != 0;
         else if (elemKind == "object") ok = yi.createObject(n) != 0;
         else if (elemKind == "volumeregion") ok = yi.createVolumeRegion(n) != 0;
-        if (!ok) error("creating " + elemKind + " '" + elemName + "' failed: " + yi.lastError());
+        if (!ok) error("creating " + elemKind + " '" + elemName + "' failed: " + YI_ERR(yi));
         yi.paramsClearAll();
     }
 };
@@ -303,15 +327,35 @@ struct ConsoleBar : yb200::progressBar_t {
     void setTag(const char *) override {}
 };
 
+// memoryIO_t-style sink (src/yafraycore/memoryIO.cc:27-43) that also keeps what arrives through putPixel(..., depth = true, z)
+// and counts the calls of the colorOutput_t interface
+struct FrameOut : yb200::colorOutput_t {
+    int w, h; std::vector<float> img, z; long nPut = 0, nDepth = 0, nFlushArea = 0, nFlush = 0;
+    FrameOut(int w_, int h_) : w(w_), h(h_), img((size_t)w_ * h_ * 4, 0.f), z((size_t)w_ * h_, 0.f) {}
+    bool putPixel(int x, int y, const float *c, bool alpha = true, bool depth = false, float zv = 0.f) {
+        float *p = img.data() + (size_t)(x + w * y) * 4;
+        p[0] = c[0]; p[1] = c[1]; p[2] = c[2]; p[3] = alpha ? c[3] : 1.f;
+        ++nPut;
+        if (depth) { z[(size_t)x + (size_t)w * y] = zv; ++nDepth; }
+        return true;
+    }
+    void flush() { ++nFlush; }
+    void flushArea(int, int, int, int) { ++nFlushArea; }
+    void highliteArea(int, int, int, int) {}
+};
+
 }  // namespace
 
 int main(int argc, char **argv)
 {
-    std::string out = "yb200.tga", scenePath;
+    std::string out = "yb200.tga", scenePath, zOut, libPath, pluginDir;
     int dev = 0, vl = 2, ow = 0, oh = 0;
     for (int i = 1; i < argc; ++i) {
         std::string a(argv[i]);
         if (a == "-o" && i + 1 < argc) out = argv[++i];
+        else if (a == "-z" && i + 1 < argc) zOut = argv[++i];
+        else if (a == "-lib" && i + 1 < argc) libPath = argv[++i];
+        else if (a == "-plugins" && i + 1 < argc) pluginDir = argv[++i];
         else if (a == "-dev" && i + 1 < argc) dev = atoi(argv[++i]);
         else if (a == "-vl" && i + 1 < argc) vl = atoi(argv[++i]);
         else if (a == "-w" && i + 1 < argc) ow = atoi(argv[++i]);
@@ -323,9 +367,22 @@ int main(int argc, char **argv)
     FILE *f = std::fopen(scenePath.c_str(), "rb");
     if (!f) { std::fprintf(stderr, "yb200-xml: cannot open %s\n", scenePath.c_str()); return 1; }
 
+#ifdef YB200_XML_REFERENCE_HEADER
+    if (libPath.empty()) { std::fprintf(stderr, "yb200-xml-refhdr: -lib <library exporting getYafray> is required\n"); return 2; }
+    void *lib = dlopen(libPath.c_str(), RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) { std::fprintf(stderr, "yb200-xml-refhdr: %s\n", dlerror()); return 1; }
+    yafaray::interfaceConstructor *ctor = (yafaray::interfaceConstructor *)dlsym(lib, "getYafray");
+    if (!ctor) { std::fprintf(stderr, "yb200-xml-refhdr: no getYafray in %s\n", libPath.c_str()); return 1; }
+    yafrayInterface_t *yip = ctor();
+    yafrayInterface_t &yi = *yip;
+    yi.setVerbosityLevel(vl);
+    yi.loadPlugins(pluginDir.empty() ? 0 : pluginDir.c_str());
+    (void)dev;
+#else
     yafrayInterface_t yi;
     yi.setVerbosityLevel(vl);
-    if (!yi.setDevice(dev)) { std::fprintf(stderr, "yb200-xml: %s\n", yi.lastError()); return 1; }
+    if (!yi.setDevice(dev)) { std::fprintf(stderr, "yb200-xml: %s\n", YI_ERR(yi)); return 1; }
+#endif
     Loader ld(yi);
     XML_Parser xp = XML_ParserCreate(NULL);
     XML_SetUserData(xp, &ld);
@@ -356,14 +413,37 @@ int main(int argc, char **argv)
     yi.paramsSetInt("width", w);
     yi.paramsSetInt("height", h);
 
-    std::vector<float> img((size_t)w * h * 4, 0.f);
-    yb200::memoryIO_t mem(w, h, img.data());
+    FrameOut mem(w, h);
+    std::vector<float> &img = mem.img;
     yi.render(mem, vl >= 3 ? new ConsoleBar() : 0);
-    if (!yi.renderSucceeded()) { std::fprintf(stderr, "yb200-xml: render failed: %s\n", yi.lastError()); return 1; }
+#ifdef YB200_XML_REFERENCE_HEADER
+    // more calls through the reference's vtable, printed for the test: slots behind render() and the by-value matrix of addInstance
+    {
+        yafaray::matrix4x4_t ident;
+        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) ident[i][j] = i == j ? 1.f : 0.f;
+        const bool inst = yi.addInstance(0x7ffffff0u, ident);                     // no such base object: must come back false
+        yi.setDrawParams(true);
+        const bool dp1 = yi.getDrawParams();
+        yi.setDrawParams(false);
+        const bool dp0 = yi.getDrawParams();
+        const std::string fmt = yi.getImageFormatFromFullName("no such format");
+        std::fprintf(stderr, "refhdr: version='%s' putPixel=%ld depthPixels=%ld flushArea=%ld flush=%ld addInstance(bad)=%d drawParams=%d/%d "
+                     "handlers=%zu format='%s'\n", yi.getVersion(), mem.nPut, mem.nDepth, mem.nFlushArea, mem.nFlush, (int)inst, (int)dp1, (int)dp0,
+                     yi.listImageHandlers().size(), fmt.c_str());
+    }
+    if (mem.nPut == 0) { std::fprintf(stderr, "yb200-xml-refhdr: render delivered no pixels\n"); return 1; }
+#else
+    if (!yi.renderSucceeded()) { std::fprintf(stderr, "yb200-xml: render failed: %s\n", YI_ERR(yi)); return 1; }
     yb200_stats st;
     if (yi.getStats(st))
         std::fprintf(stderr, "yb200-xml: %llu tris, %llu rays, build %.1f ms, render %.1f ms\n", (unsigned long long)st.n_triangles,
                      (unsigned long long)(st.rays_closest + st.rays_shadow), st.build_ms, st.render_ms);
+#endif
+    if (!zOut.empty()) {
+        FILE *o = std::fopen(zOut.c_str(), "wb");
+        if (!o || std::fwrite(mem.z.data(), sizeof(float), mem.z.size(), o) != mem.z.size()) { std::fprintf(stderr, "yb200-xml: cannot write %s\n", zOut.c_str()); return 1; }
+        std::fclose(o);
+    }
     const std::string ext = out.size() > 4 ? out.substr(out.size() - 4) : "";
     bool ok;
     if (ext == ".pfm") ok = writePFM(out.c_str(), img.data(), w, h);
