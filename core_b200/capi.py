@@ -90,6 +90,7 @@ _PRODUCT_ONLY = {
     "trace_batch_static": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int]),
     "selftest": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
     "probe_latency": (C.c_int, [C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
+    "set_devices": (C.c_int, [C.POINTER(C.c_int), C.c_int]),
 }
 EXPORTED_SYMBOLS = (["create", "version"] + sorted(_CTX_FUNCS) + sorted(_PRODUCT_ONLY))
 

@@ -19,7 +19,7 @@
 
 namespace yb {
 
-uint64_t g_kernel_launches = 0;
+thread_local uint64_t g_kernel_launches = 0;     // per thread: one host thread drives each device of a multi-GPU render
 
 // order-preserving float <-> int map for atomic min/max
 YB_HD int32_t f2ord(float f) { int32_t i = f2i(f); return i >= 0 ? i : (int32_t)(i ^ 0x7fffffff); }

@@ -34,6 +34,27 @@ int yb200_set_device(yb200_ctx *ctx, int dev)
     CTX.device = dev;
     return 1;
 }
+int yb200_set_devices(yb200_ctx *ctx, const int *devices, int n)
+{
+#ifdef YB_HOSTEMU
+    (void)devices;
+    return n == 1 ? 1 : (CTX.fail("set_devices: several devices are not part of the host emulator") ? 1 : 0);
+#else
+    int have = 0;
+    if (n < 1 || !devices) return CTX.fail("set_devices: empty device list") ? 1 : 0;
+    if (cudaGetDeviceCount(&have) != cudaSuccess) return CTX.fail("set_devices: no CUDA device") ? 1 : 0;
+    for (int i = 0; i < n; ++i) {
+        if (devices[i] < 0 || devices[i] >= have) return CTX.fail("set_devices: no such CUDA device " + std::to_string(devices[i])) ? 1 : 0;
+        for (int j = 0; j < i; ++j) if (devices[j] == devices[i]) return CTX.fail("set_devices: device listed twice") ? 1 : 0;
+    }
+    if (CTX.stream && CTX.device != devices[0]) return CTX.fail("set_devices: context already bound to another device (the first entry is the leader)") ? 1 : 0;
+    CTX.device = devices[0];
+    for (size_t i = 0; i < CTX.helpers.size(); ++i) delete CTX.helpers[i];
+    CTX.helpers.clear();
+    for (int i = 1; i < n; ++i) { Context *h = new Context(); h->device = devices[i]; CTX.helpers.push_back(h); }
+    return 1;
+#endif
+}
 void yb200_set_verbosity(yb200_ctx *ctx, int level) { CTX.verbosity = level; }
 void yb200_clear_all(yb200_ctx *ctx) { CTX.clearAll(); }
 
@@ -144,6 +165,8 @@ int yb200_render(yb200_ctx *ctx, float *rgba, int width, int height, const yb200
     if (!CTX.sceneStarted) return CTX.fail("render: no scene") ? 1 : 0;
     if (!CTX.setupRender(width, height)) return 0;
     if (!CTX.updateScene()) return 0;
+    if (!CTX.helpers.empty())       // yb200_set_devices: tiles over all devices, films summed on the leader over NVLink
+        return render_group(CTX, rgba, cb ? cb->should_abort : 0, cb ? cb->progress : 0, cb ? cb->user : 0) ? 1 : 0;
     const size_t npx = (size_t)CTX.sc.film.w * CTX.sc.film.h;
     ctx->io.film.reserve(npx * 5);
     rt_memset(ctx->io.film.p, 0, npx * 5 * sizeof(float), CTX.stream);
@@ -159,7 +182,7 @@ int yb200_depth_resolve(yb200_ctx *ctx, const float *dev_depth_film, float *z)
     GUARD_END(0)
 }
 int yb200_get_depth(yb200_ctx *ctx, float *z) { return yb200_depth_resolve(ctx, depth_film_device(CTX), z); }
-void yb200_abort(yb200_ctx *ctx) { CTX.abortFlag = 1; }
+void yb200_abort(yb200_ctx *ctx) { CTX.abortFlag = 1; for (size_t i = 0; i < CTX.helpers.size(); ++i) CTX.helpers[i]->abortFlag = 1; }
 
 int yb200_trace_batch(yb200_ctx *ctx, const float *rays, size_t n, int mode, int shadow_depth, void *out, int on_device)
 {

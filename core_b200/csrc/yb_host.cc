@@ -54,7 +54,7 @@ bool ParaMap::getColor(const std::string &n, col3 &c) const
 Context::Context()
     : verbosity(2), device(-1), stream(0), streamOwned(false), cparams(&params), sceneStarted(false), sceneMode(0),
       curObj(0), curId(0), lastVertId(0), curOrco(false), nextFreeID(INT_MAX), geomChanged(true), abortFlag(0),
-      nTris(0), nNodes(0), bvhDepth(0), haveNormals(false), sceneReady(false), rb(0)
+      nTris(0), nNodes(0), bvhDepth(0), haveNormals(false), sceneReady(false), rb(0), meshSrc(0)
 {
     memset(&sc, 0, sizeof(sc));
     memset(&stats, 0, sizeof(stats));
@@ -62,6 +62,10 @@ Context::Context()
 }
 Context::~Context()
 {
+    for (size_t i = 0; i < helpers.size(); ++i) delete helpers[i];
+#ifndef YB_HOSTEMU
+    if (device >= 0) cudaSetDevice(device);        // the buffers below are freed on the device that owns them
+#endif
     render_release(rb);
 #ifndef YB_HOSTEMU
     if (streamOwned && stream) cudaStreamDestroy(stream);
@@ -1147,8 +1151,9 @@ bool Context::uploadTables()
     for (size_t i = 0; i < lights.size(); ++i) {
         Light &l = lights[i];
         if (l.type != LIGHT_MESH) continue;
-        std::map<unsigned, MeshObj>::const_iterator it = meshes.find(lightObj[i]);
-        if (it == meshes.end() || it->second.base) return fail("meshlight: object " + std::to_string(lightObj[i]) + " is not a triangle mesh of this scene");
+        const std::map<unsigned, MeshObj> &allMeshes = meshSrc ? *meshSrc : meshes;
+        std::map<unsigned, MeshObj>::const_iterator it = allMeshes.find(lightObj[i]);
+        if (it == allMeshes.end() || it->second.base) return fail("meshlight: object " + std::to_string(lightObj[i]) + " is not a triangle mesh of this scene");
         const MeshObj &o = it->second;
         const size_t nt = o.tri_mat.size();
         if (nt == 0) return fail("meshlight: object " + std::to_string(lightObj[i]) + " has no triangles");
@@ -1360,6 +1365,43 @@ bool Context::flattenAndBuild()
     stats.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (nTris == 0) warn("Scene: Scene is empty...");
     return true;
+}
+
+// Helper of a multi-GPU context: take over the leader's scene.  Host tables are copied (they carry device pointers that are
+// patched per device in uploadTables); the big buffers - BVH nodes, triangles in leaf order, vertex normals, per-primitive
+// texture coordinates - come over NVLink with cudaMemcpyPeerAsync instead of a second flatten + upload + build.
+bool Context::adoptScene(Context &L)
+{
+#ifdef YB_HOSTEMU
+    (void)L;
+    return fail("several devices are not part of the host emulator");
+#else
+    if (!ensureDevice()) return false;
+    try {
+        verbosity = L.verbosity;
+        materials = L.materials; textures = L.textures; texPixels = L.texPixels; texPixOffset = L.texPixOffset;
+        shaderNodes = L.shaderNodes; lights = L.lights; lightObj = L.lightObj; meshSrc = &L.meshes;
+        nTris = L.nTris; nNodes = L.nNodes; bvhDepth = L.bvhDepth; haveNormals = L.haveNormals; boundLo = L.boundLo; boundHi = L.boundHi;
+        sc = L.sc;                                  // camera, film, integrator, counts; every pointer is replaced below
+        struct Copy { void *dst; const void *src; size_t bytes; };
+        std::vector<Copy> copies;
+        d_nodes.reserve((size_t)nNodes + 1); copies.push_back({d_nodes.p, L.d_nodes.p, (size_t)nNodes * sizeof(BvhNode)});
+        d_tri_v.reserve(3 * (size_t)nTris + 1); copies.push_back({d_tri_v.p, L.d_tri_v.p, 3 * (size_t)nTris * sizeof(f4)});
+        sc.nodes = d_nodes.p; sc.tri_v = d_tri_v.p; sc.tri_n = 0; sc.prim_uv = 0; sc.prim_orco = 0; sc.prim_ng = 0;
+        if (L.sc.tri_n) { d_tri_n.reserve(3 * (size_t)nTris + 1); copies.push_back({d_tri_n.p, L.d_tri_n.p, 3 * (size_t)nTris * sizeof(v3)}); sc.tri_n = d_tri_n.p; }
+        if (L.sc.prim_uv) { d_prim_uv.reserve(6 * (size_t)nTris + 1); copies.push_back({d_prim_uv.p, L.d_prim_uv.p, 6 * (size_t)nTris * sizeof(float)}); sc.prim_uv = d_prim_uv.p; }
+        if (L.sc.prim_orco) { d_prim_orco.reserve(3 * (size_t)nTris + 1); copies.push_back({d_prim_orco.p, L.d_prim_orco.p, 3 * (size_t)nTris * sizeof(v3)}); sc.prim_orco = d_prim_orco.p; }
+        if (L.sc.prim_ng) { d_prim_ng.reserve((size_t)nTris + 1); copies.push_back({d_prim_ng.p, L.d_prim_ng.p, (size_t)nTris * sizeof(v3)}); sc.prim_ng = d_prim_ng.p; }
+        for (size_t i = 0; i < copies.size(); ++i)
+            if (copies[i].bytes) YB_CUDA_CHECK(cudaMemcpyPeerAsync(copies[i].dst, device, copies[i].src, L.device, copies[i].bytes, stream));
+        if (!uploadTables()) return false;          // materials, lights (+ mesh-light geometry), textures, shader nodes; syncs the stream
+        sc.materials = d_materials.p; sc.lights = d_lights.p;
+        sc.nLights = (int32_t)lights.size(); sc.nMaterials = (int32_t)materials.size();
+        stats.n_triangles = nTris; stats.n_bvh_nodes = nNodes;
+        sceneReady = true; geomChanged = false; sceneStarted = true;
+    } catch (const RtError &e) { return fail(std::string("scene copy to device ") + std::to_string(device) + " failed: " + e.what()); }
+    return true;
+#endif
 }
 
 bool Context::updateScene()

@@ -144,6 +144,9 @@ YB_D void film_splat_sample(const RenderArgs &a, uint32_t tid)
     float dx, dy;
     sample_dxdy(f, id, dx, dy);
     f4 c = a.acc[tid];                                           // wt == 1 for the perspective camera
+#ifdef YB_HOSTEMU      // emulator only: per-sample radiance dump for chasing a differing pixel against the reference
+    if (getenv("YB200_DEBUG_ACC")) fprintf(stderr, "ACC %u %d %d %d %.9g %.9g %.9g %.9g\n", tid, id.x, id.y, id.s, c.x, c.y, c.z, c.w);
+#endif
     if (f.clamp) {
         c.x = c.x < 0.f ? 0.f : (c.x > 1.f ? 1.f : c.x); c.y = c.y < 0.f ? 0.f : (c.y > 1.f ? 1.f : c.y); c.z = c.z < 0.f ? 0.f : (c.z > 1.f ? 1.f : c.z);
     }
@@ -362,6 +365,11 @@ struct RenderBuffers {
     DevBuf<float> film, rgba;
     DevBuf<float> depthT, depthFilm, depthZ;   // z_channel
     DevBuf<char> io_in, io_out;     // staging for host-pointer ray batches
+    // the pixels a rank owns depend only on the film window, the tile size and (rank, world): kept across frames, on the host
+    // and - while `pix` still holds them - on the device (2 M push_backs + 8 MB of H2D per 1080p frame otherwise)
+    std::vector<uint32_t> owned;
+    int ownedKey[7] = {-1, -1, -1, -1, -1, -1, -1};
+    bool ownedOnDevice = false;
 };
 void render_release(RenderBuffers *rb) { delete rb; }
 
@@ -457,9 +465,12 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         const Integrator &I = c.sc.integ;
         auto tstart = std::chrono::steady_clock::now();
         // ---- owned pixels: tiles of imageSpliter_t (imagesplitter.cc:29-52) dealt round-robin to ranks
-        std::vector<uint32_t> owned;
-        {
+        std::vector<uint32_t> &owned = rb.owned;
+        const int ownedKey[7] = {f.w, f.h, f.cx0, f.cy0, f.tileSize, rank, world};
+        if (memcmp(ownedKey, rb.ownedKey, sizeof(ownedKey)) != 0) {
             if (f.cx1 > 65535 || f.cy1 > 65535) return c.fail("render: image coordinates above 65535 are not supported");
+            owned.clear(); rb.ownedOnDevice = false;
+            memcpy(rb.ownedKey, ownedKey, sizeof(ownedKey));
             const int bs = f.tileSize, nx = (f.w + bs - 1) / bs, ny = (f.h + bs - 1) / bs;
             int tile = 0;
             for (int j = 0; j < ny; ++j)
@@ -535,9 +546,12 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         const uint64_t totalSamples = (uint64_t)pix.size() * (uint64_t)passSamples;
         if (totalSamples >= 0xffffffffull) return c.fail("render: more than 2^32 camera samples per rank are not supported");
         if (totalSamples == 0) continue;
-        rb.pix.reserve(pix.size() + 1);
-        rt_h2d(rb.pix.p, pix.data(), pix.size() * sizeof(uint32_t), s);
-        rt_sync(s);
+        if (!(pixv == &owned && rb.ownedOnDevice)) {
+            rb.pix.reserve(pix.size() + 1);
+            rt_h2d(rb.pix.p, pix.data(), pix.size() * sizeof(uint32_t), s);
+            rt_sync(s);
+            rb.ownedOnDevice = (pixv == &owned);
+        }
 #ifdef YB_HOSTEMU
         const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)512 << 20), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 16);
 #else
@@ -719,6 +733,135 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         st.render_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tstart).count();
     } catch (const RtError &e) { return c.fail(std::string("render failed: ") + e.what()); }
     return true;
+}
+
+// ------------------------------------------------------------------------------------------------ several devices, one context
+struct AddArgs { float *dst; const float *src; };
+YB_KERNEL(k_film_add, AddArgs) { a.dst[tid] += a.src[tid]; }
+void film_add_device(float *d_dst, const float *d_src, size_t n, rt_stream s)
+{
+    AddArgs a; a.dst = d_dst; a.src = d_src;
+    for (size_t o = 0; o < n; o += (size_t)1 << 30) { AddArgs b = a; b.dst += o; b.src += o; k_film_add((uint32_t)std::min<size_t>(n - o, (size_t)1 << 30), b, s); }
+}
+
+}  // namespace yb
+#ifndef YB_HOSTEMU
+#include <thread>
+#include <atomic>
+#endif
+namespace yb {
+
+#ifndef YB_HOSTEMU
+static int group_should_abort(void *flag) { return ((std::atomic<int> *)flag)->load() != 0; }
+// dst (on the leader's device, leader's stream) += src (on device srcDev) through the staging buffer tmp
+static void film_add_peer(Context &L, float *dst, const float *src, int srcDev, float *tmp, size_t n)
+{
+    YB_CUDA_CHECK(cudaMemcpyPeerAsync(tmp, L.device, src, srcDev, n * sizeof(float), L.stream));
+    film_add_device(dst, tmp, n, L.stream);
+}
+#endif
+
+// The tiles of the frame are dealt round-robin over the devices (rank = position in yb200_set_devices' list), every device runs
+// the same wavefront driver on its own stream from its own host thread, and the films - raw sums, so the reduction is a plain
+// addition - meet on the leader's device by peer copies.  Adaptive passes need the sum of all films between
+// passes (imageFilm_t::nextPass looks at neighbouring pixels): it is reduced and handed back to every device after each pass.
+bool render_group(Context &c, float *rgba_host, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user)
+{
+#ifdef YB_HOSTEMU
+    (void)rgba_host; (void)should_abort; (void)progress; (void)user;
+    return c.fail("several devices are not part of the host emulator");
+#else
+    const int world = 1 + (int)c.helpers.size();
+    if (!c.ensureDevice()) return false;
+    const Film &f = c.sc.film;
+    const size_t npx = (size_t)f.w * f.h, nf = npx * 5;
+    const int nPasses = std::max(1, f.AA_passes);
+    try {
+        auto t0 = std::chrono::steady_clock::now();
+        // ---- 1. the scene reaches the other devices (peer copies of the leader's buffers), all helpers at once
+        {
+            std::vector<std::thread> th;
+            std::vector<int> ok(c.helpers.size(), 0);
+            for (size_t i = 0; i < c.helpers.size(); ++i)
+                th.emplace_back([&, i]() { ok[i] = c.helpers[i]->adoptScene(c) ? 1 : 0; });
+            for (size_t i = 0; i < th.size(); ++i) th[i].join();
+            for (size_t i = 0; i < ok.size(); ++i) if (!ok[i]) return c.fail("device " + std::to_string(c.helpers[i]->device) + ": " + c.helpers[i]->err);
+        }
+        const double adoptMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        YB_CUDA_CHECK(cudaSetDevice(c.device));
+        c.groupFilm.reserve(nf); c.groupFilmAll.reserve(nf); c.groupTmp.reserve(std::max(nf, 2 * npx));
+        rt_memset(c.groupFilm.p, 0, nf * sizeof(float), c.stream);
+        std::atomic<int> abortAll(0);
+        Stats total; memset(&total, 0, sizeof(total));
+        for (int pass = 0; pass < nPasses; ++pass) {
+            if (c.abortFlag || (should_abort && should_abort(user))) abortAll = 1;
+            if (abortAll.load()) break;
+            // ---- 2. every device renders its tiles of this pass
+            std::vector<std::thread> th;
+            std::vector<int> ok(c.helpers.size(), 0);
+            for (size_t i = 0; i < c.helpers.size(); ++i)
+                th.emplace_back([&, i, pass]() {
+                    Context &h = *c.helpers[i];
+                    if (cudaSetDevice(h.device) != cudaSuccess) { h.fail("cudaSetDevice failed"); return; }
+                    try {
+                        h.groupFilm.reserve(nf);
+                        if (nPasses > 1) h.groupFilmAll.reserve(nf);      // allocated here: this thread has the helper's device current
+                        if (pass == 0) { rt_memset(h.groupFilm.p, 0, nf * sizeof(float), h.stream); h.abortFlag = 0; }
+                        ok[i] = render_film_device(h, h.groupFilm.p, pass > 0 ? h.groupFilmAll.p : 0, (int)i + 1, world, nPasses > 1 ? pass : -1,
+                                                   group_should_abort, 0, &abortAll) ? 1 : 0;
+                    } catch (const std::exception &e) { h.fail(e.what()); }
+                });
+            struct LeaderCb { int (*fn)(void *); void *user; std::atomic<int> *all; };
+            LeaderCb lcb = {should_abort, user, &abortAll};
+            const bool okL = render_film_device(c, c.groupFilm.p, pass > 0 ? c.groupFilmAll.p : 0, 0, world, nPasses > 1 ? pass : -1,
+                                                [](void *u) -> int {
+                                                    LeaderCb *l = (LeaderCb *)u;
+                                                    if (l->fn && l->fn(l->user)) l->all->store(1);
+                                                    return l->all->load();
+                                                }, progress ? progress : 0, &lcb);
+            for (size_t i = 0; i < th.size(); ++i) th[i].join();
+            if (!okL) return false;
+            for (size_t i = 0; i < ok.size(); ++i) if (!ok[i]) return c.fail("device " + std::to_string(c.helpers[i]->device) + ": " + c.helpers[i]->err);
+            YB_CUDA_CHECK(cudaSetDevice(c.device));
+            // counters of this pass
+            total.rays_closest += c.stats.rays_closest; total.rays_shadow += c.stats.rays_shadow; total.camera_samples += c.stats.camera_samples;
+            total.kernel_launches += c.stats.kernel_launches;
+            double ms[5] = {c.stats.trace_closest_ms, c.stats.trace_shadow_ms, c.stats.shade_ms, c.stats.film_ms, c.stats.render_ms};
+            for (size_t i = 0; i < c.helpers.size(); ++i) {
+                const Stats &hs = c.helpers[i]->stats;
+                total.rays_closest += hs.rays_closest; total.rays_shadow += hs.rays_shadow; total.camera_samples += hs.camera_samples;
+                total.kernel_launches += hs.kernel_launches;
+                ms[0] = std::max(ms[0], hs.trace_closest_ms); ms[1] = std::max(ms[1], hs.trace_shadow_ms); ms[2] = std::max(ms[2], hs.shade_ms);
+                ms[3] = std::max(ms[3], hs.film_ms); ms[4] = std::max(ms[4], hs.render_ms);
+            }
+            total.trace_closest_ms += ms[0]; total.trace_shadow_ms += ms[1]; total.shade_ms += ms[2]; total.film_ms += ms[3];
+            // ---- 3. sum of the films on the leader's device
+            rt_d2d(c.groupFilmAll.p, c.groupFilm.p, nf * sizeof(float), c.stream);
+            for (size_t i = 0; i < c.helpers.size(); ++i) film_add_peer(c, c.groupFilmAll.p, c.helpers[i]->groupFilm.p, c.helpers[i]->device, c.groupTmp.p, nf);
+            rt_sync(c.stream);
+            if (pass + 1 < nPasses)       // every device needs the whole picture to flag its pixels for the next pass
+                for (size_t i = 0; i < c.helpers.size(); ++i) {
+                    Context &h = *c.helpers[i];
+                    YB_CUDA_CHECK(cudaMemcpyPeerAsync(h.groupFilmAll.p, h.device, c.groupFilmAll.p, c.device, nf * sizeof(float), c.stream));
+                }
+            rt_sync(c.stream);
+        }
+        // depth channel: the raw depth films add up like the colour film
+        if (f.zChan && depth_film_device(c))
+            for (size_t i = 0; i < c.helpers.size(); ++i)
+                if (depth_film_device(*c.helpers[i])) film_add_peer(c, depth_film_device(c), depth_film_device(*c.helpers[i]), c.helpers[i]->device, c.groupTmp.p, 2 * npx);
+        // ---- 4. imageFilm_t::flush on the leader
+        c.groupTmp.reserve(std::max(nf, 4 * npx));
+        film_resolve_device(c, c.groupFilmAll.p, c.groupTmp.p);
+        rt_d2h(rgba_host, c.groupTmp.p, npx * 4 * sizeof(float), c.stream);
+        const double build_ms = c.stats.build_ms;
+        const uint64_t nt = c.stats.n_triangles, nn = c.stats.n_bvh_nodes, bb = c.stats.bvh_bytes, tb = c.stats.tri_bytes;
+        c.stats = total;
+        c.stats.build_ms = build_ms + adoptMs; c.stats.n_triangles = nt; c.stats.n_bvh_nodes = nn; c.stats.bvh_bytes = bb; c.stats.tri_bytes = tb;
+        c.stats.render_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    } catch (const RtError &e) { return c.fail(std::string("multi-device render failed: ") + e.what()); }
+    return true;
+#endif
 }
 
 void film_resolve_device(Context &c, const float *d_film, float *d_rgba)

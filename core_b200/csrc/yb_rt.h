@@ -126,6 +126,6 @@ inline uint32_t emu_exch(uint32_t *p, uint32_t v) { uint32_t o = *p; *p = v; ret
 #define YB_THREADFENCE()
 #endif
 
-extern uint64_t g_kernel_launches;
+extern thread_local uint64_t g_kernel_launches;
 
 }  // namespace yb

@@ -123,6 +123,13 @@ struct Context {
     bool sceneReady;
     RenderBuffers *rb;
     Stats stats;
+    // ---- several GPUs behind ONE context (yb200_set_devices): this context is the leader on `device`; every further device
+    //      has a helper context that owns the device-side copy of the scene there.  The leader flattens, uploads and builds
+    //      once; helpers receive nodes / triangles / normals by peer copy over NVLink and only upload the small tables.
+    std::vector<Context *> helpers;
+    const std::map<unsigned, MeshObj> *meshSrc;   // helper: the leader's meshes (mesh-light emitters are read from there)
+    DevBuf<float> groupFilm, groupFilmAll, groupTmp;   // helper: its film; leader: sum of all films / staging for the peer copies
+    bool adoptScene(Context &leader);              // helper: host tables + device geometry of the leader -> this device
 
     Context();
     ~Context();
@@ -182,5 +189,9 @@ void film_resolve_device(Context &c, const float *d_film, float *d_rgba);
 float *depth_film_device(Context &c);
 bool depth_resolve_device(Context &c, const float *d_depthFilm, float *z_host);
 void render_release(RenderBuffers *rb);
+// yafrayInterface_t::render over all devices of the context (leader + helpers): tiles dealt round-robin over the devices, films
+// summed on the leader's device by peer copies, resolved into the HOST buffer rgba (w*h*4 floats)
+bool render_group(Context &c, float *rgba_host, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user);
+void film_add_device(float *d_dst, const float *d_src, size_t n, rt_stream s);
 
 }  // namespace yb

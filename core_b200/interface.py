@@ -205,6 +205,12 @@ class YafrayInterface:
         self._call("get_stats", C.byref(s))
         return {k: getattr(s, k) for k, _ in capi.Stats._fields_}
 
+    def setDevices(self, devices):
+        """Several GPUs behind this one context (yb200_set_devices): render() then spreads the tiles over them."""
+        arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+        if not self._call("set_devices", arr, len(devices)):
+            raise RuntimeError("set_devices failed: " + self.lastError())
+
     def probeLatency(self, nbytes, steps=20000):
         """ns per dependent load through a random cycle over nbytes (yb200_probe_latency)."""
         ns = C.c_double(0.0)

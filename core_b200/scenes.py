@@ -343,7 +343,8 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
 # ----------------------------------------------------------------------------- C4: glossy / coated / glass materials
 def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
                     integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None,
-                    extra_materials=None, order=None, emitters=None, textures=None, uv_orco=False, image_files=None, **render_extra):
+                    extra_materials=None, order=None, emitters=None, textures=None, uv_orco=False, image_files=None, cam_res=None,
+                    **render_extra):
     """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
     coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
     shinydiffuse; sun (1 degree, 4 samples) + point + area (8 samples) lights; pathtracing with 8 bounces
@@ -410,7 +411,7 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     cp = dict(type="perspective", focal=1.3)
     cp.update(cam_params or {})
     create(yi, "camera", "cam", **{"from": (0.0, -9.5, 4.2)}, to=(0.0, 1.0, 0.8),
-           up=(0.0, -9.5, 5.2), resx=width, resy=height, **cp)
+           up=(0.0, -9.5, 5.2), resx=cam_res[0] if cam_res else width, resy=cam_res[1] if cam_res else height, **cp)
     create(yi, "background", "bg", type="constant", color=(0.35, 0.45, 0.7, 1.0))
     ip = dict(type=integrator, raydepth=raydepth)
     if integrator == "pathtracing":

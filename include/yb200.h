@@ -28,6 +28,13 @@ void        yb200_destroy(yb200_ctx *c);
 const char *yb200_last_error(yb200_ctx *c);
 const char *yb200_version(void);                               /* yafrayinterface.cc:313-320 getVersion */
 int         yb200_set_device(yb200_ctx *c, int cuda_device);   /* new: which GPU this context renders on */
+/* new: several GPUs of this node behind ONE context, so that the reference-facing call - yb200_render, i.e.
+ * yafrayInterface_t::render - scales without the caller doing anything else.  devices[0] is the leader (scene
+ * update, BVH build, final film); the other devices get the BVH and triangles by peer copy over NVLink, render the tiles
+ * i, i + n, ... (imageSpliter_t order) on their own streams from their own host threads, and their raw films are summed on
+ * the leader before imageFilm_t::flush.  n == 1 goes back to one device.  Applies to yb200_render / yb200_get_depth; the
+ * explicit rank/world forms below stay per device. */
+int         yb200_set_devices(yb200_ctx *c, const int *devices, int n);
 void        yb200_set_verbosity(yb200_ctx *c, int level);      /* yafrayinterface.cc:360-384 (0 mute .. 3 info) */
 void        yb200_clear_all(yb200_ctx *c);                     /* yafrayinterface.cc:47-64 */
 
