@@ -64,11 +64,18 @@ Context::~Context()
 {
     for (size_t i = 0; i < helpers.size(); ++i) delete helpers[i];
 #ifndef YB_HOSTEMU
-    if (device >= 0) cudaSetDevice(device);        // the buffers below are freed on the device that owns them
+    int callerDevice = -1;
+    cudaGetDevice(&callerDevice);
+    if (device >= 0) cudaSetDevice(device);        // the buffers of this context are freed with the device that owns them current
 #endif
-    render_release(rb);
+    render_release(rb); rb = 0;
 #ifndef YB_HOSTEMU
     if (streamOwned && stream) cudaStreamDestroy(stream);
+    d_nodes.release(); d_tri_v.release(); d_tri_n.release(); d_materials.release(); d_lights.release(); d_tex_pixels.release();
+    d_textures.release(); d_shaderNodes.release(); d_prim_uv.release(); d_prim_orco.release(); d_prim_ng.release();
+    d_light_tris.release(); d_light_cdf.release(); d_traceCounter.release(); d_in_v.release(); d_in_n.release();
+    groupFilm.release(); groupFilmAll.release(); groupTmp.release();
+    if (callerDevice >= 0) cudaSetDevice(callerDevice);      // leave the caller's current device as it was
 #endif
 }
 bool Context::fail(const std::string &msg)
@@ -1408,6 +1415,7 @@ bool Context::updateScene()
 {
     if (!sceneStarted) return fail("no scene: call startScene first");
     if (stateStack.back() != ST_READY) return fail("scene update inside startGeometry/startTriMesh");
+    if (stream && !ensureDevice()) return false;     // the caller's thread may have another device current
     if (!setupRender(0, 0)) return false;
     if (geomChanged || !sceneReady) { if (!flattenAndBuild()) return false; }
     else {
