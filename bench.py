@@ -25,6 +25,16 @@ import numpy as np
 if os.environ.get("NCCL_DEBUG"):
     os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
+# ... and the reference library and NCCL print banners on fd 1 from native code: everything but the final line goes to stderr
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -184,7 +194,7 @@ def main():
             return 0
         r = cpu_reference_run(wl, args.steps, args.warmup)
         if r is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libyref.so missing (build it with make -C oracle ref)"}))
+            emit({"impl": "reference", "unavailable": "oracle/_ref/libyref.so missing (build it with make -C oracle ref)"})
             return 0
         config["n_triangles"] = r["n_tris"]
         # what this arm really renders: a bounded sample of the workload, compared per ray
@@ -202,7 +212,7 @@ def main():
                 "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": r["cores"], "kind": "reference", "sample": sample,
                                  "rays_per_step": rays, "sec_per_step": r["sec"]},
                 "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     # ------------------------------------------------------------------ B200 arm
@@ -331,16 +341,21 @@ def main():
         if rank == 0:
             c._call("film_resolve", film.data_ptr(), host.ctypes.data, 0)
 
+    step_log = []
+
     def pipelined(steps):
         update(ctxs[0])
         for i in range(steps):
             cur, nxt = i % 2, (i + 1) % 2
             th = threading.Thread(target=update, args=(ctxs[nxt],)) if i + 1 < steps else None
+            ta = time.time()
             if th:
                 th.start()
             render_step(ctxs[cur], exts[cur], host_out)
+            tb = time.time()
             if th:
                 th.join()
+            step_log.append(((tb - ta) * 1e3, (time.time() - tb) * 1e3))
 
     pipelined(2)
     barrier()
@@ -435,6 +450,7 @@ def main():
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "sec_per_frame": e2e_s, "steps": e2e_steps,
                     "pipeline": "two contexts: the scene update (flatten + H2D + BVH build) of step i+1 runs while step i renders; every step does all of it inside the timed region",
+                    "rank0_ms_render_step_then_wait_for_update": [[round(a, 2), round(b, 2)] for a, b in step_log[-e2e_steps:]],
                     "unpipelined": {"value": rays_per_frame / e2e_latency_s / 1e6, "sec_per_frame": e2e_latency_s,
                                     "note": "one step after the other, nothing overlapped (latency of a single frame)"},
                     "call": "yb200_render (yafrayInterface_t::render) with a host RGBA buffer" if world == 1 else "yb200_render_film + NCCL reduce + yb200_film_resolve to a host buffer",
@@ -476,7 +492,7 @@ def main():
                                     "rays_per_step": r["rays"], "sec_per_step": r["sec"]}
         else:
             line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference", "sample": "oracle/_ref missing"}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -54,7 +54,7 @@ bool ParaMap::getColor(const std::string &n, col3 &c) const
 Context::Context()
     : verbosity(2), device(-1), stream(0), streamOwned(false), cparams(&params), sceneStarted(false), sceneMode(0),
       curObj(0), curId(0), lastVertId(0), curOrco(false), nextFreeID(INT_MAX), geomChanged(true), abortFlag(0),
-      nTris(0), nNodes(0), bvhDepth(0), haveNormals(false), sceneReady(false), rb(0), meshSrc(0)
+      nTris(0), nNodes(0), bvhDepth(0), haveNormals(false), sceneReady(false), rb(0), photonBufs(0), meshSrc(0)
 {
     memset(&sc, 0, sizeof(sc));
     memset(&stats, 0, sizeof(stats));
@@ -69,6 +69,7 @@ Context::~Context()
     if (device >= 0) cudaSetDevice(device);        // the buffers of this context are freed with the device that owns them current
 #endif
     render_release(rb); rb = 0;
+    photon_release(photonBufs); photonBufs = 0;
 #ifndef YB_HOSTEMU
     if (streamOwned && stream) cudaStreamDestroy(stream);
     d_nodes.release(); d_tri_v.release(); d_tri_n.release(); d_materials.release(); d_lights.release(); d_tex_pixels.release();
@@ -1028,14 +1029,23 @@ uintptr_t Context::createIntegrator(const char *name)   // environment.cc:367-40
         if (type == "directlighting") {
             bool caustics = false, do_AO = false; int AO_samples = 32; double AO_dist = 1.0; col3 AO_col(1.f);
             p.get("caustics", caustics); p.get("do_AO", do_AO); p.get("AO_samples", AO_samples); p.get("AO_distance", AO_dist); p.getColor("AO_color", AO_col);
-            if (caustics) { fail("integrator '" + std::string(name) + "': caustic photon maps are not supported"); return 0; }
+            // caustic photon map (directlight.cc:204-231 defaults and keys)
+            int search = 100, photons = 500000, cDepth = 10; double cRad = 0.25;
+            p.get("photons", photons); p.get("caustic_mix", search); p.get("caustic_depth", cDepth); p.get("caustic_radius", cRad);
+            I.usePhotonCaustics = caustics ? 1 : 0; I.nCausPhotons = photons; I.nCausSearch = search; I.causDepth = cDepth; I.causRadius = (float)cRad;
             I.type = INTEG_DIRECT; I.useAO = do_AO; I.aoSamples = AO_samples; I.aoDist = (float)AO_dist; I.aoCol = AO_col;
         } else {
             bool noRec = false; int path_samples = 32, bounces = 3; std::string cMethod;
             p.get("path_samples", path_samples); p.get("bounces", bounces); p.get("no_recursive", noRec);
             if (p.get("caustic_type", cMethod)) {
-                if (cMethod == "photon" || cMethod == "both") { fail("integrator '" + std::string(name) + "': caustic_type '" + cMethod + "' (photon maps) is not supported"); return 0; }
-                I.traceCaustics = (cMethod == "none") ? 0 : 1;     // pathtracer.cc:370-372,113 (default PATH)
+                // pathtracer.cc:366-385,100-113: "photon" = map only, "both" = map + caustic paths, "none", anything else = paths (default)
+                const bool usePhotons = cMethod == "photon" || cMethod == "both";
+                I.traceCaustics = (cMethod == "none" || cMethod == "photon") ? 0 : 1;
+                if (usePhotons) {
+                    int search = 100, photons = 500000, cDepth = 10; double cRad = 0.25;
+                    p.get("photons", photons); p.get("caustic_mix", search); p.get("caustic_depth", cDepth); p.get("caustic_radius", cRad);
+                    I.usePhotonCaustics = 1; I.nCausPhotons = photons; I.nCausSearch = search; I.causDepth = cDepth; I.causRadius = (float)cRad;
+                }
             } else I.traceCaustics = 1;
             I.type = INTEG_PATH; I.nPaths = path_samples; I.maxBounces = bounces; I.noRecursive = noRec;
             // opt-in extension, not in the reference (SURVEY.md discrepancy 1): unbiased Russian roulette on path throughput
@@ -1385,6 +1395,13 @@ bool Context::adoptScene(Context &L)
 #else
     if (!ensureDevice()) return false;
     try {
+        // direct NVLink DMA between the two devices (without it cudaMemcpyPeer stages through host memory)
+        int can = 0;
+        if (cudaDeviceCanAccessPeer(&can, device, L.device) == cudaSuccess && can) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(L.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) warn(std::string("peer access to the leader device: ") + cudaGetErrorString(e));
+            cudaGetLastError();
+        }
         verbosity = L.verbosity;
         materials = L.materials; textures = L.textures; texPixels = L.texPixels; texPixOffset = L.texPixOffset;
         shaderNodes = L.shaderNodes; lights = L.lights; lightObj = L.lightObj; meshSrc = &L.meshes;

@@ -338,7 +338,9 @@ YB_HD Ray cam_shootRay(const Camera &c, float px, float py, float lu, float lv, 
 
 // triangle_t::getSurface (triangle.cc:12-108) without orco/uv (rejected at flatten time):
 // sp.N from the vertex normals, createCS(N, NU, NV); Ng = normalize((b-a)^(c-a)) as recNormal (triangle_inline.h:100-107)
-YB_HD void tri_getSurface(const SceneDev &sc, int tri, v3 hitP, float b1, float b2, Surf &sp)
+// the geometry tables it reads, so that the traversal kernel (which carries no SceneDev) can call it too
+struct SurfTables { const f4 *tri_v; const v3 *tri_n; const Material *materials; const v3 *prim_ng; };
+YB_HD void tri_getSurface(const SurfTables &sc, int tri, v3 hitP, float b1, float b2, Surf &sp)
 {
     const f4 A = sc.tri_v[3 * tri], B = sc.tri_v[3 * tri + 1], C = sc.tri_v[3 * tri + 2];
     v3 a(A.x, A.y, A.z), b(B.x, B.y, B.z), c(C.x, C.y, C.z);
@@ -355,6 +357,12 @@ YB_HD void tri_getSurface(const SceneDev &sc, int tri, v3 hitP, float b1, float 
     sp.P = hitP;
     sp.mat = &sc.materials[info & TRI_MAT_MASK];
     createCS(sp.N, sp.NU, sp.NV);
+}
+
+YB_HD void tri_getSurface(const SceneDev &sc, int tri, v3 hitP, float b1, float b2, Surf &sp)
+{
+    SurfTables t; t.tri_v = sc.tri_v; t.tri_n = sc.tri_n; t.materials = sc.materials; t.prim_ng = sc.prim_ng;
+    tri_getSurface(t, tri, hitP, b1, b2, sp);
 }
 
 // the texture-coordinate part of triangle_t::getSurface (triangle.cc:28-105): orco point / normal, interpolated UV and - when

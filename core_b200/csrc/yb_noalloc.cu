@@ -100,6 +100,7 @@ extern "C" int yb200_trace_batch_static(yb200_ctx *ctx, const float *rays, size_
         FastJob j;
         j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = d_rays; j.stride = (uint32_t)kRayBytes; j.n = (uint32_t)n;
         j.order = 0; j.nPtr = 0; j.counterZeroed = false; j.counter = (uint32_t *)scratch; j.out = d_out; j.acc = 0; j.nNodes = c.sc.nNodes;
+        j.surf.tri_v = 0; j.surf.tri_n = 0; j.surf.materials = 0; j.surf.prim_ng = 0; j.shadowDepth = 0;
         j.oneBits = 0x3F800000u; j.burst = 6; j.refillIdle = YB_REFILL_IDLE; j.triThreshold = 1;
         // launch_trace_fast clears the counter on the stream (cudaMemsetAsync) before the kernel: the last call's value must not survive
         if (mode == YB200_TRACE_CLOSEST) launch_trace_fast<false, OUT_CLOSEST_PRIM>(j, c.stream);

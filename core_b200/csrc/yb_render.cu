@@ -406,6 +406,7 @@ static uint32_t tri_threshold()
 
 static void trace_tuning(FastJob &j)
 {
+    j.surf.tri_v = 0; j.surf.tri_n = 0; j.surf.materials = 0; j.surf.prim_ng = 0; j.shadowDepth = 0;
     static const uint32_t burst = (uint32_t)env_size("YB200_BURST", 6), idle = (uint32_t)env_size("YB200_REFILL_IDLE", 8);
     j.triThreshold = tri_threshold(); j.oneBits = 0x3F800000u;
     j.burst = burst < 1u ? 1u : burst; j.refillIdle = idle < 1u ? 1u : (idle > 32u ? 32u : idle);
@@ -450,6 +451,12 @@ bool depth_resolve_device(Context &c, const float *d_depthFilm, float *z_host)
     k_resolve_depth((uint32_t)npx, da, c.stream);
     rt_d2h(z_host, c.rb->depthZ.p, npx * sizeof(float), c.stream);
     return true;
+}
+
+// transparent shadows in the persistent kernel: the tables material->getTransparency needs (materials without shader nodes only)
+static void trace_tshadow(FastJob &j, const Context &c, int shadowDepth)
+{
+    j.surf.tri_v = c.sc.tri_v; j.surf.tri_n = c.sc.tri_n; j.surf.materials = c.sc.materials; j.surf.prim_ng = c.sc.prim_ng; j.shadowDepth = shadowDepth;
 }
 
 bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int rank, int world, int onlyPass,
@@ -511,6 +518,9 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
             if (onlyPass <= 0) rt_memset(rb.depthFilm.p, 0, 2 * npx * sizeof(float), s);
             if (f.zNorm) { if (!precalc_depths(c, fz)) return false; }
         }
+        // mcIntegrator_t::createCausticMap in preprocess() (directlight.cc:78-83, pathtracer.cc:90-93): once per frame
+        if (onlyPass <= 0 && !build_caustic_map(c)) return false;
+        const bool gatherCaustics = c.sc.photonGrid.nPhotons > 0;
         StageTimer tc(s), tsh(s), tsd(s), tf(s);
         uint64_t raysClosest = 0, raysShadow = 0, samplesDone = 0; double msClosest = 0, msShadow = 0, msShade = 0, msFilm = 0;
         const uint64_t launches0 = g_kernel_launches;
@@ -583,7 +593,8 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         // longest chain of tasks one camera sample can spawn when every task has at most one child: the camera task, one path
         // vertex per bounce, one specular child per recursion level (raylevel is capped at rDepth, mcintegrator.cc:428,588)
         const int maxChain = 1 + (I.type == INTEG_PATH ? std::max(0, I.maxBounces) : 0) + (specChildren ? std::max(0, I.rDepth) + 1 : 0);
-        const bool deviceWaves = F <= 1 && useFast && !I.trShad && !sortRays && !logWaves && env_size("YB200_DEVICE_WAVES", 1) != 0;
+        const bool tsFast = useFast && !nodeShade;      // IntersectTS in the persistent kernel (node materials evaluate their graph: per-ray kernel)
+        const bool deviceWaves = F <= 1 && useFast && (!I.trShad || tsFast) && !sortRays && !logWaves && env_size("YB200_DEVICE_WAVES", 1) != 0;
         const int nBatches = (int)((totalSamples + B - 1) / B);
         for (int b = 0; b < nBatches; ++b) {
             if (c.abortFlag || (should_abort && should_abort(user))) break;
@@ -627,6 +638,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                         if (nodeShade) launch_shade_nodes(pending, a, s);
                         else if (extShade) launch_shade_ext(pending, a, s);
                         else launch_shade_base(pending, a, s);
+                        if (gatherCaustics) launch_caustic_gather(pending, a, s);
 #ifndef YB_HOSTEMU
                         YB_CUDA_CHECK(cudaEventRecord(rb.event(4 * (size_t)w + 2), s));
 #endif
@@ -635,7 +647,8 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                             FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask);
                             j.n = (uint32_t)std::min<size_t>((size_t)pending * S, 0xffffffffu); j.nPtr = a.counters + 1; j.order = 0;
                             j.counter = a.counters + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j); j.counterZeroed = true;
-                            launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
+                            if (I.trShad) { trace_tshadow(j, c, I.sDepth); launch_trace_fast<true, OUT_TSHADOW_ACC>(j, s); }
+                            else launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
                         }
 #ifndef YB_HOSTEMU
                         YB_CUDA_CHECK(cudaEventRecord(rb.event(4 * (size_t)w + 3), s));
@@ -687,6 +700,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 if (nodeShade) launch_shade_nodes((uint32_t)M, a, s);
                 else if (extShade) launch_shade_ext((uint32_t)M, a, s);
                 else launch_shade_base((uint32_t)M, a, s);
+                if (gatherCaustics) launch_caustic_gather((uint32_t)M, a, s);
                 tsd.stop();
                 firstWave = false;
                 uint32_t cnt[4];
@@ -698,6 +712,10 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                     j.order = (sortRays >= 2 && (!firstShadowWave || sortRays >= 3)) ? sort_rays((const char *)a.shadow, sizeof(ShadowTask), cnt[1], c.sc.boundLo, c.sc.boundHi, c.raySort, s) : 0;
                     j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j);
                     launch_trace_fast<true, OUT_SHADOW_ACC>(j, s);
+                } else if (tsFast && I.trShad) {
+                    FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.shadow; j.stride = sizeof(ShadowTask); j.n = cnt[1]; j.nPtr = 0; j.counterZeroed = false;
+                    j.order = 0; j.counter = rb.counters.p + 3; j.out = 0; j.acc = a.acc; j.nNodes = c.sc.nNodes; trace_tuning(j); trace_tshadow(j, c, I.sDepth);
+                    launch_trace_fast<true, OUT_TSHADOW_ACC>(j, s);
                 } else
                     k_trace_shadow(cnt[1], a, s);
                 tsh.stop();
@@ -789,6 +807,11 @@ bool render_group(Context &c, float *rgba_host, int (*should_abort)(void *), voi
         }
         const double adoptMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         YB_CUDA_CHECK(cudaSetDevice(c.device));
+        for (size_t i = 0; i < c.helpers.size(); ++i) {      // the films come back over NVLink as well
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, c.device, c.helpers[i]->device) == cudaSuccess && can) cudaDeviceEnablePeerAccess(c.helpers[i]->device, 0);
+            cudaGetLastError();
+        }
         c.groupFilm.reserve(nf); c.groupFilmAll.reserve(nf); c.groupTmp.reserve(std::max(nf, 2 * npx));
         rt_memset(c.groupFilm.p, 0, nf * sizeof(float), c.stream);
         std::atomic<int> abortAll(0);
@@ -878,12 +901,15 @@ void trace_batch_device(Context &c, const float *d_rays, size_t n, int mode, int
     for (size_t o = 0; o < n; o += step) {
         const uint32_t m = (uint32_t)std::min(step, n - o);
         TraceArgs t2 = ta; t2.rays = ta.rays + o;
-        if (useFast && mode != TRACE_TSHADOW) {
+        bool anyNodes = false;
+        for (size_t i = 0; i < c.materials.size(); ++i) if (c.materials[i].nNodes > 0) anyNodes = true;
+        if (useFast && (mode != TRACE_TSHADOW || !anyNodes)) {
             c.d_traceCounter.reserve(4);
             FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)(ta.rays + o); j.stride = sizeof(Ray); j.n = m;
             j.order = 0; j.nPtr = 0; j.counterZeroed = false; j.counter = c.d_traceCounter.p; j.acc = 0; j.nNodes = c.sc.nNodes; trace_tuning(j);
             if (mode == TRACE_CLOSEST) { j.out = (ClosestOut *)d_out + o; launch_trace_fast<false, OUT_CLOSEST_PRIM>(j, c.stream); }
-            else { j.out = (int32_t *)d_out + o; launch_trace_fast<true, OUT_SHADOW_FLAG>(j, c.stream); }
+            else if (mode == TRACE_SHADOW) { j.out = (int32_t *)d_out + o; launch_trace_fast<true, OUT_SHADOW_FLAG>(j, c.stream); }
+            else { j.out = (TShadowOut *)d_out + o; trace_tshadow(j, c, shadow_depth); launch_trace_fast<true, OUT_TSHADOW_RES>(j, c.stream); }
             continue;
         }
         if (mode == TRACE_CLOSEST) { t2.out = (ClosestOut *)d_out + o; k_batch_closest(m, t2, c.stream); }

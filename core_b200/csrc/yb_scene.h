@@ -60,9 +60,11 @@ struct Stats {
     uint64_t n_triangles, n_bvh_nodes, rays_closest, rays_shadow, camera_samples, kernel_launches;
     double build_ms, render_ms, trace_closest_ms, trace_shadow_ms, shade_ms, film_ms;
     uint64_t bvh_bytes, tri_bytes;
+    uint64_t caustic_photons;         // photons stored in the caustic map of the last render
 };
 
 struct RenderBuffers;   // wavefront queues (yb_render.cu)
+struct PhotonBuffers;   // caustic photon map (yb_photon.cu)
 
 // Scratch of the BVH build, kept across builds so that a rebuild (animation, the bench's host-to-host step) never
 // goes through cudaMalloc / cudaFree, which serialise with the whole device.
@@ -122,6 +124,7 @@ struct Context {
     SceneDev sc;                     // filled by updateScene / setupRender
     bool sceneReady;
     RenderBuffers *rb;
+    PhotonBuffers *photonBufs;
     Stats stats;
     // ---- several GPUs behind ONE context (yb200_set_devices): this context is the leader on `device`; every further device
     //      has a helper context that owns the device-side copy of the scene there.  The leader flattens, uploads and builds
@@ -189,6 +192,12 @@ void film_resolve_device(Context &c, const float *d_film, float *d_rgba);
 float *depth_film_device(Context &c);
 bool depth_resolve_device(Context &c, const float *d_depthFilm, float *z_host);
 void render_release(RenderBuffers *rb);
+// mcIntegrator_t::createCausticMap: shoot the caustic photons of the scene's lights and sort them into the gather grid
+// (c.sc.photonGrid); a no-op unless the integrator asks for photon caustics.  Runs once per frame before the first wave.
+bool build_caustic_map(Context &c);
+void photon_release(PhotonBuffers *p);
+struct RenderArgs;
+void launch_caustic_gather(uint32_t n, const RenderArgs &a, rt_stream s);   // estimateCausticPhotons for the integrate() tasks of a wave
 // yafrayInterface_t::render over all devices of the context (leader + helpers): tiles dealt round-robin over the devices, films
 // summed on the leader's device by peer copies, resolved into the HOST buffer rgba (w*h*4 floats)
 bool render_group(Context &c, float *rgba_host, int (*should_abort)(void *), void (*progress)(void *, int, int), void *user);

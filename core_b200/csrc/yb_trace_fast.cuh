@@ -82,7 +82,10 @@ static uint64_t g_stat_nodes = 0, g_stat_tris = 0, g_stat_rays = 0;
 struct StatPrinter { ~StatPrinter() { if (g_stat_rays) fprintf(stderr, "TRACE STATS: rays %llu nodes/ray %.2f tris/ray %.2f\n", (unsigned long long)g_stat_rays, (double)g_stat_nodes / g_stat_rays, (double)g_stat_tris / g_stat_rays); } };
 static StatPrinter g_stat_printer;
 #endif
-enum { OUT_HITS = 0, OUT_SHADOW_ACC = 1, OUT_SHADOW_FLAG = 2, OUT_CLOSEST_PRIM = 3 };
+// OUT_TSHADOW_*: scene_t::isShadowed(state, ray, maxDepth, filt) -> IntersectTS (scene.cc:904-928, kdtree.cc:953-1108): an opaque
+// hit shadows the ray; a transparent one multiplies filt by material->getTransparency, more than shadowDepth of them shadow it too.
+// A BVH holds every triangle in exactly one leaf, so the std::set the kd-tree needs against double counting is not needed.
+enum { OUT_HITS = 0, OUT_SHADOW_ACC = 1, OUT_SHADOW_FLAG = 2, OUT_CLOSEST_PRIM = 3, OUT_TSHADOW_ACC = 4, OUT_TSHADOW_RES = 5 };
 
 struct FastJob {
     const BvhNode *nodes;
@@ -99,6 +102,8 @@ struct FastJob {
     uint32_t oneBits;        // 0x3F800000 (see plane_f)
     uint32_t burst, refillIdle;   // traversal steps between refill checks; idle lanes that trigger a refill
     uint32_t triThreshold;   // triangle phase runs when this many lanes (or as many as still have node work) hold a triangle group
+    // transparent shadows only (OUT_TSHADOW_*): what material->getTransparency needs at the hit
+    SurfTables surf; int32_t shadowDepth;
 };
 
 // replicate the msb of every byte over the byte (prmt sign mode; __byte_perm only honours 3 selector bits per nibble)
@@ -136,6 +141,8 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
     uint2 tg = make_uint2(0, 0);      // triangle group: x = triangle base, y = hit bits (0..23)
     int hitTri = -1; float hitT = 0, hitU = 0, hitV = 0;
     bool tgFresh = false;
+    constexpr bool TSHADOW = (OUT == OUT_TSHADOW_ACC || OUT == OUT_TSHADOW_RES);
+    float filtR = 1.f, filtG = 1.f, filtB = 1.f; int tsDepth = 0;      // transparent shadows: filter colour so far, transparent hits so far
 
     for (;;) {
         // ------------------------------------------------------------ refill idle lanes (warp-converged here)
@@ -158,7 +165,8 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                         dx = r1.x; dy = r1.y; dz = r1.z;
                         if (ANYHIT) {          // scene_t::isShadowed: advance the origin by tmin, dist = tmax - 2 tmin (scene.cc:884-889)
                             ox = r0.x + dx * r0.w; oy = r0.y + dy * r0.w; oz = r0.z + dz * r0.w;
-                            tlo = 0.f; thi = r1.w < 0 ? INFINITY : r1.w - 2 * r0.w;
+                            tlo = TSHADOW ? r0.w : 0.f; thi = r1.w < 0 ? INFINITY : r1.w - 2 * r0.w;     // IntersectTS accepts t >= tmin once more (kdtree.cc:1055)
+                            filtR = filtG = filtB = 1.f; tsDepth = 0;
                         } else {               // scene_t::intersect (scene.cc:856-857)
                             ox = r0.x; oy = r0.y; oz = r0.z;
                             tlo = r0.w; thi = r1.w < 0 ? INFINITY : r1.w;
@@ -176,6 +184,7 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                         if (!active) {          // empty scene: miss
                             if (OUT == OUT_HITS || OUT == OUT_CLOSEST_PRIM) ((int4 *)job.out)[i] = make_int4(-1, 0, 0, 0);
                             else if (OUT == OUT_SHADOW_FLAG) ((int32_t *)job.out)[i] = 0;
+                            else if (OUT == OUT_TSHADOW_RES) ((float4 *)job.out)[i] = make_float4(__int_as_float(0), 1.f, 1.f, 1.f);
                             else { const float4 c = __ldg((const float4 *)(job.rays + (size_t)i * job.stride + 32));
                                    const uint32_t sid = __float_as_uint(c.w);
                                    atomicAdd(&job.acc[sid].x, c.x); atomicAdd(&job.acc[sid].y, c.y); atomicAdd(&job.acc[sid].z, c.z); }
@@ -279,7 +288,17 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                         g_stat_tris++;
 #endif
                         if (tri_intersect(v3(A.x, A.y, A.z), v3(B.x, B.y, B.z), v3(C.x, C.y, C.z), v3(ox, oy, oz), v3(dx, dy, dz), t, u, v) && t < thi && t >= tlo) {
-                            if (ANYHIT) { hitTri = (int)ti; done = true; }
+                            if (TSHADOW) {
+                                const Material &m = job.surf.materials[(uint32_t)__float_as_int(B.w) & TRI_MAT_MASK];
+                                if (!mat_isTransparent<1>(m) || tsDepth >= job.shadowDepth) { hitTri = (int)ti; done = true; }
+                                else {
+                                    Surf sps;
+                                    tri_getSurface(job.surf, (int)ti, v3(ox, oy, oz) + t * v3(dx, dy, dz), u, v, sps);
+                                    const col3 tr = mat_getTransparency<1>(m, sps, v3(dx, dy, dz));
+                                    filtR *= tr.x; filtG *= tr.y; filtB *= tr.z;
+                                    ++tsDepth;
+                                }
+                            } else if (ANYHIT) { hitTri = (int)ti; done = true; }
                             else { thi = t; hitTri = (int)ti; hitT = t; hitU = u; hitV = v; }
                         }
                     }
@@ -297,9 +316,11 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                     const int prim = hitTri >= 0 ? __float_as_int(__ldg(&job.tri_v[3 * (size_t)hitTri].w)) : -1;
                     ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(prim), hitT, hitU, hitV);
                 } else if (OUT == OUT_SHADOW_FLAG) ((int32_t *)job.out)[rayIdx] = hitTri >= 0 ? 1 : 0;
+                else if (OUT == OUT_TSHADOW_RES) ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(hitTri >= 0 ? 1 : 0), filtR, filtG, filtB);
                 else if (hitTri < 0) {
-                    const float4 c = __ldg((const float4 *)(job.rays + (size_t)rayIdx * job.stride + 32));
+                    float4 c = __ldg((const float4 *)(job.rays + (size_t)rayIdx * job.stride + 32));
                     const uint32_t sid = __float_as_uint(c.w);
+                    if (TSHADOW) { c.x *= filtR; c.y *= filtG; c.z *= filtB; }
                     atomicAdd(&job.acc[sid].x, c.x); atomicAdd(&job.acc[sid].y, c.y); atomicAdd(&job.acc[sid].z, c.z);
                 }
             }

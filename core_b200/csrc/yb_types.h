@@ -163,6 +163,22 @@ struct Integrator {
     col3 bgColor;
     int32_t russianRoulette;          // opt-in extension (north_star); OFF by default and in every parity test
     float rrMinProb;
+    // caustic photon map (mcintegrator.h: usePhotonCaustics / nCausPhotons / nCausSearch / causDepth / causRadius)
+    int32_t usePhotonCaustics, nCausPhotons, nCausSearch, causDepth;
+    float causRadius;
+};
+
+// photon_t as the caustic map keeps it (photon.h:67-133 without _SMALL_PHOTONS): position, incoming direction, power
+struct Photon { v3 pos; v3 dir; col3 c; };
+// the caustic photon map on the device (replaces photonMap_t + pointKdTree, photon.h / pkdtree.h): photons sorted by the cell of a
+// uniform grid whose cells are at least the gather radius wide; cellStart[c] .. cellStart[c + 1] are the photons of cell c
+struct PhotonGrid {
+    const Photon *photons; const uint32_t *cellStart;
+    v3 lo; float invCell;
+    int32_t nx, ny, nz;
+    uint32_t nPhotons;                // 0: no map (causticMap.ready() == false)
+    int32_t nPaths, nSearch;          // photonMap_t::nPaths(), nCausSearch
+    float radius;                     // causRadius
 };
 
 #define YB_FILTER_TABLE_SIZE 16
@@ -228,6 +244,7 @@ struct SceneDev {
     Camera cam;
     Integrator integ;
     Film film;
+    PhotonGrid photonGrid;
 };
 
 // ---- trace records ----------------------------------------------------------------------------------

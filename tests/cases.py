@@ -250,6 +250,22 @@ IMAGE_CASES = {
                                                                 premult=True, clamp_rgb=True)),
     "c2_field_crop": (scenes.icosphere_field, dict(n_tris=6000, subdiv=1, width=40, height=24, spp=2, bounces=3,
                                                    xstart=17, ystart=9, cam_res=(96, 54))),
+    # caustic photon map: mcIntegrator_t::createCausticMap / estimateCausticPhotons for both integrators - photons from
+    # the sun, a point and an area light through glass / mirror / glossy spheres, gathered on the diffuse ground
+    "c4_caustics_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting",
+                                                        order=["glass", "mirror", "glass2", "coated", "gdiff", "glossy", "glass", "shiny"],
+                                                        integ_params=dict(caustics=True, photons=30000, caustic_mix=40, caustic_depth=6,
+                                                                          caustic_radius=0.35))),
+    "c4_caustics_path_both": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4,
+                                                           order=["glass", "mirror", "glass2", "coated", "gdiff", "glossy", "glass", "shiny"],
+                                                           integ_params=dict(caustic_type="both", photons=20000, caustic_mix=30, caustic_depth=5,
+                                                                             caustic_radius=0.4))),
+    "c4_caustics_lights_photon": (scenes.materials_scene, dict(width=64, height=36, spp=1, bounces=3, order=["glass", "mirror", "glass2", "gdiff"] * 2,
+        integ_params=dict(caustic_type="photon", photons=24000, caustic_mix=25, caustic_depth=4, caustic_radius=0.5), lights=[
+        ("d", dict(type="directional", direction=(0.3, -0.5, 0.8), color=(1.0, 0.95, 0.9, 1.0), power=0.6)),
+        ("s", dict(type="spotlight", to=(0.5, 0.5, 0.5), color=(1.0, 0.9, 0.8, 1.0), power=60.0, cone_angle=35.0, blend=0.3,
+                   **{"from": (-3.0, -4.0, 6.0)})),
+        ("sp", dict(type="spherelight", color=(0.8, 0.9, 1.0, 1.0), power=25.0, radius=0.4, samples=2, **{"from": (1.0, -3.0, 4.5)}))])),
     # configs[4] (reduced): tessellated fBm terrain, sun + sky, pathtracing 4 bounces
     "c5_terrain_path": (scenes.terrain, dict(grid=60, width=64, height=36, spp=2, bounces=4)),
 }
