@@ -20,13 +20,15 @@ from core_b200.interface import YafrayInterface  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--gpus-list", default="", help="comma-separated device counts measured one after the other on ONE scene (e.g. 1,2,4,8)")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--workload", default="c2", choices=["c2", "c5"])
     ap.add_argument("--spp", type=int, default=0)
     args = ap.parse_args()
+    counts = [int(x) for x in args.gpus_list.split(",")] if args.gpus_list else [args.gpus]
     yi = YafrayInterface()
-    yi.setDevices(list(range(args.gpus)))
+    yi.setDevices(list(range(counts[0])))
     if args.workload == "c2":
         W, H, spp = 1920, 1080, args.spp or 64
         n_tris = scenes.icosphere_field(yi, n_tris=1_000_000, width=W, height=H, spp=spp, bounces=4)
@@ -36,6 +38,14 @@ def main():
         n_tris = scenes.terrain(yi, grid=5000, width=W, height=H, spp=spp, bounces=4)
         name = "c5_terrain_50M_4k_%dspp" % spp
     out = np.zeros((H, W, 4), np.float32)
+    for k, ngpu in enumerate(counts):
+        if k:
+            yi.setDevices(list(range(ngpu)))
+        args.gpus = ngpu
+        measure(yi, args, out, W, H, name, n_tris)
+
+
+def measure(yi, args, out, W, H, name, n_tris):
     times, rays = [], 0
     for i in range(args.warmup + args.steps):
         yi.touchGeometry()
@@ -56,7 +66,7 @@ def main():
                                  "call": "yb200_set_devices + yb200_render (host RGBA buffer out, geometry rebuilt every step)"},
                       "rays_per_frame": rays, "build_ms_incl_peer_copies": st["build_ms"], "render_ms": st["render_ms"],
                       "kernel_ms_max_over_devices": {k: st[k] for k in ("trace_closest_ms", "trace_shadow_ms", "shade_ms", "film_ms")},
-                      "image_mean": float(out[..., :3].mean())}))
+                      "image_mean": float(out[..., :3].mean())}), flush=True)
 
 
 if __name__ == "__main__":
