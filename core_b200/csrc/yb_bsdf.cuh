@@ -834,28 +834,29 @@ YB_HD void rg_sample2(const Material &m, const Surf &sp, v3 wo, v3 *dir, col3 *c
 }
 
 // ================================================================== dispatch over the leaf materials: material_t virtuals
-YB_HD void leaf_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
+// FIX >= 0: the material type is known at compile time (staged direct lighting: one kernel per material type, the dispatch folds)
+template <int FIX = -1> YB_HD void leaf_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
 {
     bsdfs = m.bsdfFlags;
-    switch (m.type) {
+    switch (FIX >= 0 ? FIX : m.type) {
         case MAT_SHINYDIFFUSE: sd_initBSDF(m, d); break;
         case MAT_GLOSSY: case MAT_COATED_GLOSSY: gl_initBSDF(m, d); break;
         case MAT_NULL: bsdfs = BSDF_NONE;   // glass.cc:374
         default: d.c[0] = d.c[1] = d.c[2] = d.c[3] = 0.f; break;
     }
 }
-YB_HD col3 leaf_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
+template <int FIX = -1> YB_HD col3 leaf_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
 {
-    switch (m.type) {
+    switch (FIX >= 0 ? FIX : m.type) {
         case MAT_SHINYDIFFUSE: return sd_eval(m, d, sp, wo, wl, bsdfs);
         case MAT_GLOSSY: return gl_eval(m, d, sp, wo, wl, bsdfs);
         case MAT_COATED_GLOSSY: return cg_eval(m, d, sp, wo, wl, bsdfs);
         default: return col3(0.f);
     }
 }
-template <int EXT> YB_HD col3 leaf_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
+template <int EXT, int FIX = -1> YB_HD col3 leaf_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
 {
-    switch (m.type) {
+    switch (FIX >= 0 ? FIX : m.type) {
         case MAT_SHINYDIFFUSE: return sd_sample(m, d, sp, wo, wi, s, W);
         case MAT_GLOSSY: return gl_sample(m, d, sp, wo, wi, s, W);
         case MAT_COATED_GLOSSY: return cg_sample(m, d, sp, wo, wi, s, W);
@@ -871,9 +872,9 @@ template <int EXT> YB_HD col3 leaf_sample(const Material &m, const MatDat &d, co
             return col3(0.f);
     }
 }
-YB_HD float leaf_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
+template <int FIX = -1> YB_HD float leaf_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
 {
-    switch (m.type) {
+    switch (FIX >= 0 ? FIX : m.type) {
         case MAT_SHINYDIFFUSE: return sd_pdf(m, d, sp, wo, wi, bsdfs);
         case MAT_GLOSSY: return gl_pdf(m, d, sp, wo, wi, bsdfs);
         case MAT_COATED_GLOSSY: return cg_pdf(m, d, sp, wo, wi, bsdfs);
@@ -941,9 +942,9 @@ YB_HD const Material &blend_m2(const Material &m) { return (&m)[m.blendOff2]; }
 YB_HD float blend_ival(float val) { return fminf_(1.f, fmaxf_(0.f, 1.f - val)); }                       // :60
 YB_HD uint32_t blend_flags(const Material &sub) { return sub.type == MAT_NULL ? (uint32_t)BSDF_NONE : sub.bsdfFlags; }   // mat1Flags / mat2Flags
 
-template <int EXT> YB_HD void mat_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
+template <int EXT, int FIX = -1> YB_HD void mat_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
 {
-    if (!EXT || m.type != MAT_BLEND) { leaf_initBSDF(m, d, bsdfs); return; }
+    if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) { leaf_initBSDF<FIX>(m, d, bsdfs); return; }
     d.c[0] = d.c[1] = d.c[2] = d.c[3] = 0.f;
     bsdfs = blend_flags(blend_m1(m)) | blend_flags(blend_m2(m));
 }
@@ -958,9 +959,9 @@ template <int EXT> YB_HD void mat_blendSurface(const Material &m, Surf &sp)
     sp.NU = sp.NU * a + sp.NU * b;
     sp.NV = sp.NV * a + sp.NV * b;
 }
-template <int EXT> YB_HD col3 mat_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
+template <int EXT, int FIX = -1> YB_HD col3 mat_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
 {
-    if (!EXT || m.type != MAT_BLEND) return leaf_eval(m, d, sp, wo, wl, bsdfs);
+    if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_eval<FIX>(m, d, sp, wo, wl, bsdfs);
     const float val = m.blendVal, ival = blend_ival(val);
     MatDat d1, d2; uint32_t f;
     leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);
@@ -968,9 +969,9 @@ template <int EXT> YB_HD col3 mat_eval(const Material &m, const MatDat &d, const
     col3 col2 = leaf_eval(blend_m2(m), d2, sp, wo, wl, bsdfs);
     return col1 * ival + col2 * val;
 }
-template <int EXT> YB_HD col3 mat_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
+template <int EXT, int FIX = -1> YB_HD col3 mat_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
 {
-    if (!EXT || m.type != MAT_BLEND) return leaf_sample<EXT>(m, d, sp, wo, wi, s, W);
+    if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_sample<EXT, FIX>(m, d, sp, wo, wi, s, W);
     const float val = m.blendVal, ival = blend_ival(val);
     const Material &m1 = blend_m1(m), &m2 = blend_m2(m);
     bool mat1Sampled = false, mat2Sampled = false;
@@ -995,9 +996,9 @@ template <int EXT> YB_HD col3 mat_sample(const Material &m, const MatDat &d, con
     }
     return col1;
 }
-template <int EXT> YB_HD float mat_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
+template <int EXT, int FIX = -1> YB_HD float mat_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
 {
-    if (!EXT || m.type != MAT_BLEND) return leaf_pdf(m, d, sp, wo, wi, bsdfs);
+    if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_pdf<FIX>(m, d, sp, wo, wi, bsdfs);
     const float val = m.blendVal, ival = blend_ival(val);
     MatDat d1, d2; uint32_t f;
     leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);

@@ -11,8 +11,10 @@ namespace yb {
 struct LSample { float s1, s2; col3 col; float pdf; };   // lSample_t fields used on this path (light.h)
 
 // light_t::diracLight / canIntersect of the six light types
-YB_HD bool light_dirac(const Light &l) { return l.type == LIGHT_POINT || l.type == LIGHT_DIRECTIONAL || (l.type == LIGHT_SPOT && !l.softShadows); }
-YB_HD bool light_canIntersect(const Light &l) { return l.type == LIGHT_SUN || l.type == LIGHT_AREA || l.type == LIGHT_MESH || (l.type == LIGHT_SPOT && l.softShadows); }
+// LT >= 0: the light type is known at compile time (the staged direct-lighting kernels, one per light type: every switch on
+// the type folds); LT < 0: read it from the record
+template <int LT = -1> YB_HD bool light_dirac(const Light &l) { const int ty = LT >= 0 ? LT : l.type; return ty == LIGHT_POINT || ty == LIGHT_DIRECTIONAL || (ty == LIGHT_SPOT && !l.softShadows); }
+template <int LT = -1> YB_HD bool light_canIntersect(const Light &l) { const int ty = LT >= 0 ? LT : l.type; return ty == LIGHT_SUN || ty == LIGHT_AREA || ty == LIGHT_MESH || (ty == LIGHT_SPOT && l.softShadows); }
 YB_HD bool tri_intersect(v3 a, v3 b, v3 c, v3 from, v3 dir, float &t, float &u, float &v);   // yb_trace.cuh
 
 // spot cone falloff (spotlight.cc:117-126,163-172,263-272): smoothstep between cosEnd and cosStart
@@ -24,9 +26,10 @@ YB_HD float spot_falloff(const Light &l, float cosa)
 }
 // pointLight_t::illuminate (pointlight.cc:54-70), directionalLight_t::illuminate (directional.cc:77-97),
 // spotLight_t::illuminate (spotlight.cc:103-132)
-YB_HD bool light_illuminate(const Light &l, v3 P, col3 &col, Ray &wi)
+template <int LT = -1> YB_HD bool light_illuminate(const Light &l, v3 P, col3 &col, Ray &wi)
 {
-    if (l.type == LIGHT_DIRECTIONAL) {
+    const int ty = LT >= 0 ? LT : l.type;
+    if (ty == LIGHT_DIRECTIONAL) {
         if (!l.infinite) {               // outside of the illuminated cylinder?
             v3 vec = l.position - P;
             float dist = length(cross(l.direction, vec));
@@ -38,7 +41,7 @@ YB_HD bool light_illuminate(const Light &l, v3 P, col3 &col, Ray &wi)
         col = l.color;
         return true;
     }
-    if (l.type == LIGHT_SPOT) {
+    if (ty == LIGHT_SPOT) {
         if (l.photonOnly) return false;
         v3 ldir = l.position - P;
         float dist_sqr = dot(ldir, ldir);
@@ -58,7 +61,7 @@ YB_HD bool light_illuminate(const Light &l, v3 P, col3 &col, Ray &wi)
         wi.dir = ldir;
         return true;
     }
-    if (l.type != LIGHT_POINT) return false;
+    if (ty != LIGHT_POINT) return false;
     v3 ldir = l.position - P;
     float dist_sqr = ldir.x * ldir.x + ldir.y * ldir.y + ldir.z * ldir.z;
     float dist = fSqrt(dist_sqr);
@@ -105,9 +108,10 @@ YB_HD bool mesh_sampleSurface(const Light &l, v3 &p, v3 &n, float s1, float s2)
     n = v3(A.w, B.w, C.w);
     return true;
 }
-template <int EXT> YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s, Ray &wi)
+template <int EXT, int LT = -1> YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s, Ray &wi)
 {
-    if (EXT && l.type == LIGHT_MESH) {           // meshLight_t::illumSample (meshlight.cc:100-137)
+    const int ty = LT >= 0 ? LT : l.type;
+    if (EXT && ty == LIGHT_MESH) {           // meshLight_t::illumSample (meshlight.cc:100-137)
         v3 n(0.f), p(0.f);
         mesh_sampleSurface(l, p, n, s.s1, s.s2);
         v3 ldir = p - P;
@@ -127,14 +131,14 @@ template <int EXT> YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s
         s.pdf = (float)((double)dist_sqr * YB_M_PI / (double)((area_mul_cosangle == 0.f) ? 1e-8f : area_mul_cosangle));
         return true;
     }
-    if (l.type == LIGHT_SUN) {
+    if (ty == LIGHT_SUN) {
         wi.dir = sampleCone(l.direction, l.du, l.dv, (float)l.cosAngle, s.s1, s.s2);
         wi.tmax = -1.f;
         s.col = l.colPdf;
         s.pdf = l.pdf;
         return true;
     }
-    if (l.type == LIGHT_SPOT) {                  // spotLight_t::illumSample (spotlight.cc:134-177)
+    if (ty == LIGHT_SPOT) {                  // spotLight_t::illumSample (spotlight.cc:134-177)
         if (l.photonOnly) return false;
         v3 ldir = l.position - P;
         float dist_sqr = dot(ldir, ldir);
@@ -149,7 +153,7 @@ template <int EXT> YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s
         s.pdf = dist_sqr;
         return true;
     }
-    if (l.type == LIGHT_SPHERE) {                // sphereLight_t::illumSample (spherelight.cc:100-132)
+    if (ty == LIGHT_SPHERE) {                // sphereLight_t::illumSample (spherelight.cc:100-132)
         v3 cdir = l.position - P;
         float dist_sqr = dot(cdir, cdir);
         if (dist_sqr <= l.squareRadius) return false;     // only emits on the outside
@@ -167,7 +171,7 @@ template <int EXT> YB_HD bool light_illumSample(const Light &l, v3 P, LSample &s
         s.col = l.color;
         return true;
     }
-    if (l.type == LIGHT_AREA) {
+    if (ty == LIGHT_AREA) {
         v3 p = l.corner + s.s1 * l.toX + s.s2 * l.toY;
         v3 ldir = p - P;
         float dist_sqr = dot(ldir, ldir);
@@ -202,9 +206,10 @@ YB_HD bool light_triIntersect(v3 a, v3 b, v3 c, v3 from, v3 dir, float &t)
     return true;
 }
 // sunLight_t::intersect (sunlight.cc:87-95), areaLight_t::intersect (arealight.cc:136-154)
-template <int EXT> YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, float tmin, float &t, col3 &col, float &ipdf)
+template <int EXT, int LT = -1> YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, float tmin, float &t, col3 &col, float &ipdf)
 {
-    if (EXT && l.type == LIGHT_MESH) {           // meshLight_t::intersect (meshlight.cc:181-205): closest hit on the emitter's own triangles
+    const int ty = LT >= 0 ? LT : l.type;
+    if (EXT && ty == LIGHT_MESH) {           // meshLight_t::intersect (meshlight.cc:181-205): closest hit on the emitter's own triangles
         // (the reference walks a private kd-tree; here the emitter list is tested in order, acceptance rule of kdtree.cc:772,791)
         float Z = t < 0 ? INFINITY : t;
         int hit = -1;
@@ -227,7 +232,7 @@ template <int EXT> YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, f
         col = l.color;
         return true;
     }
-    if (l.type == LIGHT_SUN) {
+    if (ty == LIGHT_SUN) {
         float cosine = dot(dir, l.direction);
         if ((double)cosine < l.cosAngle) return false;
         col = l.colPdf;
@@ -235,7 +240,7 @@ template <int EXT> YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, f
         ipdf = l.invpdf;
         return true;
     }
-    if (l.type == LIGHT_SPOT) {                  // spotLight_t::intersect (spotlight.cc:243-280), quirks included
+    if (ty == LIGHT_SPOT) {                  // spotLight_t::intersect (spotlight.cc:243-280), quirks included
         float cosA = dot(l.direction, dir);
         if (cosA == 0.f) return false;
         t = dot(l.direction, l.position - from) / cosA;
@@ -252,7 +257,7 @@ template <int EXT> YB_HD bool light_intersect(const Light &l, v3 from, v3 dir, f
         }
         return false;
     }
-    if (l.type == LIGHT_AREA) {
+    if (ty == LIGHT_AREA) {
         float cos_angle = dot(dir, l.fnormal);
         if (cos_angle <= 0) return false;
         if (!light_triIntersect(l.corner, l.c2, l.c3, from, dir, t)) {

@@ -135,6 +135,62 @@ static void bin_tasks(uint32_t n, const RenderArgs &a, rt_stream s)
     g_kernel_launches += 2;
 }
 
+// ---- staged direct lighting: group the (task, light) jobs of a wave by (light type x material class) so that each group runs as
+//      one launch of its own specialised kernel (yb_direct.cu).  The job count lives in device memory (counters[YB_CNT_LJOBS]); the
+//      host reads the group sizes afterwards, together with the other counters of the wave.
+#ifndef YB_HOSTEMU
+__global__ void __launch_bounds__(256) k_ljob_count_kernel(const RenderArgs a)
+{
+    __shared__ uint32_t h[YB_LBINS];
+    const uint32_t n = min(a.counters[YB_CNT_LJOBS], a.ljobCap);
+    if (threadIdx.x < YB_LBINS) h[threadIdx.x] = 0u;
+    __syncthreads();
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) atomicAdd(&h[a.ljobs[t].lightKey >> 24], 1u);
+    __syncthreads();
+    if (threadIdx.x < YB_LBINS && h[threadIdx.x]) atomicAdd(&a.counters[YB_CNT_LBINS + threadIdx.x], h[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256) k_ljob_scatter_kernel(const RenderArgs a)
+{
+    __shared__ uint32_t h[YB_LBINS], base[YB_LBINS];
+    const uint32_t n = min(a.counters[YB_CNT_LJOBS], a.ljobCap);
+    for (uint32_t c0 = blockIdx.x * blockDim.x; c0 < n; c0 += gridDim.x * blockDim.x) {     // same trip count for the whole block
+        if (threadIdx.x < YB_LBINS) h[threadIdx.x] = 0u;
+        __syncthreads();
+        const uint32_t t = c0 + threadIdx.x;
+        LightJob j; j.task = 0u; j.lightKey = 0u;
+        uint32_t k = 0u, rank = 0u;
+        if (t < n) { j = a.ljobs[t]; k = j.lightKey >> 24; rank = atomicAdd(&h[k], 1u); }
+        __syncthreads();
+        if (threadIdx.x < YB_LBINS) {
+            uint32_t before = 0u;
+            for (uint32_t b = 0; b < threadIdx.x; ++b) before += a.counters[YB_CNT_LBINS + b];
+            base[threadIdx.x] = before + (h[threadIdx.x] ? atomicAdd(&a.counters[YB_CNT_LCURSOR + threadIdx.x], h[threadIdx.x]) : 0u);
+        }
+        __syncthreads();
+        if (t < n) a.ljobsSorted[base[k] + rank] = j;
+        __syncthreads();
+    }
+}
+#endif
+static void group_light_jobs(size_t maxJobs, const RenderArgs &a, rt_stream s)
+{
+#ifndef YB_HOSTEMU
+    uint32_t blocks = (uint32_t)std::min<size_t>((maxJobs + 255u) / 256u, 148u * 8u);
+    if (blocks < 1u) blocks = 1u;
+    k_ljob_count_kernel<<<blocks, 256, 0, s>>>(a);
+    k_ljob_scatter_kernel<<<blocks, 256, 0, s>>>(a);
+    YB_CUDA_CHECK(cudaGetLastError());
+#else
+    (void)maxJobs;
+    const uint32_t n = std::min(a.counters[YB_CNT_LJOBS], a.ljobCap);
+    for (uint32_t t = 0; t < n; ++t) a.counters[YB_CNT_LBINS + (a.ljobs[t].lightKey >> 24)]++;
+    uint32_t base[YB_LBINS], acc = 0;
+    for (int b = 0; b < YB_LBINS; ++b) { base[b] = acc; acc += a.counters[YB_CNT_LBINS + b]; }
+    for (uint32_t t = 0; t < n; ++t) a.ljobsSorted[base[a.ljobs[t].lightKey >> 24]++] = a.ljobs[t];
+#endif
+    g_kernel_launches += 2;
+}
+
 // ------------------------------------------------------------------------------------------------ film
 // imageFilm_t::addSample (imagefilm.cc:453-511); film layout (x + w*y)*5 = r,g,b,a,weight (pixel_t)
 YB_D void film_splat_sample(const RenderArgs &a, uint32_t tid)
@@ -349,10 +405,30 @@ struct RenderBuffers {
     DevBuf<Task> poolA, poolB;
     DevBuf<Hit> hits;
     DevBuf<ShadowTask> shadow;
+    DevBuf<LightJob> ljobs, ljobsSorted;     // staged direct lighting
     DevBuf<uint32_t> counters, order, bins, waveCnt;
 #ifndef YB_HOSTEMU
     std::vector<cudaEvent_t> events;     // per-wave stage timers of the device-counted wave loop, read once per batch
-    ~RenderBuffers() { for (size_t i = 0; i < events.size(); ++i) cudaEventDestroy(events[i]); }
+    // staged direct lighting: the groups of a wave are independent launches; side streams let the small ones (a few dozen CTAs that
+    // would each hold the GPU for the latency of one job) run beside the large ones
+    enum { kSideStreams = 4 };
+    cudaStream_t side[kSideStreams] = {0, 0, 0, 0};
+    cudaEvent_t sideDone[kSideStreams] = {0, 0, 0, 0}, sideFork = 0;
+    void sideStreams()
+    {
+        if (sideFork) return;
+        for (int i = 0; i < kSideStreams; ++i) {
+            YB_CUDA_CHECK(cudaStreamCreateWithFlags(&side[i], cudaStreamNonBlocking));
+            YB_CUDA_CHECK(cudaEventCreateWithFlags(&sideDone[i], cudaEventDisableTiming));
+        }
+        YB_CUDA_CHECK(cudaEventCreateWithFlags(&sideFork, cudaEventDisableTiming));
+    }
+    ~RenderBuffers()
+    {
+        for (size_t i = 0; i < events.size(); ++i) cudaEventDestroy(events[i]);
+        for (int i = 0; i < kSideStreams; ++i) { if (side[i]) cudaStreamDestroy(side[i]); if (sideDone[i]) cudaEventDestroy(sideDone[i]); }
+        if (sideFork) cudaEventDestroy(sideFork);
+    }
     cudaEvent_t event(size_t i)
     {
         while (events.size() <= i) { cudaEvent_t e; YB_CUDA_CHECK(cudaEventCreate(&e)); events.push_back(e); }
@@ -567,12 +643,16 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
 #else
         const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)24 << 30), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 22);
 #endif
-        const size_t perSample = (F + 1) * sizeof(Task) * 2 + S * sizeof(ShadowTask) + sizeof(Hit) + sizeof(f4);
+        // staged direct lighting (yb_direct.cu): where tasks fan out (so that the host counts every wave anyway) and the base build shades
+        const bool stageDirect = F > 1 && !extShade && !nodeShade && !c.lights.empty() && env_size("YB200_STAGE_DIRECT", 1) != 0;
+        const size_t L = stageDirect ? c.lights.size() : 0;       // jobs per task: every light (integrate) or one (path vertex)
+        const size_t perSample = (F + 1) * sizeof(Task) * 2 + S * sizeof(ShadowTask) + sizeof(Hit) + sizeof(f4) + 2 * L * sizeof(LightJob);
         size_t B = std::min<size_t>(Bmax, std::max<size_t>(1024, budget / perSample));
         B = std::min<size_t>(B, (size_t)totalSamples);
         const size_t poolCap = B * (F + 1), shadowCap = B * S;
         rb.poolA.reserve(poolCap); rb.poolB.reserve(poolCap);
-        rb.hits.reserve(B); rb.shadow.reserve(shadowCap); rb.counters.reserve(4); rb.acc.reserve(B);
+        rb.hits.reserve(B); rb.shadow.reserve(shadowCap); rb.counters.reserve(YB_CNT_WORDS); rb.acc.reserve(B);
+        if (stageDirect) { rb.ljobs.reserve(B * L); rb.ljobsSorted.reserve(B * L); }
         rb.order.reserve(B); rb.keys.reserve(B); rb.bins.reserve(2 * YB_SHADE_BINS);
         if (f.zChan) rb.depthT.reserve(B);
         RenderArgs a;
@@ -584,17 +664,20 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         const bool filmFast = env_size("YB200_FILM_FAST", 1) != 0;       // warp-aggregated film splat (k_film_fast_kernel)
         (void)filmFast;      // also bin the camera wave (pixel order is already coherent)
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
+        const bool sideStreams = env_size("YB200_SIDE_STREAMS", 1) != 0;       // staged direct lighting: groups of a wave on several streams
+        (void)sideStreams;
         // coherence sort of the ray waves: 0 off, 1 closest-hit waves after the camera wave, 2 + shadow waves after the first, 3 all
         const int sortRays = (int)env_size("YB200_SORT_RAYS", 0);
         a.depthT = f.zChan ? rb.depthT.p : 0; a.depthFilm = f.zChan ? rb.depthFilm.p : 0;
         a.film = d_film; a.shadowCap = (uint32_t)std::min<size_t>(shadowCap, 0xffffffffu);
+        a.ljobs = stageDirect ? rb.ljobs.p : 0; a.ljobsSorted = stageDirect ? rb.ljobsSorted.p : 0; a.ljobCap = (uint32_t)std::min<size_t>(B * L, 0xffffffffu);
         Task *pool = rb.poolA.p, *alt = rb.poolB.p;
         const bool useFast = env_size("YB200_SIMPLE_TRACE", 0) == 0;
         // longest chain of tasks one camera sample can spawn when every task has at most one child: the camera task, one path
         // vertex per bounce, one specular child per recursion level (raylevel is capped at rDepth, mcintegrator.cc:428,588)
         const int maxChain = 1 + (I.type == INTEG_PATH ? std::max(0, I.maxBounces) : 0) + (specChildren ? std::max(0, I.rDepth) + 1 : 0);
         const bool tsFast = useFast && !nodeShade;      // IntersectTS in the persistent kernel (node materials evaluate their graph: per-ray kernel)
-        const bool deviceWaves = F <= 1 && useFast && (!I.trShad || tsFast) && !sortRays && !logWaves && env_size("YB200_DEVICE_WAVES", 1) != 0;
+        const bool deviceWaves = !stageDirect && F <= 1 && useFast && (!I.trShad || tsFast) && !sortRays && !logWaves && env_size("YB200_DEVICE_WAVES", 1) != 0;
         const int nBatches = (int)((totalSamples + B - 1) / B);
         for (int b = 0; b < nBatches; ++b) {
             if (c.abortFlag || (should_abort && should_abort(user))) break;
@@ -684,7 +767,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 a.tasks = pool + (top - M);
                 a.out_tasks = whole ? alt : pool + top;
                 a.outCap = (uint32_t)std::min<size_t>(whole ? poolCap : poolCap - top, 0xffffffffu);
-                rt_memset(rb.counters.p, 0, 4 * sizeof(uint32_t), s);
+                rt_memset(rb.counters.p, 0, YB_CNT_WORDS * sizeof(uint32_t), s);
                 tc.start();
                 if (useFast) {
                     FastJob j; j.nodes = c.sc.nodes; j.tri_v = c.sc.tri_v; j.rays = (const char *)a.tasks; j.stride = sizeof(Task); j.n = (uint32_t)M; j.nPtr = 0; j.counterZeroed = false;
@@ -699,12 +782,49 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 if (binShade && (!firstWave || binFirst)) { bin_tasks((uint32_t)M, a, s); a.order = rb.order.p; }
                 if (nodeShade) launch_shade_nodes((uint32_t)M, a, s);
                 else if (extShade) launch_shade_ext((uint32_t)M, a, s);
+                else if (stageDirect) launch_shade_staged((uint32_t)M, a, s);
                 else launch_shade_base((uint32_t)M, a, s);
                 if (gatherCaustics) launch_caustic_gather((uint32_t)M, a, s);
+                uint32_t cnt[YB_CNT_WORDS];
+                if (stageDirect) {      // the queued estimates, one launch per (light type x material class) group present in this wave
+                    group_light_jobs(M * L, a, s);
+                    rt_d2h(cnt, rb.counters.p, sizeof(cnt), s);
+                    if (cnt[YB_CNT_LJOBS] > a.ljobCap) throw RtError("render: internal queue overflow (light jobs)");
+                    uint32_t gbase[YB_LBINS], base = 0;
+                    for (uint32_t k = 0; k < YB_LBINS; ++k) { gbase[k] = base; base += cnt[YB_CNT_LBINS + k]; }
+#ifndef YB_HOSTEMU
+                    if (sideStreams) {
+                        // largest first (a sampled light costs about eight point lights per job), dealt round-robin over the main stream
+                        // and the side streams; the shadow queue takes the pushes of all of them through one atomic counter
+                        std::vector<std::pair<uint64_t, uint32_t>> groups;
+                        for (uint32_t k = 0; k < YB_LBINS; ++k)
+                            if (cnt[YB_CNT_LBINS + k]) {
+                                const uint32_t lt = (k >> 1) / YB_LJOB_MCLASSES;
+                                groups.push_back(std::make_pair((uint64_t)cnt[YB_CNT_LBINS + k] * ((lt == LIGHT_POINT || lt == LIGHT_DIRECTIONAL) ? 1u : 8u), k));
+                            }
+                        std::sort(groups.begin(), groups.end(), [](const std::pair<uint64_t, uint32_t> &x, const std::pair<uint64_t, uint32_t> &y) { return x.first > y.first; });
+                        rb.sideStreams();
+                        YB_CUDA_CHECK(cudaEventRecord(rb.sideFork, s));
+                        bool used[RenderBuffers::kSideStreams] = {false, false, false, false};
+                        for (size_t g = 0; g < groups.size(); ++g) {
+                            const uint32_t k = groups[g].second;
+                            const size_t lane = g % (RenderBuffers::kSideStreams + 1);
+                            rt_stream st = s;
+                            if (lane > 0) {
+                                st = rb.side[lane - 1];
+                                if (!used[lane - 1]) { YB_CUDA_CHECK(cudaStreamWaitEvent(st, rb.sideFork, 0)); used[lane - 1] = true; }
+                            }
+                            launch_direct(k, gbase[k], cnt[YB_CNT_LBINS + k], a, st);
+                        }
+                        for (int i = 0; i < RenderBuffers::kSideStreams; ++i)
+                            if (used[i]) { YB_CUDA_CHECK(cudaEventRecord(rb.sideDone[i], rb.side[i])); YB_CUDA_CHECK(cudaStreamWaitEvent(s, rb.sideDone[i], 0)); }
+                    } else
+#endif
+                    for (uint32_t k = 0; k < YB_LBINS; ++k) launch_direct(k, gbase[k], cnt[YB_CNT_LBINS + k], a, s);
+                }
                 tsd.stop();
                 firstWave = false;
-                uint32_t cnt[4];
-                rt_d2h(cnt, rb.counters.p, sizeof(cnt), s);
+                rt_d2h(cnt, rb.counters.p, 4 * sizeof(uint32_t), s);
                 if (cnt[0] > a.outCap || cnt[1] > a.shadowCap) throw RtError("render: internal queue overflow");
                 tsh.start();
                 if (useFast && !I.trShad) {

@@ -49,6 +49,18 @@ YB_D double scrHalton(int dim, uint32_t n)
     return value < 1.0e-36 ? 1.0e-36 : (value > 1.0 ? 1.0 : value);
 }
 
+// one direct-lighting estimate still to do: task index in the current wave, light index | group key << 24
+struct LightJob { uint32_t task, lightKey; };
+// group of a job: light type (LIGHT_POINT .. LIGHT_SPHERE; mesh lights run in the ext build, which is not staged) x material class
+// (0..2 = shinydiffuse / glossy / coated_glossy, the materials with eval / pdf bodies; 3 = everything else) x (trajectory split or not:
+// a sampled light takes light.samples / rayDivision samples, and a warp that mixes 8-sample and 1-sample jobs idles 3/4 of its lanes)
+#define YB_LJOB_MCLASSES 4
+YB_HD uint32_t light_job_key(int lightType, int matType, uint32_t rayDivision)
+{
+    const bool sampled = !(lightType == LIGHT_POINT || lightType == LIGHT_DIRECTIONAL);
+    return (((uint32_t)lightType * YB_LJOB_MCLASSES + (uint32_t)(matType < 3 ? matType : 3)) << 1) | (sampled && rayDivision > 1 ? 1u : 0u);
+}
+
 struct RenderArgs {
     SceneDev sc;
     Task *tasks;            // chunk being processed
@@ -66,7 +78,15 @@ struct RenderArgs {
     float *depthFilm;       // z_channel: (x + w*y)*2: sum(depth*w), sum(w)  (gray2DImage_t / pixelGray_t)
     uint32_t sampleBase;    // first global camera-sample index of this batch
     uint32_t outCap, shadowCap;
+    // staged direct lighting (yb_direct.cu): (task, light) jobs queued by the staged shade kernel, then grouped by
+    // (light type x material class); counters[YB_CNT_LJOBS] = number of jobs, counters[YB_CNT_LBINS + key] = jobs per group
+    LightJob *ljobs, *ljobsSorted;
+    uint32_t ljobCap;
 };
+
+// slots of the per-wave counter block (RenderArgs::counters)
+enum { YB_CNT_TASKS = 0, YB_CNT_SHADOW = 1, YB_CNT_TRACE_A = 2, YB_CNT_TRACE_B = 3, YB_CNT_LJOBS = 4, YB_CNT_LBINS = 8, YB_LBINS = 64,
+       YB_CNT_LCURSOR = YB_CNT_LBINS + YB_LBINS, YB_CNT_WORDS = YB_CNT_LCURSOR + YB_LBINS };
 
 // per-camera-sample identity (integrator.cc:251-273)
 struct SampleId { int x, y, s; uint32_t samplingOffs; int pixelSample; };
@@ -120,6 +140,14 @@ YB_D void push_task(const RenderArgs &a, const Task &t)
     a.out_tasks[i] = t;
 }
 
+YB_D void push_light_job(const RenderArgs &a, uint32_t task, uint32_t light, uint32_t key)
+{
+    const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + YB_CNT_LJOBS, 1u);
+    if (i >= a.ljobCap) return;                               // cannot happen: sized for (tasks of a wave) x (lights)
+    LightJob j; j.task = task; j.lightKey = light | (key << 24);
+    a.ljobs[i] = j;
+}
+
 // the light estimateOneDirectLight picks for path sample n (mcintegrator.cc:62-66)
 YB_D int pick_one_light(int n, int lightNum)
 {
@@ -136,5 +164,9 @@ YB_D int pick_one_light(int n, int lightNum)
 void launch_shade_base(uint32_t n, const RenderArgs &a, rt_stream s);
 void launch_shade_ext(uint32_t n, const RenderArgs &a, rt_stream s);
 void launch_shade_nodes(uint32_t n, const RenderArgs &a, rt_stream s);
+// staged form of the base build: launch_shade_staged queues the direct-lighting estimates, launch_direct evaluates the n jobs
+// of one (light type, material class) group that start at ljobsSorted[base]
+void launch_shade_staged(uint32_t n, const RenderArgs &a, rt_stream s);
+void launch_direct(uint32_t key, uint32_t base, uint32_t n, const RenderArgs &a, rt_stream s);
 
 }  // namespace yb

@@ -33,7 +33,11 @@ CONFIGS["c4img"] = ("materials scene with image textures, projections, bump and 
                     scenes.materials_scene, dict(width=1920, height=1080, spp=16, bounces=4, **cases._IMAGED), 2)
 
 for key in (sys.argv[1:] or ["c1", "c2", "c3", "c4", "c5"]):
+    key, _, over = key.partition(":")              # "c4:spp=4" overrides keyword arguments of the scene (profiling runs)
     desc, fn, kw, reps = CONFIGS[key]
+    if over:
+        kw = dict(kw, **{k: int(v) for k, v in (o.split("=") for o in over.split(","))})
+        desc += " [" + over + "]"
     yi = YafrayInterface(device=0)
     t0 = time.time()
     fn(yi, **kw)
