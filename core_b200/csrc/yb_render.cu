@@ -63,31 +63,30 @@ YB_KERNEL(k_trace_shadow, RenderArgs)
 // ---- shading order.  After the first wave the tasks of one warp take very different code paths (hit / miss, the
 // light estimateOneDirectLight picks): measured 8 of 32 lanes active.  Tasks are binned by a small key so that warps
 // of the shade kernel are homogeneous; the kernel then gathers its task through `order`.
-#define YB_SHADE_BINS 32
-// key: 0 = miss; 1..7 = integrate() task by material type of the hit (the BSDF code of the material classes shares nothing, and
+#define YB_SHADE_BINS 256
+// key: 0 = miss; 8..35 = integrate() task by material type of the hit (the BSDF code of the material classes shares nothing, and
 // recursiveRaytrace children of a glossy / specular surface land on every material: 1080p materials scene, shade 14.4 s -> see
-// profiles/); 8..31 = path vertex by (light estimateOneDirectLight picks: 0, 1, 2+) x (material type)
+// profiles/) x material slot (index & 3: materials of one type still branch on their parameters - Blinn / anisotropic lobe,
+// Lambert / Oren-Nayar, mirror / transparency components); 64..255 = path vertex by (light estimateOneDirectLight picks: 0, 1, 2+;
+// not when direct lighting is staged) x (material type) x (material slot)
 YB_D uint32_t shade_key(const RenderArgs &a, uint32_t t)
 {
     const int tri = a.hits[t].tri;
     if (tri < 0) return 0u;
     const uint32_t bits = a.tasks[t].bits;
-    if (task_kind(bits) == TASK_INTEGRATE) {
-        const uint32_t info = (uint32_t)f2i(a.sc.tri_v[3 * (size_t)tri + 1].w);
-        const uint32_t ty = (uint32_t)a.sc.materials[info & TRI_MAT_MASK].type;
-        return 1u + (ty < 6u ? ty : 6u);
-    }
-    const uint32_t info = (uint32_t)f2i(a.sc.tri_v[3 * (size_t)tri + 1].w);
-    const uint32_t ty = (uint32_t)a.sc.materials[info & TRI_MAT_MASK].type;
-    const int l = pick_one_light((int)a.tasks[t].pathOffs, a.sc.nLights);
-    return 8u + 8u * (uint32_t)(l < 0 ? 0 : (l < 2 ? l : 2)) + (ty < 7u ? ty : 7u);      // l = -1 without lights
+    const uint32_t mi = (uint32_t)f2i(a.sc.tri_v[3 * (size_t)tri + 1].w) & TRI_MAT_MASK;
+    const uint32_t ty = (uint32_t)a.sc.materials[mi].type;
+    if (task_kind(bits) == TASK_INTEGRATE) return 8u + 4u * (ty < 6u ? ty : 6u) + (mi & 3u);
+    const int l = a.ljobs ? 0 : pick_one_light((int)a.tasks[t].pathOffs, a.sc.nLights);
+    return 64u + 64u * (uint32_t)(l < 0 ? 0 : (l < 2 ? l : 2)) + 4u * (ty < 7u ? ty : 7u) + (mi & 3u);      // l = -1 without lights
 }
 #ifndef YB_HOSTEMU
 __global__ void __launch_bounds__(256) k_bin_count_kernel(uint32_t n, const RenderArgs a)
 {
     __shared__ uint32_t h[YB_SHADE_BINS];
+    static_assert(YB_SHADE_BINS == 256, "one thread per bin");
     if (a.nPtr) n = min(n, *a.nPtr);
-    if (threadIdx.x < YB_SHADE_BINS) h[threadIdx.x] = 0u;
+    h[threadIdx.x] = 0u;
     __syncthreads();
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
         const uint32_t k = shade_key(a, t);
@@ -95,26 +94,40 @@ __global__ void __launch_bounds__(256) k_bin_count_kernel(uint32_t n, const Rend
         atomicAdd(&h[k], 1u);
     }
     __syncthreads();
-    if (threadIdx.x < YB_SHADE_BINS && h[threadIdx.x]) atomicAdd(&a.bins[threadIdx.x], h[threadIdx.x]);
+    if (h[threadIdx.x]) atomicAdd(&a.bins[threadIdx.x], h[threadIdx.x]);
+}
+// exclusive prefix over 256 per-thread values (one per bin), result in sh[threadIdx.x]
+__device__ __forceinline__ void block_exclusive_scan_256(uint32_t own, uint32_t *sh)
+{
+    uint32_t v = own;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (uint32_t off = 1; off < 256u; off <<= 1) {
+        const uint32_t add = threadIdx.x >= off ? sh[threadIdx.x - off] : 0u;
+        __syncthreads();
+        v += add; sh[threadIdx.x] = v;
+        __syncthreads();
+    }
+    sh[threadIdx.x] = v - own;
+    __syncthreads();
 }
 __global__ void __launch_bounds__(256) k_bin_scatter_kernel(uint32_t n, const RenderArgs a)
 {
-    __shared__ uint32_t h[YB_SHADE_BINS], base[YB_SHADE_BINS];
+    __shared__ uint32_t h[YB_SHADE_BINS], base[YB_SHADE_BINS], start[YB_SHADE_BINS];
     if (a.nPtr) n = min(n, *a.nPtr);
-    if (blockIdx.x * blockDim.x >= n) return;
-    if (threadIdx.x < YB_SHADE_BINS) h[threadIdx.x] = 0u;
-    __syncthreads();
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t k = 0u, rank = 0u;
-    if (t < n) { k = a.keys[t]; rank = atomicAdd(&h[k], 1u); }
-    __syncthreads();
-    if (threadIdx.x < YB_SHADE_BINS) {
-        uint32_t before = 0u;
-        for (uint32_t b = 0; b < threadIdx.x; ++b) before += a.bins[b];
-        base[threadIdx.x] = before + (h[threadIdx.x] ? atomicAdd(&a.bins[YB_SHADE_BINS + threadIdx.x], h[threadIdx.x]) : 0u);
+    block_exclusive_scan_256(a.bins[threadIdx.x], start);
+    for (uint32_t c0 = blockIdx.x * blockDim.x; c0 < n; c0 += gridDim.x * blockDim.x) {     // same trip count for the whole block
+        h[threadIdx.x] = 0u;
+        __syncthreads();
+        const uint32_t t = c0 + threadIdx.x;
+        uint32_t k = 0u, rank = 0u;
+        if (t < n) { k = a.keys[t]; rank = atomicAdd(&h[k], 1u); }
+        __syncthreads();
+        base[threadIdx.x] = start[threadIdx.x] + (h[threadIdx.x] ? atomicAdd(&a.bins[YB_SHADE_BINS + threadIdx.x], h[threadIdx.x]) : 0u);
+        __syncthreads();
+        if (t < n) a.orderOut[base[k] + rank] = t;
+        __syncthreads();
     }
-    __syncthreads();
-    if (t < n) a.orderOut[base[k] + rank] = t;
 }
 #endif
 static void bin_tasks(uint32_t n, const RenderArgs &a, rt_stream s)
@@ -123,7 +136,7 @@ static void bin_tasks(uint32_t n, const RenderArgs &a, rt_stream s)
 #ifndef YB_HOSTEMU
     uint32_t blocks = (n + 255u) / 256u;
     k_bin_count_kernel<<<blocks > 148u * 8u ? 148u * 8u : blocks, 256, 0, s>>>(n, a);
-    k_bin_scatter_kernel<<<blocks, 256, 0, s>>>(n, a);
+    k_bin_scatter_kernel<<<blocks > 148u * 8u ? 148u * 8u : blocks, 256, 0, s>>>(n, a);
     YB_CUDA_CHECK(cudaGetLastError());
 #else
     if (a.nPtr && *a.nPtr < n) n = *a.nPtr;
@@ -143,29 +156,27 @@ __global__ void __launch_bounds__(256) k_ljob_count_kernel(const RenderArgs a)
 {
     __shared__ uint32_t h[YB_LBINS];
     const uint32_t n = min(a.counters[YB_CNT_LJOBS], a.ljobCap);
-    if (threadIdx.x < YB_LBINS) h[threadIdx.x] = 0u;
+    h[threadIdx.x] = 0u;
     __syncthreads();
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) atomicAdd(&h[a.ljobs[t].lightKey >> 24], 1u);
     __syncthreads();
-    if (threadIdx.x < YB_LBINS && h[threadIdx.x]) atomicAdd(&a.counters[YB_CNT_LBINS + threadIdx.x], h[threadIdx.x]);
+    if (h[threadIdx.x]) atomicAdd(&a.counters[YB_CNT_LBINS + threadIdx.x], h[threadIdx.x]);
 }
 __global__ void __launch_bounds__(256) k_ljob_scatter_kernel(const RenderArgs a)
 {
-    __shared__ uint32_t h[YB_LBINS], base[YB_LBINS];
+    __shared__ uint32_t h[YB_LBINS], base[YB_LBINS], start[YB_LBINS];
     const uint32_t n = min(a.counters[YB_CNT_LJOBS], a.ljobCap);
+    static_assert(YB_LBINS == 256, "one thread per bin");
+    block_exclusive_scan_256(a.counters[YB_CNT_LBINS + threadIdx.x], start);
     for (uint32_t c0 = blockIdx.x * blockDim.x; c0 < n; c0 += gridDim.x * blockDim.x) {     // same trip count for the whole block
-        if (threadIdx.x < YB_LBINS) h[threadIdx.x] = 0u;
+        h[threadIdx.x] = 0u;
         __syncthreads();
         const uint32_t t = c0 + threadIdx.x;
         LightJob j; j.task = 0u; j.lightKey = 0u;
         uint32_t k = 0u, rank = 0u;
         if (t < n) { j = a.ljobs[t]; k = j.lightKey >> 24; rank = atomicAdd(&h[k], 1u); }
         __syncthreads();
-        if (threadIdx.x < YB_LBINS) {
-            uint32_t before = 0u;
-            for (uint32_t b = 0; b < threadIdx.x; ++b) before += a.counters[YB_CNT_LBINS + b];
-            base[threadIdx.x] = before + (h[threadIdx.x] ? atomicAdd(&a.counters[YB_CNT_LCURSOR + threadIdx.x], h[threadIdx.x]) : 0u);
-        }
+        base[threadIdx.x] = start[threadIdx.x] + (h[threadIdx.x] ? atomicAdd(&a.counters[YB_CNT_LCURSOR + threadIdx.x], h[threadIdx.x]) : 0u);
         __syncthreads();
         if (t < n) a.ljobsSorted[base[k] + rank] = j;
         __syncthreads();
@@ -790,17 +801,21 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                     group_light_jobs(M * L, a, s);
                     rt_d2h(cnt, rb.counters.p, sizeof(cnt), s);
                     if (cnt[YB_CNT_LJOBS] > a.ljobCap) throw RtError("render: internal queue overflow (light jobs)");
-                    uint32_t gbase[YB_LBINS], base = 0;
-                    for (uint32_t k = 0; k < YB_LBINS; ++k) { gbase[k] = base; base += cnt[YB_CNT_LBINS + k]; }
+                    uint32_t gbase[YB_LGROUPS], gcount[YB_LGROUPS], base = 0;
+                    for (uint32_t k = 0; k < YB_LGROUPS; ++k) {
+                        gbase[k] = base; gcount[k] = 0;
+                        for (uint32_t q = 0; q < 4; ++q) gcount[k] += cnt[YB_CNT_LBINS + 4 * k + q];
+                        base += gcount[k];
+                    }
 #ifndef YB_HOSTEMU
                     if (sideStreams) {
                         // largest first (a sampled light costs about eight point lights per job), dealt round-robin over the main stream
                         // and the side streams; the shadow queue takes the pushes of all of them through one atomic counter
                         std::vector<std::pair<uint64_t, uint32_t>> groups;
-                        for (uint32_t k = 0; k < YB_LBINS; ++k)
-                            if (cnt[YB_CNT_LBINS + k]) {
+                        for (uint32_t k = 0; k < YB_LGROUPS; ++k)
+                            if (gcount[k]) {
                                 const uint32_t lt = (k >> 1) / YB_LJOB_MCLASSES;
-                                groups.push_back(std::make_pair((uint64_t)cnt[YB_CNT_LBINS + k] * ((lt == LIGHT_POINT || lt == LIGHT_DIRECTIONAL) ? 1u : 8u), k));
+                                groups.push_back(std::make_pair((uint64_t)gcount[k] * ((lt == LIGHT_POINT || lt == LIGHT_DIRECTIONAL) ? 1u : 8u), k));
                             }
                         std::sort(groups.begin(), groups.end(), [](const std::pair<uint64_t, uint32_t> &x, const std::pair<uint64_t, uint32_t> &y) { return x.first > y.first; });
                         rb.sideStreams();
@@ -814,13 +829,13 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                                 st = rb.side[lane - 1];
                                 if (!used[lane - 1]) { YB_CUDA_CHECK(cudaStreamWaitEvent(st, rb.sideFork, 0)); used[lane - 1] = true; }
                             }
-                            launch_direct(k, gbase[k], cnt[YB_CNT_LBINS + k], a, st);
+                            launch_direct(k, gbase[k], gcount[k], a, st);
                         }
                         for (int i = 0; i < RenderBuffers::kSideStreams; ++i)
                             if (used[i]) { YB_CUDA_CHECK(cudaEventRecord(rb.sideDone[i], rb.side[i])); YB_CUDA_CHECK(cudaStreamWaitEvent(s, rb.sideDone[i], 0)); }
                     } else
 #endif
-                    for (uint32_t k = 0; k < YB_LBINS; ++k) launch_direct(k, gbase[k], cnt[YB_CNT_LBINS + k], a, s);
+                    for (uint32_t k = 0; k < YB_LGROUPS; ++k) launch_direct(k, gbase[k], gcount[k], a, s);
                 }
                 tsd.stop();
                 firstWave = false;

@@ -49,7 +49,9 @@ YB_D double scrHalton(int dim, uint32_t n)
     return value < 1.0e-36 ? 1.0e-36 : (value > 1.0 ? 1.0 : value);
 }
 
-// one direct-lighting estimate still to do: task index in the current wave, light index | group key << 24
+// one direct-lighting estimate still to do: task index in the current wave, light index | bin << 24 (bin = group key x 4 + slot of the
+// material within the group: jobs are ordered by bin, a group's kernel runs over its four bins at once - materials of one class still
+// take different branches (Blinn / anisotropic lobes, Lambert / Oren-Nayar), so a warp should see one material where it can)
 struct LightJob { uint32_t task, lightKey; };
 // group of a job: light type (LIGHT_POINT .. LIGHT_SPHERE; mesh lights run in the ext build, which is not staged) x material class
 // (0..2 = shinydiffuse / glossy / coated_glossy, the materials with eval / pdf bodies; 3 = everything else) x (trajectory split or not:
@@ -85,7 +87,7 @@ struct RenderArgs {
 };
 
 // slots of the per-wave counter block (RenderArgs::counters)
-enum { YB_CNT_TASKS = 0, YB_CNT_SHADOW = 1, YB_CNT_TRACE_A = 2, YB_CNT_TRACE_B = 3, YB_CNT_LJOBS = 4, YB_CNT_LBINS = 8, YB_LBINS = 64,
+enum { YB_CNT_TASKS = 0, YB_CNT_SHADOW = 1, YB_CNT_TRACE_A = 2, YB_CNT_TRACE_B = 3, YB_CNT_LJOBS = 4, YB_CNT_LBINS = 8, YB_LGROUPS = 64, YB_LBINS = 4 * YB_LGROUPS,
        YB_CNT_LCURSOR = YB_CNT_LBINS + YB_LBINS, YB_CNT_WORDS = YB_CNT_LCURSOR + YB_LBINS };
 
 // per-camera-sample identity (integrator.cc:251-273)
@@ -140,8 +142,9 @@ YB_D void push_task(const RenderArgs &a, const Task &t)
     a.out_tasks[i] = t;
 }
 
-YB_D void push_light_job(const RenderArgs &a, uint32_t task, uint32_t light, uint32_t key)
+YB_D void push_light_job(const RenderArgs &a, uint32_t task, uint32_t light, uint32_t key, const Material *mat)
 {
+    key = (key << 2) | ((uint32_t)(mat - a.sc.materials) & 3u);
     const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + YB_CNT_LJOBS, 1u);
     if (i >= a.ljobCap) return;                               // cannot happen: sized for (tasks of a wave) x (lights)
     LightJob j; j.task = task; j.lightKey = light | (key << 24);
