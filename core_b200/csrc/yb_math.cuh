@@ -266,6 +266,15 @@ YB_HD uint32_t fnv_32a_buf(uint32_t value)                                     /
 // mcqmc.h:29-94 — incremental Halton; FP64 state, getNext() advances THEN returns.
 // The base is a template parameter so the digit loop divides by a constant (mul-hi instead of a 30-instruction
 // runtime division); the FP64 operation sequence — and so every bit of the stream — is the reference's.
+// factor of digit k in HaltonT::setStart: invBase multiplied k times by invBase, in the same FP64 operations as the loop (a
+// compile-time constant wherever k is one)
+constexpr double halton_digit_factor(uint32_t base, int k)
+{
+    const double inv = 1.0 / (double)base;
+    double f = inv;
+    for (int j = 0; j < k; ++j) f *= inv;
+    return f;
+}
 template <uint32_t BASE> struct HaltonT {
     double mValue;
     YB_HD HaltonT() : mValue(0) {}
@@ -281,6 +290,22 @@ template <uint32_t BASE> struct HaltonT {
             r = ((r >> 8) & 0x00ff00ffu) | ((r & 0x00ff00ffu) << 8);
             r = (r >> 16) | (r << 16);
             mValue = (double)r * 2.3283064365386963e-10;   // 2^-32
+            return;
+        }
+        if (BASE == 3u) {
+            // same partial sums as the loop below, digit by digit: the factors are constants, digit * factor is exact (0, f, 2 f),
+            // adding a zero digit changes nothing - what is left per digit is one mul-hi division and one FP64 add
+            mValue = 0.0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int k = 0; k < 21; ++k) {                     // 3^21 > 2^32
+                if (i == 0u) break;
+                const uint32_t q = i / 3u, d = i - 3u * q;
+                const double f = halton_digit_factor(3u, k);
+                if (d) mValue += (d == 1u ? f : 2.0 * f);
+                i = q;
+            }
             return;
         }
         const double mInvBase = invBase();

@@ -649,13 +649,15 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
             rt_sync(s);
             rb.ownedOnDevice = (pixv == &owned);
         }
+        // staged direct lighting (yb_direct.cu): where tasks fan out (so that the host counts every wave anyway) and the base build shades
+        const bool stageDirect = F > 1 && !extShade && !nodeShade && !c.lights.empty() && env_size("YB200_STAGE_DIRECT", 1) != 0;
 #ifdef YB_HOSTEMU
         const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)512 << 20), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 16);
 #else
-        const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)24 << 30), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 22);
+        // camera samples per batch: 4 M; 8 M with staged direct lighting, whose waves are cut into one launch per job group and want to
+        // be longer (materials config, 1080p / 256 spp: 6.2 s per frame at 4 M, 5.9 s at 8 M, no change at 16 M)
+        const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)32 << 30), Bmax = env_size("YB200_BATCH_SAMPLES", stageDirect ? (size_t)1 << 23 : (size_t)1 << 22);
 #endif
-        // staged direct lighting (yb_direct.cu): where tasks fan out (so that the host counts every wave anyway) and the base build shades
-        const bool stageDirect = F > 1 && !extShade && !nodeShade && !c.lights.empty() && env_size("YB200_STAGE_DIRECT", 1) != 0;
         const size_t L = stageDirect ? c.lights.size() : 0;       // jobs per task: every light (integrate) or one (path vertex)
         const size_t perSample = (F + 1) * sizeof(Task) * 2 + S * sizeof(ShadowTask) + sizeof(Hit) + sizeof(f4) + 2 * L * sizeof(LightJob);
         size_t B = std::min<size_t>(Bmax, std::max<size_t>(1024, budget / perSample));

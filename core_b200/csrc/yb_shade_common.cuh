@@ -9,10 +9,17 @@ namespace yb {
 
 #if defined(__CUDACC__) && !defined(YB_HOSTEMU)
 #define YB_TABLE static __device__ __constant__
+#define YB_TABLE_DIVERGENT static __device__
 #else
 #define YB_TABLE static
+#define YB_TABLE_DIVERGENT static
 #endif
 #include "yb_faure.inc"
+#if defined(__CUDA_ARCH__)
+#define YB_LDG_U8(p) __ldg(p)
+#else
+#define YB_LDG_U8(p) (*(p))
+#endif
 
 #define YB_MIN_RAYDIST 0.00005f      // CMakeLists.txt:44
 #define YB_SHADOW_BIAS 0.0005f       // CMakeLists.txt:48
@@ -40,7 +47,7 @@ YB_D double scrHalton(int dim, uint32_t n)
             // n % base without a runtime division: the mul-hi quotient is exact or one too large
             uint32_t r = n - yb_umulhi(n, magic) * base;
             if ((int32_t)r < 0) r += base;
-            value += (double)sigma[r] * factor;
+            value += (double)YB_LDG_U8(sigma + r) * factor;
             dn *= f;
             n = (uint32_t)dn;
             factor *= f;
@@ -142,13 +149,16 @@ YB_D void push_task(const RenderArgs &a, const Task &t)
     a.out_tasks[i] = t;
 }
 
-YB_D void push_light_job(const RenderArgs &a, uint32_t task, uint32_t light, uint32_t key, const Material *mat)
+YB_D void put_light_job(const RenderArgs &a, uint32_t i, uint32_t task, uint32_t light, uint32_t key, const Material *mat)
 {
     key = (key << 2) | ((uint32_t)(mat - a.sc.materials) & 3u);
-    const uint32_t i = YB_ATOMIC_ADD_U32(a.counters + YB_CNT_LJOBS, 1u);
     if (i >= a.ljobCap) return;                               // cannot happen: sized for (tasks of a wave) x (lights)
     LightJob j; j.task = task; j.lightKey = light | (key << 24);
     a.ljobs[i] = j;
+}
+YB_D void push_light_job(const RenderArgs &a, uint32_t task, uint32_t light, uint32_t key, const Material *mat)
+{
+    put_light_job(a, YB_ATOMIC_ADD_U32(a.counters + YB_CNT_LJOBS, 1u), task, light, key, mat);
 }
 
 // the light estimateOneDirectLight picks for path sample n (mcintegrator.cc:62-66)
