@@ -650,7 +650,9 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
             rb.ownedOnDevice = (pixv == &owned);
         }
         // staged direct lighting (yb_direct.cu): where tasks fan out (so that the host counts every wave anyway) and the base build shades
-        const bool stageDirect = F > 1 && !extShade && !nodeShade && !c.lights.empty() && env_size("YB200_STAGE_DIRECT", 1) != 0;
+        // (YB200_STAGE_DIRECT = 0: never, 2: also without fan-out - the waves are then counted by the host)
+        const size_t stageKnob = env_size("YB200_STAGE_DIRECT", 1);
+        const bool stageDirect = (F > 1 || stageKnob == 2) && !extShade && !nodeShade && !c.lights.empty() && stageKnob != 0;
 #ifdef YB_HOSTEMU
         const size_t budget = env_size("YB200_QUEUE_BYTES", (size_t)512 << 20), Bmax = env_size("YB200_BATCH_SAMPLES", (size_t)1 << 16);
 #else
