@@ -140,7 +140,6 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
     uint2 ng = make_uint2(0, 0);      // node group: x = child base, y = ordered hit bits << 24 | imask
     uint2 tg = make_uint2(0, 0);      // triangle group: x = triangle base, y = hit bits (0..23)
     int hitTri = -1; float hitT = 0, hitU = 0, hitV = 0;
-    bool tgFresh = false;
     constexpr bool TSHADOW = (OUT == OUT_TSHADOW_ACC || OUT == OUT_TSHADOW_RES);
     float filtR = 1.f, filtG = 1.f, filtB = 1.f; int tsDepth = 0;      // transparent shadows: filter colour so far, transparent hits so far
 
@@ -200,17 +199,23 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
 #pragma unroll 1
         for (int burst = 0; burst < (int)job.burst; ++burst) {
             bool done = false;
-            // ---- node phase: lanes without pending triangles pop / descend one node
-            if (active && tg.y == 0u) {
-                if (ng.y <= 0x00ffffffu) {                  // current node group exhausted: pop
-                    if (sp == 0) done = true;
-                    else {
-                        --sp;
-                        const uint2 e = (sp < YB_SSTACK) ? sstack[sp][threadIdx.x] : lstack[sp - YB_SSTACK];
-                        if (e.y > 0x00ffffffu) ng = e; else { tg = e; ng.y = 0u; }
-                    }
+            // ---- node phase: every lane that has a node to visit descends one node - also while it still holds triangles of an
+            //      earlier leaf (those are tested in the triangle phase of the same round, so a lane advances on both fronts per
+            //      round instead of sitting out the node step once per triangle; triangles found meanwhile are parked on the stack).
+            //      Closest hit: a parked triangle is tested a little later than in strict order, i.e. against a `thi` that can only
+            //      be smaller - the result is the same, a few more nodes are visited.
+            bool progressed = false;
+            if (active) {
+                // current node group exhausted: take the next one from the stack; parked triangle groups above it are picked up on the
+                // way if this lane holds none (otherwise they stay and this round is a triangle step only)
+                while (ng.y <= 0x00ffffffu && sp > 0) {
+                    const uint2 e = (sp - 1 < YB_SSTACK) ? sstack[sp - 1][threadIdx.x] : lstack[sp - 1 - YB_SSTACK];
+                    if (e.y > 0x00ffffffu) { ng = e; --sp; }
+                    else if (tg.y == 0u) { tg = e; --sp; progressed = true; }
+                    else break;
                 }
-                if (!done && tg.y == 0u) {
+                if (ng.y > 0x00ffffffu) {
+                    progressed = true;
                     const int bit = 31 - __clz((int)ng.y);
                     ng.y &= ~(1u << bit);
                     if (ng.y > 0x00ffffffu) {               // siblings still pending: push the rest of the group
@@ -262,20 +267,21 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                         }
                     }
                     ng = make_uint2(n1.x, (hitmask & 0xff000000u) | (n0.w >> 24));
-                    tg = make_uint2(n1.y, hitmask & 0x00ffffffu);
-                    tgFresh = true;
+                    const uint2 tnew = make_uint2(n1.y, hitmask & 0x00ffffffu);
+                    if (tnew.y != 0u) {
+                        if (tg.y == 0u) tg = tnew;
+                        else { if (sp < YB_SSTACK) sstack[sp][threadIdx.x] = tnew; else lstack[sp - YB_SSTACK] = tnew; ++sp; }
+                    }
                 }
             }
-            // ---- triangle phase (warp-synchronous, postponed): every lane holding a triangle group tests ONE triangle,
-            //      but only when enough of the warp holds one (or nobody has node work left).  Otherwise a lane whose
-            //      group is fresh from the node step parks it on its stack and keeps descending (Ylitie et al. 2017,
-            //      "triangle postponing"); a group that came back from the stack just waits for the next pass.
+            // ---- triangle phase (warp-synchronous): every lane holding a triangle group tests ONE triangle.  With a threshold above
+            //      one (YB200_TRI_THRESHOLD) the phase waits until that many lanes hold a group or no lane could advance on its nodes.
             const bool hasTri = active && !done && tg.y != 0u;
             const unsigned triMask = __ballot_sync(FULL, hasTri);
             if (triMask != 0u) {
-                const unsigned nodeMask = __ballot_sync(FULL, active && !done && tg.y == 0u);
-                const int nT = __popc(triMask), nN = __popc(nodeMask);
-                if (nT >= (nN < (int)job.triThreshold ? nN : (int)job.triThreshold)) {
+                bool run = true;
+                if (job.triThreshold > 1u) run = __popc(triMask) >= (int)job.triThreshold || __ballot_sync(FULL, progressed && !hasTri) == 0u;
+                if (run) {
                     if (hasTri) {
                         const int tb = 31 - __clz((int)tg.y);
                         tg.y &= ~(1u << tb);
@@ -302,13 +308,10 @@ __global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
                             else { thi = t; hitTri = (int)ti; hitT = t; hitU = u; hitV = v; }
                         }
                     }
-                } else if (hasTri && tgFresh) {
-                    if (sp < YB_SSTACK) sstack[sp][threadIdx.x] = tg; else lstack[sp - YB_SSTACK] = tg;
-                    ++sp;
-                    tg.y = 0u;
                 }
             }
-            tgFresh = false;
+            // nothing left on any front: the ray ends in this round (not in the node phase of the next one)
+            if (active && ng.y <= 0x00ffffffu && sp == 0 && tg.y == 0u) done = true;
             if (done) {
                 active = false;
                 if (OUT == OUT_HITS) ((float4 *)job.out)[rayIdx] = make_float4(__int_as_float(hitTri), hitT, hitU, hitV);
