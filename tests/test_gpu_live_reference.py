@@ -53,9 +53,15 @@ def _check_frames(a, s, b, tag, strict_bar=(1e-5, 85.0), release_bar=(2e-4, 50.0
         rel3, psnr3, _ = cases.compare_images(s, a)
         msg += "; vs strict build rel %.2e psnr %.1f dB, %.2f %% off (the two builds of the reference between themselves: %.2e, %.1f dB)" % (
             rs[0], rs[1], 100 * rs[3], rel3, psnr3)
+    # alpha: exact against the strict build; against the release build as far as the reference's two builds agree with each other
+    # (50 M-triangle terrain: one camera sample of the -ffast-math build slips between two sub-pixel triangles, alpha 6/7 in that pixel)
+    alpha_bar = 1e-5
+    if s is not None:
+        alpha_bar += float(np.abs(s[..., 3].astype(np.float64) - a[..., 3]).max())
+        msg += "; alpha: vs release %.3g, vs strict %.3g, release vs strict %.3g" % (ra[2], rs[2], alpha_bar - 1e-5)
     print(msg)
     assert np.isfinite(b).all()
-    assert ra[0] <= release_bar[0] and ra[1] >= release_bar[1] and ra[2] <= 1e-5 and ra[3] <= release_bar[2], msg
+    assert ra[0] <= release_bar[0] and ra[1] >= release_bar[1] and ra[2] <= alpha_bar and ra[3] <= release_bar[2], msg
     if rs is not None:
         assert rs[0] <= strict_bar[0] and rs[1] >= strict_bar[1] and rs[2] <= 1e-5, msg
 
