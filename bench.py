@@ -427,7 +427,7 @@ def main():
     roofline["dependent_fetch_rounds"] = R
     if t_miss:
         roofline["latency_bound_grays"] = 148 * 64 * 32 / (R * t_miss * 1e-9) / 1e9          # all 64 warps per SM resident
-        roofline["latency_bound_grays_at_kernel_occupancy"] = 148 * 6 * 128 / (R * t_miss * 1e-9) / 1e9   # k_trace_fast: 6 x 128 threads per SM
+        roofline["latency_bound_grays_at_kernel_occupancy"] = 148 * 8 * 128 / (R * t_miss * 1e-9) / 1e9   # k_trace_fast: 8 x 128 threads per SM (YB_TRACE_CTAS)
     roofline["hbm_bound_grays"] = peak / A
     ifiles = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if "trace_inst" in f and f.endswith(".json"))
     if ifiles and args.workload == "c2_field_1M_1080p_64spp":

@@ -76,6 +76,9 @@ namespace yb {
 #define YB_SSTACK 8          // shared-memory stack entries per lane
 #define YB_LSTACK (YB_STACK_SIZE - YB_SSTACK)
 #define YB_REFILL_IDLE 8     // refill when at least this many lanes are idle (or all are)
+#ifndef YB_TRACE_CTAS
+#define YB_TRACE_CTAS 8      // resident CTAs per SM the kernel is compiled for (8 x 128 threads: 64 registers, no spills)
+#endif
 
 #if defined(YB_HOSTEMU) && defined(YB_TRACE_STATS)
 static uint64_t g_stat_nodes = 0, g_stat_tris = 0, g_stat_rays = 0;
@@ -128,7 +131,7 @@ __device__ __forceinline__ float plane_f(uint32_t w, uint32_t one, uint32_t sel)
 #define ANYHIT_WAITS 1
 #endif
 template <bool ANYHIT, int OUT, bool SORTED>
-__global__ void __launch_bounds__(YB_TB, 6) k_trace_fast(const FastJob job)
+__global__ void __launch_bounds__(YB_TB, YB_TRACE_CTAS) k_trace_fast(const FastJob job)
 {
     __shared__ uint2 sstack[YB_SSTACK][YB_TB];
     uint2 lstack[YB_LSTACK];
@@ -353,7 +356,7 @@ static void launch_trace_fast(const FastJob &job, rt_stream s)
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    uint32_t blocks = (uint32_t)sms * 6u;
+    uint32_t blocks = (uint32_t)sms * (uint32_t)YB_TRACE_CTAS;
     const uint32_t need = (job.n + YB_TB - 1) / YB_TB;
     if (blocks > need) blocks = need;
     if (job.order) k_trace_fast<ANYHIT, OUT, true><<<blocks, YB_TB, 0, s>>>(job);
