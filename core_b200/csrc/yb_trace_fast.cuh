@@ -73,7 +73,9 @@ static yb::emu::tidx_ threadIdx = {0};
 
 namespace yb {
 
+#ifndef YB_SSTACK
 #define YB_SSTACK 8          // shared-memory stack entries per lane
+#endif
 #define YB_LSTACK (YB_STACK_SIZE - YB_SSTACK)
 #define YB_REFILL_IDLE 8     // refill when at least this many lanes are idle (or all are)
 #ifndef YB_TRACE_CTAS
