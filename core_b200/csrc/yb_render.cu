@@ -679,6 +679,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         const bool filmFast = env_size("YB200_FILM_FAST", 1) != 0;       // warp-aggregated film splat (k_film_fast_kernel)
         (void)filmFast;      // also bin the camera wave (pixel order is already coherent)
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
+        const bool kindShade = env_size("YB200_KIND_SHADE", 1) != 0;           // device-counted waves: shade kernel compiled for the wave's kind of task
         const bool sideStreams = env_size("YB200_SIDE_STREAMS", 1) != 0;       // staged direct lighting: groups of a wave on several streams
         (void)sideStreams;
         // coherence sort of the ray waves: 0 off, 1 closest-hit waves after the camera wave, 2 + shadow waves after the first, 3 all
@@ -710,6 +711,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
             //      (160 waves per frame of the benchmark scene).
             if (deviceWaves) {
                 uint32_t pending = nb;
+                bool firstWaveOfBatch = true;      // the chain of waves below starts with the camera wave only in its first round
                 while (pending > 0) {
                     const size_t nSlots = (size_t)maxChain + 1;
                     rb.waveCnt.reserve(4 * nSlots);
@@ -733,8 +735,12 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
 #endif
                         a.order = 0;
                         if (binShade && (!firstWave || binFirst)) { bin_tasks(pending, a, s); a.order = rb.order.p; }
+                        // without fan-out a wave holds one kind of task: the camera wave integrate() calls, the later ones path vertices
+                        // (pathtracing) or the integrate() calls of the one specular child (directlighting)
+                        const uint32_t waveKind = (firstWaveOfBatch && w == 0) ? (uint32_t)TASK_INTEGRATE : (I.type == INTEG_PATH ? (uint32_t)TASK_PATH : (uint32_t)TASK_INTEGRATE);
                         if (nodeShade) launch_shade_nodes(pending, a, s);
                         else if (extShade) launch_shade_ext(pending, a, s);
+                        else if (kindShade) launch_shade_base_kind(waveKind, pending, a, s);
                         else launch_shade_base(pending, a, s);
                         if (gatherCaustics) launch_caustic_gather(pending, a, s);
 #ifndef YB_HOSTEMU
@@ -769,6 +775,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
 #endif
                     }
                     pending = hc[4 * (size_t)maxChain];      // tasks still alive after maxChain waves (none unless the bound below is too low)
+                    firstWaveOfBatch = false;
                 }
                 top = 0;
                 a.nPtr = 0; a.counters = rb.counters.p;
