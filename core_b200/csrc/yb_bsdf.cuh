@@ -881,19 +881,20 @@ template <int FIX = -1> YB_HD float leaf_pdf(const Material &m, const MatDat &d,
         default: return 0.f;
     }
 }
-YB_HD col3 leaf_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
+template <int FIX = -1> YB_HD col3 leaf_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
 {
-    if (m.type == MAT_SHINYDIFFUSE) return m.emitColor;                 // shinydiffuse.cc:251-257
-    if (m.type == MAT_LIGHT) {                                          // simple.cc:63-70
+    const int ty = FIX >= 0 ? FIX : m.type;
+    if (ty == MAT_SHINYDIFFUSE) return m.emitColor;                     // shinydiffuse.cc:251-257
+    if (ty == MAT_LIGHT) {                                          // simple.cc:63-70
         if (!includeLights) return col3(0.f);
         if (m.doubleSided) return m.lightCol;
         return (dot(wo, sp.N) > 0) ? m.lightCol : col3(0.f);
     }
     return col3(0.f);
 }
-YB_HD void leaf_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
+template <int FIX = -1> YB_HD void leaf_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
 {
-    switch (m.type) {
+    switch (FIX >= 0 ? FIX : m.type) {
         case MAT_SHINYDIFFUSE: sd_getSpecular(m, d, sp, wo, refl, refr, dir, col); break;
         case MAT_COATED_GLOSSY: cg_getSpecular(m, sp, wo, raylevel, refl, refr, dir, col); break;
         case MAT_GLASS: glass_getSpecular(m, sp, wo, raylevel, refl, refr, dir, col); break;
@@ -919,15 +920,16 @@ YB_HD col3 leaf_getTransparency(const Material &m, const Surf &sp, v3 wo)
     if (m.type == MAT_GLASS || m.type == MAT_ROUGH_GLASS) return glass_getTransparency(m, sp, wo);   // roughglass.cc:238-244 is the same formula
     return col3(0.f);
 }
-YB_HD float leaf_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
+template <int FIX = -1> YB_HD float leaf_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
 {
-    if (m.type == MAT_SHINYDIFFUSE) return sd_getAlpha(m, d, sp, wo);
-    if (m.type == MAT_GLASS) {                                          // glass.cc:198-202
+    const int ty = FIX >= 0 ? FIX : m.type;
+    if (ty == MAT_SHINYDIFFUSE) return sd_getAlpha(m, d, sp, wo);
+    if (ty == MAT_GLASS) {                                          // glass.cc:198-202
         float alpha = (float)(1.0 - col_energy(glass_getTransparency(m, sp, wo)));
         if (alpha < 0.0f) alpha = 0.0f;
         return alpha;
     }
-    if (m.type == MAT_ROUGH_GLASS)                                      // roughglass.cc:246-250
+    if (ty == MAT_ROUGH_GLASS)                                          // roughglass.cc:246-250
         return fmaxf_(0.f, fminf_(1.f, 1.f - col_energy(glass_getTransparency(m, sp, wo))));
     return 1.f;
 }
@@ -1005,16 +1007,16 @@ template <int EXT, int FIX = -1> YB_HD float mat_pdf(const Material &m, const Ma
     float pdf1 = leaf_pdf(blend_m1(m), d1, sp, wo, wi, bsdfs), pdf2 = leaf_pdf(blend_m2(m), d2, sp, wo, wi, bsdfs);
     return pdf1 * ival + pdf2 * val;
 }
-template <int EXT> YB_HD col3 mat_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
+template <int EXT, int FIX = -1> YB_HD col3 mat_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
 {
-    if (!EXT || m.type != MAT_BLEND) return leaf_emit(m, sp, wo, includeLights);
+    if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_emit<FIX>(m, sp, wo, includeLights);
     const float val = m.blendVal, ival = blend_ival(val);
     col3 col1 = leaf_emit(blend_m1(m), sp, wo, includeLights), col2 = leaf_emit(blend_m2(m), sp, wo, includeLights);
     return col1 * ival + col2 * val;
 }
-template <int EXT> YB_HD void mat_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
+template <int EXT, int FIX = -1> YB_HD void mat_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
 {
-    if (!EXT || m.type != MAT_BLEND) { leaf_getSpecular(m, d, sp, wo, raylevel, refl, refr, dir, col); return; }
+    if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) { leaf_getSpecular<FIX>(m, d, sp, wo, raylevel, refl, refr, dir, col); return; }
     const float val = m.blendVal, ival = blend_ival(val);
     refl = false; refr = false;
     bool m1_refl = false, m1_refr = false;
@@ -1046,9 +1048,9 @@ template <int EXT> YB_HD col3 mat_getTransparency(const Material &m, const Surf 
     col3 col1 = leaf_getTransparency(blend_m1(m), sp, wo), col2 = leaf_getTransparency(blend_m2(m), sp, wo);
     return col1 * ival + col2 * val;
 }
-template <int EXT> YB_HD float mat_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
+template <int EXT, int FIX = -1> YB_HD float mat_getAlpha(const Material &m, const MatDat &d, const Surf &sp, v3 wo)
 {
-    if (!EXT || m.type != MAT_BLEND) return leaf_getAlpha(m, d, sp, wo);
+    if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_getAlpha<FIX>(m, d, sp, wo);
     if (!mat_isTransparent<EXT>(m)) return 1.f;
     MatDat d1, d2; uint32_t f;
     leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);

@@ -577,9 +577,10 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                 }
         }
         // ---- worst-case fan-out per task, from the integrator and the materials present
-        bool anyGlossy = false, anyRoughGlass = false, extShade = false, nodeShade = false; int specChildren = 0;
+        bool anyGlossy = false, anyRoughGlass = false, extShade = false, nodeShade = false, allShinyDiffuse = !c.materials.empty(); int specChildren = 0;
         for (size_t i = 0; i < c.materials.size(); ++i) {
             const Material &m = c.materials[i];
+            if (m.type != MAT_SHINYDIFFUSE) allShinyDiffuse = false;
             if (m.bsdfFlags & BSDF_GLOSSY) anyGlossy = true;
             if (m.type == MAT_ROUGH_GLASS) anyRoughGlass = true;     // two children per glossy sample
             if (m.type == MAT_ROUGH_GLASS || m.type == MAT_BLEND) extShade = true;
@@ -740,6 +741,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
                         const uint32_t waveKind = (firstWaveOfBatch && w == 0) ? (uint32_t)TASK_INTEGRATE : (I.type == INTEG_PATH ? (uint32_t)TASK_PATH : (uint32_t)TASK_INTEGRATE);
                         if (nodeShade) launch_shade_nodes(pending, a, s);
                         else if (extShade) launch_shade_ext(pending, a, s);
+                        else if (kindShade && allShinyDiffuse) launch_shade_sd_kind(waveKind, pending, a, s);
                         else if (kindShade) launch_shade_base_kind(waveKind, pending, a, s);
                         else launch_shade_base(pending, a, s);
                         if (gatherCaustics) launch_caustic_gather(pending, a, s);

@@ -179,6 +179,8 @@ void launch_shade_ext(uint32_t n, const RenderArgs &a, rt_stream s);
 void launch_shade_nodes(uint32_t n, const RenderArgs &a, rt_stream s);
 // the base build for waves that hold one kind of task only (kind = TASK_INTEGRATE / TASK_PATH): half the kernel each
 void launch_shade_base_kind(uint32_t kind, uint32_t n, const RenderArgs &a, rt_stream s);
+// the same for scenes whose materials are all shinydiffuse (material dispatch folded)
+void launch_shade_sd_kind(uint32_t kind, uint32_t n, const RenderArgs &a, rt_stream s);
 // staged form of the base build: launch_shade_staged queues the direct-lighting estimates, launch_direct evaluates the n jobs
 // of one (light type, material class) group that start at ljobsSorted[base]
 void launch_shade_staged(uint32_t n, const RenderArgs &a, rt_stream s);
