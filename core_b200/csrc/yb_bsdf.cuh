@@ -147,59 +147,67 @@ YB_HD col3 sd_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, 
     float Kr;
     sd_getFresnel(m, wo, N, Kr);
     sd_accumulate(d.c, accumC, Kr);
-    float sum = 0.f, val[4], width[4];
-    uint32_t choice[4];
-    int nMatch = 0, pick = -1;
-    for (int i = 0; i < m.nBSDF; ++i) {
-        if ((s.flags & m.cFlags[i]) == m.cFlags[i]) {
-            width[nMatch] = accumC[m.cIndex[i]];
-            sum += width[nMatch];
-            choice[nMatch] = m.cFlags[i];
-            val[nMatch] = sum;
-            ++nMatch;
-        }
-    }
+    // component list of shinyDiffuseMat_t::sample (shinydiffuse.cc:268-296), walked in its fixed order (mirror, transparency,
+    // translucency, diffuse: cFlags / cIndex are filled in that order) with static indices: the same partial sums, the same
+    // normalisation and the same pick as the arrays val[] / width[] / choice[] of the reference, kept in registers
+    const uint32_t CF[4] = {BSDF_SPECULAR | BSDF_REFLECT, BSDF_TRANSMIT | BSDF_FILTER, BSDF_DIFFUSE | BSDF_TRANSMIT, BSDF_DIFFUSE | BSDF_REFLECT};
+    const bool on[4] = {m.isMirror && (s.flags & CF[0]) == CF[0], m.isTransparent && (s.flags & CF[1]) == CF[1],
+                        m.isTranslucent && (s.flags & CF[2]) == CF[2], m.isDiffuse && (s.flags & CF[3]) == CF[3]};
+    float sum = 0.f, val[4] = {0.f, 0.f, 0.f, 0.f};
+    int nMatch = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int c = 0; c < 4; ++c)
+        if (on[c]) { sum += accumC[c]; val[c] = sum; ++nMatch; }
     if (!nMatch || sum < 0.00001) { s.sampledFlags = BSDF_NONE; s.pdf = 0.f; return col3(1.f); }
     float inv_sum = 1.f / sum;
-    for (int i = 0; i < nMatch; ++i) {
-        val[i] *= inv_sum;
-        width[i] *= inv_sum;
-        if ((s.s1 <= val[i]) && (pick < 0)) pick = i;
-    }
-    if (pick < 0) pick = nMatch - 1;
+    int pc = -1, lastOn = 0;
+    float wPick = 0.f, prevPick = 0.f, lastW = 0.f, lastPrev = 0.f, runPrev = 0.f;
+    bool hasPrevPick = false, lastHasPrev = false, anyPrev = false;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int c = 0; c < 4; ++c)
+        if (on[c]) {
+            const float vN = val[c] * inv_sum, wN = accumC[c] * inv_sum;
+            if (pc < 0 && s.s1 <= vN) { pc = c; wPick = wN; prevPick = runPrev; hasPrevPick = anyPrev; }
+            lastOn = c; lastW = wN; lastPrev = runPrev; lastHasPrev = anyPrev;
+            runPrev = vN; anyPrev = true;
+        }
+    if (pc < 0) { pc = lastOn; wPick = lastW; prevPick = lastPrev; hasPrevPick = lastHasPrev; }
     float s1;
-    if (pick > 0) s1 = (s.s1 - val[pick - 1]) / width[pick];
-    else s1 = s.s1 / width[pick];
+    if (hasPrevPick) s1 = (s.s1 - prevPick) / wPick;
+    else s1 = s.s1 / wPick;
     col3 scolor(0.f);
-    switch (choice[pick]) {
-        case (BSDF_SPECULAR | BSDF_REFLECT):
+    switch (pc) {
+        case 0:         // BSDF_SPECULAR | BSDF_REFLECT
             wi = reflect_dir(N, wo);
-            s.pdf = width[pick];
+            s.pdf = wPick;
             scolor = m.mirrorColor * accumC[0];
             scolor *= 1.f / fabsf(dot(sp.N, wi));
             break;
-        case (BSDF_TRANSMIT | BSDF_FILTER):
+        case 1:         // BSDF_TRANSMIT | BSDF_FILTER
             wi = -wo;
             scolor = accumC[1] * (m.transmitFilterStrength * m.diffuseColor + col3(1.f - m.transmitFilterStrength));
             cos_N = fabsf(dot(wi, N));
-            if (cos_N < 1e-6) s.pdf = 0.f; else s.pdf = width[pick];
+            if (cos_N < 1e-6) s.pdf = 0.f; else s.pdf = wPick;
             break;
-        case (BSDF_DIFFUSE | BSDF_TRANSMIT):
+        case 2:         // BSDF_DIFFUSE | BSDF_TRANSMIT
             wi = SampleCosHemisphere(-N, sp.NU, sp.NV, s1, s.s2);
             cos_Ng_wi = dot(sp.Ng, wi);
             if (cos_Ng_wo * cos_Ng_wi < 0) scolor = accumC[2] * m.diffuseColor;
-            s.pdf = fabsf(dot(wi, N)) * width[pick];
+            s.pdf = fabsf(dot(wi, N)) * wPick;
             break;
-        case (BSDF_DIFFUSE | BSDF_REFLECT):
-        default:
+        default:        // BSDF_DIFFUSE | BSDF_REFLECT
             wi = SampleCosHemisphere(N, sp.NU, sp.NV, s1, s.s2);
             cos_Ng_wi = dot(sp.Ng, wi);
             if (cos_Ng_wo * cos_Ng_wi > 0) scolor = accumC[3] * m.diffuseColor;
             if (m.useOrenNayar) scolor *= sd_OrenNayar(m, wo, wi, N);
-            s.pdf = fabsf(dot(wi, N)) * width[pick];
+            s.pdf = fabsf(dot(wi, N)) * wPick;
             break;
     }
-    s.sampledFlags = choice[pick];
+    s.sampledFlags = pc == 0 ? CF[0] : (pc == 1 ? CF[1] : (pc == 2 ? CF[2] : CF[3]));
     W = fabsf(dot(wi, sp.N)) / (s.pdf * 0.99f + 0.01f);
     return scolor;
 }
@@ -212,23 +220,23 @@ YB_HD float sd_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3
     float Kr;
     sd_getFresnel(m, wo, N, Kr);
     sd_accumulate(d.c, accumC, Kr);
+    // the component list in its fixed order (see sd_sample), static indices
     float sum = 0.f, width;
     int nMatch = 0;
-    for (int i = 0; i < m.nBSDF; ++i) {
-        if (bsdfs & m.cFlags[i]) {
-            width = accumC[m.cIndex[i]];
-            sum += width;
-            switch (m.cFlags[i]) {
-                case (BSDF_DIFFUSE | BSDF_TRANSMIT):
-                    cos_Ng_wi = dot(sp.Ng, wi);
-                    if (cos_Ng_wo * cos_Ng_wi < 0) pdf += fabsf(dot(wi, N)) * width;
-                    break;
-                case (BSDF_DIFFUSE | BSDF_REFLECT):
-                    pdf += fabsf(dot(wi, N)) * width;
-                    break;
-            }
-            ++nMatch;
-        }
+    if (m.isMirror && (bsdfs & (BSDF_SPECULAR | BSDF_REFLECT))) { sum += accumC[0]; ++nMatch; }
+    if (m.isTransparent && (bsdfs & (BSDF_TRANSMIT | BSDF_FILTER))) { sum += accumC[1]; ++nMatch; }
+    if (m.isTranslucent && (bsdfs & (BSDF_DIFFUSE | BSDF_TRANSMIT))) {
+        width = accumC[2];
+        sum += width;
+        cos_Ng_wi = dot(sp.Ng, wi);
+        if (cos_Ng_wo * cos_Ng_wi < 0) pdf += fabsf(dot(wi, N)) * width;
+        ++nMatch;
+    }
+    if (m.isDiffuse && (bsdfs & (BSDF_DIFFUSE | BSDF_REFLECT))) {
+        width = accumC[3];
+        sum += width;
+        pdf += fabsf(dot(wi, N)) * width;
+        ++nMatch;
     }
     if (!nMatch || sum < 0.00001) return 0.f;
     return pdf / sum;
