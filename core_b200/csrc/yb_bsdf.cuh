@@ -474,45 +474,58 @@ YB_HD col3 cg_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, 
     s.pdf = 0.f;
     float Kr, Kt, wiN = 0.f, woN = 0.f;
     fresnel(wo, N, m.ior, Kr, Kt);
-    bool use[3] = {false, false, false};
-    float sum = 0.f, accumC[3], val[3], width[3];
-    int cIndex[3] = {0, 0, 0}, rcIndex[3] = {0, 0, 0};
+    // component list of coatedGlossyMat_t::sample (coatedglossy.cc:213-252) in its fixed order (specular, glossy, diffuse) with static
+    // indices: the same partial sums, normalisation (none when a single component matches: width 1) and pick as the reference's
+    // arrays val[] / width[] / cIndex[] / rcIndex[], kept in registers; wN[i] = normalised width of component i
+    float accumC[3];
     accumC[0] = Kr;
     accumC[1] = Kt * (1.f - d.c[2]);
     accumC[2] = Kt * (d.c[2]);
-    int nMatch = 0, pick = -1;
-    for (int i = 0; i < m.nBSDF; ++i) {
-        if ((s.flags & m.cFlags[i]) == m.cFlags[i]) {
-            use[i] = true;
-            width[nMatch] = accumC[i];
-            cIndex[nMatch] = i;
-            rcIndex[i] = nMatch;
-            sum += width[nMatch];
-            val[nMatch] = sum;
-            ++nMatch;
-        }
-    }
+    const bool use[3] = {m.nBSDF > 0 && (s.flags & m.cFlags[0]) == m.cFlags[0], m.nBSDF > 1 && (s.flags & m.cFlags[1]) == m.cFlags[1],
+                         m.nBSDF > 2 && (s.flags & m.cFlags[2]) == m.cFlags[2]};
+    float sum = 0.f, val[3] = {0.f, 0.f, 0.f}, wN[3] = {0.f, 0.f, 0.f};
+    int nMatch = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int i = 0; i < 3; ++i)
+        if (use[i]) { sum += accumC[i]; val[i] = sum; ++nMatch; }
     if (!nMatch || sum < 0.00001) return col3(0.f);
-    else if (nMatch == 1) { pick = 0; width[0] = 1.f; }
-    else {
+    int pc = -1, lastOn = 0;
+    float wPick = 0.f, prevPick = 0.f, lastW = 0.f, lastPrev = 0.f, runPrev = 0.f;
+    bool hasPrevPick = false, lastHasPrev = false, anyPrev = false;
+    if (nMatch == 1) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int i = 0; i < 3; ++i)
+            if (use[i]) { pc = i; wN[i] = 1.f; }
+        wPick = 1.f;
+    } else {
         float inv_sum = 1.f / sum;
-        for (int i = 0; i < nMatch; ++i) {
-            val[i] *= inv_sum;
-            width[i] *= inv_sum;
-            if ((s.s1 <= val[i]) && (pick < 0)) pick = i;
-        }
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int i = 0; i < 3; ++i)
+            if (use[i]) {
+                const float vN = val[i] * inv_sum;
+                wN[i] = accumC[i] * inv_sum;
+                if (pc < 0 && s.s1 <= vN) { pc = i; wPick = wN[i]; prevPick = runPrev; hasPrevPick = anyPrev; }
+                lastOn = i; lastW = wN[i]; lastPrev = runPrev; lastHasPrev = anyPrev;
+                runPrev = vN; anyPrev = true;
+            }
+        if (pc < 0) { pc = lastOn; wPick = lastW; prevPick = lastPrev; hasPrevPick = lastHasPrev; }
     }
-    if (pick < 0) pick = nMatch - 1;
     float s1;
-    if (pick > 0) s1 = (s.s1 - val[pick - 1]) / width[pick];
-    else s1 = s.s1 / width[pick];
+    if (hasPrevPick) s1 = (s.s1 - prevPick) / wPick;
+    else s1 = s.s1 / wPick;
     col3 scolor(0.f);
     wi = v3(0.f);   // reference reads an uninitialised wi for the glossy pick before overwriting wiN; value unused
-    switch (cIndex[pick]) {
+    switch (pc) {
         case YB_C_SPECULAR:
             wi = reflect_dir(N, wo);
             scolor = m.mirrorColor * Kr;
-            s.pdf = width[pick];
+            s.pdf = wPick;
             break;
         case YB_C_GLOSSY:
             if (m.anisotropic) AS_Aniso_Sample(Hs, s1, s.s2, m.expU, m.expV);
@@ -526,11 +539,11 @@ YB_HD col3 cg_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, 
     }
     wiN = fabsf(dot(wi, N));
     woN = fabsf(dot(wo, N));
-    if (cIndex[pick] != YB_C_SPECULAR) {
+    if (pc != YB_C_SPECULAR) {
         if (use[YB_C_GLOSSY]) {
             float glossy, cos_wo_H;
             v3 H(0.f);
-            if (cIndex[pick] != YB_C_GLOSSY) {
+            if (pc != YB_C_GLOSSY) {
                 H = normalize(wi + wo);
                 Hs = v3(dot(H, sp.NU), dot(H, sp.NV), dot(H, N));
                 cos_wo_H = dot(wo, H);
@@ -544,22 +557,22 @@ YB_HD col3 cg_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, 
             }
             wiN = fabsf(dot(wi, N));
             if (m.anisotropic) {
-                s.pdf += AS_Aniso_Pdf(Hs, cos_wo_H, m.expU, m.expV) * width[rcIndex[YB_C_GLOSSY]];
+                s.pdf += AS_Aniso_Pdf(Hs, cos_wo_H, m.expU, m.expV) * wN[YB_C_GLOSSY];
                 glossy = AS_Aniso_D(Hs, m.expU, m.expV) * SchlickFresnel(cos_wo_H, d.c[1]) / ASDivisor(cos_wo_H, woN, wiN);
             } else {
                 float cosHN = dot(H, N);
-                s.pdf += Blinn_Pdf(cosHN, cos_wo_H, m.exponent) * width[rcIndex[YB_C_GLOSSY]];
+                s.pdf += Blinn_Pdf(cosHN, cos_wo_H, m.exponent) * wN[YB_C_GLOSSY];
                 glossy = Blinn_D(cosHN, m.exponent) * SchlickFresnel(cos_wo_H, d.c[1]) / ASDivisor(cos_wo_H, woN, wiN);
             }
             scolor = (glossy * Kt) * m.glossColor;
         }
         if (use[YB_C_DIFFUSE]) {
             scolor += Kt * diffuseReflect(wiN, woN, d.c[1], d.c[0], m.diffColor) * (m.orenNayar ? gl_OrenNayar(m, wi, wo, N) : 1.f);
-            s.pdf += wiN * width[rcIndex[YB_C_DIFFUSE]];
+            s.pdf += wiN * wN[YB_C_DIFFUSE];
         }
         W = wiN / (s.pdf * 0.99f + 0.01f);
     } else W = 1.f;
-    s.sampledFlags = m.cFlags[cIndex[pick]];
+    s.sampledFlags = pc == 0 ? m.cFlags[0] : (pc == 1 ? m.cFlags[1] : m.cFlags[2]);
     return scolor;
 }
 YB_HD float cg_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t flags)     // :338-382
@@ -574,8 +587,11 @@ YB_HD float cg_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3
     accumC[1] = Kt * (1.f - d.c[2]);
     accumC[2] = Kt * (d.c[2]);
     int nMatch = 0;
-    for (int i = 0; i < m.nBSDF; ++i) {
-        if ((flags & m.cFlags[i]) == m.cFlags[i]) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int i = 0; i < 3; ++i) {           // static indices (see cg_sample)
+        if (i < m.nBSDF && (flags & m.cFlags[i]) == m.cFlags[i]) {
             width = accumC[i];
             sum += width;
             if (i == YB_C_GLOSSY) {
