@@ -111,18 +111,36 @@ __device__ __forceinline__ void block_exclusive_scan_256(uint32_t own, uint32_t 
     sh[threadIdx.x] = v - own;
     __syncthreads();
 }
+// rank of this thread's item among the items of the same bin in the block, in thread order (a stable counting sort), and the bin
+// sizes of the block in h[]; 256 threads, keys < 256
+__device__ __forceinline__ uint32_t block_stable_rank_256(uint32_t k, bool valid, uint32_t (*wcnt)[256], uint32_t *h)
+{
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) wcnt[w][threadIdx.x] = 0u;
+    __syncthreads();
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? k : 0x100u + lane);
+    const uint32_t r = (uint32_t)__popc(peers & ((1u << lane) - 1u));
+    if (valid && r == 0u) wcnt[warp][k] = (uint32_t)__popc(peers);
+    __syncthreads();
+    uint32_t run = 0u;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { const uint32_t c = wcnt[w][threadIdx.x]; wcnt[w][threadIdx.x] = run; run += c; }
+    h[threadIdx.x] = run;
+    __syncthreads();
+    return valid ? wcnt[warp][k] + r : 0u;
+}
 __global__ void __launch_bounds__(256) k_bin_scatter_kernel(uint32_t n, const RenderArgs a)
 {
     __shared__ uint32_t h[YB_SHADE_BINS], base[YB_SHADE_BINS], start[YB_SHADE_BINS];
     if (a.nPtr) n = min(n, *a.nPtr);
     block_exclusive_scan_256(a.bins[threadIdx.x], start);
+    __shared__ uint32_t wcnt[8][YB_SHADE_BINS];
     for (uint32_t c0 = blockIdx.x * blockDim.x; c0 < n; c0 += gridDim.x * blockDim.x) {     // same trip count for the whole block
-        h[threadIdx.x] = 0u;
-        __syncthreads();
         const uint32_t t = c0 + threadIdx.x;
-        uint32_t k = 0u, rank = 0u;
-        if (t < n) { k = a.keys[t]; rank = atomicAdd(&h[k], 1u); }
-        __syncthreads();
+        uint32_t k = 0u;
+        if (t < n) k = a.keys[t];
+        const uint32_t rank = block_stable_rank_256(k, t < n, wcnt, h);      // tasks of a bin keep their pool order within the block
         base[threadIdx.x] = start[threadIdx.x] + (h[threadIdx.x] ? atomicAdd(&a.bins[YB_SHADE_BINS + threadIdx.x], h[threadIdx.x]) : 0u);
         __syncthreads();
         if (t < n) a.orderOut[base[k] + rank] = t;
@@ -168,14 +186,15 @@ __global__ void __launch_bounds__(256) k_ljob_scatter_kernel(const RenderArgs a)
     const uint32_t n = min(a.counters[YB_CNT_LJOBS], a.ljobCap);
     static_assert(YB_LBINS == 256, "one thread per bin");
     block_exclusive_scan_256(a.counters[YB_CNT_LBINS + threadIdx.x], start);
+    __shared__ uint32_t wcnt[8][YB_LBINS];
     for (uint32_t c0 = blockIdx.x * blockDim.x; c0 < n; c0 += gridDim.x * blockDim.x) {     // same trip count for the whole block
-        h[threadIdx.x] = 0u;
-        __syncthreads();
         const uint32_t t = c0 + threadIdx.x;
         LightJob j; j.task = 0u; j.lightKey = 0u;
-        uint32_t k = 0u, rank = 0u;
-        if (t < n) { j = a.ljobs[t]; k = j.lightKey >> 24; rank = atomicAdd(&h[k], 1u); }
-        __syncthreads();
+        uint32_t k = 0u;
+        if (t < n) { j = a.ljobs[t]; k = j.lightKey >> 24; }
+        // stable rank of the job among the jobs of its bin in this block (order of arrival kept: neighbouring jobs stay neighbours, and
+        // with them the surface points whose shadow rays one warp of the direct-lighting kernel queues side by side)
+        const uint32_t rank = block_stable_rank_256(k, t < n, wcnt, h);
         base[threadIdx.x] = start[threadIdx.x] + (h[threadIdx.x] ? atomicAdd(&a.counters[YB_CNT_LCURSOR + threadIdx.x], h[threadIdx.x]) : 0u);
         __syncthreads();
         if (t < n) a.ljobsSorted[base[k] + rank] = j;
