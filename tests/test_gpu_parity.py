@@ -52,6 +52,28 @@ def test_opt_in_knobs_keep_the_image(monkeypatch):
         assert rel <= 1e-5 and psnr >= 100.0, (var, rel, psnr)
 
 
+@pytest.mark.parametrize("name,var", [("c4_materials_path", "YB200_STAGE_DIRECT"), ("c4_materials_direct", "YB200_STAGE_DIRECT"),
+                                      ("c4_materials_path", "YB200_SIDE_STREAMS"), ("c2_field_path", "YB200_KIND_SHADE"),
+                                      ("c1_cornell_direct", "YB200_KIND_SHADE")])
+def test_shade_kernel_variants_render_the_same_frame(name, var, monkeypatch):
+    """Staged direct lighting (yb_direct.cu), its side streams and the shade builds per kind of task / material set run the same
+    functions on the same inputs as the single inline kernel: switching them off (env = 0) must not move the frame (float atomics
+    arrive in another order: 1e-6), and the ray counts are identical."""
+    fn, kw = cases.IMAGE_CASES[name]
+    frames, rays = [], []
+    for val in ("1", "0"):
+        monkeypatch.setenv(var, val)
+        yi = YafrayInterface()
+        fn(yi, **kw)
+        frames.append(yi.render(kw["width"], kw["height"]))
+        st = yi.getStats()
+        rays.append((st["rays_closest"], st["rays_shadow"]))
+        monkeypatch.delenv(var)
+    rel, psnr, da = cases.compare_images(frames[0], frames[1])
+    assert rays[0] == rays[1], (name, var, rays)
+    assert rel <= 1e-6 and psnr >= 110.0 and da <= 1e-6, (name, var, rel, psnr, da)
+
+
 @pytest.mark.parametrize("name", list(cases.DEPTH_CASES))
 def test_depth_channel_golden(name):
     fn, kw = cases.DEPTH_CASES[name]
