@@ -78,3 +78,24 @@ def test_russian_roulette_extension_is_unbiased():
                            integ_params=dict(bounces=6, path_samples=1, russian_roulette=rr))
         out.append(yi.render(32, 32)[..., :3].mean())
     assert abs(out[0] - out[1]) / out[0] < 0.03, out
+
+
+@pytest.mark.parametrize("name,var", [("c4_materials_path", "YB200_STAGE_DIRECT"), ("c4_materials_direct", "YB200_STAGE_DIRECT"),
+                                      ("c2_field_path", "YB200_KIND_SHADE"), ("c1_cornell_direct", "YB200_KIND_SHADE")])
+def test_shade_variants_render_the_same_frame(name, var, monkeypatch):
+    """Staged direct lighting (job queue + one evaluation per light type x material class) and the shade builds per kind of task /
+    material set against the single inline kernel: the emulator runs tasks in order, so the frames agree to float rounding of the
+    accumulation order and the ray counts are equal (same test on the GPU: test_gpu_parity.py)."""
+    fn, kw = cases.IMAGE_CASES[name]
+    frames, rays = [], []
+    for val in ("1", "0"):
+        monkeypatch.setenv(var, val)
+        yi = refapi.EmuInterface()
+        fn(yi, **kw)
+        frames.append(yi.render(kw["width"], kw["height"]))
+        st = yi.getStats()
+        rays.append((st["rays_closest"], st["rays_shadow"]))
+        monkeypatch.delenv(var)
+    rel, psnr, da = cases.compare_images(frames[0], frames[1])
+    assert rays[0] == rays[1], (name, var, rays)
+    assert rel <= 1e-6 and psnr >= 110.0 and da <= 1e-6, (name, var, rel, psnr, da)
