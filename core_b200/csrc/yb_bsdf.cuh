@@ -16,6 +16,9 @@ namespace yb {
 struct Surf {            // the fields of surfacePoint_t the supported materials read (triangle.cc:12-108)
     v3 P, N, Ng, NU, NV;
     const Material *mat;
+    // blend_mat with a mask shader node (blend.cc:49-66): the blend value of THIS point, written by mat_resolve; the material record
+    // itself stays where it is (its sub-materials are addressed relative to it)
+    float blendVal; int32_t hasBlendVal;
 };
 struct MatDat { float c[4]; };   // SDDat_t::component[4]  |  MDat_t{mDiffuse,mGlossy,pDiffuse}
 struct BSample {                 // sample_t (material.h:49-60) minus the reverse-path fields
@@ -966,6 +969,7 @@ template <int FIX = -1> YB_HD float leaf_getAlpha(const Material &m, const MatDa
 YB_HD const Material &blend_m1(const Material &m) { return (&m)[m.blendOff1]; }
 YB_HD const Material &blend_m2(const Material &m) { return (&m)[m.blendOff2]; }
 YB_HD float blend_ival(float val) { return fminf_(1.f, fmaxf_(0.f, 1.f - val)); }                       // :60
+YB_HD float blend_val(const Material &m, const Surf &sp) { return sp.hasBlendVal ? sp.blendVal : m.blendVal; }   // getBlendVal :49-66
 YB_HD uint32_t blend_flags(const Material &sub) { return sub.type == MAT_NULL ? (uint32_t)BSDF_NONE : sub.bsdfFlags; }   // mat1Flags / mat2Flags
 
 template <int EXT, int FIX = -1> YB_HD void mat_initBSDF(const Material &m, MatDat &d, uint32_t &bsdfs)
@@ -979,7 +983,7 @@ template <int EXT, int FIX = -1> YB_HD void mat_initBSDF(const Material &m, MatD
 template <int EXT> YB_HD void mat_blendSurface(const Material &m, Surf &sp)
 {
     if (!EXT || m.type != MAT_BLEND) return;
-    const double alpha = (double)blend_ival(m.blendVal);
+    const double alpha = (double)blend_ival(blend_val(m, sp));
     const float a = (float)alpha, b = (float)(1.0 - alpha);
     sp.N = sp.N * a + sp.N * b;
     sp.NU = sp.NU * a + sp.NU * b;
@@ -988,7 +992,7 @@ template <int EXT> YB_HD void mat_blendSurface(const Material &m, Surf &sp)
 template <int EXT, int FIX = -1> YB_HD col3 mat_eval(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wl, uint32_t bsdfs)
 {
     if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_eval<FIX>(m, d, sp, wo, wl, bsdfs);
-    const float val = m.blendVal, ival = blend_ival(val);
+    const float val = blend_val(m, sp), ival = blend_ival(val);
     MatDat d1, d2; uint32_t f;
     leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);
     col3 col1 = leaf_eval(blend_m1(m), d1, sp, wo, wl, bsdfs);
@@ -998,7 +1002,7 @@ template <int EXT, int FIX = -1> YB_HD col3 mat_eval(const Material &m, const Ma
 template <int EXT, int FIX = -1> YB_HD col3 mat_sample(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 &wi, BSample &s, float &W)
 {
     if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_sample<EXT, FIX>(m, d, sp, wo, wi, s, W);
-    const float val = m.blendVal, ival = blend_ival(val);
+    const float val = blend_val(m, sp), ival = blend_ival(val);
     const Material &m1 = blend_m1(m), &m2 = blend_m2(m);
     bool mat1Sampled = false, mat2Sampled = false;
     col3 col1(0.f), col2(0.f);
@@ -1025,7 +1029,7 @@ template <int EXT, int FIX = -1> YB_HD col3 mat_sample(const Material &m, const 
 template <int EXT, int FIX = -1> YB_HD float mat_pdf(const Material &m, const MatDat &d, const Surf &sp, v3 wo, v3 wi, uint32_t bsdfs)
 {
     if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_pdf<FIX>(m, d, sp, wo, wi, bsdfs);
-    const float val = m.blendVal, ival = blend_ival(val);
+    const float val = blend_val(m, sp), ival = blend_ival(val);
     MatDat d1, d2; uint32_t f;
     leaf_initBSDF(blend_m1(m), d1, f); leaf_initBSDF(blend_m2(m), d2, f);
     float pdf1 = leaf_pdf(blend_m1(m), d1, sp, wo, wi, bsdfs), pdf2 = leaf_pdf(blend_m2(m), d2, sp, wo, wi, bsdfs);
@@ -1034,14 +1038,14 @@ template <int EXT, int FIX = -1> YB_HD float mat_pdf(const Material &m, const Ma
 template <int EXT, int FIX = -1> YB_HD col3 mat_emit(const Material &m, const Surf &sp, v3 wo, bool includeLights)
 {
     if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) return leaf_emit<FIX>(m, sp, wo, includeLights);
-    const float val = m.blendVal, ival = blend_ival(val);
+    const float val = blend_val(m, sp), ival = blend_ival(val);
     col3 col1 = leaf_emit(blend_m1(m), sp, wo, includeLights), col2 = leaf_emit(blend_m2(m), sp, wo, includeLights);
     return col1 * ival + col2 * val;
 }
 template <int EXT, int FIX = -1> YB_HD void mat_getSpecular(const Material &m, const MatDat &d, const Surf &sp, v3 wo, int raylevel, bool &refl, bool &refr, v3 *dir, col3 *col)
 {
     if (!EXT || (FIX >= 0 ? FIX : m.type) != MAT_BLEND) { leaf_getSpecular<FIX>(m, d, sp, wo, raylevel, refl, refr, dir, col); return; }
-    const float val = m.blendVal, ival = blend_ival(val);
+    const float val = blend_val(m, sp), ival = blend_ival(val);
     refl = false; refr = false;
     bool m1_refl = false, m1_refr = false;
     v3 m1_dir[2]; col3 m1_col[2];
@@ -1068,7 +1072,7 @@ template <int EXT> YB_HD bool mat_isTransparent(const Material &m)
 template <int EXT> YB_HD col3 mat_getTransparency(const Material &m, const Surf &sp, v3 wo)
 {
     if (!EXT || m.type != MAT_BLEND) return leaf_getTransparency(m, sp, wo);
-    const float val = m.blendVal, ival = blend_ival(val);
+    const float val = blend_val(m, sp), ival = blend_ival(val);
     col3 col1 = leaf_getTransparency(blend_m1(m), sp, wo), col2 = leaf_getTransparency(blend_m2(m), sp, wo);
     return col1 * ival + col2 * val;
 }
@@ -1093,6 +1097,11 @@ template <int EXT> YB_HD const Material &mat_resolve(const SceneDev &sc, const M
 {
     if (EXT < 2 || m.nNodes <= 0) return m;
     NodeRes st[YB_MAX_NODES];
+    if (m.type == MAT_BLEND) {          // only the mask is a shader node here (blend.cc:406-414): its scalar is the blend value of this point
+        for (int i = 0; i < m.nNodes && i < YB_MAX_NODES; ++i) node_eval(sc.shaderNodes[m.nodeBase + i], sc.textures, P, Ng, tp, st, i);
+        if (sp && m.slot[SLOT_BLEND_MASK] >= 0) { sp->blendVal = st[m.slot[SLOT_BLEND_MASK]].f; sp->hasBlendVal = 1; }
+        return m;
+    }
     if (sp && m.slot[SLOT_BUMP] >= 0) {
         for (int i = 0; i < m.nNodes && i < YB_MAX_NODES; ++i)
             if (m.bumpMask & (1u << i)) node_evalDerivative(sc.shaderNodes[m.nodeBase + i], sc.textures, P, Ng, sp->NU, sp->NV, tp, st, i);

@@ -798,13 +798,18 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         if (!p.get("material1", n1) || !p.get("material2", n2)) { fail("blend_mat '" + std::string(name) + "': material1 / material2 missing"); return 0; }
         std::map<std::string, int>::const_iterator i1 = materialNames.find(n1), i2 = materialNames.find(n2);
         if (i1 == materialNames.end() || i2 == materialNames.end()) { fail("blend_mat '" + std::string(name) + "': material '" + (i1 == materialNames.end() ? n1 : n2) + "' does not exist"); return 0; }
-        if (p.has("mask")) { fail("blend_mat '" + std::string(name) + "': a blend mask shader node is not supported (constant blend_value only)"); return 0; }
         if (materials[i1->second].nNodes > 0 || materials[i2->second].nNodes > 0) { fail("blend_mat '" + std::string(name) + "': blending materials with shader nodes is not supported"); return 0; }
         if (materials[i1->second].type == MAT_BLEND || materials[i2->second].type == MAT_BLEND) { fail("blend_mat '" + std::string(name) + "': blending a blend_mat is not supported (one level only)"); return 0; }
         p.get("blend_value", blend_val);
         const int self = (int)materials.size();
         m.type = MAT_BLEND; m.blendOff1 = i1->second - self; m.blendOff2 = i2->second - self; m.blendVal = (float)blend_val;
         m.bsdfFlags = materials[i1->second].bsdfFlags | materials[i2->second].bsdfFlags;
+        if (p.has("mask")) {                        // blend.cc:406-427: the scalar of this node is the blend value at every point
+            const size_t nodesBefore = shaderNodes.size();
+            static const char *const keys[] = {"mask"};
+            static const int ids[] = {SLOT_BLEND_MASK};
+            if (!loadMaterialNodes(name, m, keys, ids, 1)) { shaderNodes.resize(nodesBefore); return 0; }
+        }
     } else if (type == "mirror") {                // glass.cc:336-371
         col3 col(1.f); float refl = 1.f;
         p.getColor("color", col); p.get("reflect", refl);

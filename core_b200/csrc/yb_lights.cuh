@@ -350,6 +350,7 @@ YB_HD void tri_getSurface(const SurfTables &sc, int tri, v3 hitP, float b1, floa
     const f4 A = sc.tri_v[3 * tri], B = sc.tri_v[3 * tri + 1], C = sc.tri_v[3 * tri + 2];
     v3 a(A.x, A.y, A.z), b(B.x, B.y, B.z), c(C.x, C.y, C.z);
     uint32_t info = (uint32_t)f2i(B.w);
+    sp.hasBlendVal = 0; sp.blendVal = 0.f;
     // instances keep the BASE triangle's normal pushed through objToWorld (not perpendicular under non-uniform scale)
     sp.Ng = (info & TRI_EXPLICIT_NG) ? sc.prim_ng[f2i(A.w)] : normalize(cross(b - a, c - a));
     float u = 1 - b1 - b2, v = b1, w = b2;        // data.b0, b1, b2

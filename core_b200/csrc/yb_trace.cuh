@@ -159,7 +159,7 @@ YB_HD bool bvh_traverse(const SceneDev &sc, v3 from, v3 dir, float tlo, float th
                     tri_getSurface(sc, (int)ti, from + t * dir, u, v, sps);
                     Material rmat;                      // shinydiffuse.cc:435-455 evaluates the nodes itself for shadow rays
                     const Material *mp = &m;
-                    if (m.nNodes > 0) { TexPoint tp; tri_getTexPoint(sc, (int)ti, sps.P, u, v, sps.Ng, tp); mp = &mat_resolve<2>(sc, m, sps.P, sps.Ng, tp, rmat); }
+                    if (m.nNodes > 0) { TexPoint tp; tri_getTexPoint(sc, (int)ti, sps.P, u, v, sps.Ng, tp); mp = &mat_resolve<2>(sc, m, sps.P, sps.Ng, tp, rmat, m.type == MAT_BLEND ? &sps : 0); }
                     filt *= mat_getTransparency<1>(*mp, sps, dir);
                     ++depth;
                 }

@@ -58,7 +58,8 @@ struct Material {
     float emitStrength;
     uint32_t bumpMask;               // nodes of the bump_shader tree (nodeMaterial_t::bumpNodes), bit i = node i of this material
 };
-enum ShaderSlot : int32_t { SLOT_DIFFUSE = 0, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT, SLOT_BUMP, SLOT_COUNT };
+enum ShaderSlot : int32_t { SLOT_DIFFUSE = 0, SLOT_MIRROR_COLOR, SLOT_MIRROR, SLOT_TRANSPARENCY, SLOT_TRANSLUCENCY, SLOT_GLOSSY, SLOT_GLOSSY_REFLECT, SLOT_BUMP, SLOT_COUNT,
+                            SLOT_BLEND_MASK = SLOT_DIFFUSE /* blend_mat has no other slot */ };
 #define YB_MAX_NODES 8               // nodes per material (creation fails beyond)
 
 // texture_t implementations evaluated on the device (src/textures/basictex.cc): rgb_cube, blend, clouds, marble, wood with the

@@ -70,6 +70,21 @@ _TEXTURED = dict(
                                  dict(name="tl", type="mix", mode=6, input1="c2", color2=(0.5, 0.5, 0.5, 1.0), factor="tr")]))],
     order=["m_clouds", "m_layer", "m_glossy", "m_glass", "m_coated", "m_transp", "mirror", "gdiff"])
 
+# blend_mat with a mask shader node (blend.cc:49-66,406-427): the blend value is the scalar of a node graph at the shaded point -
+# a texture_mapper over clouds, a marble texture through a layer node, and a constant value node
+_BLEND_MASK = dict(
+    uv_orco=True,
+    textures=_TEXTURED["textures"],
+    extra_materials=[
+        ("bm_gs", dict(type="blend_mat", material1="glossy", material2="shiny", blend_value=0.35, mask="msk",
+                       nodes=[_mapper("msk", "tclouds_hard", "orco", scale=(2.0, 2.0, 2.0))])),
+        ("bm_gc", dict(type="blend_mat", material1="glass", material2="coated", blend_value=0.6, mask="lay",
+                       nodes=[_mapper("marb", "tmarble", "global", scale=(0.7, 0.7, 0.7)),
+                              dict(name="lay", type="layer", input="marb", mode=0, do_scalar=True, valfac=0.8, def_val=0.2)])),
+        ("bm_md", dict(type="blend_mat", material1="gdiff", material2="mirror", blend_value=0.75, mask="val",
+                       nodes=[dict(name="val", type="value", color=(0.5, 0.5, 0.5, 1.0), alpha=1.0, scalar=0.3)]))],
+    order=["bm_gs", "glossy", "coated", "bm_gc", "gdiff", "shiny", "bm_md", "mirror"])
+
 # the other noise bases of newNoise (blender = Blender's default basis, voronoi f1..crackle, cellnoise) under clouds / marble / wood
 _NOISES = dict(
     uv_orco=True,
@@ -196,6 +211,10 @@ IMAGE_CASES = {
     # rough_glass (GGX refraction: two-direction sample of recursiveRaytrace) and blend_mat of two leaf materials
     "c4_roughglass_blend_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_RG_BLEND)),
     "c4_roughglass_blend_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=5, **_RG_BLEND)),
+    "c4_blendmask_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_BLEND_MASK)),
+    "c4_blendmask_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4, **_BLEND_MASK)),
+    "c4_blendmask_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
+                                                          integ_params=dict(transpShad=True, shadowDepth=4), **_BLEND_MASK)),
     "c4_roughglass_blend_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
                                                                  integ_params=dict(transpShad=True, shadowDepth=4, bg_transp=True,
                                                                                    bg_transp_refract=True), **_RG_BLEND)),
