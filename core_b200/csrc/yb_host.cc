@@ -1003,11 +1003,20 @@ uintptr_t Context::createBackground(const char *name)   // environment.cc:332-36
     std::string type;
     if (!params.get("type", type)) { fail(std::string("Environment: Type of background not specified for ") + name); return 0; }
     if (backgrounds.count(name)) { warn(std::string("Environment: Sorry, background already in table: ") + name); return 0; }
-    if (type != "constant") { fail("Environment: background type '" + type + "' is not supported by the B200 path (supported: constant)"); return 0; }
+    if (type != "constant" && type != "gradientback") { fail("Environment: background type '" + type + "' is not supported by the B200 path (supported: constant, gradientback)"); return 0; }
     col3 col(0.f); float power = 1.0f; bool ibl = false;
     params.getColor("color", col); params.get("power", power); params.get("ibl", ibl);
     if (ibl) { fail("background '" + std::string(name) + "': ibl=true (background light) is not supported"); return 0; }
-    BackgroundDesc b; b.color = col * power;
+    BackgroundDesc b;
+    memset((void *)&b, 0, sizeof(b));
+    b.color = col * power;
+    if (type == "gradientback") {                 // gradientback.cc:82-115
+        col3 szenith(0.4f, 0.5f, 1.f), shoriz(1.f);
+        params.getColor("horizon_color", shoriz); params.getColor("zenith_color", szenith);
+        col3 gzenith = szenith, ghoriz = shoriz;
+        params.getColor("horizon_ground_color", ghoriz); params.getColor("zenith_ground_color", gzenith);
+        b.gradient = 1; b.gzenith = gzenith * power; b.ghoriz = ghoriz * power; b.szenith = szenith * power; b.shoriz = shoriz * power;
+    }
     backgrounds[name] = b;
     return 0x42000000u | (uintptr_t)backgrounds.size();
 }
@@ -1107,11 +1116,14 @@ bool Context::setupRender(int width, int height)   // environment.cc:596-694 + c
     if (vi == integrators.end() || !vi->second.volume_none)
         return fail("volume integrator '" + name + "' must be of type 'none' (participating media are not supported)");
     sc.integ = ii->second.p;
-    sc.integ.hasBackground = 0; sc.integ.bgColor = col3(0.f);
+    sc.integ.hasBackground = 0; sc.integ.bgColor = col3(0.f); sc.integ.bgGradient = 0;
     if (p.get("background_name", name)) {
         std::map<std::string, BackgroundDesc>::iterator bi = backgrounds.find(name);
         if (bi == backgrounds.end()) { if (verbosity >= 1) fprintf(stderr, "ERROR: yb200: please specify an _existing_ Background!!\n"); }
-        else { sc.integ.hasBackground = 1; sc.integ.bgColor = bi->second.color; }
+        else {
+            sc.integ.hasBackground = 1; sc.integ.bgColor = bi->second.color; sc.integ.bgGradient = bi->second.gradient;
+            sc.integ.bgGZenith = bi->second.gzenith; sc.integ.bgGHoriz = bi->second.ghoriz; sc.integ.bgSZenith = bi->second.szenith; sc.integ.bgSHoriz = bi->second.shoriz;
+        }
     }
     sc.cam = ci->second.cam;
     int AA_passes = 1, AA_samples = 1, AA_inc = 1; double AA_threshold = 0.05; bool z_chan = false, norm_z_chan = true;

@@ -54,7 +54,7 @@ struct MeshObj {
 
 struct IntegratorDesc { bool surface; bool volume_none; Integrator p; };
 struct CameraDesc { Camera cam; };
-struct BackgroundDesc { col3 color; };
+struct BackgroundDesc { col3 color; int gradient; col3 gzenith, ghoriz, szenith, shoriz; };
 
 struct Stats {
     uint64_t n_triangles, n_bvh_nodes, rays_closest, rays_shadow, camera_samples, kernel_launches;

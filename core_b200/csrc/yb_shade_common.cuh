@@ -161,6 +161,18 @@ YB_D void push_light_job(const RenderArgs &a, uint32_t task, uint32_t light, uin
     put_light_job(a, YB_ATOMIC_ADD_U32(a.counters + YB_CNT_LJOBS, 1u), task, light, key, mat);
 }
 
+// background_t::operator() of the supported backgrounds: constant (constant colour) and gradientBackground_t::eval (gradientback.cc:60-80)
+YB_D col3 background_eval(const Integrator &I, v3 dir)
+{
+    if (!I.bgGradient) return I.bgColor;
+    float blend = dir.z;
+    col3 color;
+    if (blend >= 0.f) color = blend * I.bgSZenith + (1.f - blend) * I.bgSHoriz;
+    else { blend = -blend; color = blend * I.bgGZenith + (1.f - blend) * I.bgGHoriz; }
+    if (fminf_(color.x, fminf_(color.y, color.z)) < 1e-6f) color = col3(1e-5f);
+    return color;
+}
+
 // the light estimateOneDirectLight picks for path sample n (mcintegrator.cc:62-66)
 YB_D int pick_one_light(int n, int lightNum)
 {

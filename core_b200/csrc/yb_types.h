@@ -162,6 +162,9 @@ struct Integrator {
     int32_t transpBackground, transpRefractedBackground;
     int32_t hasBackground;
     col3 bgColor;
+    // gradientBackground_t (gradientback.cc:60-80): colour by ray direction z; bgGradient = 0: constant bgColor
+    int32_t bgGradient;
+    col3 bgGZenith, bgGHoriz, bgSZenith, bgSHoriz;
     int32_t russianRoulette;          // opt-in extension (north_star); OFF by default and in every parity test
     float rrMinProb;
     // caustic photon map (mcintegrator.h: usePhotonCaustics / nCausPhotons / nCausSearch / causDepth / causRadius)

@@ -233,7 +233,7 @@ def cornell_box(yi, width=512, height=512, spp=16, integrator="directlighting", 
 # ----------------------------------------------------------------------------- C2: icosphere field
 def icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=64, bounces=4, seed=1,
                     subdiv=3, smooth=True, threads=1, integrator="pathtracing", integ_params=None, cam_res=None,
-                    **render_extra):
+                    background=None, **render_extra):
     """Subdivided icospheres (1280 tris each at subdiv=3) on a jittered grid over a ground quad;
     sun + point light; pathtracing (BASELINE.json configs[1])."""
     rng = np.random.Generator(np.random.PCG64(seed))
@@ -271,7 +271,7 @@ def icosphere_field(yi, n_tris=1_000_000, width=1920, height=1080, spp=64, bounc
     d = 0.55 * ext
     create(yi, "camera", "cam", type="perspective", **{"from": (0.0, -d * 1.6, d * 0.9)}, to=(0.0, 0.0, 0.5),
            up=(0.0, -d * 1.6, d * 0.9 + 1.0), resx=cam_res[0] if cam_res else width, resy=cam_res[1] if cam_res else height, focal=1.1)
-    create(yi, "background", "bg", type="constant", color=(0.5, 0.6, 0.8, 1.0))
+    create(yi, "background", "bg", **(background or dict(type="constant", color=(0.5, 0.6, 0.8, 1.0))))
     ip = dict(type=integrator, raydepth=5)
     if integrator == "pathtracing":
         ip.update(bounces=bounces, path_samples=1)
@@ -344,6 +344,7 @@ def primary_rays(cam_from, cam_to, cam_up, width, height, focal, n=None, seed=0,
 def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, threads=1, integrator="pathtracing",
                     integ_params=None, area_samples=8, sun_samples=4, raydepth=5, cam_params=None, lights=None,
                     extra_materials=None, order=None, emitters=None, textures=None, uv_orco=False, image_files=None, cam_res=None,
+                    background=None,
                     **render_extra):
     """Row of tessellated spheres over a ground plane with glossy (Blinn exp 50 and anisotropic 20/200),
     coated_glossy (IOR 1.4), glass (IOR 1.5, fake_shadows on and off), mirror and a transparent/mirror
@@ -412,7 +413,7 @@ def materials_scene(yi, width=1920, height=1080, spp=256, bounces=8, subdiv=3, t
     cp.update(cam_params or {})
     create(yi, "camera", "cam", **{"from": (0.0, -9.5, 4.2)}, to=(0.0, 1.0, 0.8),
            up=(0.0, -9.5, 5.2), resx=cam_res[0] if cam_res else width, resy=cam_res[1] if cam_res else height, **cp)
-    create(yi, "background", "bg", type="constant", color=(0.35, 0.45, 0.7, 1.0))
+    create(yi, "background", "bg", **(background or dict(type="constant", color=(0.35, 0.45, 0.7, 1.0))))
     ip = dict(type=integrator, raydepth=raydepth)
     if integrator == "pathtracing":
         ip.update(bounces=bounces, path_samples=1)

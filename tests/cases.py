@@ -211,6 +211,15 @@ IMAGE_CASES = {
     # rough_glass (GGX refraction: two-direction sample of recursiveRaytrace) and blend_mat of two leaf materials
     "c4_roughglass_blend_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_RG_BLEND)),
     "c4_roughglass_blend_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=5, **_RG_BLEND)),
+    # gradientBackground_t (gradientback.cc): sky / ground colours by ray direction, seen directly, through glass and in mirrors
+    "c2_field_gradient_path": (scenes.icosphere_field, dict(n_tris=20000, width=96, height=54, spp=2, bounces=3,
+                                                            background=dict(type="gradientback", horizon_color=(1.0, 0.9, 0.7, 1.0),
+                                                                            zenith_color=(0.2, 0.4, 0.9, 1.0), power=1.3))),
+    "c4_materials_gradient_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting",
+                                                                  background=dict(type="gradientback", horizon_color=(0.9, 0.8, 0.6, 1.0),
+                                                                                  zenith_color=(0.1, 0.3, 0.8, 1.0),
+                                                                                  horizon_ground_color=(0.3, 0.25, 0.2, 1.0),
+                                                                                  zenith_ground_color=(0.0, 0.0, 0.0, 1.0)))),
     "c4_blendmask_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_BLEND_MASK)),
     "c4_blendmask_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4, **_BLEND_MASK)),
     "c4_blendmask_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
