@@ -77,7 +77,7 @@ void yb200_params_end_list  (yb200_ctx *c);
 yb200_handle yb200_create_light     (yb200_ctx *c, const char *name);  /* pointlight | sunlight | arealight | meshlight | directional | spotlight | spherelight */
 yb200_handle yb200_create_material  (yb200_ctx *c, const char *name);  /* shinydiffusemat | glossy | coated_glossy | glass | rough_glass | blend_mat | mirror | null | light_mat; shader nodes = the parameter list */
 yb200_handle yb200_create_camera    (yb200_ctx *c, const char *name);  /* perspective | architect | orthographic | angular */
-yb200_handle yb200_create_background(yb200_ctx *c, const char *name);  /* constant */
+yb200_handle yb200_create_background(yb200_ctx *c, const char *name);  /* constant, gradientback */
 yb200_handle yb200_create_integrator(yb200_ctx *c, const char *name);  /* directlighting | pathtracing | none (volume) */
 yb200_handle yb200_create_texture   (yb200_ctx *c, const char *name);  /* rgb_cube | blend | clouds | marble | wood | image (basictex.cc, imagetex.cc) */
 /* Decoded pixels for an image texture, keyed by the `filename` the texture's parameters name: what imageHandler_t::getPixel
