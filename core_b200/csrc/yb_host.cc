@@ -658,6 +658,24 @@ bool Context::loadMaterialNodes(const char *name, Material &m, const char *const
     return true;
 }
 
+// glass.cc:275-304 / roughglass.cc:288-316: an `absorption` colour below white gives the material a "beer" volume handler for its inside
+// (beer.cc:24-33: sigma_a = -log(colour) / absorption_dist, distance 1 unless given) and BSDF_VOLUMETRIC
+static void setBeerAbsorption(const ParaMap &p, Material &m)
+{
+    col3 absorp(1.f);
+    if (!p.getColor("absorption", absorp) || !(absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) return;
+    double dist = 1.f;
+    p.get("absorption_dist", dist);
+    const float maxlog = (float)log(1e38);
+    col3 sigma;
+    sigma.x = (absorp.x > 1e-38f) ? (float)-log((double)absorp.x) : maxlog;
+    sigma.y = (absorp.y > 1e-38f) ? (float)-log((double)absorp.y) : maxlog;
+    sigma.z = (absorp.z > 1e-38f) ? (float)-log((double)absorp.z) : maxlog;
+    if (dist != 0.0) sigma = sigma * (float)(1.f / dist);
+    m.hasBeer = 1; m.beerSigma = sigma;
+    m.bsdfFlags |= BSDF_VOLUMETRIC;
+}
+
 uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 + the plugins' factory()
 {
     std::string type;
@@ -763,7 +781,6 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         p.get("IOR", IOR); p.getColor("filter_color", filtCol); p.get("transmit_filter", filt); p.getColor("mirror_color", srCol);
         p.get("dispersion_power", disp_power); p.get("fake_shadows", fake);
         if (disp_power > 0.0) { fail("glass '" + std::string(name) + "': dispersion is not supported"); return 0; }
-        if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
         {
             static const char *const keys[] = {"mirror_color_shader", "bump_shader"};
             static const int ids[] = {SLOT_MIRROR_COLOR, SLOT_BUMP};
@@ -775,12 +792,12 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         m.specRefCol = srCol; m.fakeShadow = fake;
         m.bsdfFlags = BSDF_ALL_SPECULAR;
         if (fake) m.bsdfFlags |= BSDF_FILTER;
+        setBeerAbsorption(p, m);
     } else if (type == "rough_glass") {           // roughglass.cc:257-285
         float IOR = 1.4f, filt = 0.f, alpha = 0.5f, disp_power = 0.f; col3 filtCol(1.f), absorp(1.f), srCol(1.f); bool fake = false;
         p.get("IOR", IOR); p.getColor("filter_color", filtCol); p.get("transmit_filter", filt); p.getColor("mirror_color", srCol);
         p.get("alpha", alpha); p.get("dispersion_power", disp_power); p.get("fake_shadows", fake);
         if (disp_power > 0.0) { fail("rough_glass '" + std::string(name) + "': dispersion is not supported"); return 0; }
-        if (p.getColor("absorption", absorp) && (absorp.x < 1.f || absorp.y < 1.f || absorp.z < 1.f)) { fail("rough_glass '" + std::string(name) + "': absorption (beer volume) is not supported"); return 0; }
         alpha = std::max(1e-4f, std::min(alpha * 0.5f, 1.f));
         {
             static const char *const keys[] = {"mirror_color_shader", "bump_shader"};
@@ -793,6 +810,7 @@ uintptr_t Context::createMaterial(const char *name)   // environment.cc:218-250 
         m.specRefCol = srCol; m.fakeShadow = fake;
         m.bsdfFlags = BSDF_ALL_GLOSSY;
         if (fake) m.bsdfFlags |= BSDF_FILTER;
+        setBeerAbsorption(p, m);
     } else if (type == "blend_mat") {             // blend.cc:395-431 + ctor :32-41
         std::string n1, n2; double blend_val = 0.5;
         if (!p.get("material1", n1) || !p.get("material2", n2)) { fail("blend_mat '" + std::string(name) + "': material1 / material2 missing"); return 0; }

@@ -361,8 +361,10 @@ bool build_caustic_map(Context &c)
     if (I.nCausSearch > YB_MAX_CAUS_SEARCH || I.nCausSearch < 1)
         return c.fail("caustic_mix (photons per estimate) must be between 1 and " + std::to_string(YB_MAX_CAUS_SEARCH));
     if (c.lights.empty() || I.nCausPhotons <= 0 || c.nTris == 0) return true;       // "No caustic source lights found"
-    for (size_t i = 0; i < c.materials.size(); ++i)
+    for (size_t i = 0; i < c.materials.size(); ++i) {
+        if (c.materials[i].hasBeer) return c.fail("caustic photon maps: photons through absorbing glass (beer volume, mcintegrator.cc:296-302) are not supported");
         if (c.materials[i].type == MAT_BLEND) return c.fail("caustic photon maps: blend_mat scatters photons through both sub-materials (blend.cc:359-380), which is not supported");
+    }
     try {
         if (!c.photonBufs) c.photonBufs = new PhotonBuffers();
         PhotonBuffers &pb = *c.photonBufs;

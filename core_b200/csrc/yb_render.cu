@@ -602,7 +602,7 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
             if (m.type != MAT_SHINYDIFFUSE) allShinyDiffuse = false;
             if (m.bsdfFlags & BSDF_GLOSSY) anyGlossy = true;
             if (m.type == MAT_ROUGH_GLASS) anyRoughGlass = true;     // two children per glossy sample
-            if (m.type == MAT_ROUGH_GLASS || m.type == MAT_BLEND) extShade = true;
+            if (m.type == MAT_ROUGH_GLASS || m.type == MAT_BLEND || m.hasBeer) extShade = true;     // absorbing glass: Beer's law lives in the ext build
             if (m.nNodes > 0) nodeShade = true;
             int sc_ = 0;
             if (m.type == MAT_GLASS || m.type == MAT_BLEND) sc_ = 2;

@@ -50,6 +50,9 @@ struct Material {
     //     material table (sub-materials are leaf materials: a blend of blends is rejected at creation)
     int32_t blendOff1, blendOff2;
     float blendVal;
+    // glass / rough_glass with absorption: beer_t volume handler of the inside (beer.cc:24-45), sigma_a = -log(absorption) / absorption_dist
+    int32_t hasBeer;
+    col3 beerSigma;
     // --- nodeMaterial_t (nodematerial.cc:77-243): the material's shader nodes in evaluation order (allSorted) live at
     //     [nodeBase, nodeBase + nNodes) of the scene's node table; slot[s] = index (relative to nodeBase) of the node bound to
     //     shader slot s, -1 = the constant above is used.  emitStrength: shinydiffuse.cc:251-257 scales the diffuse NODE colour

@@ -85,6 +85,16 @@ _BLEND_MASK = dict(
                        nodes=[dict(name="val", type="value", color=(0.5, 0.5, 0.5, 1.0), alpha=1.0, scalar=0.3)]))],
     order=["bm_gs", "glossy", "coated", "bm_gc", "gdiff", "shiny", "bm_md", "mirror"])
 
+# glass / rough_glass with absorption (glass.cc:275-304, beer.cc): Beer's law over the segments inside the material - in the
+# specular / glossy recursion (mcintegrator.cc:474-477,535-574,603-619) and along path segments (pathtracer.cc:290-293)
+_ABSORB = dict(
+    extra_materials=[
+        ("ag", dict(type="glass", IOR=1.5, filter_color=(1.0, 1.0, 1.0, 1.0), transmit_filter=0.0, absorption=(0.9, 0.3, 0.2, 1.0),
+                    absorption_dist=0.7, fake_shadows=True)),
+        ("ag2", dict(type="glass", IOR=1.33, filter_color=(0.9, 1.0, 0.9, 1.0), transmit_filter=0.3, absorption=(0.2, 0.5, 0.95, 1.0))),
+        ("arg", dict(type="rough_glass", IOR=1.5, alpha=0.2, absorption=(0.4, 0.9, 0.5, 1.0), absorption_dist=1.5))],
+    order=["ag", "glossy", "arg", "ag2", "gdiff", "ag", "mirror", "arg"])
+
 # the other noise bases of newNoise (blender = Blender's default basis, voronoi f1..crackle, cellnoise) under clouds / marble / wood
 _NOISES = dict(
     uv_orco=True,
@@ -220,6 +230,8 @@ IMAGE_CASES = {
                                                                                   zenith_color=(0.1, 0.3, 0.8, 1.0),
                                                                                   horizon_ground_color=(0.3, 0.25, 0.2, 1.0),
                                                                                   zenith_ground_color=(0.0, 0.0, 0.0, 1.0)))),
+    "c4_absorb_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_ABSORB)),
+    "c4_absorb_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=5, **_ABSORB)),
     "c4_blendmask_direct": (scenes.materials_scene, dict(width=80, height=45, spp=2, integrator="directlighting", **_BLEND_MASK)),
     "c4_blendmask_path": (scenes.materials_scene, dict(width=64, height=36, spp=2, bounces=4, **_BLEND_MASK)),
     "c4_blendmask_tshadow": (scenes.materials_scene, dict(width=64, height=36, spp=1, integrator="directlighting",
