@@ -961,6 +961,13 @@ template <int FIX = -1> YB_HD float leaf_getAlpha(const Material &m, const MatDa
     return 1.f;
 }
 
+// beer_t::transmittance (beer.cc:35-45) over a ray that ended at distance t (no hit: tmax stays -1 - black)
+YB_HD col3 beer_transmittance(col3 sigma, bool hit, float t)
+{
+    if (!hit || t < 0.f || t > 1e30f) return col3(0.f);
+    return col3(fExp(-t * sigma.x), fExp(-t * sigma.y), fExp(-t * sigma.z));
+}
+
 // ================================================================== blendMat_t (blend.cc:49-393) over two leaf materials, constant blend_value
 // EXT: the shade kernel is compiled twice (yb_render.cu); scenes without rough_glass / blend_mat / mesh lights run the EXT = 0
 // build, which carries none of this code (register pressure of the common path)

@@ -193,9 +193,13 @@ YB_D void photon_path(const ShootArgs &a, uint32_t curr)
     if (isBlack(pcol)) return;
     int nBounces = 0;
     bool causticPhoton = false, directPhoton = true;
+    bool prevBeer = false; col3 prevSigma(0.f); v3 prevNg(0.f);           // the material the segment leaves: its inside absorbs (beer volume)
     Hit H;
     while (scene_intersect(a.sc, ray, H)) {
         if (pcol.x != pcol.x || pcol.y != pcol.y || pcol.z != pcol.z) break;
+        // mcintegrator.cc:294-304: transmittance of the segment just traversed, by the volume handler of the material it left
+        col3 transm(1.f);
+        if (prevBeer && dot(prevNg, ray.dir) < 0.f) transm = beer_transmittance(prevSigma, true, H.t);
         Surf sp;
         tri_getSurface(a.sc, H.tri, ray.from + H.t * ray.dir, H.b1, H.b2, sp);
         Material rmat;
@@ -222,7 +226,7 @@ YB_D void photon_path(const ShootArgs &a, uint32_t curr)
         float W = 0.f; v3 wo(0.f);
         const col3 scol = mat_sample<EXT>(mat, md, sp, wi, wo, s, W);
         if (!(s.pdf > 1.0e-6f)) break;
-        const col3 cnew = mul(pcol, scol) * W;                                   // lcol * alpha (= 1: no volumes) * scol * W
+        const col3 cnew = mul(mul(pcol, transm), scol) * W;                      // lcol * alpha * scol * W
         const float new_max = fmaxf_(cnew.x, fmaxf_(cnew.y, cnew.z)), old_max = fmaxf_(pcol.x, fmaxf_(pcol.y, pcol.z));
         const float prob = fminf_(1.f, new_max / old_max);
         if (!(s7 <= prob && prob > 1e-4f)) break;                                // absorbed
@@ -233,6 +237,7 @@ YB_D void photon_path(const ShootArgs &a, uint32_t curr)
         causticPhoton = nc;
         directPhoton = (sf & BSDF_FILTER) && directPhoton;
         if (!(causticPhoton || directPhoton)) break;
+        prevBeer = (bsdfs & BSDF_VOLUMETRIC) && mat.hasBeer; prevSigma = mat.beerSigma; prevNg = sp.Ng;
         ray.from = sp.P; ray.dir = wo; ray.tmin = YB_MIN_RAYDIST; ray.tmax = -1.f;
         ++nBounces;
     }
@@ -362,7 +367,6 @@ bool build_caustic_map(Context &c)
         return c.fail("caustic_mix (photons per estimate) must be between 1 and " + std::to_string(YB_MAX_CAUS_SEARCH));
     if (c.lights.empty() || I.nCausPhotons <= 0 || c.nTris == 0) return true;       // "No caustic source lights found"
     for (size_t i = 0; i < c.materials.size(); ++i) {
-        if (c.materials[i].hasBeer) return c.fail("caustic photon maps: photons through absorbing glass (beer volume, mcintegrator.cc:296-302) are not supported");
         if (c.materials[i].type == MAT_BLEND) return c.fail("caustic photon maps: blend_mat scatters photons through both sub-materials (blend.cc:359-380), which is not supported");
     }
     try {
