@@ -275,8 +275,9 @@ YB_D void film_splat_sample(const RenderArgs &a, uint32_t tid)
 }
 YB_KERNEL(k_film, RenderArgs) { film_splat_sample(a, tid); }
 #ifndef YB_HOSTEMU
-// Warp-aggregated form of the splat for the common case (no premult, footprint inside the 3x3 neighbourhood of the pixel: box /
-// gauss filters up to AA_pixelwidth 2): consecutive lanes hold consecutive samples of the same pixel, so the 3x3 x 5 partial sums
+// Warp-aggregated form of the splat for the common case (no premult, footprint of every sample of the warp inside the 3x3
+// neighbourhood of its pixel: filter half-width up to about 1.5 pixels - box and lanczos: AA_pixelwidth / 2, gauss: AA_pixelwidth,
+// mitchell: 1.3 AA_pixelwidth; wider filters send the warp to the per-sample path): consecutive lanes hold consecutive samples of the same pixel, so the 3x3 x 5 partial sums
 // are reduced over each run of equal pixels with shuffles and only the run's first lane touches the film - 45 atomics per pixel
 // and warp instead of 20 per sample.  Anything else (wide filters, premult, the depth channel) takes k_film's per-sample path.
 __global__ void __launch_bounds__(256) k_film_fast_kernel(uint32_t n, const RenderArgs a)
@@ -695,9 +696,9 @@ bool render_film_device(Context &c, float *d_film, const float *d_filmAll, int r
         a.sc = c.sc; a.sc.film.minDepth = fz.minDepth; a.sc.film.maxDepth = fz.maxDepth; a.sc.film.n_samples = passSamples; a.sc.film.pass_offs = passOffs; a.hits = rb.hits.p; a.shadow = rb.shadow.p; a.counters = rb.counters.p; a.acc = rb.acc.p; a.pix = rb.pix.p;
         a.orderOut = rb.order.p; a.keys = rb.keys.p; a.bins = rb.bins.p;
         const bool binShade = env_size("YB200_BIN_SHADE", 1) != 0;
-        const bool binFirst = env_size("YB200_BIN_FIRST", 0) != 0;
+        const bool binFirst = env_size("YB200_BIN_FIRST", 0) != 0;       // also bin the camera wave (its pixel order is already coherent: off)
         const bool filmFast = env_size("YB200_FILM_FAST", 1) != 0;       // warp-aggregated film splat (k_film_fast_kernel)
-        (void)filmFast;      // also bin the camera wave (pixel order is already coherent)
+        (void)filmFast;                                                  // (unused in the emulator build)
         const bool logWaves = env_size("YB200_LOG_WAVES", 0) != 0;
         const bool kindShade = env_size("YB200_KIND_SHADE", 1) != 0;           // device-counted waves: shade kernel compiled for the wave's kind of task
         const bool sideStreams = env_size("YB200_SIDE_STREAMS", 1) != 0;       // staged direct lighting: groups of a wave on several streams
